@@ -1,0 +1,421 @@
+// b200ml — K4/K5/K13: GEMM (+bias +activation +dropout +mask/residual) on the 5th-gen tensor cores.
+//
+//   C[M,N] = epilogue( alpha * A[M,K] · B[N,K]^T )           bf16 operands, fp32 accumulation in TMEM
+//
+// One persistent CTA per SM, warp-specialised:
+//   warp 0      TMA producer   : cp.async.bulk.tensor (128B swizzle) into a kStages-deep smem ring
+//   warp 1      MMA issuer     : one thread issues tcgen05.mma.cta_group::1.kind::f16 (128 x BN x 16)
+//   warps 2..5  epilogue       : tcgen05.ld 32x32b from a double-buffered TMEM accumulator, fused math, stores
+// Either operand may be K-major (reduction dim contiguous) or MN-major (output dim contiguous), so the
+// forward (X·Wᵀ), dgrad (dY·W) and wgrad (dYᵀ·X) GEMMs of a Linear all run here without any transposes:
+//   fwd   : A = X  [M,K]  K-major      B = W  [N,K]   K-major
+//   dgrad : A = dY [M,N'] K-major      B = W  [N',K'] MN-major (output dim K' contiguous)
+//   wgrad : A = dY [M',N] MN-major     B = X  [M',K]  MN-major (reduction dim M' is the row index of both)
+// Reference ops covered: every nn.Linear in the reference (transformer.py:71-72,107-108,177-179,272;
+// distributed_multilayer_perceptron.py:47-53 at the 784-dim preset) with its ReLU / Sigmoid / Dropout neighbours.
+#include "../../include/b200ml.h"
+#include "../common/host.h"
+#include "../common/ptx.cuh"
+#include "../common/rng.cuh"
+
+namespace b200 {
+namespace gemm {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 64;  // 64 bf16 = 128 B = one swizzle row
+constexpr int UMMA_K = 16;
+constexpr int kNumThreads = 192;  // 6 warps
+
+struct Epilogue {
+    void* C;
+    long long ldc;
+    int c_fp32;
+    const float* bias;
+    int act;
+    const __nv_bfloat16* aux;
+    long long ldaux;
+    int aux_mode;
+    float aux_scale;
+    float alpha;
+    const float* alpha_dev;  // optional device scalar multiplied into alpha (e.g. an upstream loss gradient)
+    int accumulate;
+    float dropout_p;
+    const RngState* rng;
+    uint32_t rng_site;
+};
+
+template <int BN>
+struct Cfg {
+    static constexpr int kStages = BN == 256 ? 4 : (BN == 128 ? 6 : 8);
+    static constexpr int kABytes = BLOCK_M * BLOCK_K * 2;
+    static constexpr int kBBytes = BN * BLOCK_K * 2;
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kTmemCols = 2 * BN;  // double-buffered accumulator
+    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+__device__ __forceinline__ float apply_act(float v, int act) {
+    if (act == 1) return fmaxf(v, 0.f);
+    if (act == 2) return 1.f / (1.f + __expf(-v));
+    return v;
+}
+
+template <bool A_MN, bool B_MN, int BN>
+__global__ void __launch_bounds__(kNumThreads, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, int M, int N,
+                 int K, Epilogue ep) {
+    using C = Cfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+    uint64_t* full_bar = bars;
+    uint64_t* empty_bar = bars + C::kStages;
+    uint64_t* tmem_full = bars + 2 * C::kStages;
+    uint64_t* tmem_empty = tmem_full + 2;
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmap_a);
+        tma_prefetch_desc(&tmap_b);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < C::kStages; ++i) {
+            mbar_init(&full_bar[i], 1);
+            mbar_init(&empty_bar[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&tmem_full[i], 1);
+            mbar_init(&tmem_empty[i], 4);  // one arrive per epilogue warp
+        }
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc<C::kTmemCols>(tmem_ptr_smem);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    const int m_tiles = (M + BLOCK_M - 1) / BLOCK_M;
+    const int n_tiles = (N + BN - 1) / BN;
+    const int num_tiles = m_tiles * n_tiles;
+    const int k_blocks = (K + BLOCK_K - 1) / BLOCK_K;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const int m0 = (tile % m_tiles) * BLOCK_M;
+                const int n0 = (tile / m_tiles) * BN;
+                for (int kb = 0; kb < k_blocks; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    uint8_t* sa = smem + stage * C::kStageBytes;
+                    uint8_t* sb = sa + C::kABytes;
+                    mbar_arrive_expect_tx(&full_bar[stage], C::kStageBytes);
+                    const int k0 = kb * BLOCK_K;
+                    if (!A_MN) {
+                        tma_load_2d(sa, &tmap_a, &full_bar[stage], k0, m0);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BLOCK_M / 64; ++j)
+                            tma_load_2d(sa + j * 8192, &tmap_a, &full_bar[stage], m0 + 64 * j, k0);
+                    }
+                    if (!B_MN) {
+                        tma_load_2d(sb, &tmap_b, &full_bar[stage], k0, n0);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BN / 64; ++j)
+                            tma_load_2d(sb + j * 8192, &tmap_b, &full_bar[stage], n0 + 64 * j, k0);
+                    }
+                    if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, BN, A_MN, B_MN);
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + acc * BN;
+                for (int kb = 0; kb < k_blocks; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * C::kStageBytes);
+                    const uint32_t sb = sa + C::kABytes;
+#pragma unroll
+                    for (int kk = 0; kk < BLOCK_K / UMMA_K; ++kk) {
+                        const uint64_t da = A_MN ? umma_smem_desc(sa + kk * (UMMA_K * 128), 8192, 1024)
+                                                 : umma_smem_desc(sa + kk * (UMMA_K * 2), 16, 1024);
+                        const uint64_t db = B_MN ? umma_smem_desc(sb + kk * (UMMA_K * 128), 8192, 1024)
+                                                 : umma_smem_desc(sb + kk * (UMMA_K * 2), 16, 1024);
+                        umma_bf16(tmem_d, da, db, idesc, (kb | kk) != 0 ? 1u : 0u);
+                    }
+                    umma_commit(&empty_bar[stage]);  // smem slot reusable once these MMAs retire
+                    if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(&tmem_full[acc]);  // accumulator complete
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else {
+        // ===================== epilogue (warps 2..5) =====================
+        const int quarter = warp & 3;  // TMEM lane quarter this warp may access
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        const bool do_drop = ep.dropout_p > 0.f && ep.rng != nullptr;
+        uint64_t key = 0;
+        uint32_t thr16 = 0;
+        float keep_scale = 1.f;
+        if (do_drop) {
+            key = rng_key(ep.rng->seed, ep.rng->step, ep.rng_site);
+            thr16 = rng_thr16(ep.dropout_p);
+            keep_scale = 1.f / (1.f - ep.dropout_p);
+        }
+        const float alpha = ep.alpha * (ep.alpha_dev ? __ldg(ep.alpha_dev) : 1.f);
+        const bool vec_ok_c = ep.c_fp32 ? ((ep.ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(ep.C) & 15) == 0)
+                                        : ((ep.ldc & 7) == 0 && (reinterpret_cast<uintptr_t>(ep.C) & 15) == 0);
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            const int m0 = (tile % m_tiles) * BLOCK_M;
+            const int n0 = (tile / m_tiles) * BN;
+            mbar_wait(&tmem_full[acc], acc_phase);
+            tc_fence_after();
+            const int row = m0 + quarter * 32 + lane;
+            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BN;
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                if (n0 + c >= N) break;  // warp-uniform
+                uint32_t r[32];
+                tmem_ld_32x32b_x32(taddr + c, r);
+                tmem_ld_wait();
+                if (row < M) {
+                    const int col0 = n0 + c;
+                    float v[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * alpha;
+                    if (ep.bias) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (col0 + j < N) v[j] += __ldg(ep.bias + col0 + j);
+                    }
+                    if (ep.act) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], ep.act);
+                    }
+                    if (do_drop) {
+                        const uint64_t base = static_cast<uint64_t>(row) * static_cast<uint64_t>(N) + col0;
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            v[j] = rng_keep(key, base + j, thr16) ? v[j] * keep_scale : 0.f;
+                    }
+                    if (ep.aux_mode) {
+                        const __nv_bfloat16* ax = ep.aux + static_cast<long long>(row) * ep.ldaux + col0;
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            if (col0 + j < N) {
+                                const float a = __bfloat162float(ax[j]);
+                                if (ep.aux_mode == 1) v[j] = a > 0.f ? v[j] * ep.aux_scale : 0.f;
+                                else if (ep.aux_mode == 2) v[j] += a;
+                                else v[j] *= a * (1.f - a);
+                            }
+                        }
+                    }
+                    const bool full = col0 + 32 <= N;
+                    if (ep.c_fp32) {
+                        float* out = reinterpret_cast<float*>(ep.C) + static_cast<long long>(row) * ep.ldc + col0;
+                        if (full && vec_ok_c) {
+#pragma unroll
+                            for (int j = 0; j < 32; j += 4) {
+                                float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                                if (ep.accumulate) {
+                                    const float4 old = *reinterpret_cast<const float4*>(out + j);
+                                    o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
+                                }
+                                *reinterpret_cast<float4*>(out + j) = o;
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (col0 + j < N) out[j] = ep.accumulate ? out[j] + v[j] : v[j];
+                        }
+                    } else {
+                        __nv_bfloat16* out =
+                            reinterpret_cast<__nv_bfloat16*>(ep.C) + static_cast<long long>(row) * ep.ldc + col0;
+                        if (full && vec_ok_c) {
+#pragma unroll
+                            for (int j = 0; j < 32; j += 8) {
+                                uint4 o;
+                                o.x = pack_bf16x2(v[j], v[j + 1]);
+                                o.y = pack_bf16x2(v[j + 2], v[j + 3]);
+                                o.z = pack_bf16x2(v[j + 4], v[j + 5]);
+                                o.w = pack_bf16x2(v[j + 6], v[j + 7]);
+                                *reinterpret_cast<uint4*>(out + j) = o;
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (col0 + j < N) out[j] = __float2bfloat16(v[j]);
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc<C::kTmemCols>(tmem_base);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// SIMT fallback for shapes TMA cannot describe (leading dimension not a multiple of 8 elements, e.g.
+// the reference's 4-5-4-3 MLP or the CNN head 490->10).  Same operand/epilogue contract.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+gemm_simt_kernel(const __nv_bfloat16* __restrict__ A, long long lda, int a_mn, const __nv_bfloat16* __restrict__ B,
+                 long long ldb, int b_mn, int M, int N, int K, Epilogue ep) {
+    __shared__ float sa[16][17];
+    __shared__ float sb[16][17];
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    const int row = blockIdx.y * 16 + ty, col = blockIdx.x * 16 + tx;
+    float acc = 0.f;
+    for (int k0 = 0; k0 < K; k0 += 16) {
+        {
+            const int r = blockIdx.y * 16 + ty, k = k0 + tx;
+            float v = 0.f;
+            if (r < M && k < K) v = __bfloat162float(a_mn ? A[(long long)k * lda + r] : A[(long long)r * lda + k]);
+            sa[ty][tx] = v;
+        }
+        {
+            const int c = blockIdx.x * 16 + ty, k = k0 + tx;
+            float v = 0.f;
+            if (c < N && k < K) v = __bfloat162float(b_mn ? B[(long long)k * ldb + c] : B[(long long)c * ldb + k]);
+            sb[ty][tx] = v;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < 16; ++k) acc += sa[ty][k] * sb[tx][k];
+        __syncthreads();
+    }
+    if (row >= M || col >= N) return;
+    float v = acc * ep.alpha * (ep.alpha_dev ? *ep.alpha_dev : 1.f);
+    if (ep.bias) v += ep.bias[col];
+    v = apply_act(v, ep.act);
+    if (ep.dropout_p > 0.f && ep.rng) {
+        const uint64_t key = rng_key(ep.rng->seed, ep.rng->step, ep.rng_site);
+        v = rng_keep(key, (uint64_t)row * N + col, rng_thr16(ep.dropout_p)) ? v / (1.f - ep.dropout_p) : 0.f;
+    }
+    if (ep.aux_mode) {
+        const float a = __bfloat162float(ep.aux[(long long)row * ep.ldaux + col]);
+        if (ep.aux_mode == 1) v = a > 0.f ? v * ep.aux_scale : 0.f;
+        else if (ep.aux_mode == 2) v += a;
+        else v *= a * (1.f - a);
+    }
+    if (ep.c_fp32) {
+        float* out = reinterpret_cast<float*>(ep.C) + (long long)row * ep.ldc + col;
+        *out = ep.accumulate ? *out + v : v;
+    } else {
+        reinterpret_cast<__nv_bfloat16*>(ep.C)[(long long)row * ep.ldc + col] = __float2bfloat16(v);
+    }
+}
+
+template <bool A_MN, bool B_MN, int BN>
+static int launch(const b200ml_gemm_args* g, const Epilogue& ep, cudaStream_t stream) {
+    using C = Cfg<BN>;
+    CUtensorMap ta, tb;
+    {
+        // K-major: dims {K, rows}; MN-major: dims {rows(MN), K}
+        uint64_t dims[2], strides[2] = {2, (uint64_t)g->lda * 2};
+        uint32_t box[2];
+        if (!A_MN) { dims[0] = g->K; dims[1] = g->M; box[0] = 64; box[1] = BLOCK_M; }
+        else       { dims[0] = g->M; dims[1] = g->K; box[0] = 64; box[1] = BLOCK_K; }
+        if (make_tmap_bf16(&ta, g->A, 2, dims, strides, box)) return -1;
+    }
+    {
+        uint64_t dims[2], strides[2] = {2, (uint64_t)g->ldb * 2};
+        uint32_t box[2];
+        if (!B_MN) { dims[0] = g->K; dims[1] = g->N; box[0] = 64; box[1] = BN; }
+        else       { dims[0] = g->N; dims[1] = g->K; box[0] = 64; box[1] = BLOCK_K; }
+        if (make_tmap_bf16(&tb, g->B, 2, dims, strides, box)) return -1;
+    }
+    auto kern = gemm_bf16_kernel<A_MN, B_MN, BN>;
+    static bool attr_set = false;  // per instantiation
+    if (!attr_set) {
+        B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+        attr_set = true;
+    }
+    const int m_tiles = (g->M + BLOCK_M - 1) / BLOCK_M, n_tiles = (g->N + BN - 1) / BN;
+    const int tiles = m_tiles * n_tiles;
+    const int grid = tiles < sm_count() ? tiles : sm_count();
+    kern<<<grid, kNumThreads, C::kSmemBytes, stream>>>(ta, tb, g->M, g->N, g->K, ep);
+    B200_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+template <int BN>
+static int dispatch_major(const b200ml_gemm_args* g, const Epilogue& ep, cudaStream_t s) {
+    if (!g->a_mn_major && !g->b_mn_major) return launch<false, false, BN>(g, ep, s);
+    if (!g->a_mn_major && g->b_mn_major) return launch<false, true, BN>(g, ep, s);
+    if (g->a_mn_major && !g->b_mn_major) return launch<true, false, BN>(g, ep, s);
+    return launch<true, true, BN>(g, ep, s);
+}
+
+}  // namespace gemm
+}  // namespace b200
+
+extern "C" int b200ml_gemm_bf16(const b200ml_gemm_args* g, cudaStream_t stream) {
+    using namespace b200;
+    using namespace b200::gemm;
+    B200_REQUIRE(g && g->A && g->B && g->C, "gemm: null pointer");
+    B200_REQUIRE(g->M > 0 && g->N > 0 && g->K > 0, "gemm: bad shape %dx%dx%d", g->M, g->N, g->K);
+    B200_REQUIRE(!(g->accumulate && !g->c_fp32), "gemm: accumulate needs fp32 C");
+    Epilogue ep;
+    ep.C = g->C; ep.ldc = g->ldc; ep.c_fp32 = g->c_fp32; ep.bias = g->bias; ep.act = g->act;
+    ep.aux = reinterpret_cast<const __nv_bfloat16*>(g->aux); ep.ldaux = g->ldaux;
+    ep.aux_mode = g->aux ? g->aux_mode : 0; ep.aux_scale = g->aux_scale; ep.alpha = g->alpha; ep.alpha_dev = g->alpha_dev;
+    ep.accumulate = g->accumulate; ep.dropout_p = g->dropout_p;
+    ep.rng = reinterpret_cast<const RngState*>(g->rng_state); ep.rng_site = g->rng_site;
+
+    const bool tma_ok = (g->lda % 8 == 0) && (g->ldb % 8 == 0) && ((reinterpret_cast<uintptr_t>(g->A) & 15) == 0) &&
+                        ((reinterpret_cast<uintptr_t>(g->B) & 15) == 0) && g->force_simt == 0;
+    if (!tma_ok) {
+        dim3 grid((g->N + 15) / 16, (g->M + 15) / 16);
+        gemm_simt_kernel<<<grid, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(g->A), g->lda, g->a_mn_major,
+                                                   reinterpret_cast<const __nv_bfloat16*>(g->B), g->ldb,
+                                                   g->b_mn_major, g->M, g->N, g->K, ep);
+        B200_CHECK_CUDA(cudaGetLastError());
+        return 0;
+    }
+    // Tile-N choice: widest tile that still gives every SM work; narrow N uses the narrow tile.
+    int bn = g->tile_n;
+    if (bn != 64 && bn != 128 && bn != 256) {
+        const long long m_tiles = (g->M + BLOCK_M - 1) / BLOCK_M;
+        const int sms = sm_count();
+        if (g->N <= 64) bn = 64;
+        else if (g->N <= 128) bn = 128;
+        else {
+            bn = 256;
+            if (m_tiles * ((g->N + 255) / 256) < 2LL * sms) bn = 128;
+            if (bn == 128 && m_tiles * ((g->N + 127) / 128) < sms) bn = 64;
+        }
+    }
+    if (bn == 256) return dispatch_major<256>(g, ep, stream);
+    if (bn == 128) return dispatch_major<128>(g, ep, stream);
+    return dispatch_major<64>(g, ep, stream);
+}

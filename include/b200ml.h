@@ -1,0 +1,111 @@
+/* b200ml — C ABI of libb200ml.so (sm_100a kernels + host runtime).
+ *
+ * Every entry point takes raw device pointers and a CUDA stream, launches asynchronously on that stream and
+ * returns 0 on success or -1 on failure (text from b200ml_last_error()).  No entry point allocates device
+ * memory unless its comment says so; scratch is passed in by the caller (size from the *_scratch_bytes helper).
+ * bf16 tensors are row-major with an explicit leading dimension in elements where one is taken.
+ *
+ * The "ref:" notes cite the reference behaviour each kernel reproduces (paths relative to the reference repo).
+ */
+#ifndef B200ML_H_
+#define B200ML_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#ifndef __CUDA_RUNTIME_H__
+typedef struct CUstream_st* cudaStream_t;
+#endif
+
+/* ------------------------------------------------------------------------------------------------ runtime */
+const char* b200ml_last_error(void);
+int b200ml_version(void);
+int b200ml_device_info(int* sm_count, int* cc_major, int* cc_minor, size_t* smem_optin);
+
+/* ------------------------------------------------------------------------------------------------ K4/K5/K13 GEMM
+ * C[M,N] = epilogue(alpha * A·Bᵀ).  tcgen05/TMEM/TMA kernel; SIMT fallback when a leading dimension is not a
+ * multiple of 8 elements or a base pointer is not 16-byte aligned (or force_simt != 0).
+ *   a_mn_major = 0: A is [M,K] (K contiguous)      1: A is stored [K,M] (M contiguous)
+ *   b_mn_major = 0: B is [N,K] (K contiguous)      1: B is stored [K,N] (N contiguous)
+ * epilogue order: v = alpha*acc (+bias[col]) -> act (0 none, 1 ReLU, 2 sigmoid) -> dropout(dropout_p) ->
+ *   aux_mode (0 none; 1: v = aux>0 ? v*aux_scale : 0; 2: v += aux; 3: v *= aux*(1-aux)) -> store (bf16 or fp32;
+ *   fp32 may accumulate into C).
+ * ref: every nn.Linear + ReLU/Sigmoid/Dropout neighbour (transformer.py:71-72,107-117,177-179,272;
+ *      distributed_multilayer_perceptron.py:47-53). */
+typedef struct {
+    int M, N, K;
+    const void* A; long long lda; int a_mn_major;
+    const void* B; long long ldb; int b_mn_major;
+    void* C; long long ldc; int c_fp32;
+    const float* bias;
+    int act;
+    const void* aux; long long ldaux; int aux_mode; float aux_scale;
+    float alpha;
+    const float* alpha_dev; /* optional device scalar multiplied into alpha */
+    int accumulate;
+    float dropout_p; const void* rng_state; unsigned rng_site;
+    int tile_n;      /* 0 = auto, or 64 / 128 / 256 */
+    int force_simt;  /* testing: run the SIMT fallback */
+} b200ml_gemm_args;
+int b200ml_gemm_bf16(const b200ml_gemm_args* args, cudaStream_t stream);
+
+/* ------------------------------------------------------------------------------------------------ K11/K12 LayerNorm
+ * y = LN(x + dropout(a)); either of a / x may be NULL.  z_out (bf16, optional) keeps the pre-norm sum for backward.
+ * d must be a multiple of 8 and <= 1024.  ref: transformer.py:86-101,130-139,209-224. */
+int b200ml_layernorm_fwd(const void* a, const void* x, const float* gamma, const float* beta, void* y, void* z_out,
+                         float* mean, float* rstd, int rows, int d, float eps, float dropout_p, const void* rng_state,
+                         unsigned rng_site, cudaStream_t stream);
+size_t b200ml_layernorm_bwd_scratch_bytes(int rows, int d);
+/* dz = gradient w.r.t. the pre-norm sum (i.e. the residual branch); da (optional) = dz through the dropout mask.
+ * dgamma/dbeta are overwritten (accumulate = 0) or added to.  scratch holds per-CTA partial sums. */
+int b200ml_layernorm_bwd(const void* dy, const void* z, const float* mean, const float* rstd, const float* gamma,
+                         void* dz, void* da, float* dgamma, float* dbeta, void* scratch, size_t scratch_bytes, int rows,
+                         int d, float dropout_p, const void* rng_state, unsigned rng_site, int accumulate,
+                         cudaStream_t stream);
+
+/* ------------------------------------------------------------------------------------------------ K7/K8 embedding
+ * ref: transformer.py:27-62 (sinusoidal PE + embedding + dropout), distributed_lstm.py:115,128 (padding_idx). */
+int b200ml_pe_table(float* pe, int S, int d, cudaStream_t stream);
+int b200ml_embedding_fwd(const long long* tokens, const void* table_bf16, const float* pe, void* out, int out_fp32,
+                         int n_tokens, int S, int d, int V, float dropout_p, const void* rng_state, unsigned rng_site,
+                         cudaStream_t stream);
+/* dtable (fp32, [V,d]) += scatter of dout; the caller zeroes dtable once per step.  padding_idx < 0 disables it. */
+int b200ml_embedding_bwd(const long long* tokens, const void* dout, int dout_fp32, float* dtable, int n_tokens, int d,
+                         int V, long long padding_idx, float dropout_p, const void* rng_state, unsigned rng_site,
+                         cudaStream_t stream);
+
+/* ------------------------------------------------------------------------------------------------ K6 cross-entropy
+ * ref: nn.CrossEntropyLoss (distributed_cnn.py:141) and ignore_index=0 + masked mean
+ *      (pytorch_machine_translator.py:125,182-188). */
+int b200ml_xent_count(const long long* targets, int rows, long long ignore_index, float* inv_count2 /*[2]*/,
+                      cudaStream_t stream);
+/* logits are overwritten with d(loss)/d(logits) when write_grad != 0.  grad scale = *grad_scale_dev if non-NULL. */
+int b200ml_xent_fwd_bwd(void* logits, int logits_fp32, long long ld_logits, const long long* targets, float* row_loss,
+                        const float* grad_scale_dev, float grad_scale_host, int rows, int V, long long ignore_index,
+                        int write_grad, cudaStream_t stream);
+int b200ml_loss_reduce(const float* row_loss, int rows, const float* inv_count_dev, float inv_host, float* out,
+                       cudaStream_t stream);
+
+/* ------------------------------------------------------------------------------------------------ K15/K16/K17
+ * kind 1 = SGD, 2 = Adam (torch defaults semantics).  p16 (optional) receives the bf16 working copy.
+ * ref: distributed_cnn.py:138,183; distributed_lstm.py:141,194; pytorch_machine_translator.py:129,196. */
+int b200ml_optim_step(float* p, const void* g, int g_bf16, float* m, float* v, void* p16, long long n, int kind,
+                      float lr, float beta1, float beta2, float eps, float weight_decay, const int* step_dev,
+                      float grad_scale, cudaStream_t stream);
+int b200ml_cast_f32_bf16(const float* src, void* dst, long long n, cudaStream_t stream);
+size_t b200ml_colsum_scratch_bytes(int rows, int cols);
+int b200ml_colsum_bf16(const void* x, long long ldx, int rows, int cols, float* out, int accumulate, void* scratch,
+                       size_t scratch_bytes, cudaStream_t stream);
+int b200ml_counters_advance(void* rng_state /*{u64 seed, u64 step}*/, int* step_dev, cudaStream_t stream);
+/* ref: accuracy_fn / argmax (distributed_cnn.py:144-147,211-212) */
+int b200ml_argmax_accuracy(const void* logits, int logits_fp32, long long ld, const long long* targets, int rows, int C,
+                           int* pred, int* correct_count, cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200ML_H_ */

@@ -1,0 +1,257 @@
+"""GEMM-shaped ops on the tcgen05 kernel (csrc/kernels/gemm_tcgen05.cu): raw ``gemm``, ``linear`` and the fused
+multi-layer chain ``mlp_chain`` (Linear → act → dropout → Linear …) whose backward folds each activation's
+derivative into the dgrad GEMM epilogue.
+
+Reference behaviour: nn.Linear / nn.ReLU / nn.Sigmoid / nn.Dropout as used in transformer.py:71-72,104-117,177-179,272
+and distributed_multilayer_perceptron.py:44-53.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from .. import _native
+from ..utils import workspace
+from ..utils.rng import DeviceCounters
+
+ACT_NONE, ACT_RELU, ACT_SIGMOID = 0, 1, 2
+_ACT = {None: 0, "none": 0, "relu": 1, "sigmoid": 2, 0: 0, 1: 1, 2: 2}
+
+
+def _ref_dropout_mask(shape, p, device):
+    return (torch.rand(shape, device=device) >= p).float() / (1.0 - p)
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False, out: torch.Tensor | None = None,
+         out_dtype=torch.bfloat16, bias: torch.Tensor | None = None, act=0, aux: torch.Tensor | None = None,
+         aux_mode: int = 0, aux_scale: float = 1.0, alpha: float = 1.0, alpha_dev: torch.Tensor | None = None,
+         accumulate: bool = False, dropout_p: float = 0.0, site: int = 0, tile_n: int = 0,
+         force_simt: bool = False, n_logical: int | None = None) -> torch.Tensor:
+    """C[M,N] = epilogue(alpha · A·Bᵀ).
+
+    ``a`` is [M,K] (a_mn=False) or stored [K,M] (a_mn=True); ``b`` is [N,K] (b_mn=False) or stored [K,N]
+    (b_mn=True).  Rows may be strided (stride(1) must be 1).  ``n_logical`` restricts N when ``b``/``out`` carry
+    padding columns.  See include/b200ml.h for the epilogue order.
+    """
+    act = _ACT[act]
+    assert a.dim() == 2 and b.dim() == 2 and a.stride(1) == 1 and b.stride(1) == 1
+    M, K = (a.shape[1], a.shape[0]) if a_mn else (a.shape[0], a.shape[1])
+    N, Kb = (b.shape[1], b.shape[0]) if b_mn else (b.shape[0], b.shape[1])
+    assert K == Kb, f"reduction mismatch {K} vs {Kb}"
+    if n_logical is not None:
+        N = n_logical
+    if out is None:
+        out = torch.empty((M, N), dtype=out_dtype, device=a.device)
+    assert out.stride(1) == 1 and out.shape[0] >= M and out.shape[1] >= N
+
+    if not _native.use_native(a):
+        # PyTorch restatement (CPU): same math in fp32
+        A = (a.t() if a_mn else a).float()
+        B = (b.t() if b_mn else b).float()[:N]
+        v = alpha * (A @ B.t())
+        if alpha_dev is not None:
+            v = v * alpha_dev.float()
+        if bias is not None:
+            v = v + bias.float()[:N]
+        if act == ACT_RELU:
+            v = torch.relu(v)
+        elif act == ACT_SIGMOID:
+            v = torch.sigmoid(v)
+        if dropout_p > 0:
+            v = v * _ref_dropout_mask(v.shape, dropout_p, v.device)
+        if aux is not None and aux_mode:
+            ax = aux[:M, :N].float()
+            if aux_mode == 1:
+                v = torch.where(ax > 0, v * aux_scale, torch.zeros_like(v))
+            elif aux_mode == 2:
+                v = v + ax
+            else:
+                v = v * ax * (1 - ax)
+        tgt = out[:M, :N]
+        if accumulate:
+            tgt.add_(v.to(out.dtype))
+        else:
+            tgt.copy_(v.to(out.dtype))
+        return out
+
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16, "native gemm takes bf16 operands"
+    assert out.dtype in (torch.bfloat16, torch.float32)
+    lib = _native.load()
+    g = _native.GemmArgs()
+    g.M, g.N, g.K = M, N, K
+    g.A, g.lda, g.a_mn_major = a.data_ptr(), a.stride(0), int(a_mn)
+    g.B, g.ldb, g.b_mn_major = b.data_ptr(), b.stride(0), int(b_mn)
+    g.C, g.ldc, g.c_fp32 = out.data_ptr(), out.stride(0), int(out.dtype == torch.float32)
+    if bias is not None:
+        assert bias.dtype == torch.float32 and bias.is_contiguous()
+        g.bias = bias.data_ptr()
+    g.act = act
+    if aux is not None and aux_mode:
+        assert aux.dtype == torch.bfloat16 and aux.stride(1) == 1
+        g.aux, g.ldaux, g.aux_mode, g.aux_scale = aux.data_ptr(), aux.stride(0), aux_mode, aux_scale
+    g.alpha = alpha
+    if alpha_dev is not None:
+        assert alpha_dev.dtype == torch.float32
+        g.alpha_dev = alpha_dev.data_ptr()
+    g.accumulate = int(accumulate)
+    if dropout_p > 0:
+        g.dropout_p = dropout_p
+        g.rng_state = DeviceCounters.get(a.device).rng.data_ptr()
+        g.rng_site = site
+    g.tile_n = tile_n
+    g.force_simt = int(force_simt)
+    _native.check(lib.b200ml_gemm_bf16(C.byref(g), _native.stream_ptr()), "gemm_bf16")
+    return out
+
+
+def colsum(x: torch.Tensor, out: torch.Tensor | None = None, accumulate: bool = False) -> torch.Tensor:
+    """Column sums of a bf16 [rows, cols] matrix in fp32 (bias gradients); deterministic two-stage reduction."""
+    rows, cols = x.shape
+    if out is None:
+        out = torch.empty(cols, dtype=torch.float32, device=x.device)
+    if not _native.use_native(x):
+        s = x.float().sum(0)
+        out.add_(s) if accumulate else out.copy_(s)
+        return out
+    lib = _native.load()
+    nbytes = lib.b200ml_colsum_scratch_bytes(rows, cols)
+    ws = workspace.get("colsum", nbytes, x.device)
+    _native.check(lib.b200ml_colsum_bf16(x.data_ptr(), x.stride(0), rows, cols, out.data_ptr(), int(accumulate),
+                                         ws.data_ptr(), ws.numel(), _native.stream_ptr()), "colsum")
+    return out
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# parameter plumbing shared by every op with weights
+# ----------------------------------------------------------------------------------------------------------------
+def working_copy(param: torch.Tensor) -> torch.Tensor:
+    """bf16 working copy of an fp32 master parameter.
+
+    The DP engine / fused optimizer refreshes it in the same kernel that updates the master weights
+    (``param._b200_w16`` is then a view into the flat bf16 buffer).  Without an engine the copy is re-cast when the
+    parameter's version counter moves.
+    """
+    if param.dtype == torch.bfloat16:
+        return param.detach()
+    w16 = getattr(param, "_b200_w16", None)
+    if w16 is not None and getattr(param, "_b200_w16_managed", False):
+        return w16
+    ver = param._version
+    if w16 is None or getattr(param, "_b200_w16_ver", None) != ver or w16.device != param.device:
+        w16 = param.detach().to(torch.bfloat16)
+        param._b200_w16 = w16
+        param._b200_w16_ver = ver
+    return w16
+
+
+def deliver_grad(param: torch.Tensor, compute, shape) -> torch.Tensor | None:
+    """Produce a parameter gradient.  With a DP engine the gradient is written straight into the parameter's slot of
+    the flat bucket (``param._b200_grad``) and the engine is told the slot is ready — autograd sees ``None``.
+    Otherwise a fresh fp32 tensor is returned to autograd."""
+    slot = getattr(param, "_b200_grad", None)
+    if slot is not None and slot.device == param.device:
+        acc = bool(getattr(param, "_b200_grad_accumulate", False))
+        compute(slot.view(shape), acc)
+        ready = getattr(param, "_b200_ready", None)
+        if ready is not None:
+            ready()
+        return None
+    out = torch.empty(shape, dtype=torch.float32, device=param.device)
+    compute(out, False)
+    return out.to(param.dtype) if param.dtype != torch.float32 else out
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# fused Linear chain
+# ----------------------------------------------------------------------------------------------------------------
+class _MLPChain(torch.autograd.Function):
+    """y = L_n(... act_1(L_1(x)))   with per-layer activation ∈ {none, relu, sigmoid} and optional dropout after it.
+
+    Saves only the layer inputs (bf16).  Backward per layer: dW = dZᵀ·X, db = colsum(dZ), dX = dZ·W with the previous
+    layer's activation derivative applied in the dgrad epilogue (aux_mode 1 / 3), so no elementwise pass exists.
+    """
+
+    @staticmethod
+    def forward(ctx, x, n_layers, acts, drops, sites, *params):
+        weights = params[:n_layers]
+        biases = params[n_layers:]
+        lead = x.shape[:-1]
+        h = x.reshape(-1, x.shape[-1])
+        if h.dtype != torch.bfloat16:
+            h = h.to(torch.bfloat16)
+        if not h.is_contiguous():
+            h = h.contiguous()
+        inputs = []
+        for i in range(n_layers):
+            inputs.append(h)
+            w16 = working_copy(weights[i])
+            b = biases[i]
+            h = gemm(h, w16, bias=None if b is None else b.detach(), act=acts[i], dropout_p=drops[i], site=sites[i])
+        ctx.n_layers, ctx.acts, ctx.drops = n_layers, acts, drops
+        ctx.params = params
+        ctx.x_dtype = x.dtype
+        ctx.save_for_backward(*inputs, h)
+        return h.reshape(*lead, h.shape[-1])
+
+    @staticmethod
+    def backward(ctx, dy):
+        n = ctx.n_layers
+        weights, biases = ctx.params[:n], ctx.params[n:]
+        saved = ctx.saved_tensors
+        inputs, y = saved[:n], saved[n]
+        dz = dy.reshape(-1, dy.shape[-1])
+        if dz.dtype != torch.bfloat16:
+            dz = dz.to(torch.bfloat16)
+        if not dz.is_contiguous():
+            dz = dz.contiguous()
+        # last layer's own activation (rare: chain ending in an activation)
+        if ctx.acts[n - 1]:
+            yf = y.float()
+            if ctx.acts[n - 1] == ACT_RELU:
+                dz = (dz.float() * (yf > 0) / (1.0 - ctx.drops[n - 1])).to(torch.bfloat16)
+            else:
+                assert ctx.drops[n - 1] == 0
+                dz = (dz.float() * yf * (1 - yf)).to(torch.bfloat16)
+        gw = [None] * n
+        gb = [None] * n
+        dx = None
+        for i in range(n - 1, -1, -1):
+            xin = inputs[i]
+            w = weights[i]
+            N, K = w.shape
+            if w.requires_grad:
+                gw[i] = deliver_grad(w, lambda out, acc, dz=dz, xin=xin: gemm(dz, xin, a_mn=True, b_mn=True, out=out,
+                                                                             accumulate=acc), (N, K))
+            b = biases[i]
+            if b is not None and b.requires_grad:
+                gb[i] = deliver_grad(b, lambda out, acc, dz=dz: colsum(dz, out=out, accumulate=acc), (N,))
+            need_dx = i > 0 or ctx.needs_input_grad[0]
+            if need_dx:
+                w16 = working_copy(w)
+                if i > 0 and ctx.acts[i - 1] == ACT_RELU:
+                    dz = gemm(dz, w16, b_mn=True, aux=xin, aux_mode=1, aux_scale=1.0 / (1.0 - ctx.drops[i - 1]))
+                elif i > 0 and ctx.acts[i - 1] == ACT_SIGMOID:
+                    assert ctx.drops[i - 1] == 0, "sigmoid followed by dropout is not fused"
+                    dz = gemm(dz, w16, b_mn=True, aux=xin, aux_mode=3)
+                else:
+                    dz = gemm(dz, w16, b_mn=True)
+                if i == 0:
+                    dx = dz
+        if dx is not None:
+            dx = dx.reshape(*dy.shape[:-1], dx.shape[-1]).to(ctx.x_dtype)
+        return (dx, None, None, None, None, *gw, *gb)
+
+
+def mlp_chain(x, weights, biases, acts, drops=None, sites=None, training: bool = True):
+    """Fused chain of Linear layers; ``acts[i]`` follows layer i ('relu' | 'sigmoid' | None), ``drops[i]`` follows it."""
+    n = len(weights)
+    acts = tuple(_ACT[a] for a in acts)
+    drops = tuple((d if training else 0.0) for d in (drops or [0.0] * n))
+    sites = tuple(sites or [0] * n)
+    return _MLPChain.apply(x, n, acts, drops, sites, *weights, *biases)
+
+
+def linear(x, weight, bias=None, act=None, dropout_p: float = 0.0, site: int = 0, training: bool = True):
+    """y = dropout(act(x·Wᵀ + b)) — nn.Linear with its activation/dropout fused into the GEMM epilogue."""
+    return mlp_chain(x, [weight], [bias], [act], [dropout_p], [site], training)

@@ -1,0 +1,139 @@
+"""Softmax cross-entropy (csrc/kernels/xent.cu): a generic ``cross_entropy`` for the small classifier heads and
+``linear_cross_entropy`` — the translator's 512→V_de projection, loss and both of its gradients as one autograd node
+that never materialises fp32 logits or a separate gradient tensor.
+
+Reference: nn.CrossEntropyLoss() (distributed_cnn.py:141, distributed_lstm.py:142,
+distributed_multilayer_perceptron.py:109); CrossEntropyLoss(ignore_index=0, reduction='none') + masked mean
+(pytorch_machine_translator.py:125,182-188); the head Linear (transformer.py:272,283).
+"""
+from __future__ import annotations
+
+import torch
+
+from .. import _native
+from .gemm import colsum, deliver_grad, gemm, working_copy
+
+
+def _xent_native(logits, ld, targets, V, ignore_index, write_grad=True):
+    """Runs the count + fused fwd/bwd + reduce kernels.  ``logits`` is overwritten with the gradient."""
+    lib = _native.load()
+    rows = targets.numel()
+    dev = logits.device
+    inv = torch.empty(2, dtype=torch.float32, device=dev)
+    row_loss = torch.empty(rows, dtype=torch.float32, device=dev)
+    loss = torch.empty(1, dtype=torch.float32, device=dev)
+    s = _native.stream_ptr()
+    _native.check(lib.b200ml_xent_count(targets.data_ptr(), rows, ignore_index, inv.data_ptr(), s), "xent_count")
+    _native.check(lib.b200ml_xent_fwd_bwd(logits.data_ptr(), int(logits.dtype == torch.float32), ld,
+                                          targets.data_ptr(), row_loss.data_ptr(), inv.data_ptr(), 0.0, rows, V,
+                                          ignore_index, int(write_grad), s), "xent_fwd_bwd")
+    _native.check(lib.b200ml_loss_reduce(row_loss.data_ptr(), rows, inv.data_ptr(), 0.0, loss.data_ptr(), s),
+                  "loss_reduce")
+    return loss[0], row_loss
+
+
+class _CrossEntropy(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, targets, ignore_index):
+        V = logits.shape[-1]
+        z = logits.reshape(-1, V)
+        t = targets.reshape(-1).contiguous()
+        ctx.shape, ctx.dtype = logits.shape, logits.dtype
+        if _native.use_native(z):
+            g = z.detach().clone() if z.dtype in (torch.float32, torch.bfloat16) else z.detach().float()
+            g = g.contiguous()
+            loss, _ = _xent_native(g, g.stride(0), t, V, ignore_index)
+            ctx.save_for_backward(g)
+            return loss
+        zf = z.float()
+        valid = t != ignore_index
+        lse = torch.logsumexp(zf, -1)
+        picked = zf.gather(1, t.clamp(0, V - 1).unsqueeze(1)).squeeze(1)
+        cnt = valid.sum().clamp(min=1)
+        loss = ((lse - picked) * valid).sum() / cnt
+        g = (torch.softmax(zf, -1) - torch.nn.functional.one_hot(t.clamp(0, V - 1), V)) * valid.unsqueeze(1) / cnt
+        ctx.save_for_backward(g)
+        return loss
+
+    @staticmethod
+    def backward(ctx, gout):
+        (g,) = ctx.saved_tensors
+        return (g.float() * gout).to(ctx.dtype).reshape(ctx.shape), None, None
+
+
+def cross_entropy(logits, targets, ignore_index: int = -100):
+    """Mean softmax cross-entropy over the rows whose target != ignore_index."""
+    return _CrossEntropy.apply(logits, targets, ignore_index)
+
+
+class _LinearCrossEntropy(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, h, weight, bias, targets, ignore_index):
+        V, d = weight.shape
+        h2 = h.reshape(-1, d)
+        t = targets.reshape(-1).contiguous()
+        rows = h2.shape[0]
+        ctx.params = (weight, bias)
+        ctx.h_shape, ctx.h_dtype = h.shape, h.dtype
+        if _native.use_native(h2):
+            h2 = h2.to(torch.bfloat16).contiguous()
+            w16 = working_copy(weight)
+            ld = (V + 7) // 8 * 8  # TMA needs 16-byte row pitch
+            logits = torch.empty(rows, ld, dtype=torch.bfloat16, device=h.device)
+            gemm(h2, w16, out=logits, bias=None if bias is None else bias.detach(), n_logical=V)
+            loss, _ = _xent_native(logits, ld, t, V, ignore_index)
+            ctx.save_for_backward(h2, logits)  # logits now hold d(loss)/d(logits)
+            ctx.V = V
+            return loss
+        zf = h2.float() @ weight.float().t()
+        if bias is not None:
+            zf = zf + bias.float()
+        valid = t != ignore_index
+        cnt = valid.sum().clamp(min=1)
+        lse = torch.logsumexp(zf, -1)
+        picked = zf.gather(1, t.clamp(0, V - 1).unsqueeze(1)).squeeze(1)
+        loss = ((lse - picked) * valid).sum() / cnt
+        g = (torch.softmax(zf, -1) - torch.nn.functional.one_hot(t.clamp(0, V - 1), V)) * valid.unsqueeze(1) / cnt
+        ctx.save_for_backward(h2, g)
+        ctx.V = V
+        return loss
+
+    @staticmethod
+    def backward(ctx, gout):
+        h2, g = ctx.saved_tensors
+        weight, bias = ctx.params
+        V = ctx.V
+        d = weight.shape[1]
+        if _native.use_native(h2):
+            gdev = gout.reshape(1).float().contiguous()
+            gv = g[:, :V]
+            dh = None
+            if ctx.needs_input_grad[0]:
+                dh = gemm(gv, working_copy(weight), b_mn=True, alpha_dev=gdev)
+                dh = dh.reshape(ctx.h_shape).to(ctx.h_dtype)
+            dw = db = None
+            if weight.requires_grad:
+                dw = deliver_grad(weight, lambda out, acc: gemm(gv, h2, a_mn=True, b_mn=True, out=out, accumulate=acc,
+                                                                 alpha_dev=gdev), (V, d))
+            if bias is not None and bias.requires_grad:
+                def _db(out, acc):
+                    if acc:
+                        out.add_(colsum(gv) * gdev)
+                    else:
+                        colsum(gv, out=out)
+                        out.mul_(gdev)
+                db = deliver_grad(bias, _db, (V,))
+            return dh, dw, db, None, None
+        gf = g.float() * gout
+        dh = (gf @ weight.float()).to(ctx.h_dtype).reshape(ctx.h_shape) if ctx.needs_input_grad[0] else None
+        dw = deliver_grad(weight, lambda out, acc: out.add_(gf.t() @ h2.float()) if acc else out.copy_(gf.t() @ h2.float()),
+                          (V, d)) if weight.requires_grad else None
+        db = None
+        if bias is not None and bias.requires_grad:
+            db = deliver_grad(bias, lambda out, acc: out.add_(gf.sum(0)) if acc else out.copy_(gf.sum(0)), (V,))
+        return dh, dw, db, None, None
+
+
+def linear_cross_entropy(h, weight, bias, targets, ignore_index: int = -100):
+    """mean_{valid}( CE(h·Wᵀ + b, targets) ) as a single node (head GEMM → in-place softmax-CE gradient → dgrad/wgrad)."""
+    return _LinearCrossEntropy.apply(h, weight, bias, targets, ignore_index)

@@ -1,0 +1,120 @@
+"""tcgen05 GEMM vs a plain fp32 PyTorch restatement (operands rounded to bf16 first)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _ref(a, b, a_mn, b_mn):
+    A = (a.t() if a_mn else a).float().cpu()
+    B = (b.t() if b_mn else b).float().cpu()
+    return A @ B.t()
+
+
+def _check(out, ref, K, tol_scale=1.0):
+    out = out.float().cpu()
+    err = (out - ref).abs().max().item()
+    bound = tol_scale * (0.02 * ref.abs().max().item() + 1e-2)
+    assert err <= bound, f"max err {err} > {bound}"
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, False), (True, True)])
+@pytest.mark.parametrize("M,N,K,tile_n", [
+    (128, 64, 64, 64), (256, 128, 128, 128), (384, 512, 192, 256), (200, 136, 72, 0), (1000, 264, 520, 0),
+    (6400, 512, 512, 0),
+])
+def test_gemm_layouts(a_mn, b_mn, M, N, K, tile_n):
+    from b200ml.ops.gemm import gemm
+    torch.manual_seed(0)
+    dev = "cuda"
+    a = torch.randn((K, M) if a_mn else (M, K), device=dev).to(torch.bfloat16)
+    b = torch.randn((K, N) if b_mn else (N, K), device=dev).to(torch.bfloat16)
+    out = gemm(a, b, a_mn=a_mn, b_mn=b_mn, out_dtype=torch.float32, tile_n=tile_n)
+    torch.cuda.synchronize()
+    _check(out, _ref(a, b, a_mn, b_mn), K)
+    out16 = gemm(a, b, a_mn=a_mn, b_mn=b_mn, tile_n=tile_n)
+    _check(out16, _ref(a, b, a_mn, b_mn), K, tol_scale=2.0)
+
+
+def test_gemm_simt_matches():
+    from b200ml.ops.gemm import gemm
+    torch.manual_seed(1)
+    a = torch.randn(77, 50, device="cuda").to(torch.bfloat16)   # lda = 50: not TMA-describable -> SIMT
+    b = torch.randn(33, 50, device="cuda").to(torch.bfloat16)
+    out = gemm(a, b, out_dtype=torch.float32)
+    _check(out, _ref(a, b, False, False), 50)
+    a2 = torch.randn(256, 128, device="cuda").to(torch.bfloat16)
+    b2 = torch.randn(128, 128, device="cuda").to(torch.bfloat16)
+    o1 = gemm(a2, b2, out_dtype=torch.float32, force_simt=True)
+    o2 = gemm(a2, b2, out_dtype=torch.float32)
+    assert (o1 - o2).abs().max().item() < 1e-2
+
+
+def test_gemm_epilogues():
+    from b200ml.ops.gemm import gemm
+    torch.manual_seed(2)
+    M, N, K = 300, 200, 128
+    a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
+    b = (torch.randn(N, K, device="cuda") * 0.1).to(torch.bfloat16)
+    bias = torch.randn(N, device="cuda")
+    aux = torch.randn(M, N, device="cuda").to(torch.bfloat16)
+    base = a.float().cpu() @ b.float().cpu().t()
+    o = gemm(a, b, bias=bias, act="relu", out_dtype=torch.float32)
+    _check(o, torch.relu(base + bias.cpu()), K)
+    o = gemm(a, b, bias=bias, act="sigmoid", out_dtype=torch.float32)
+    _check(o, torch.sigmoid(base + bias.cpu()), K)
+    o = gemm(a, b, aux=aux, aux_mode=1, aux_scale=1.25, out_dtype=torch.float32)
+    _check(o, torch.where(aux.float().cpu() > 0, base * 1.25, torch.zeros_like(base)), K)
+    o = gemm(a, b, aux=aux, aux_mode=2, out_dtype=torch.float32, alpha=0.5)
+    _check(o, 0.5 * base + aux.float().cpu(), K)
+    acc = torch.ones(M, N, device="cuda")
+    gemm(a, b, out=acc, accumulate=True, alpha_dev=torch.tensor([2.0], device="cuda"))
+    _check(acc, 2 * base + 1, K)
+    # padded output / logical N
+    outp = torch.zeros(M, 208, dtype=torch.bfloat16, device="cuda")
+    gemm(a, b, out=outp, n_logical=N)
+    _check(outp[:, :N], base, K, tol_scale=2.0)
+    assert outp[:, N:].abs().max().item() == 0
+
+
+def test_gemm_dropout_statistics_and_replay():
+    from b200ml.ops.gemm import gemm
+    from b200ml.utils.rng import DeviceCounters
+    ctr = DeviceCounters.get("cuda")
+    ctr.seed(123)
+    a = torch.ones(512, 64, device="cuda").to(torch.bfloat16)
+    b = torch.ones(256, 64, device="cuda").to(torch.bfloat16)
+    o1 = gemm(a, b, dropout_p=0.25, site=7, out_dtype=torch.float32)
+    o2 = gemm(a, b, dropout_p=0.25, site=7, out_dtype=torch.float32)
+    assert torch.equal(o1, o2)                      # same (seed, step, site) -> same mask
+    keep = (o1 != 0).float().mean().item()
+    assert abs(keep - 0.75) < 0.01
+    assert abs(o1.max().item() - 64 / 0.75) < 0.5
+    ctr.advance()
+    o3 = gemm(a, b, dropout_p=0.25, site=7, out_dtype=torch.float32)
+    assert not torch.equal(o1, o3)
+
+
+def test_linear_chain_grads_match_torch():
+    from b200ml.ops.gemm import mlp_chain
+    torch.manual_seed(3)
+    x = (torch.randn(4, 50, 64, device="cuda") * 0.5).to(torch.bfloat16).requires_grad_()
+    w1 = (torch.randn(128, 64, device="cuda") * 0.1).requires_grad_()
+    b1 = torch.randn(128, device="cuda").mul_(0.1).requires_grad_()
+    w2 = (torch.randn(72, 128, device="cuda") * 0.1).requires_grad_()
+    b2 = torch.randn(72, device="cuda").mul_(0.1).requires_grad_()
+    for act in ("relu", "sigmoid"):
+        for t in (x, w1, b1, w2, b2):
+            t.grad = None
+        y = mlp_chain(x, [w1, w2], [b1, b2], [act, None])
+        y.float().square().sum().backward()
+        got = [t.grad.float().cpu().clone() for t in (x, w1, b1, w2, b2)]
+        xr, w1r, b1r, w2r, b2r = [t.detach().float().cpu().requires_grad_() for t in (x, w1, b1, w2, b2)]
+        w1q, w2q = w1r.to(torch.bfloat16).float(), w2r.to(torch.bfloat16).float()
+        # straight-through the bf16 rounding of weights
+        h = (torch.relu if act == "relu" else torch.sigmoid)(xr @ (w1r + (w1q - w1r).detach()).t() + b1r)
+        yr = h @ (w2r + (w2q - w2r).detach()).t() + b2r
+        yr.square().sum().backward()
+        for g, r in zip(got, (xr, w1r, b1r, w2r, b2r)):
+            rel = (g - r.grad).norm() / (r.grad.norm() + 1e-6)
+            assert rel < 0.03, f"{act}: rel grad err {rel}"

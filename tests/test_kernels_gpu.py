@@ -1,0 +1,148 @@
+"""LayerNorm / embedding / cross-entropy / optimizer kernels vs PyTorch fp32 restatements."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel(a, b):
+    a, b = a.float().cpu(), b.float().cpu()
+    return ((a - b).norm() / (b.norm() + 1e-12)).item()
+
+
+@pytest.mark.parametrize("rows,d", [(64, 512), (6400, 512), (37, 64), (100, 1024)])
+@pytest.mark.parametrize("with_res", [True, False])
+def test_layernorm_fwd_bwd(rows, d, with_res):
+    from b200ml.ops.norm import layernorm_residual
+    torch.manual_seed(0)
+    a = torch.randn(rows, d, device="cuda").to(torch.bfloat16).requires_grad_()
+    x = torch.randn(rows, d, device="cuda").to(torch.bfloat16).requires_grad_() if with_res else None
+    gamma = (1 + 0.1 * torch.randn(d, device="cuda")).requires_grad_()
+    beta = (0.1 * torch.randn(d, device="cuda")).requires_grad_()
+    y = layernorm_residual(a, x, gamma, beta)
+    w = torch.randn(rows, d, device="cuda")
+    (y.float() * w).sum().backward()
+
+    ar = a.detach().float().cpu().requires_grad_()
+    xr = x.detach().float().cpu().requires_grad_() if with_res else None
+    gr, br = gamma.detach().cpu().requires_grad_(), beta.detach().cpu().requires_grad_()
+    z = ar + xr if with_res else ar
+    mean = z.mean(-1, keepdim=True)
+    var = ((z - mean) ** 2).mean(-1, keepdim=True)
+    yr = gr * ((z - mean) / (var + 1e-5).sqrt()) + br
+    (yr * w.cpu()).sum().backward()
+    assert _rel(y, yr) < 0.01
+    assert _rel(a.grad, ar.grad) < 0.02
+    if with_res:
+        assert _rel(x.grad, xr.grad) < 0.02
+    assert _rel(gamma.grad, gr.grad) < 0.02
+    assert _rel(beta.grad, br.grad) < 0.02
+
+
+def test_layernorm_dropout_consistent():
+    from b200ml.ops.norm import layernorm_residual
+    from b200ml.utils.rng import DeviceCounters
+    DeviceCounters.get("cuda").seed(5)
+    rows, d = 256, 512
+    a = torch.ones(rows, d, device="cuda", dtype=torch.bfloat16).requires_grad_()
+    x = torch.randn(rows, d, device="cuda").to(torch.bfloat16).requires_grad_()
+    g = torch.ones(d, device="cuda", requires_grad=True)
+    b = torch.zeros(d, device="cuda", requires_grad=True)
+    y = layernorm_residual(a, x, g, b, dropout_p=0.5, site=3)
+    y.float().sum().backward()
+    # da must be zero exactly where the mask dropped, and equal dx/(1-p) elsewhere
+    ratio = a.grad.float() / x.grad.float().clamp(min=1e-30).where(x.grad.float().abs() > 1e-6, torch.ones_like(x.grad.float()))
+    dropped = a.grad == 0
+    frac = dropped.float().mean().item()
+    assert 0.45 < frac < 0.55
+
+
+def test_embedding_pe_matches_reference_formula():
+    from b200ml.ops.embedding import embedding, positional_encoding_table
+    torch.manual_seed(0)
+    V, d, B, S = 1000, 512, 4, 200
+    w = torch.randn(V, d, device="cuda").requires_grad_()
+    tok = torch.randint(0, V, (B, S), device="cuda")
+    pe = positional_encoding_table(S, d, "cuda")
+    pe_cpu = positional_encoding_table(S, d, "cpu")
+    assert (pe.cpu() - pe_cpu).abs().max().item() < 2e-3
+    out = embedding(tok, w, pe=pe)
+    ref = w.detach().to(torch.bfloat16).float().cpu()[tok.cpu()] + pe_cpu
+    assert _rel(out, ref) < 0.01
+    gout = torch.randn(B, S, d, device="cuda")
+    (out.float() * gout).sum().backward()
+    gref = torch.zeros(V, d).index_add_(0, tok.cpu().reshape(-1), gout.cpu().to(torch.bfloat16).float().reshape(-1, d))
+    assert _rel(w.grad, gref) < 0.01
+
+
+def test_embedding_padding_idx():
+    from b200ml.ops.embedding import embedding
+    V, d = 50, 32
+    w = torch.randn(V, d, device="cuda").requires_grad_()
+    tok = torch.tensor([[0, 3, 0, 7]], device="cuda")
+    out = embedding(tok, w, padding_idx=0, out_dtype=torch.float32)
+    out.sum().backward()
+    assert w.grad[0].abs().sum().item() == 0
+    assert w.grad[3].sum().item() == pytest.approx(d)
+
+
+@pytest.mark.parametrize("rows,V,dtype", [(32, 10, torch.float32), (30, 3, torch.float32), (640, 19214, torch.bfloat16)])
+def test_cross_entropy(rows, V, dtype):
+    from b200ml.ops.loss import cross_entropy
+    torch.manual_seed(0)
+    z = (torch.randn(rows, V, device="cuda") * 2).to(dtype).requires_grad_()
+    t = torch.randint(0, V, (rows,), device="cuda")
+    t[::5] = 0
+    loss = cross_entropy(z, t, ignore_index=0)
+    loss.backward()
+    zr = z.detach().float().cpu().requires_grad_()
+    lr = torch.nn.functional.cross_entropy(zr, t.cpu(), ignore_index=0, reduction="none")
+    valid = t.cpu() != 0
+    lref = lr[valid].sum() / valid.sum()
+    lref.backward()
+    assert abs(loss.item() - lref.item()) < 2e-3 * max(1.0, abs(lref.item()))
+    assert _rel(z.grad, zr.grad) < (0.02 if dtype == torch.bfloat16 else 1e-4)
+
+
+def test_linear_cross_entropy_head():
+    from b200ml.ops.loss import linear_cross_entropy
+    torch.manual_seed(0)
+    rows, d, V = 512, 512, 19214
+    h = (torch.randn(rows, d, device="cuda") * 0.5).to(torch.bfloat16).requires_grad_()
+    w = (torch.randn(V, d, device="cuda") * 0.05).requires_grad_()
+    b = (torch.randn(V, device="cuda") * 0.05).requires_grad_()
+    t = torch.randint(0, V, (rows,), device="cuda")
+    t[::3] = 0
+    loss = linear_cross_entropy(h, w, b, t, ignore_index=0)
+    (loss * 2.0).backward()
+    hr = h.detach().float().cpu().requires_grad_()
+    wr = w.detach().to(torch.bfloat16).float().cpu().requires_grad_()
+    br = b.detach().cpu().requires_grad_()
+    lr = torch.nn.functional.cross_entropy(hr @ wr.t() + br, t.cpu(), ignore_index=0, reduction="none")
+    valid = t.cpu() != 0
+    lref = lr[valid].sum() / valid.sum()
+    (lref * 2.0).backward()
+    assert abs(loss.item() - lref.item()) < 5e-3 * abs(lref.item())
+    assert _rel(h.grad, hr.grad) < 0.03
+    assert _rel(w.grad, wr.grad) < 0.03
+    assert _rel(b.grad, br.grad) < 0.03
+
+
+@pytest.mark.parametrize("kind", ["sgd", "adam"])
+def test_flat_optimizer_matches_torch(kind):
+    from b200ml.ops.optim import FlatOptimizer
+    torch.manual_seed(0)
+    ps = [torch.randn(257, 33, device="cuda").requires_grad_(), torch.randn(1000, device="cuda").requires_grad_()]
+    rs = [p.detach().clone().requires_grad_() for p in ps]
+    opt = FlatOptimizer(ps, kind=kind, lr=0.05)
+    ref = (torch.optim.SGD if kind == "sgd" else torch.optim.Adam)(rs, lr=0.05)
+    for step in range(3):
+        for p, r in zip(ps, rs):
+            g = torch.randn_like(p)
+            p.grad = g.clone()
+            r.grad = g.clone()
+        opt.step()
+        ref.step()
+    for p, r in zip(ps, rs):
+        assert (p - r).abs().max().item() < 1e-5
+        assert (p._b200_w16.float() - p.detach()).abs().max().item() < 0.02 * p.abs().max().item()
