@@ -1,0 +1,566 @@
+// b200ml — K10: multi-head scaled-dot-product attention, forward and backward, on tcgen05 / TMEM / TMA.
+//
+// Reference semantics (transformer.py:12-25,74-83,179-191): scores = q·kᵀ/√d_k (+ mask), softmax over keys, ·v, with
+// q/k/v taken from the *per-head interleaved* output of the fused qkv / kv Linear ([B,S,H,3·hd] resp. [B,S,H,2·hd]).
+// The reference permutes/chunks those into separate tensors and materialises fp32 [B,H,S,S] scores and probabilities;
+// here strided 3-D TMA descriptors read each head's q/k/v slice straight out of the GEMM output, the S×S tile lives in
+// TMEM, and only O (and the per-row log-sum-exp for backward) reach HBM.
+//
+// mask_mode: 0 none | 1 "reference": the boolean look-ahead mask is *added* (True -> +1.0) after being transposed, i.e.
+//            +1.0 where key < query (transformer.py:17-20 as written; the padding mask adds a per-row constant and is a
+//            softmax no-op) | 2 causal: -inf where key > query (what the reference intended).
+//
+// Shapes: head_dim = 64, S_q and S_kv <= 256 (the translator uses 200); one CTA per (128-row tile, head, batch).
+//   fwd    : S = Q·Kᵀ (UMMA 128×S_kv×64) -> softmax in registers (1 thread = 1 row = 1 TMEM lane) -> P (bf16, 128B-swizzled
+//            smem) -> O = P·V (V consumed MN-major from the very bytes TMA wrote) -> O/rowsum, lse
+//   bwd_q  : S, dP = dO·Vᵀ -> dS = P∘(dP − D)·scale -> dQ = dS·K
+//   bwd_kv : Sᵀ = K·Qᵀ, dPᵀ = V·dOᵀ (this CTA owns 128 keys) -> Pᵀ, dSᵀ -> dV = Pᵀ·dO, dK = dSᵀ·Q
+// No atomics, every gradient element is written exactly once => bit-reproducible.
+#include "../../include/b200ml.h"
+#include "../common/host.h"
+#include "../common/ptx.cuh"
+
+namespace b200 {
+namespace attn {
+
+constexpr int HD = 64;
+constexpr int TILE = 128;
+constexpr int MAXS = 256;
+constexpr float kLog2e = 1.4426950408889634f;
+
+struct Operand {           // device view of one b200ml_attn_operand
+    __nv_bfloat16* ptr;
+    long long ld;
+    int col0, head_stride;
+};
+
+__device__ __forceinline__ float bias_of(int mask_mode, int q, int k) {
+    if (mask_mode == 1) return k < q ? 1.f : 0.f;
+    if (mask_mode == 2) return k > q ? -INFINITY : 0.f;
+    return 0.f;
+}
+
+// Write 32 consecutive bf16 values of one row into 128B-swizzled K-major tiles ([rows][64] per tile, 16 KB apart
+// for 128-row tiles).
+__device__ __forceinline__ void store_row_chunk32(uint8_t* tiles, uint32_t tile_bytes, int row, int col0,
+                                                  const float (&v)[32]) {
+    const int tile = col0 >> 6;
+    const int chunk0 = (col0 & 63) >> 3;  // 16-byte chunk index inside the 128-byte row
+    uint8_t* base = tiles + (size_t)tile * tile_bytes;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        uint4 u;
+        u.x = pack_bf16x2(v[c * 8 + 0], v[c * 8 + 1]);
+        u.y = pack_bf16x2(v[c * 8 + 2], v[c * 8 + 3]);
+        u.z = pack_bf16x2(v[c * 8 + 4], v[c * 8 + 5]);
+        u.w = pack_bf16x2(v[c * 8 + 6], v[c * 8 + 7]);
+        *reinterpret_cast<uint4*>(base + swz128_offset(row, chunk0 + c)) = u;
+    }
+}
+
+// D[128 x N] = A[128 x 64] · B[N x 64]ᵀ, both K-major single-tile operands (4 UMMAs of K=16).
+__device__ __forceinline__ void mma_k64(uint32_t tmem_d, uint32_t sA, uint32_t sB, int N) {
+    const uint32_t idesc = umma_idesc_bf16(TILE, N, false, false);
+#pragma unroll
+    for (int kk = 0; kk < 4; ++kk)
+        umma_bf16(tmem_d, umma_smem_desc(sA + kk * 32, 16, 1024), umma_smem_desc(sB + kk * 32, 16, 1024), idesc,
+                  kk ? 1u : 0u);
+}
+// D[128 x 64] = A[128 x Kpad] · B[Kpad x 64]; A = K-major 128-row tiles of 64 columns (16 KB each), B = MN-major
+// (rows = reduction index, 64 contiguous outputs per 128-byte row).
+__device__ __forceinline__ void mma_tiles_x_mn(uint32_t tmem_d, uint32_t sA_tiles, uint32_t sB, int Kpad) {
+    const uint32_t idesc = umma_idesc_bf16(TILE, HD, false, true);
+    const int steps = Kpad >> 4;
+    for (int kk = 0; kk < steps; ++kk) {
+        const uint32_t a = sA_tiles + (kk >> 2) * (TILE * 128) + (kk & 3) * 32;
+        const uint32_t b = sB + kk * (16 * 128);
+        umma_bf16(tmem_d, umma_smem_desc(a, 16, 1024), umma_smem_desc(b, 8192, 1024), idesc, kk ? 1u : 0u);
+    }
+}
+
+struct SmemLayout {  // offsets from the 1024-aligned base; see kernels for aliasing
+    static constexpr int kTileA = 0;                 // 16 KB : Q tile (fwd, bwd_q) / K tile (bwd_kv)
+    static constexpr int kTileB = 16384;             // 16 KB : dO tile (bwd_q) / V tile (bwd_kv)
+};
+
+// ------------------------------------------------------------------------------------------------ forward
+// smem: [Q 16K][K 32K][P-extra 16K][V 32K] ; P (4 x 16 KB tiles) aliases Q+K+extra once S has been computed.
+constexpr int kFwdSmem = 16384 + 32768 + 16384 + 32768 + 1024 + 128;
+
+__global__ void __launch_bounds__(128, 2)
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tk,
+                const __grid_constant__ CUtensorMap tv, Operand q, Operand k, Operand v, Operand o,
+                float* __restrict__ lse, int H, int Sq, int Skv, int skv_pad, float scale, int mask_mode) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sQ = smem;
+    uint8_t* sK = smem + 16384;
+    uint8_t* sV = smem + 16384 + 32768 + 16384;
+    uint8_t* sP = smem;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 16384 + 32768 + 16384 + 32768);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
+
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int q0 = blockIdx.x * TILE, h = blockIdx.y, b = blockIdx.z;
+    if (tid == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        mbar_init(&bars[2], 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) tmem_alloc<256>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (tid == 0) {
+        mbar_arrive_expect_tx(&bars[0], TILE * 128 + 2 * skv_pad * 128);
+        tma_load_3d(sQ, &tq, &bars[0], q.col0 + h * q.head_stride, q0, b);
+        tma_load_3d(sK, &tk, &bars[0], k.col0 + h * k.head_stride, 0, b);
+        tma_load_3d(sV, &tv, &bars[0], v.col0 + h * v.head_stride, 0, b);
+        mbar_wait(&bars[0], 0);
+        tc_fence_after();
+        mma_k64(tmem, smem_u32(sQ), smem_u32(sK), skv_pad);
+        umma_commit(&bars[1]);
+    }
+    mbar_wait(&bars[1], 0);
+    tc_fence_after();
+
+    const int qrow = q0 + tid;
+    const uint32_t trow = tmem + (static_cast<uint32_t>(warp * 32) << 16);
+    const float sc = scale * kLog2e;
+    // pass 1: row maximum (log2 domain)
+    float mx = -INFINITY;
+    for (int c = 0; c < skv_pad; c += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(trow + c, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            const int kc = c + j;
+            const float x = __uint_as_float(r[j]) * sc + bias_of(mask_mode, qrow, kc) * kLog2e;
+            if (kc < Skv) mx = fmaxf(mx, x);
+        }
+    }
+    if (mx == -INFINITY) mx = 0.f;
+    // pass 2: probabilities -> smem (bf16), row sum.  All threads passed bars[1], so Q/K smem is dead: P may alias it.
+    float sum = 0.f;
+    for (int c = 0; c < skv_pad; c += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(trow + c, r);
+        tmem_ld_wait();
+        float p[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            const int kc = c + j;
+            const float x = __uint_as_float(r[j]) * sc + bias_of(mask_mode, qrow, kc) * kLog2e;
+            float e = kc < Skv ? exp2f(x - mx) : 0.f;
+            e = __bfloat162float(__float2bfloat16(e));  // the value the tensor core will see
+            p[j] = e;
+            sum += e;
+        }
+        store_row_chunk32(sP, TILE * 128, tid, c, p);
+    }
+    tc_fence_before();
+    fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the tensor core (async proxy)
+    __syncthreads();
+    if (tid == 0) {
+        tc_fence_after();
+        mma_tiles_x_mn(tmem, smem_u32(sP), smem_u32(sV), skv_pad);  // O overwrites the first 64 columns of S
+        umma_commit(&bars[2]);
+    }
+    mbar_wait(&bars[2], 0);
+    tc_fence_after();
+    const float inv = 1.f / sum;
+    {
+        __nv_bfloat16* out = o.ptr + ((long long)b * Sq + qrow) * o.ld + o.col0 + h * o.head_stride;
+#pragma unroll
+        for (int c = 0; c < HD; c += 32) {
+            uint32_t r[32];
+            tmem_ld_32x32b_x32(trow + c, r);  // .sync.aligned: executed by the whole warp, stores are predicated
+            tmem_ld_wait();
+            if (qrow < Sq) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 8) {
+                    uint4 u;
+                    u.x = pack_bf16x2(__uint_as_float(r[j]) * inv, __uint_as_float(r[j + 1]) * inv);
+                    u.y = pack_bf16x2(__uint_as_float(r[j + 2]) * inv, __uint_as_float(r[j + 3]) * inv);
+                    u.z = pack_bf16x2(__uint_as_float(r[j + 4]) * inv, __uint_as_float(r[j + 5]) * inv);
+                    u.w = pack_bf16x2(__uint_as_float(r[j + 6]) * inv, __uint_as_float(r[j + 7]) * inv);
+                    *reinterpret_cast<uint4*>(out + c + j) = u;
+                }
+            }
+        }
+        // natural-log LSE of the biased, scaled scores
+        if (qrow < Sq) lse[((long long)b * H + h) * Sq + qrow] = (mx + log2f(sum)) / kLog2e;
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        tmem_dealloc<256>(tmem);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ backward, dQ
+// smem: [Q 16K][dO 16K][V 32K][K 32K] ; dS (4 x 16 KB tiles) aliases Q+dO+V after S and dP are in TMEM.
+constexpr int kBwdQSmem = 16384 + 16384 + 32768 + 32768 + 1024 + 128;
+
+__global__ void __launch_bounds__(128, 1)
+attn_bwd_q_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tdo,
+                  const __grid_constant__ CUtensorMap tk, const __grid_constant__ CUtensorMap tv, Operand q, Operand k,
+                  Operand v, Operand o, Operand dout, Operand dq, const float* __restrict__ lse, int H, int Sq, int Skv,
+                  int skv_pad, float scale, int mask_mode) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sQ = smem;
+    uint8_t* sdO = smem + 16384;
+    uint8_t* sV = smem + 32768;
+    uint8_t* sK = smem + 65536;
+    uint8_t* sdS = smem;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 98304);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
+
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int q0 = blockIdx.x * TILE, h = blockIdx.y, b = blockIdx.z;
+    if (tid == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        mbar_init(&bars[2], 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) tmem_alloc<512>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (tid == 0) {
+        mbar_arrive_expect_tx(&bars[0], 2 * TILE * 128 + 2 * skv_pad * 128);
+        tma_load_3d(sQ, &tq, &bars[0], q.col0 + h * q.head_stride, q0, b);
+        tma_load_3d(sdO, &tdo, &bars[0], dout.col0 + h * dout.head_stride, q0, b);
+        tma_load_3d(sK, &tk, &bars[0], k.col0 + h * k.head_stride, 0, b);
+        tma_load_3d(sV, &tv, &bars[0], v.col0 + h * v.head_stride, 0, b);
+        mbar_wait(&bars[0], 0);
+        tc_fence_after();
+        mma_k64(tmem, smem_u32(sQ), smem_u32(sK), skv_pad);          // S   -> cols [0, 256)
+        mma_k64(tmem + 256, smem_u32(sdO), smem_u32(sV), skv_pad);   // dP  -> cols [256, 512)
+        umma_commit(&bars[1]);
+    }
+    // D = rowsum(dO ∘ O) for this thread's query row, from global (two 128-byte rows)
+    const int qrow = q0 + tid;
+    float D = 0.f, l2 = 0.f;
+    if (qrow < Sq) {
+        const uint4* po = reinterpret_cast<const uint4*>(o.ptr + ((long long)b * Sq + qrow) * o.ld + o.col0 +
+                                                         h * o.head_stride);
+        const uint4* pd = reinterpret_cast<const uint4*>(dout.ptr + ((long long)b * Sq + qrow) * dout.ld + dout.col0 +
+                                                         h * dout.head_stride);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const uint4 a = po[i], c = pd[i];
+            const __nv_bfloat162* ha = reinterpret_cast<const __nv_bfloat162*>(&a);
+            const __nv_bfloat162* hc = reinterpret_cast<const __nv_bfloat162*>(&c);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float2 x = __bfloat1622float2(ha[j]), y = __bfloat1622float2(hc[j]);
+                D += x.x * y.x + x.y * y.y;
+            }
+        }
+        l2 = lse[((long long)b * H + h) * Sq + qrow] * kLog2e;
+    }
+    mbar_wait(&bars[1], 0);
+    tc_fence_after();
+    const uint32_t trow = tmem + (static_cast<uint32_t>(warp * 32) << 16);
+    const float sc = scale * kLog2e;
+    for (int c = 0; c < skv_pad; c += 32) {
+        uint32_t rs[32], rp[32];
+        tmem_ld_32x32b_x32(trow + c, rs);
+        tmem_ld_32x32b_x32(trow + 256 + c, rp);
+        tmem_ld_wait();
+        float ds[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            const int kc = c + j;
+            const float x = __uint_as_float(rs[j]) * sc + bias_of(mask_mode, qrow, kc) * kLog2e;
+            const bool ok = kc < Skv && qrow < Sq;
+            const float p = ok ? exp2f(x - l2) : 0.f;
+            ds[j] = ok ? p * (__uint_as_float(rp[j]) - D) * scale : 0.f;
+        }
+        store_row_chunk32(sdS, TILE * 128, tid, c, ds);
+    }
+    tc_fence_before();
+    fence_proxy_async_smem();
+    __syncthreads();
+    if (tid == 0) {
+        tc_fence_after();
+        mma_tiles_x_mn(tmem, smem_u32(sdS), smem_u32(sK), skv_pad);  // dQ -> cols [0, 64)
+        umma_commit(&bars[2]);
+    }
+    mbar_wait(&bars[2], 0);
+    tc_fence_after();
+    __nv_bfloat16* out = dq.ptr + ((long long)b * Sq + qrow) * dq.ld + dq.col0 + h * dq.head_stride;
+#pragma unroll
+    for (int c = 0; c < HD; c += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(trow + c, r);
+        tmem_ld_wait();
+        if (qrow < Sq) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+                uint4 u;
+                u.x = pack_bf16x2(__uint_as_float(r[j]), __uint_as_float(r[j + 1]));
+                u.y = pack_bf16x2(__uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+                u.z = pack_bf16x2(__uint_as_float(r[j + 4]), __uint_as_float(r[j + 5]));
+                u.w = pack_bf16x2(__uint_as_float(r[j + 6]), __uint_as_float(r[j + 7]));
+                *reinterpret_cast<uint4*>(out + c + j) = u;
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        tmem_dealloc<512>(tmem);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ backward, dK / dV
+// smem: [Pᵀ 64K][dSᵀ 64K][Q 32K][dO 32K][lse 1K][D 1K]; the K and V tiles (16 KB each) sit in the first 32 KB and are
+// dead by the time Pᵀ is written.
+constexpr int kBwdKVSmem = 65536 + 65536 + 32768 + 32768 + 2048 + 1024 + 128;
+
+__global__ void __launch_bounds__(128, 1)
+attn_bwd_kv_kernel(const __grid_constant__ CUtensorMap tk, const __grid_constant__ CUtensorMap tv,
+                   const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tdo, Operand q, Operand k,
+                   Operand v, Operand o, Operand dout, Operand dk, Operand dv, const float* __restrict__ lse, int H,
+                   int Sq, int Skv, int sq_pad, float scale, int mask_mode) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sK = smem;
+    uint8_t* sV = smem + 16384;
+    uint8_t* sPt = smem;
+    uint8_t* sdSt = smem + 65536;
+    uint8_t* sQ = smem + 131072;
+    uint8_t* sdO = smem + 131072 + 32768;
+    float* s_lse = reinterpret_cast<float*>(smem + 196608);
+    float* s_D = s_lse + MAXS;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 196608 + 2048);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
+
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int k0 = blockIdx.x * TILE, h = blockIdx.y, b = blockIdx.z;
+    if (tid == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        mbar_init(&bars[2], 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) tmem_alloc<512>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (tid == 0) {
+        mbar_arrive_expect_tx(&bars[0], 2 * TILE * 128 + 2 * sq_pad * 128);
+        tma_load_3d(sK, &tk, &bars[0], k.col0 + h * k.head_stride, k0, b);
+        tma_load_3d(sV, &tv, &bars[0], v.col0 + h * v.head_stride, k0, b);
+        tma_load_3d(sQ, &tq, &bars[0], q.col0 + h * q.head_stride, 0, b);
+        tma_load_3d(sdO, &tdo, &bars[0], dout.col0 + h * dout.head_stride, 0, b);
+        mbar_wait(&bars[0], 0);
+        tc_fence_after();
+        mma_k64(tmem, smem_u32(sK), smem_u32(sQ), sq_pad);          // Sᵀ  = K·Qᵀ   -> cols [0, 256)
+        mma_k64(tmem + 256, smem_u32(sV), smem_u32(sdO), sq_pad);   // dPᵀ = V·dOᵀ  -> cols [256, 512)
+        umma_commit(&bars[1]);
+    }
+    // per-query statistics for every query row of this (b, h): lse and D = rowsum(dO ∘ O)
+    for (int qr = tid; qr < MAXS; qr += 128) {
+        float D = 0.f, l2 = 0.f;
+        if (qr < Sq) {
+            const uint4* po = reinterpret_cast<const uint4*>(o.ptr + ((long long)b * Sq + qr) * o.ld + o.col0 +
+                                                             h * o.head_stride);
+            const uint4* pd = reinterpret_cast<const uint4*>(dout.ptr + ((long long)b * Sq + qr) * dout.ld +
+                                                             dout.col0 + h * dout.head_stride);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const uint4 a = po[i], c = pd[i];
+                const __nv_bfloat162* ha = reinterpret_cast<const __nv_bfloat162*>(&a);
+                const __nv_bfloat162* hc = reinterpret_cast<const __nv_bfloat162*>(&c);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float2 x = __bfloat1622float2(ha[j]), y = __bfloat1622float2(hc[j]);
+                    D += x.x * y.x + x.y * y.y;
+                }
+            }
+            l2 = lse[((long long)b * H + h) * Sq + qr] * kLog2e;
+        }
+        s_lse[qr] = l2;
+        s_D[qr] = D;
+    }
+    __syncthreads();
+    mbar_wait(&bars[1], 0);
+    tc_fence_after();
+    const int krow = k0 + tid;
+    const uint32_t trow = tmem + (static_cast<uint32_t>(warp * 32) << 16);
+    const float sc = scale * kLog2e;
+    for (int c = 0; c < sq_pad; c += 32) {
+        uint32_t rs[32], rp[32];
+        tmem_ld_32x32b_x32(trow + c, rs);
+        tmem_ld_32x32b_x32(trow + 256 + c, rp);
+        tmem_ld_wait();
+        float pt[32], ds[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            const int qc = c + j;
+            const float x = __uint_as_float(rs[j]) * sc + bias_of(mask_mode, qc, krow) * kLog2e;
+            const bool ok = qc < Sq && krow < Skv;
+            const float p = ok ? exp2f(x - s_lse[qc]) : 0.f;
+            pt[j] = p;
+            ds[j] = ok ? p * (__uint_as_float(rp[j]) - s_D[qc]) * scale : 0.f;
+        }
+        store_row_chunk32(sPt, TILE * 128, tid, c, pt);
+        store_row_chunk32(sdSt, TILE * 128, tid, c, ds);
+    }
+    tc_fence_before();
+    fence_proxy_async_smem();
+    __syncthreads();
+    if (tid == 0) {
+        tc_fence_after();
+        mma_tiles_x_mn(tmem, smem_u32(sPt), smem_u32(sdO), sq_pad);       // dV -> cols [0, 64)
+        mma_tiles_x_mn(tmem + 64, smem_u32(sdSt), smem_u32(sQ), sq_pad);  // dK -> cols [64, 128)
+        umma_commit(&bars[2]);
+    }
+    mbar_wait(&bars[2], 0);
+    tc_fence_after();
+#pragma unroll
+    for (int which = 0; which < 2; ++which) {
+        const Operand& dst = which == 0 ? dv : dk;
+        __nv_bfloat16* out = dst.ptr + ((long long)b * Skv + krow) * dst.ld + dst.col0 + h * dst.head_stride;
+#pragma unroll
+        for (int c = 0; c < HD; c += 32) {
+            uint32_t r[32];
+            tmem_ld_32x32b_x32(trow + which * 64 + c, r);
+            tmem_ld_wait();
+            if (krow < Skv) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 8) {
+                    uint4 u;
+                    u.x = pack_bf16x2(__uint_as_float(r[j]), __uint_as_float(r[j + 1]));
+                    u.y = pack_bf16x2(__uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+                    u.z = pack_bf16x2(__uint_as_float(r[j + 4]), __uint_as_float(r[j + 5]));
+                    u.w = pack_bf16x2(__uint_as_float(r[j + 6]), __uint_as_float(r[j + 7]));
+                    *reinterpret_cast<uint4*>(out + c + j) = u;
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        tmem_dealloc<512>(tmem);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ host
+static int head_tmap(CUtensorMap* m, const b200ml_attn_operand* op, int B, int S, int H, int box_rows) {
+    // dims: {columns reachable by any head, S, B}
+    const uint64_t ncols = (uint64_t)op->col0 + (uint64_t)(H - 1) * op->head_stride + HD;
+    uint64_t dims[3] = {ncols, (uint64_t)S, (uint64_t)B};
+    uint64_t strides[3] = {2, (uint64_t)op->ld * 2, (uint64_t)op->ld * 2 * (uint64_t)S};
+    uint32_t box[3] = {64, (uint32_t)box_rows, 1};
+    return make_tmap_bf16(m, op->ptr, 3, dims, strides, box);
+}
+static Operand dev_op(const b200ml_attn_operand* op) {
+    Operand o;
+    o.ptr = reinterpret_cast<__nv_bfloat16*>(const_cast<void*>(op->ptr));
+    o.ld = op->ld;
+    o.col0 = op->col0;
+    o.head_stride = op->head_stride;
+    return o;
+}
+static int check_operand(const b200ml_attn_operand* op, const char* name) {
+    if (!op || !op->ptr) return set_error("attention: operand %s is null", name);
+    if (op->ld % 8 || op->col0 % 8 || op->head_stride % 8 || (reinterpret_cast<uintptr_t>(op->ptr) & 15))
+        return set_error("attention: operand %s must be 16-byte aligned (ld, col0, head_stride multiples of 8)", name);
+    return 0;
+}
+
+}  // namespace attn
+}  // namespace b200
+
+extern "C" {
+
+int b200ml_attn_fwd(const b200ml_attn_operand* q, const b200ml_attn_operand* k, const b200ml_attn_operand* v,
+                    const b200ml_attn_operand* out, float* lse, int B, int H, int Sq, int Skv, float scale,
+                    int mask_mode, cudaStream_t stream) {
+    using namespace b200;
+    using namespace b200::attn;
+    if (check_operand(q, "q") || check_operand(k, "k") || check_operand(v, "v") || check_operand(out, "out")) return -1;
+    B200_REQUIRE(lse, "attention: lse is null");
+    B200_REQUIRE(Sq >= 1 && Skv >= 1 && Sq <= 65535 && Skv <= MAXS, "attention fwd: need S_kv <= %d (got %d)", MAXS, Skv);
+    const int skv_pad = (Skv + 15) / 16 * 16;
+    CUtensorMap tq, tk, tv;
+    if (head_tmap(&tq, q, B, Sq, H, TILE) || head_tmap(&tk, k, B, Skv, H, skv_pad) ||
+        head_tmap(&tv, v, B, Skv, H, skv_pad))
+        return -1;
+    static bool attr = false;
+    if (!attr) {
+        B200_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem));
+        attr = true;
+    }
+    dim3 grid((Sq + TILE - 1) / TILE, H, B);
+    attn_fwd_kernel<<<grid, 128, kFwdSmem, stream>>>(tq, tk, tv, dev_op(q), dev_op(k), dev_op(v), dev_op(out), lse, H,
+                                                     Sq, Skv, skv_pad, scale, mask_mode);
+    B200_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int b200ml_attn_bwd(const b200ml_attn_operand* q, const b200ml_attn_operand* k, const b200ml_attn_operand* v,
+                    const b200ml_attn_operand* out, const b200ml_attn_operand* dout, const float* lse,
+                    const b200ml_attn_operand* dq, const b200ml_attn_operand* dk, const b200ml_attn_operand* dv, int B,
+                    int H, int Sq, int Skv, float scale, int mask_mode, cudaStream_t stream) {
+    using namespace b200;
+    using namespace b200::attn;
+    if (check_operand(q, "q") || check_operand(k, "k") || check_operand(v, "v") || check_operand(out, "out") ||
+        check_operand(dout, "dout") || check_operand(dq, "dq") || check_operand(dk, "dk") || check_operand(dv, "dv"))
+        return -1;
+    B200_REQUIRE(lse, "attention: lse is null");
+    B200_REQUIRE(Sq >= 1 && Skv >= 1 && Sq <= MAXS && Skv <= MAXS, "attention bwd: need S <= %d (got %d, %d)", MAXS, Sq,
+                 Skv);
+    const int skv_pad = (Skv + 15) / 16 * 16, sq_pad = (Sq + 15) / 16 * 16;
+    static bool attr = false;
+    if (!attr) {
+        B200_CHECK_CUDA(
+            cudaFuncSetAttribute(attn_bwd_q_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdQSmem));
+        B200_CHECK_CUDA(
+            cudaFuncSetAttribute(attn_bwd_kv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdKVSmem));
+        attr = true;
+    }
+    {
+        CUtensorMap tq, tdo, tk, tv;
+        if (head_tmap(&tq, q, B, Sq, H, TILE) || head_tmap(&tdo, dout, B, Sq, H, TILE) ||
+            head_tmap(&tk, k, B, Skv, H, skv_pad) || head_tmap(&tv, v, B, Skv, H, skv_pad))
+            return -1;
+        dim3 grid((Sq + TILE - 1) / TILE, H, B);
+        attn_bwd_q_kernel<<<grid, 128, kBwdQSmem, stream>>>(tq, tdo, tk, tv, dev_op(q), dev_op(k), dev_op(v),
+                                                            dev_op(out), dev_op(dout), dev_op(dq), lse, H, Sq, Skv,
+                                                            skv_pad, scale, mask_mode);
+        B200_CHECK_CUDA(cudaGetLastError());
+    }
+    {
+        CUtensorMap tk, tv, tq, tdo;
+        if (head_tmap(&tk, k, B, Skv, H, TILE) || head_tmap(&tv, v, B, Skv, H, TILE) ||
+            head_tmap(&tq, q, B, Sq, H, sq_pad) || head_tmap(&tdo, dout, B, Sq, H, sq_pad))
+            return -1;
+        dim3 grid((Skv + TILE - 1) / TILE, H, B);
+        attn_bwd_kv_kernel<<<grid, 128, kBwdKVSmem, stream>>>(tk, tv, tq, tdo, dev_op(q), dev_op(k), dev_op(v),
+                                                              dev_op(out), dev_op(dout), dev_op(dk), dev_op(dv), lse, H,
+                                                              Sq, Skv, sq_pad, scale, mask_mode);
+        B200_CHECK_CUDA(cudaGetLastError());
+    }
+    return 0;
+}
+
+}  // extern "C"

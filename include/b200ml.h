@@ -105,6 +105,26 @@ int b200ml_counters_advance(void* rng_state /*{u64 seed, u64 step}*/, int* step_
 int b200ml_argmax_accuracy(const void* logits, int logits_fp32, long long ld, const long long* targets, int rows, int C,
                            int* pred, int* correct_count, cudaStream_t stream);
 
+/* ------------------------------------------------------------------------------------------------ K10 attention
+ * One head of q/k/v/o lives in 64 consecutive columns of a row-major bf16 matrix [B*S, ld] starting at column
+ * col0 + h*head_stride, so the interleaved qkv / kv Linear outputs are consumed (and their gradients produced) in place.
+ * head_dim = 64; forward needs S_kv <= 256, backward S_q, S_kv <= 256.  lse: fp32 [B, H, S_q].
+ * mask_mode: 0 none, 1 reference (+1.0 where key < query), 2 causal (-inf where key > query).
+ * ref: transformer.py:12-25,74-83,179-191. */
+typedef struct {
+    const void* ptr;
+    long long ld;
+    int col0;
+    int head_stride;
+} b200ml_attn_operand;
+int b200ml_attn_fwd(const b200ml_attn_operand* q, const b200ml_attn_operand* k, const b200ml_attn_operand* v,
+                    const b200ml_attn_operand* out, float* lse, int B, int H, int Sq, int Skv, float scale,
+                    int mask_mode, cudaStream_t stream);
+int b200ml_attn_bwd(const b200ml_attn_operand* q, const b200ml_attn_operand* k, const b200ml_attn_operand* v,
+                    const b200ml_attn_operand* out, const b200ml_attn_operand* dout, const float* lse,
+                    const b200ml_attn_operand* dq, const b200ml_attn_operand* dk, const b200ml_attn_operand* dv, int B,
+                    int H, int Sq, int Skv, float scale, int mask_mode, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,7 +1,6 @@
-"""Signatures of the optional kernel groups (attention, comm, conv, lstm, mlp, ...).
+"""Signatures of the kernel groups declared next to their Python ops (attention, comm, conv, lstm, mlp, ...).
 
-Kept apart from ``_native.py`` so a library built before a group existed still loads; ``declare`` skips symbols
-the loaded .so does not export.
+``register`` may run before or after the library is loaded; ``declare`` skips symbols the loaded .so does not export.
 """
 from __future__ import annotations
 
@@ -13,18 +12,23 @@ SIGNATURES: dict[str, list] = {}
 SIZE_T_RETURNS: dict[str, list] = {}
 
 
+def _apply(lib, name, args, size_t_return):
+    fn = getattr(lib, name, None)
+    if fn is not None:
+        fn.argtypes = args
+        fn.restype = sz if size_t_return else i
+
+
 def register(name: str, argtypes: list, size_t_return: bool = False) -> None:
     (SIZE_T_RETURNS if size_t_return else SIGNATURES)[name] = argtypes
+    from . import _native
+
+    if _native._lib is not None:
+        _apply(_native._lib, name, argtypes, size_t_return)
 
 
 def declare(lib) -> None:
     for name, args in SIGNATURES.items():
-        fn = getattr(lib, name, None)
-        if fn is not None:
-            fn.argtypes = args
-            fn.restype = i
+        _apply(lib, name, args, False)
     for name, args in SIZE_T_RETURNS.items():
-        fn = getattr(lib, name, None)
-        if fn is not None:
-            fn.argtypes = args
-            fn.restype = sz
+        _apply(lib, name, args, True)

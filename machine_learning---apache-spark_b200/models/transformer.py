@@ -1,0 +1,287 @@
+"""Encoder–decoder Transformer with the reference's class names, constructor signatures and state_dict keys
+(reference transformer.py:8-284), executed by the b200ml kernels:
+
+  SentenceEmbedding      -> one fused gather + positional-encoding + dropout kernel (PE table resident on the device)
+  MultiHeadAttention     -> qkv GEMM (tcgen05) -> attention kernel reading q/k/v in place from the interleaved layout
+  LayerNormalization     -> fused dropout + residual + LayerNorm (params ``gamma`` / ``beta``, biased variance)
+  PositionwiseFeedForward-> two tcgen05 GEMMs with bias+ReLU+dropout in the first epilogue, ReLU/dropout derivative
+                            folded into the dgrad epilogue on the way back
+  Transformer.linear     -> head GEMM; training scripts use ops.linear_cross_entropy on ``return_hidden=True`` output
+
+``mask_mode``: "reference" reproduces the reference as written — boolean masks are *added* to the scores,
+so the look-ahead mask is +1.0 on the strictly lower triangle and the padding mask is a no-op; "causal" applies a real
+causal mask in decoder self-attention.  Post-LN residual structure, dropout placement and the un-shifted decoder input
+are kept exactly.
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+from torch import nn
+
+from ..ops import attention as _att
+from ..ops.embedding import embedding as _embedding
+from ..ops.embedding import positional_encoding_table
+from ..ops.gemm import linear as _linear
+from ..ops.gemm import mlp_chain as _mlp_chain
+from ..ops.norm import layernorm_residual as _ln_res
+from ..utils.rng import new_site
+
+
+def get_device():
+    return torch.device("cuda") if torch.cuda.is_available() else torch.device("cpu")
+
+
+def _vocab_len(v) -> int:
+    return int(v) if isinstance(v, int) else len(v)
+
+
+def scaled_dot_product(q, k, v, mask=None):
+    """API-compatible restatement of transformer.py:12-25 for [B,H,S,hd] tensors (generic additive mask).  Returns
+    (values, attention).  Unlike the reference, ``mask=None`` works for any batch size."""
+    d_k = q.size(-1)
+    scaled = torch.matmul(q, k.transpose(-1, -2)) / math.sqrt(d_k)
+    if mask is not None:
+        scaled = scaled + mask.permute(0, 1, 3, 2)
+    attention = torch.softmax(scaled.float(), dim=-1).to(q.dtype)
+    return torch.matmul(attention, v), attention
+
+
+def _mask_kind(mask, model_mode: str, is_decoder_self: bool) -> str | torch.Tensor:
+    """Map a reference-style mask argument onto a kernel bias mode (shape-based; see module docstring)."""
+    if model_mode == "causal":
+        return "causal" if is_decoder_self else "none"
+    if mask is None:
+        return "none"
+    if mask.dtype == torch.bool and mask.dim() == 4:
+        if mask.shape[-2] == 1:                    # padding mask [B,1,1,S]: per-query constant after the permute
+            return "none"
+        if mask.shape[0] == 1 and mask.shape[1] == 1 and mask.shape[-1] == mask.shape[-2]:
+            return "reference"                     # look-ahead mask [1,1,S,S]
+    return mask                                    # anything else: generic additive path
+
+
+class PositionalEncoding(nn.Module):
+    def __init__(self, d_model, max_sequence_length):
+        super().__init__()
+        self.max_sequence_length = max_sequence_length
+        self.d_model = d_model
+
+    def forward(self, device=None):
+        return positional_encoding_table(self.max_sequence_length, self.d_model, device or "cpu")
+
+
+class SentenceEmbedding(nn.Module):
+    def __init__(self, max_sequence_length, d_model, input_vocab):
+        super().__init__()
+        self.vocab_size = _vocab_len(input_vocab)
+        self.max_sequence_length = max_sequence_length
+        self.embedding = nn.Embedding(self.vocab_size, d_model)
+        self.embedding.weight._b200_zero_grad = True  # backward scatter-adds into its gradient slot
+        self.language_to_index = input_vocab
+        self.position_encoder = PositionalEncoding(d_model, max_sequence_length)
+        self.dropout = nn.Dropout(p=0.1)
+        self._site = new_site()
+
+    def forward(self, x):
+        w = self.embedding.weight
+        assert x.shape[-1] <= self.max_sequence_length, "sequence longer than max_sequence_length"
+        pe = self.position_encoder(w.device)
+        out_dtype = torch.bfloat16 if w.is_cuda else torch.float32
+        return _embedding(x, w, pe=pe, dropout_p=self.dropout.p, site=self._site, out_dtype=out_dtype,
+                          training=self.training)
+
+
+class MultiHeadAttention(nn.Module):
+    def __init__(self, d_model, num_heads):
+        super().__init__()
+        self.d_model = d_model
+        self.num_heads = num_heads
+        self.head_dim = d_model // num_heads
+        self.qkv_layer = nn.Linear(d_model, 3 * d_model)
+        self.linear_layer = nn.Linear(d_model, d_model)
+
+    def forward(self, x, mask=None, mask_mode: str = "reference", decoder: bool = False):
+        kind = _mask_kind(mask, mask_mode, decoder)
+        qkv = _linear(x, self.qkv_layer.weight, self.qkv_layer.bias)
+        if isinstance(kind, torch.Tensor):
+            values = _generic_attention(qkv, None, self.num_heads, kind)
+        else:
+            values = _att.attention(qkv, num_heads=self.num_heads, mask_mode=kind)
+        return _linear(values, self.linear_layer.weight, self.linear_layer.bias)
+
+
+def _generic_attention(qsrc, kvsrc, H, mask):
+    kind = "self" if kvsrc is None else "cross"
+    d = qsrc.shape[-1] // (3 if kind == "self" else 1)
+    q, k, v = _att._split(kind, qsrc, kvsrc, H, d // H)
+    values, _ = scaled_dot_product(q, k, v, mask.to(q.dtype) if mask.dtype != torch.bool else mask.to(q.dtype))
+    B, _, S, _ = values.shape
+    return values.permute(0, 2, 1, 3).reshape(B, S, d)
+
+
+class LayerNormalization(nn.Module):
+    def __init__(self, parameters_shape, eps=1e-5):
+        super().__init__()
+        self.parameters_shape = parameters_shape
+        self.eps = eps
+        self.gamma = nn.Parameter(torch.ones(parameters_shape))
+        self.beta = nn.Parameter(torch.zeros(parameters_shape))
+
+    def forward(self, inputs, residual=None, dropout_p: float = 0.0, site: int = 0):
+        """LN(dropout(inputs) + residual); with the defaults this is the reference's plain LayerNormalization."""
+        if len(self.parameters_shape) != 1:
+            dims = [-(i + 1) for i in range(len(self.parameters_shape))]
+            z = inputs if residual is None else inputs + residual
+            mean = z.mean(dim=dims, keepdim=True)
+            var = ((z - mean) ** 2).mean(dim=dims, keepdim=True)
+            return self.gamma * ((z - mean) / (var + self.eps).sqrt()) + self.beta
+        return _ln_res(inputs, residual, self.gamma, self.beta, self.eps, dropout_p, site, self.training)
+
+
+class PositionwiseFeedForward(nn.Module):
+    def __init__(self, d_model, hidden, drop_prob=0.1):
+        super().__init__()
+        self.linear1 = nn.Linear(d_model, hidden)
+        self.linear2 = nn.Linear(hidden, d_model)
+        self.relu = nn.ReLU()
+        self.dropout = nn.Dropout(p=drop_prob)
+        self._site = new_site()
+
+    def forward(self, x):
+        return _mlp_chain(x, [self.linear1.weight, self.linear2.weight], [self.linear1.bias, self.linear2.bias],
+                          ["relu", None], [self.dropout.p, 0.0], [self._site, 0], self.training)
+
+
+class EncoderLayer(nn.Module):
+    def __init__(self, d_model, ffn_hidden, num_heads, drop_prob):
+        super().__init__()
+        self.attention = MultiHeadAttention(d_model=d_model, num_heads=num_heads)
+        self.norm1 = LayerNormalization(parameters_shape=[d_model])
+        self.dropout1 = nn.Dropout(p=drop_prob)
+        self.ffn = PositionwiseFeedForward(d_model=d_model, hidden=ffn_hidden, drop_prob=drop_prob)
+        self.norm2 = LayerNormalization(parameters_shape=[d_model])
+        self.dropout2 = nn.Dropout(p=drop_prob)
+        self._sites = (new_site(), new_site())
+        self.mask_mode = "reference"
+
+    def forward(self, x, self_attention_mask=None):
+        a = self.attention(x, mask=self_attention_mask, mask_mode=self.mask_mode, decoder=False)
+        x = self.norm1(a, x, self.dropout1.p, self._sites[0])
+        f = self.ffn(x)
+        return self.norm2(f, x, self.dropout2.p, self._sites[1])
+
+
+class SequentialEncoder(nn.Sequential):
+    def forward(self, *inputs):
+        x, self_attention_mask = inputs
+        for module in self._modules.values():
+            x = module(x, self_attention_mask)
+        return x
+
+
+class Encoder(nn.Module):
+    def __init__(self, d_model, ffn_hidden, num_heads, drop_prob, num_layers: int, max_sequence_length, input_vocab):
+        super().__init__()
+        self.sentence_embedding = SentenceEmbedding(max_sequence_length, d_model, input_vocab)
+        self.layers = SequentialEncoder(*[EncoderLayer(d_model, ffn_hidden, num_heads, drop_prob)
+                                          for _ in range(num_layers)])
+
+    def forward(self, x, self_attention_mask=None):
+        x = self.sentence_embedding(x)
+        return self.layers(x, self_attention_mask)
+
+
+class MultiHeadCrossAttention(nn.Module):
+    def __init__(self, d_model, num_heads):
+        super().__init__()
+        self.d_model = d_model
+        self.num_heads = num_heads
+        self.head_dim = d_model // num_heads
+        self.kv_layer = nn.Linear(d_model, 2 * d_model)
+        self.q_layer = nn.Linear(d_model, d_model)
+        self.linear_layer = nn.Linear(d_model, d_model)
+
+    def forward(self, x, y, mask=None, mask_mode: str = "reference"):
+        """x: encoder output (keys/values), y: decoder stream (queries)."""
+        kind = _mask_kind(mask, mask_mode, False)
+        kv = _linear(x, self.kv_layer.weight, self.kv_layer.bias)
+        q = _linear(y, self.q_layer.weight, self.q_layer.bias)
+        if isinstance(kind, torch.Tensor):
+            values = _generic_attention(q, kv, self.num_heads, kind)
+        else:
+            values = _att.attention(q, kv, num_heads=self.num_heads, mask_mode=kind)
+        return _linear(values, self.linear_layer.weight, self.linear_layer.bias)
+
+
+class DecoderLayer(nn.Module):
+    def __init__(self, d_model, ffn_hidden, num_heads, drop_prob):
+        super().__init__()
+        self.self_attention = MultiHeadAttention(d_model=d_model, num_heads=num_heads)
+        self.layer_norm1 = LayerNormalization(parameters_shape=[d_model])
+        self.dropout1 = nn.Dropout(p=drop_prob)
+        self.encoder_decoder_attention = MultiHeadCrossAttention(d_model=d_model, num_heads=num_heads)
+        self.layer_norm2 = LayerNormalization(parameters_shape=[d_model])
+        self.dropout2 = nn.Dropout(p=drop_prob)
+        self.ffn = PositionwiseFeedForward(d_model=d_model, hidden=ffn_hidden, drop_prob=drop_prob)
+        self.layer_norm3 = LayerNormalization(parameters_shape=[d_model])
+        self.dropout3 = nn.Dropout(p=drop_prob)
+        self._sites = (new_site(), new_site(), new_site())
+        self.mask_mode = "reference"
+
+    def forward(self, x, y, self_attention_mask=None, cross_attention_mask=None):
+        a = self.self_attention(y, mask=self_attention_mask, mask_mode=self.mask_mode, decoder=True)
+        y = self.layer_norm1(a, y, self.dropout1.p, self._sites[0])
+        c = self.encoder_decoder_attention(x, y, mask=cross_attention_mask, mask_mode=self.mask_mode)
+        y = self.layer_norm2(c, y, self.dropout2.p, self._sites[1])
+        f = self.ffn(y)
+        return self.layer_norm3(f, y, self.dropout3.p, self._sites[2])
+
+
+class SequentialDecoder(nn.Sequential):
+    def forward(self, *inputs):
+        x, y, self_attention_mask, cross_attention_mask = inputs
+        for module in self._modules.values():
+            y = module(x, y, self_attention_mask, cross_attention_mask)
+        return y
+
+
+class Decoder(nn.Module):
+    def __init__(self, d_model, ffn_hidden, num_heads, drop_prob, num_layers: int, max_sequence_length, input_vocab):
+        super().__init__()
+        self.sentence_embedding = SentenceEmbedding(max_sequence_length, d_model, input_vocab)
+        self.layers = SequentialDecoder(*[DecoderLayer(d_model, ffn_hidden, num_heads, drop_prob)
+                                          for _ in range(num_layers)])
+
+    def forward(self, x, y, self_attention_mask=None, cross_attention_mask=None):
+        y = self.sentence_embedding(y)
+        return self.layers(x, y, self_attention_mask, cross_attention_mask)
+
+
+class Transformer(nn.Module):
+    def __init__(self, d_model, ffn_hidden, num_heads, drop_prob, num_layers: int, max_sequence_length, de_vocab_size,
+                 input_en_vocab, input_dec_vocab, mask_mode: str = "reference"):
+        super().__init__()
+        self.encoder = Encoder(d_model, ffn_hidden, num_heads, drop_prob, num_layers, max_sequence_length,
+                               input_en_vocab)
+        self.decoder = Decoder(d_model, ffn_hidden, num_heads, drop_prob, num_layers, max_sequence_length,
+                               input_dec_vocab)
+        self.linear = nn.Linear(d_model, de_vocab_size)
+        self.device = get_device()
+        self.set_mask_mode(mask_mode)
+
+    def set_mask_mode(self, mode: str) -> None:
+        assert mode in ("reference", "causal")
+        self.mask_mode = mode
+        for m in self.modules():
+            if isinstance(m, (EncoderLayer, DecoderLayer)):
+                m.mask_mode = mode
+
+    def forward(self, x, y, encoder_self_attention_mask=None, decoder_self_attention_mask=None,
+                decoder_cross_attention_mask=None, return_hidden: bool = False):
+        x = self.encoder(x, encoder_self_attention_mask)
+        out = self.decoder(x, y, decoder_self_attention_mask, decoder_cross_attention_mask)
+        if return_hidden:
+            return out
+        return _linear(out, self.linear.weight, self.linear.bias)

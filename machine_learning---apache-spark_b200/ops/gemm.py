@@ -132,8 +132,8 @@ def working_copy(param: torch.Tensor) -> torch.Tensor:
     (``param._b200_w16`` is then a view into the flat bf16 buffer).  Without an engine the copy is re-cast when the
     parameter's version counter moves.
     """
-    if param.dtype == torch.bfloat16:
-        return param.detach()
+    if param.dtype == torch.bfloat16 or not param.is_cuda:
+        return param.detach()  # CPU restatement computes in the parameter's own precision
     w16 = getattr(param, "_b200_w16", None)
     if w16 is not None and getattr(param, "_b200_w16_managed", False):
         return w16
@@ -178,7 +178,8 @@ class _MLPChain(torch.autograd.Function):
         biases = params[n_layers:]
         lead = x.shape[:-1]
         h = x.reshape(-1, x.shape[-1])
-        if h.dtype != torch.bfloat16:
+        native = _native.use_native(x)
+        if native and h.dtype != torch.bfloat16:
             h = h.to(torch.bfloat16)
         if not h.is_contiguous():
             h = h.contiguous()
@@ -187,7 +188,8 @@ class _MLPChain(torch.autograd.Function):
             inputs.append(h)
             w16 = working_copy(weights[i])
             b = biases[i]
-            h = gemm(h, w16, bias=None if b is None else b.detach(), act=acts[i], dropout_p=drops[i], site=sites[i])
+            h = gemm(h, w16, bias=None if b is None else b.detach(), act=acts[i], dropout_p=drops[i], site=sites[i],
+                     out_dtype=torch.bfloat16 if native else h.dtype)
         ctx.n_layers, ctx.acts, ctx.drops = n_layers, acts, drops
         ctx.params = params
         ctx.x_dtype = x.dtype
@@ -201,18 +203,20 @@ class _MLPChain(torch.autograd.Function):
         saved = ctx.saved_tensors
         inputs, y = saved[:n], saved[n]
         dz = dy.reshape(-1, dy.shape[-1])
-        if dz.dtype != torch.bfloat16:
-            dz = dz.to(torch.bfloat16)
+        native = _native.use_native(dz)
+        cdt = torch.bfloat16 if native else y.dtype
+        if dz.dtype != cdt:
+            dz = dz.to(cdt)
         if not dz.is_contiguous():
             dz = dz.contiguous()
         # last layer's own activation (rare: chain ending in an activation)
         if ctx.acts[n - 1]:
             yf = y.float()
             if ctx.acts[n - 1] == ACT_RELU:
-                dz = (dz.float() * (yf > 0) / (1.0 - ctx.drops[n - 1])).to(torch.bfloat16)
+                dz = (dz.float() * (yf > 0) / (1.0 - ctx.drops[n - 1])).to(cdt)
             else:
                 assert ctx.drops[n - 1] == 0
-                dz = (dz.float() * yf * (1 - yf)).to(torch.bfloat16)
+                dz = (dz.float() * yf * (1 - yf)).to(cdt)
         gw = [None] * n
         gb = [None] * n
         dx = None
@@ -230,12 +234,13 @@ class _MLPChain(torch.autograd.Function):
             if need_dx:
                 w16 = working_copy(w)
                 if i > 0 and ctx.acts[i - 1] == ACT_RELU:
-                    dz = gemm(dz, w16, b_mn=True, aux=xin, aux_mode=1, aux_scale=1.0 / (1.0 - ctx.drops[i - 1]))
+                    dz = gemm(dz, w16, b_mn=True, aux=xin, aux_mode=1, aux_scale=1.0 / (1.0 - ctx.drops[i - 1]),
+                              out_dtype=cdt)
                 elif i > 0 and ctx.acts[i - 1] == ACT_SIGMOID:
                     assert ctx.drops[i - 1] == 0, "sigmoid followed by dropout is not fused"
-                    dz = gemm(dz, w16, b_mn=True, aux=xin, aux_mode=3)
+                    dz = gemm(dz, w16, b_mn=True, aux=xin, aux_mode=3, out_dtype=cdt)
                 else:
-                    dz = gemm(dz, w16, b_mn=True)
+                    dz = gemm(dz, w16, b_mn=True, out_dtype=cdt)
                 if i == 0:
                     dx = dz
         if dx is not None:

@@ -69,6 +69,10 @@ class FlatOptimizer:
             p.grad = None
 
     def step(self, grad_scale: float = 1.0) -> None:
+        for p in self.flat.params:  # gradients assigned by hand (not through autograd) never hit the hook
+            if p.grad is not None:
+                p._b200_grad.copy_(p.grad.reshape(-1))
+                p.grad = None
         if self.flat.device.type == "cuda":
             _native.check(_native.load().b200ml_counters_advance(None, self.step_tensor.data_ptr(),
                                                                  _native.stream_ptr()), "counters_advance")

@@ -1,0 +1,196 @@
+"""Data-parallel training engine — the role DDP(model) + optimizer.zero_grad()/step() play in the reference
+(distributed_cnn.py:156,179-183; distributed_lstm.py:160,192-194; distributed_multilayer_perceptron.py:106,134-138),
+rebuilt around flat buckets and a fused all-reduce + optimizer kernel.
+
+Per step:
+  begin_step()   bump the device RNG / optimizer-step counters, clear the few gradient slots that accumulate
+  forward/backward   wgrad kernels write straight into the flat fp32 gradient buffer; each parameter reports "ready"
+  (as buckets complete)  world > 1: the bucket is reduced across ranks and the optimizer applied in ONE kernel
+                         (parallel/comm.py: one-shot / two-shot P2P over NVLink), on a side stream, overlapping the
+                         rest of backward;  "nccl" mode (the measured baseline) uses torch.distributed.all_reduce
+  finish_step()  join the side stream (world == 1: one fused optimizer launch over the whole flat buffer)
+
+Rank 0's parameters are broadcast at construction (what DDP's constructor does); gradients are
+averaged (sum / world), so N ranks with batch B reproduce one rank with batch N·B.
+"""
+from __future__ import annotations
+
+import os
+
+import torch
+import torch.distributed as dist
+
+from .. import _native
+from ..ops.optim import KINDS, optim_step_flat
+from ..utils.rng import DeviceCounters
+from .flat import FlatParams
+
+
+class DataParallelEngine:
+    def __init__(self, module, optimizer: str = "sgd", lr: float = 1e-2, betas=(0.9, 0.999), eps: float = 1e-8,
+                 weight_decay: float = 0.0, allreduce: str = "auto", bucket_mb: float = 25.0,
+                 process_group=None, sync_gradients: bool = True):
+        self.module = module
+        self.kind = KINDS[optimizer]
+        self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
+        self.pg = process_group
+        self.world = dist.get_world_size(self.pg) if dist.is_available() and dist.is_initialized() else 1
+        self.rank = dist.get_rank(self.pg) if self.world > 1 else 0
+        self.sync_gradients = sync_gradients  # False emulates the reference as written
+        params = [p for p in module.parameters() if p.requires_grad]
+        self.flat = FlatParams(params)
+        self.device = self.flat.device
+        self.counters = DeviceCounters.get(self.device)
+        self.m = torch.zeros_like(self.flat.flat_p) if self.kind == 2 else None
+        self.v = torch.zeros_like(self.flat.flat_p) if self.kind == 2 else None
+        self.launches_in_capture = 0
+        self._graph = None
+
+        if self.world > 1:
+            dist.broadcast(self.flat.flat_p, src=0, group=self.pg)
+            self.flat.refresh_working_copy()
+
+        # buckets: contiguous ranges of the flat buffer, in registration order; gradients become ready roughly in
+        # reverse order, so the LAST bucket completes first.
+        cap = max(int(bucket_mb * (1 << 20) / 4), 1)
+        self.buckets = []  # (start, numel, [param indices])
+        start, cur, idxs = 0, 0, []
+        for i, p in enumerate(self.flat.params):
+            o, n = self.flat.slot(i)
+            end = (self.flat.offsets[i + 1] if i + 1 < len(self.flat.params) else self.flat.numel)
+            idxs.append(i)
+            cur = end - start
+            if cur >= cap:
+                self.buckets.append((start, cur, idxs))
+                start, idxs = end, []
+        if idxs:
+            self.buckets.append((start, self.flat.numel - start, idxs))
+        self._bucket_of = {}
+        for b, (_, _, ids) in enumerate(self.buckets):
+            for i in ids:
+                self._bucket_of[i] = b
+        self._pending = [0] * len(self.buckets)
+        for i, p in enumerate(self.flat.params):
+            p._b200_ready = self._make_ready(i)
+
+        self.allreduce_mode = "none"
+        self.comm = None
+        self.comm_stream = None
+        if self.world > 1 and self.sync_gradients:
+            mode = allreduce
+            if mode == "auto":
+                mode = os.environ.get("B200ML_ALLREDUCE", "fused" if self.device.type == "cuda" else "nccl")
+            if mode == "fused" and self.device.type == "cuda":
+                from .comm import FusedAllReduce
+
+                self.comm = FusedAllReduce(self.flat, self.m, self.v, self.pg)
+                self.allreduce_mode = "fused:" + self.comm.transport
+            else:
+                self.allreduce_mode = "nccl" if self.device.type == "cuda" else "gloo"
+            if self.device.type == "cuda":
+                self.comm_stream = torch.cuda.Stream(device=self.device, priority=-1)
+        self._in_step = False
+
+    # ------------------------------------------------------------------------------------------------ bucket events
+    def _make_ready(self, i):
+        def ready():
+            if not self._in_step:
+                return
+            b = self._bucket_of[i]
+            self._pending[b] -= 1
+            if self._pending[b] == 0:
+                self._bucket_ready(b)
+        return ready
+
+    def _bucket_ready(self, b: int) -> None:
+        if self.world == 1 or not self.sync_gradients:
+            return  # single fused optimizer launch in finish_step
+        start, n, _ = self.buckets[b]
+        if self.comm_stream is not None:
+            self.comm_stream.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(self.comm_stream):
+                self._reduce_and_update(start, n)
+        else:
+            self._reduce_and_update(start, n)
+
+    def _reduce_and_update(self, start: int, n: int) -> None:
+        if self.comm is not None:
+            self.comm.allreduce_update(start, n, self.kind, self.lr, self.betas, self.eps, self.weight_decay,
+                                       self.counters.opt_step)
+            return
+        g = self.flat.flat_g[start:start + n]
+        dist.all_reduce(g, group=self.pg)
+        optim_step_flat(self.flat.flat_p, self.flat.flat_g, self.m, self.v, self.flat.flat_w16, self.kind, self.lr,
+                        self.betas, self.eps, self.weight_decay, self.counters.opt_step, 1.0 / self.world, start, n)
+
+    # ------------------------------------------------------------------------------------------------ step API
+    def begin_step(self) -> None:
+        self.counters.advance(rng=True, opt=True)
+        self.flat.zero_accumulating_slots()
+        for b, (_, _, ids) in enumerate(self.buckets):
+            self._pending[b] = len(ids)
+        self._in_step = True
+
+    def finish_step(self) -> None:
+        self._in_step = False
+        if self.world == 1 or not self.sync_gradients:
+            optim_step_flat(self.flat.flat_p, self.flat.flat_g, self.m, self.v, self.flat.flat_w16, self.kind, self.lr,
+                            self.betas, self.eps, self.weight_decay, self.counters.opt_step)
+            return
+        # parameters that never reported (unused in this forward) still need their bucket processed
+        for b in range(len(self.buckets)):
+            if self._pending[b] > 0:
+                self._pending[b] = 0
+                self._bucket_ready(b)
+        if self.comm_stream is not None:
+            torch.cuda.current_stream().wait_stream(self.comm_stream)
+
+    # torch.optim-flavoured aliases so the entry scripts read like the reference loops
+    def zero_grad(self, set_to_none: bool = True) -> None:
+        self.begin_step()
+
+    def step(self) -> None:
+        self.finish_step()
+
+    # ------------------------------------------------------------------------------------------------ CUDA graph
+    def capture(self, step_fn):
+        """Capture one full training step (forward, backward, all-reduce, optimizer) into a CUDA graph."""
+        assert self.device.type == "cuda"
+        if self.world > 1 and self.comm is None:
+            return None  # NCCL baseline path stays eager
+        torch.cuda.synchronize()
+        n0 = _native.launches()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            step_fn()
+        self.launches_in_capture = _native.launches() - n0
+        self._graph = g
+        return g
+
+    # ------------------------------------------------------------------------------------------------ utilities
+    def weights_hash(self) -> float:
+        """Cheap rank-divergence check: every rank must hold bit-identical master weights."""
+        h = self.flat.flat_p.double().sum()
+        if self.world > 1:
+            lo, hi = h.clone(), h.clone()
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=self.pg)
+            dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=self.pg)
+            if (hi - lo).abs().item() != 0.0:
+                raise RuntimeError(f"rank divergence: weight checksum differs across ranks ({lo.item()} vs {hi.item()})")
+        return float(h.item())
+
+    def state_dict(self):
+        return {"step": int(self.counters.opt_step.item()), "m": self.m, "v": self.v, "kind": self.kind}
+
+    def load_state_dict(self, sd) -> None:
+        self.counters.opt_step.fill_(sd["step"])
+        if self.m is not None and sd.get("m") is not None:
+            self.m.copy_(sd["m"])
+            self.v.copy_(sd["v"])
+
+    def close(self) -> None:
+        if self.comm is not None:
+            self.comm.close()
+            self.comm = None
+        for p in self.flat.params:
+            p._b200_ready = None
