@@ -1,0 +1,237 @@
+// b200ml — K18 (+K15/K16/K17): gradient all-reduce over NVLink 5 / NVSwitch peer memory, fused with the averaging,
+// the SGD / Adam update and the bf16 re-cast of the weights.  Replaces c10d Reducer + gloo all-reduce +
+// optimizer.step() of the reference's intended DDP path (distributed_cnn.py:152-183 etc.).
+//
+// Every rank maps every peer's flat gradient / weight buffers (CUDA IPC) and the kernels dereference those peer
+// pointers directly (ld.global / st.global over NVLink):
+//   one-shot  (latency path, small buckets): barrier -> every rank sums the whole bucket from all N ranks in rank
+//             order 0..N-1 (=> bit-identical sums everywhere) -> applies the update to its own weights -> barrier.
+//   two-shot  (bandwidth path): rank r owns slice r of the bucket: pulls slice r from the N-1 peers, reduces, runs the
+//             optimizer ONCE for those elements (Adam math is not repeated N times), then pushes the updated fp32
+//             master + bf16 working weights into every rank's buffers -> barrier.  Gradients are never all-gathered:
+//             the second phase moves weights (2 or 6 bytes/param) instead of fp32 gradients.
+// Cross-GPU barriers are per-CTA flag exchanges through a peer-mapped signal pad with release/acquire at system scope;
+// flag values are a monotonically increasing epoch kept in device memory, so a captured CUDA graph replays correctly.
+// Spins are bounded: a dead peer traps the kernel instead of hanging the GPU.
+#include "../../include/b200ml.h"
+#include "../common/host.h"
+#include "../common/optim.cuh"
+#include "../common/ptx.cuh"
+
+namespace b200 {
+namespace comm {
+
+constexpr int kMaxRanks = 8;
+constexpr int kMaxBlocks = 128;
+constexpr int kThreads = 512;
+
+struct Peers {
+    int world, rank;
+    float* g[kMaxRanks];
+    float* p[kMaxRanks];
+    __nv_bfloat16* w16[kMaxRanks];
+    uint32_t* sig[kMaxRanks];  // [2][kMaxBlocks][kMaxRanks] per rank
+    uint32_t* counter;         // local: [0] epoch, [1] CTA ticket
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ float4 ld_peer_f4(const float* p) {
+    float4 v;
+    asm volatile("ld.global.relaxed.sys.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "l"(p)
+                 : "memory");
+    return v;
+}
+
+// All CTAs with the same blockIdx.x on every rank meet here.
+__device__ __forceinline__ void cross_barrier(const Peers& c, int slot, uint32_t val) {
+    __syncthreads();
+    if (threadIdx.x < c.world) {
+        const int t = threadIdx.x;
+        __threadfence_system();
+        st_release_sys(c.sig[t] + (slot * kMaxBlocks + blockIdx.x) * kMaxRanks + c.rank, val);
+        const uint32_t* mine = c.sig[c.rank] + (slot * kMaxBlocks + blockIdx.x) * kMaxRanks + t;
+        const long long t0 = clock64();
+        while ((int)(ld_acquire_sys(mine) - val) < 0) {
+            if (clock64() - t0 > 20000000000LL) {
+                printf("b200ml: all-reduce barrier timeout rank=%d peer=%d block=%d epoch=%u\n", c.rank, t, blockIdx.x,
+                       val);
+                __trap();
+            }
+        }
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ void finish_epoch(const Peers& c, uint32_t epoch) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const uint32_t done = atomicAdd(&c.counter[1], 1u);
+        if (done == gridDim.x - 1) {
+            c.counter[1] = 0;
+            __threadfence();
+            c.counter[0] = epoch + 1;
+        }
+    }
+}
+
+__device__ __forceinline__ uint2 pack4_bf16(float4 v) {
+    uint2 u;
+    u.x = pack_bf16x2(v.x, v.y);
+    u.y = pack_bf16x2(v.z, v.w);
+    return u;
+}
+
+// kind 0: out[i] = sum/N (no weight update).  `start`, `n` in elements, both multiples of 4.
+template <bool kTwoShot>
+__global__ void __launch_bounds__(kThreads)
+allreduce_update_kernel(Peers c, long long start, long long n, OptimSpec o, float* __restrict__ m,
+                        float* __restrict__ v, float* __restrict__ out, int push_master) {
+    const uint32_t epoch = c.counter[0] + 1;
+    cross_barrier(c, 0, epoch);  // every rank's gradients for this bucket are complete and visible
+
+    const float inv_world = 1.f / (float)c.world;
+    AdamCorr corr = {0.f, 0.f};
+    if (o.kind == 2) corr = adam_corr(o);
+
+    long long lo = 0, hi = n;  // range (relative to start) this rank reduces
+    if (kTwoShot) {
+        long long per = (n / 4 + c.world - 1) / c.world * 4;
+        lo = per * c.rank;
+        hi = lo + per < n ? lo + per : n;
+        if (lo > n) lo = n;
+    }
+    const long long nvec = (hi - lo) / 4;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+        const long long e = start + lo + i * 4;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int r = 0; r < kMaxRanks; ++r) {
+            if (r < c.world) {
+                const float4 t = ld_peer_f4(c.g[r] + e);
+                acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+            }
+        }
+        acc.x *= inv_world; acc.y *= inv_world; acc.z *= inv_world; acc.w *= inv_world;
+        if (o.kind == 0) {
+            *reinterpret_cast<float4*>(out + e) = acc;
+            continue;
+        }
+        float4 p = *reinterpret_cast<const float4*>(c.p[c.rank] + e);
+        if (o.kind == 2) {
+            float4 mm = *reinterpret_cast<const float4*>(m + e);
+            float4 vv = *reinterpret_cast<const float4*>(v + e);
+            p.x = adam_update(p.x, acc.x, mm.x, vv.x, o, corr);
+            p.y = adam_update(p.y, acc.y, mm.y, vv.y, o, corr);
+            p.z = adam_update(p.z, acc.z, mm.z, vv.z, o, corr);
+            p.w = adam_update(p.w, acc.w, mm.w, vv.w, o, corr);
+            *reinterpret_cast<float4*>(m + e) = mm;
+            *reinterpret_cast<float4*>(v + e) = vv;
+        } else {
+            p.x = sgd_update(p.x, acc.x, o);
+            p.y = sgd_update(p.y, acc.y, o);
+            p.z = sgd_update(p.z, acc.z, o);
+            p.w = sgd_update(p.w, acc.w, o);
+        }
+        const uint2 pb = pack4_bf16(p);
+        if (kTwoShot) {
+#pragma unroll
+            for (int r = 0; r < kMaxRanks; ++r) {
+                if (r < c.world) {
+                    if (push_master || r == c.rank) *reinterpret_cast<float4*>(c.p[r] + e) = p;
+                    *reinterpret_cast<uint2*>(c.w16[r] + e) = pb;
+                }
+            }
+        } else {
+            *reinterpret_cast<float4*>(c.p[c.rank] + e) = p;
+            *reinterpret_cast<uint2*>(c.w16[c.rank] + e) = pb;
+        }
+    }
+    // peers are done reading my gradients and (two-shot) done writing my weights
+    cross_barrier(c, 1, epoch);
+    finish_epoch(c, epoch);
+}
+
+}  // namespace comm
+}  // namespace b200
+
+extern "C" {
+
+int b200ml_comm_alloc(size_t bytes, void** ptr) {
+    B200_REQUIRE(ptr && bytes > 0, "comm_alloc: bad args");
+    B200_CHECK_CUDA(cudaMalloc(ptr, bytes));
+    B200_CHECK_CUDA(cudaMemset(*ptr, 0, bytes));
+    return 0;
+}
+int b200ml_comm_free(void* ptr) {
+    if (ptr) B200_CHECK_CUDA(cudaFree(ptr));
+    return 0;
+}
+int b200ml_ipc_export(const void* ptr, unsigned char* handle64) {
+    B200_REQUIRE(ptr && handle64, "ipc_export: bad args");
+    cudaIpcMemHandle_t h;
+    B200_CHECK_CUDA(cudaIpcGetMemHandle(&h, const_cast<void*>(ptr)));
+    static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    memcpy(handle64, &h, 64);
+    return 0;
+}
+int b200ml_ipc_import(const unsigned char* handle64, void** ptr) {
+    B200_REQUIRE(ptr && handle64, "ipc_import: bad args");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    B200_CHECK_CUDA(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return 0;
+}
+int b200ml_ipc_close(void* ptr) {
+    if (ptr) B200_CHECK_CUDA(cudaIpcCloseMemHandle(ptr));
+    return 0;
+}
+
+int b200ml_allreduce_update(const b200ml_comm* cm, long long start, long long n, int algo, int kind, float lr,
+                            float beta1, float beta2, float eps, float weight_decay, const int* step_dev, float* m,
+                            float* v, float* out, int push_master, int max_blocks, cudaStream_t stream) {
+    using namespace b200;
+    using namespace b200::comm;
+    B200_REQUIRE(cm && cm->world >= 1 && cm->world <= kMaxRanks && cm->rank >= 0 && cm->rank < cm->world,
+                 "allreduce: bad communicator");
+    B200_REQUIRE(start % 4 == 0 && n % 4 == 0 && n > 0, "allreduce: start/n must be positive multiples of 4");
+    B200_REQUIRE(kind == 0 ? out != nullptr : true, "allreduce: kind 0 needs an output buffer");
+    B200_REQUIRE(kind != 2 || (m && v), "allreduce: Adam needs m and v");
+    Peers c;
+    c.world = cm->world;
+    c.rank = cm->rank;
+    for (int r = 0; r < kMaxRanks; ++r) {
+        c.g[r] = r < cm->world ? cm->grads[r] : nullptr;
+        c.p[r] = r < cm->world ? cm->params[r] : nullptr;
+        c.w16[r] = r < cm->world ? reinterpret_cast<__nv_bfloat16*>(cm->w16[r]) : nullptr;
+        c.sig[r] = r < cm->world ? cm->signals[r] : nullptr;
+    }
+    c.counter = cm->counter;
+    OptimSpec o{kind, lr, beta1, beta2, eps, weight_decay, step_dev};
+    // two-shot pays two NVLink round trips but moves (N-1)/N of the bytes once; one-shot moves (N-1)x the bytes.
+    bool two = algo == 2 || (algo == 0 && kind != 0 && n * 4 > (512 << 10));
+    if (kind == 0) two = false;
+    const long long work = two ? (n / cm->world + 3) / 4 : n / 4;
+    long long blocks = (work + kThreads * 4 - 1) / (kThreads * 4);
+    int cap = max_blocks > 0 ? max_blocks : 64;
+    if (cap > kMaxBlocks) cap = kMaxBlocks;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    if (two)
+        allreduce_update_kernel<true><<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, out, push_master);
+    else
+        allreduce_update_kernel<false><<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, out, push_master);
+    B200_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // extern "C"

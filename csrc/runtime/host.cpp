@@ -53,6 +53,13 @@ int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t*
                    const uint32_t* box) {
     EncodeTiledFn fn = encode_fn();
     if (!fn) return set_error("cuTensorMapEncodeTiled not available from the driver");
+    // Driver-API entry points need a current context on the calling thread.  Runtime calls bind the primary context
+    // implicitly, driver calls do not — and autograd worker threads may not have issued a runtime call yet.
+    static thread_local bool ctx_bound = false;
+    if (!ctx_bound) {
+        cudaFree(nullptr);
+        ctx_bound = true;
+    }
     if ((reinterpret_cast<uintptr_t>(base) & 15) != 0) return set_error("TMA base %p not 16-byte aligned", base);
     cuuint64_t gdim[5];
     cuuint64_t gstr[5];

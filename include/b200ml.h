@@ -125,6 +125,32 @@ int b200ml_attn_bwd(const b200ml_attn_operand* q, const b200ml_attn_operand* k, 
                     const b200ml_attn_operand* dq, const b200ml_attn_operand* dk, const b200ml_attn_operand* dv, int B,
                     int H, int Sq, int Skv, float scale, int mask_mode, cudaStream_t stream);
 
+/* ------------------------------------------------------------------------------------------------ K18 all-reduce
+ * Symmetric buffers: b200ml_comm_alloc ALLOCATES (cudaMalloc + zero fill) — it is the set-up-time allocator for
+ * buffers that peers map through CUDA IPC (export on the owner, import on every peer).
+ * b200ml_allreduce_update: grads[r] / params[r] / w16[r] / signals[r] are rank r's flat gradient (fp32), master
+ * weight (fp32), working weight (bf16) and signal-pad (2*128*8 uint32, zero-initialised) buffers as mapped in THIS
+ * process; counter is a local zero-initialised uint32[2].  Elements [start, start+n) are summed over ranks in rank
+ * order, divided by world, and (kind 1 SGD / 2 Adam) applied to the weights; kind 0 writes the mean to `out`.
+ * algo: 0 auto, 1 one-shot, 2 two-shot.  Every rank must issue the same sequence of calls.
+ * ref: DDP bucket all-reduce + optimizer.step (distributed_cnn.py:156,181-183). */
+typedef struct {
+    int world, rank;
+    float* grads[8];
+    float* params[8];
+    void* w16[8];
+    unsigned* signals[8];
+    unsigned* counter;
+} b200ml_comm;
+int b200ml_comm_alloc(size_t bytes, void** ptr);
+int b200ml_comm_free(void* ptr);
+int b200ml_ipc_export(const void* ptr, unsigned char* handle64);
+int b200ml_ipc_import(const unsigned char* handle64, void** ptr);
+int b200ml_ipc_close(void* ptr);
+int b200ml_allreduce_update(const b200ml_comm* cm, long long start, long long n, int algo, int kind, float lr,
+                            float beta1, float beta2, float eps, float weight_decay, const int* step_dev, float* m,
+                            float* v, float* out, int push_master, int max_blocks, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

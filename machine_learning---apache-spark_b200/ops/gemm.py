@@ -224,12 +224,9 @@ class _MLPChain(torch.autograd.Function):
             xin = inputs[i]
             w = weights[i]
             N, K = w.shape
-            if w.requires_grad:
-                gw[i] = deliver_grad(w, lambda out, acc, dz=dz, xin=xin: gemm(dz, xin, a_mn=True, b_mn=True, out=out,
-                                                                             accumulate=acc), (N, K))
-            b = biases[i]
-            if b is not None and b.requires_grad:
-                gb[i] = deliver_grad(b, lambda out, acc, dz=dz: colsum(dz, out=out, accumulate=acc), (N,))
+            # dgrad FIRST: delivering a parameter gradient may complete a bucket, and the engine then updates that
+            # bucket's weights on its side stream — every read of this layer's weights must already be enqueued.
+            dz_this = dz
             need_dx = i > 0 or ctx.needs_input_grad[0]
             if need_dx:
                 w16 = working_copy(w)
@@ -243,6 +240,12 @@ class _MLPChain(torch.autograd.Function):
                     dz = gemm(dz, w16, b_mn=True, out_dtype=cdt)
                 if i == 0:
                     dx = dz
+            if w.requires_grad:
+                gw[i] = deliver_grad(w, lambda out, acc, g=dz_this, xin=xin: gemm(g, xin, a_mn=True, b_mn=True, out=out,
+                                                                                 accumulate=acc), (N, K))
+            b = biases[i]
+            if b is not None and b.requires_grad:
+                gb[i] = deliver_grad(b, lambda out, acc, g=dz_this: colsum(g, out=out, accumulate=acc), (N,))
         if dx is not None:
             dx = dx.reshape(*dy.shape[:-1], dx.shape[-1]).to(ctx.x_dtype)
         return (dx, None, None, None, None, *gw, *gb)

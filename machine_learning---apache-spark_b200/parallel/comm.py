@@ -1,0 +1,161 @@
+"""Symmetric (peer-mapped) buffers and the fused all-reduce + optimizer launcher (csrc/comm/allreduce.cu).
+
+Set-up (once): every rank allocates its flat gradient / weight / working-copy buffers and a signal pad with
+``b200ml_comm_alloc`` (plain cudaMalloc, so the CUDA-IPC handle maps the whole allocation at offset 0), exports the IPC
+handles, exchanges them through the process group (an object all-gather — control plane only) and imports every
+peer's handles.  From then on the data plane is our own kernels dereferencing peer pointers over NVLink; NCCL is not
+involved.  This is the B200 counterpart of gloo's TCP pairs + c10d's Reducer buckets in the reference's DDP setup
+(distributed_cnn.py:152-156).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+import torch.distributed as dist
+
+from .. import _native, _native_ext
+
+MAX_RANKS = 8
+SIGNAL_WORDS = 2 * 128 * 8
+
+
+class CommStruct(C.Structure):
+    _fields_ = [("world", C.c_int), ("rank", C.c_int), ("grads", C.c_void_p * 8), ("params", C.c_void_p * 8),
+                ("w16", C.c_void_p * 8), ("signals", C.c_void_p * 8), ("counter", C.c_void_p)]
+
+
+vp, i, ll, f = C.c_void_p, C.c_int, C.c_longlong, C.c_float
+_native_ext.register("b200ml_comm_alloc", [C.c_size_t, C.POINTER(C.c_void_p)])
+_native_ext.register("b200ml_comm_free", [vp])
+_native_ext.register("b200ml_ipc_export", [vp, C.c_char_p])
+_native_ext.register("b200ml_ipc_import", [C.c_char_p, C.POINTER(C.c_void_p)])
+_native_ext.register("b200ml_ipc_close", [vp])
+_native_ext.register("b200ml_allreduce_update", [C.POINTER(CommStruct), ll, ll, i, i, f, f, f, f, f, vp, vp, vp, vp, i,
+                                                 i, vp])
+
+
+class _RawCuda:
+    """Minimal __cuda_array_interface__ holder so torch can view memory we allocated ourselves."""
+
+    def __init__(self, ptr: int, numel: int, typestr: str):
+        self.__cuda_array_interface__ = {"shape": (numel,), "typestr": typestr, "data": (ptr, False), "version": 3}
+
+
+class SymmetricBuffer:
+    """Device buffer allocated by libb200ml and exportable over CUDA IPC; ``.tensor`` is a torch view of it."""
+
+    _DT = {torch.float32: ("<f4", 4), torch.uint8: ("|u1", 1), torch.int32: ("<i4", 4)}
+
+    def __init__(self, numel: int, dtype, device):
+        lib = _native.load()
+        self.device = torch.device(device)
+        esize = 2 if dtype == torch.bfloat16 else self._DT[dtype][1]
+        self.nbytes = max(numel * esize, 16)
+        p = C.c_void_p()
+        with torch.cuda.device(self.device):
+            rc = lib.b200ml_comm_alloc(self.nbytes, C.byref(p))
+        if rc != 0:
+            raise _native.NativeError("comm_alloc: " + lib.b200ml_last_error().decode())
+        self.ptr = p.value
+        if dtype == torch.bfloat16:
+            raw = torch.as_tensor(_RawCuda(self.ptr, numel, "<i2"), device=self.device)
+            self.tensor = raw.view(torch.bfloat16)
+        else:
+            self.tensor = torch.as_tensor(_RawCuda(self.ptr, numel, self._DT[dtype][0]), device=self.device)
+        self._keep = self  # tensors created from the interface do not own the memory
+
+    def export(self) -> bytes:
+        buf = C.create_string_buffer(64)
+        lib = _native.load()
+        if lib.b200ml_ipc_export(self.ptr, buf) != 0:
+            raise _native.NativeError("ipc_export: " + lib.b200ml_last_error().decode())
+        return buf.raw
+
+    def free(self) -> None:
+        if self.ptr:
+            _native.load().b200ml_comm_free(self.ptr)
+            self.ptr = None
+
+
+def _import(handle: bytes) -> int:
+    lib = _native.load()
+    p = C.c_void_p()
+    if lib.b200ml_ipc_import(handle, C.byref(p)) != 0:
+        raise _native.NativeError("ipc_import: " + lib.b200ml_last_error().decode())
+    return p.value
+
+
+class SymmetricAllocator:
+    """Hands FlatParams its three flat buffers as symmetric allocations."""
+
+    def __init__(self, device):
+        self.device = device
+        self.buffers: dict[str, SymmetricBuffer] = {}
+
+    def __call__(self, name: str, numel: int, dtype) -> torch.Tensor:
+        b = SymmetricBuffer(numel, dtype, self.device)
+        self.buffers[name] = b
+        return b.tensor
+
+
+class FusedAllReduce:
+    """Peer-pointer tables + launcher for b200ml_allreduce_update."""
+
+    transport = "p2p-ipc"
+
+    def __init__(self, flat, m, v, group=None, allocator: SymmetricAllocator | None = None):
+        assert allocator is not None and {"flat_p", "flat_g", "flat_w16"} <= set(allocator.buffers), \
+            "fused all-reduce needs FlatParams built on a SymmetricAllocator"
+        self.flat, self.m, self.v, self.group = flat, m, v, group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        assert self.world <= MAX_RANKS, f"fused all-reduce supports up to {MAX_RANKS} ranks per node"
+        dev = flat.device
+        self.alloc = allocator
+        self.signals = SymmetricBuffer(SIGNAL_WORDS, torch.int32, dev)
+        self.counter = torch.zeros(2, dtype=torch.int32, device=dev)
+        mine = {k: b.export() for k, b in allocator.buffers.items()}
+        mine["signals"] = self.signals.export()
+        gathered = [None] * self.world
+        dist.all_gather_object(gathered, mine, group=group)
+        self._imported = []
+        self.cs = CommStruct()
+        self.cs.world, self.cs.rank = self.world, self.rank
+        table = {"flat_g": self.cs.grads, "flat_p": self.cs.params, "flat_w16": self.cs.w16, "signals": self.cs.signals}
+        local = {"flat_g": allocator.buffers["flat_g"].ptr, "flat_p": allocator.buffers["flat_p"].ptr,
+                 "flat_w16": allocator.buffers["flat_w16"].ptr, "signals": self.signals.ptr}
+        for r in range(self.world):
+            for key, arr in table.items():
+                if r == self.rank:
+                    arr[r] = local[key]
+                else:
+                    p = _import(gathered[r][key])
+                    self._imported.append(p)
+                    arr[r] = p
+        self.cs.counter = self.counter.data_ptr()
+        self.push_master = 1
+        self.max_blocks = 0
+        torch.cuda.synchronize(dev)
+        dist.barrier(group=group)  # nobody launches before every mapping exists
+
+    def allreduce_update(self, start, n, kind, lr, betas, eps, weight_decay, step_tensor, out=None, algo: int = 0):
+        lib = _native.load()
+        n4 = (n + 3) // 4 * 4  # slots are 64-element aligned, so rounding up stays inside the bucket
+        _native.check(lib.b200ml_allreduce_update(
+            C.byref(self.cs), start, n4, algo, kind, lr, betas[0], betas[1], eps, weight_decay, step_tensor.data_ptr(),
+            None if self.m is None else self.m.data_ptr(), None if self.v is None else self.v.data_ptr(),
+            None if out is None else out.data_ptr(), self.push_master, self.max_blocks, _native.stream_ptr()),
+            "allreduce_update")
+
+    def close(self) -> None:
+        lib = _native.load()
+        try:
+            torch.cuda.synchronize(self.flat.device)
+            if dist.is_initialized():
+                dist.barrier(group=self.group)
+        except Exception:  # noqa: BLE001
+            pass
+        for p in self._imported:
+            lib.b200ml_ipc_close(p)
+        self._imported = []

@@ -38,8 +38,20 @@ class DataParallelEngine:
         self.rank = dist.get_rank(self.pg) if self.world > 1 else 0
         self.sync_gradients = sync_gradients  # False emulates the reference as written
         params = [p for p in module.parameters() if p.requires_grad]
-        self.flat = FlatParams(params)
-        self.device = self.flat.device
+        self.device = params[0].device
+        mode = "none"
+        if self.world > 1 and self.sync_gradients:
+            mode = allreduce
+            if mode == "auto":
+                mode = os.environ.get("B200ML_ALLREDUCE", "fused" if self.device.type == "cuda" else "nccl")
+            if self.device.type != "cuda":
+                mode = "gloo"
+        sym_alloc = None
+        if mode == "fused":
+            from .comm import SymmetricAllocator
+
+            sym_alloc = SymmetricAllocator(self.device)
+        self.flat = FlatParams(params, allocator=sym_alloc)
         self.counters = DeviceCounters.get(self.device)
         self.m = torch.zeros_like(self.flat.flat_p) if self.kind == 2 else None
         self.v = torch.zeros_like(self.flat.flat_p) if self.kind == 2 else None
@@ -73,20 +85,15 @@ class DataParallelEngine:
         for i, p in enumerate(self.flat.params):
             p._b200_ready = self._make_ready(i)
 
-        self.allreduce_mode = "none"
+        self.allreduce_mode = mode
         self.comm = None
         self.comm_stream = None
         if self.world > 1 and self.sync_gradients:
-            mode = allreduce
-            if mode == "auto":
-                mode = os.environ.get("B200ML_ALLREDUCE", "fused" if self.device.type == "cuda" else "nccl")
-            if mode == "fused" and self.device.type == "cuda":
+            if mode == "fused":
                 from .comm import FusedAllReduce
 
-                self.comm = FusedAllReduce(self.flat, self.m, self.v, self.pg)
+                self.comm = FusedAllReduce(self.flat, self.m, self.v, self.pg, allocator=sym_alloc)
                 self.allreduce_mode = "fused:" + self.comm.transport
-            else:
-                self.allreduce_mode = "nccl" if self.device.type == "cuda" else "gloo"
             if self.device.type == "cuda":
                 self.comm_stream = torch.cuda.Stream(device=self.device, priority=-1)
         self._in_step = False

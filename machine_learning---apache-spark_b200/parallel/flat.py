@@ -21,7 +21,7 @@ def _round_up(n: int, a: int) -> int:
 
 
 class FlatParams:
-    def __init__(self, params, bf16_copy: bool = True, order=None):
+    def __init__(self, params, bf16_copy: bool = True, order=None, allocator=None):
         params = [p for p in params if p.requires_grad]
         if order is not None:
             params = [params[i] for i in order]
@@ -34,9 +34,13 @@ class FlatParams:
             self.offsets.append(off)
             off += _round_up(p.numel(), ALIGN)
         self.numel = off
-        self.flat_p = torch.zeros(off, dtype=torch.float32, device=self.device)
-        self.flat_g = torch.zeros(off, dtype=torch.float32, device=self.device)
-        self.flat_w16 = torch.zeros(off, dtype=torch.bfloat16, device=self.device) if bf16_copy else None
+        if allocator is None:  # default: ordinary torch allocations
+            def allocator(name, numel, dtype):
+                return torch.zeros(numel, dtype=dtype, device=self.device)
+        # (a SymmetricAllocator hands out peer-mappable buffers for the fused all-reduce, parallel/comm.py)
+        self.flat_p = allocator("flat_p", off, torch.float32)
+        self.flat_g = allocator("flat_g", off, torch.float32)
+        self.flat_w16 = allocator("flat_w16", off, torch.bfloat16) if bf16_copy else None
         self.zero_ranges = []  # slots whose backward accumulates (embedding scatter-add) and need clearing per step
         for p, o in zip(params, self.offsets):
             n = p.numel()

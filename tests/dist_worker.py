@@ -1,0 +1,141 @@
+"""Worker launched by tests (torchrun or mp.spawn): data-parallel engine checks on gloo/CPU or NCCL+fused/GPU.
+
+    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29611 tests/dist_worker.py <case>
+"""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def setup():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    use_cuda = torch.cuda.is_available() and torch.cuda.device_count() >= world and os.environ.get("B200ML_TEST_CPU") != "1"
+    if use_cuda:
+        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
+        dist.init_process_group("nccl", device_id=torch.device("cuda", torch.cuda.current_device()))
+        dev = torch.device("cuda", torch.cuda.current_device())
+    else:
+        dist.init_process_group("gloo")
+        dev = torch.device("cpu")
+    return rank, world, dev
+
+
+def small_model(dev):
+    from b200ml.models.transformer import Transformer
+    torch.manual_seed(7)
+    m = Transformer(128, 256, 2, 0.0, 1, 32, 96, 80, 96).to(dev)
+    m.eval()  # SentenceEmbedding keeps the reference's hard-coded Dropout(0.1); eval() makes runs comparable
+    return m
+
+
+def train(model, engine, rank, world, dev, steps, global_batch, shard):
+    from b200ml.ops.loss import linear_cross_entropy
+    S = 32
+    g = torch.Generator().manual_seed(99)
+    losses = []
+    la = (torch.tril(torch.ones(S, S, device=dev)) == 0)[None, None]
+    for _ in range(steps):
+        src = torch.randint(1, 80, (global_batch, S), generator=g)
+        trg = torch.randint(1, 96, (global_batch, S), generator=g)
+        if shard:
+            per = global_batch // world
+            src, trg = src[rank * per:(rank + 1) * per], trg[rank * per:(rank + 1) * per]
+        src, trg = src.to(dev), trg.to(dev)
+        engine.begin_step()
+        h = model(src, trg, (src != 0)[:, None, None, :], la, la, return_hidden=True)
+        loss = linear_cross_entropy(h, model.linear.weight, model.linear.bias, trg, ignore_index=0)
+        loss.backward()
+        engine.finish_step()
+        losses.append(float(loss.detach()))
+    return losses
+
+
+def case_dp_equals_big_batch(rank, world, dev, mode):
+    """N ranks x batch B with gradient averaging == 1 rank x batch N*B (same data), and ranks stay bit-identical."""
+    from b200ml.parallel.engine import DataParallelEngine
+    model = small_model(dev)
+    ref_state = {k: v.clone() for k, v in model.state_dict().items()}
+    # SGD: the update is linear in the gradient, so summation-order noise stays at rounding level (Adam's first
+    # steps are sign-like and amplify it)
+    eng = DataParallelEngine(model, optimizer="sgd", lr=0.1, allreduce=mode, bucket_mb=0.05)
+    assert len(eng.buckets) > 2
+    train(model, eng, rank, world, dev, steps=4, global_batch=8, shard=True)
+    eng.weights_hash()
+    dp = eng.flat.flat_p.clone()
+    eng.close()
+    # single-rank oracle with the full batch (every rank computes it redundantly, no communication)
+    model2 = small_model(dev)
+    model2.load_state_dict(ref_state)
+    eng2 = DataParallelEngine(model2, optimizer="sgd", lr=0.1, sync_gradients=False)
+    train(model2, eng2, rank, world, dev, steps=4, global_batch=8, shard=False)
+    ref = eng2.flat.flat_p
+    err = (dp - ref).abs().max().item()
+    scale = ref.abs().max().item()
+    tol = 3e-2 if dev.type == "cuda" else 1e-4   # bf16 activations on GPU: per-rank rounding differs from full batch
+    assert err <= tol * scale, f"DP != big batch: err {err} scale {scale}"
+    print(f"[rank {rank}] dp_equals_big_batch ok mode={eng.allreduce_mode} err={err:.3e}")
+
+
+def case_fused_matches_nccl(rank, world, dev, mode):
+    """Fused P2P all-reduce+Adam gives the same weights as NCCL all-reduce + the flat optimizer kernel."""
+    from b200ml.parallel.engine import DataParallelEngine
+    outs = []
+    for m in ("fused", "nccl"):
+        model = small_model(dev)
+        eng = DataParallelEngine(model, optimizer="adam", lr=1e-3, allreduce=m, bucket_mb=0.05)
+        train(model, eng, rank, world, dev, steps=3, global_batch=8, shard=True)
+        eng.weights_hash()
+        outs.append(eng.flat.flat_p.clone())
+        w16 = eng.flat.flat_w16.float()
+        assert (w16 - eng.flat.flat_p).abs().max().item() <= 0.01 * eng.flat.flat_p.abs().max().item()
+        eng.close()
+    err = (outs[0] - outs[1]).abs().max().item()
+    assert err < 1e-5, f"fused vs nccl differ by {err}"
+    print(f"[rank {rank}] fused_matches_nccl ok err={err:.3e}")
+
+
+def case_allreduce_raw(rank, world, dev, mode):
+    """kind-0 reduce of random buffers vs torch.distributed.all_reduce, one-shot and two-shot sizes, SGD variant."""
+    from b200ml.parallel.comm import FusedAllReduce, SymmetricAllocator
+    from b200ml.parallel.flat import FlatParams
+    torch.manual_seed(rank)
+    ps = [torch.randn(1000, 333, device=dev).requires_grad_(), torch.randn(4099, device=dev).requires_grad_()]
+    alloc = SymmetricAllocator(dev)
+    flat = FlatParams(ps, allocator=alloc)
+    dist.broadcast(flat.flat_p, src=0)
+    flat.refresh_working_copy()
+    comm = FusedAllReduce(flat, None, None, None, allocator=alloc)
+    step = torch.ones(1, dtype=torch.int32, device=dev)
+    for algo in (1, 2):
+        flat.flat_g.copy_(torch.randn(flat.numel, device=dev))
+        expect = flat.flat_g.clone()
+        dist.all_reduce(expect)
+        expect /= world
+        out = torch.zeros_like(flat.flat_g)
+        comm.allreduce_update(0, flat.numel, 0, 0.0, (0.9, 0.999), 1e-8, 0.0, step, out=out, algo=1)
+        torch.cuda.synchronize()
+        assert (out - expect).abs().max().item() < 1e-5
+        p0 = flat.flat_p.clone()
+        comm.allreduce_update(0, flat.numel, 1, 0.5, (0.9, 0.999), 1e-8, 0.0, step, algo=algo)
+        torch.cuda.synchronize()
+        dist.barrier()
+        assert (flat.flat_p - (p0 - 0.5 * expect)).abs().max().item() < 1e-5, f"algo {algo}"
+        assert (flat.flat_w16.float() - flat.flat_p).abs().max().item() < 0.05
+    comm.close()
+    print(f"[rank {rank}] allreduce_raw ok")
+
+
+CASES = {"dp_equals_big_batch": case_dp_equals_big_batch, "fused_matches_nccl": case_fused_matches_nccl,
+         "allreduce_raw": case_allreduce_raw}
+
+if __name__ == "__main__":
+    rank, world, dev = setup()
+    mode = os.environ.get("B200ML_TEST_MODE", "auto")
+    for name in sys.argv[1:]:
+        CASES[name](rank, world, dev, mode)
+        dist.barrier()
+    dist.destroy_process_group()

@@ -1,0 +1,30 @@
+"""Multi-rank behaviour of the DP engine: gloo/CPU here (world 2), NCCL + fused P2P kernels on >= 2 GPUs."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _launch(cases, nproc, port, env_extra=None, timeout=600):
+    env = dict(os.environ)
+    env.update(env_extra or {})
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+           "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "dist_worker.py"), *cases]
+    r = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=timeout, cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-3000:] + "\n" + r.stderr[-3000:]
+    return r.stdout
+
+
+def test_dp_engine_gloo_world2():
+    out = _launch(["dp_equals_big_batch"], 2, 29611, {"B200ML_TEST_CPU": "1", "OMP_NUM_THREADS": "2"})
+    assert out.count("dp_equals_big_batch ok") == 2
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+def test_fused_allreduce_two_gpus():
+    out = _launch(["allreduce_raw", "fused_matches_nccl", "dp_equals_big_batch"], 2, 29612)
+    assert out.count("allreduce_raw ok") == 2 and out.count("fused_matches_nccl ok") == 2
