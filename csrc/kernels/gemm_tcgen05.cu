@@ -2,15 +2,18 @@
 //
 //   C[M,N] = epilogue( alpha * A[M,K] · B[N,K]^T )           bf16 operands, fp32 accumulation in TMEM
 //
-// One persistent CTA per SM, warp-specialised:
+// One persistent CTA per SM, warp-specialised (10 warps):
 //   warp 0      TMA producer   : cp.async.bulk.tensor (128B swizzle) into a kStages-deep smem ring
 //   warp 1      MMA issuer     : one thread issues tcgen05.mma.cta_group::1.kind::f16 (128 x BN x 16)
-//   warps 2..5  epilogue       : tcgen05.ld 32x32b from a double-buffered TMEM accumulator, fused math, stores
+//   warps 2..9  epilogue       : tcgen05.ld 32x32b from a double-buffered TMEM accumulator, fused math, stores;
+//                                two warps per TMEM lane quarter, each taking every other 32-column chunk
 // Either operand may be K-major (reduction dim contiguous) or MN-major (output dim contiguous), so the
 // forward (X·Wᵀ), dgrad (dY·W) and wgrad (dYᵀ·X) GEMMs of a Linear all run here without any transposes:
 //   fwd   : A = X  [M,K]  K-major      B = W  [N,K]   K-major
 //   dgrad : A = dY [M,N'] K-major      B = W  [N',K'] MN-major (output dim K' contiguous)
 //   wgrad : A = dY [M',N] MN-major     B = X  [M',K]  MN-major (reduction dim M' is the row index of both)
+// Split-K (wgrad of the small Linears: few output tiles, reduction over B·S = 6400 rows): each CTA reduces a K range
+// into an fp32 workspace slab, a second kernel sums the slabs in fixed order (deterministic, no atomics).
 // Reference ops covered: every nn.Linear in the reference (transformer.py:71-72,107-108,177-179,272;
 // distributed_multilayer_perceptron.py:47-53 at the 784-dim preset) with its ReLU / Sigmoid / Dropout neighbours.
 #include "../../include/b200ml.h"
@@ -24,7 +27,8 @@ namespace gemm {
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 64;  // 64 bf16 = 128 B = one swizzle row
 constexpr int UMMA_K = 16;
-constexpr int kNumThreads = 192;  // 6 warps
+constexpr int kEpiWarps = 8;
+constexpr int kNumThreads = 64 + kEpiWarps * 32;  // 10 warps
 
 struct Epilogue {
     void* C;
@@ -42,6 +46,7 @@ struct Epilogue {
     float dropout_p;
     const RngState* rng;
     uint32_t rng_site;
+    float* splitk_ws;        // != nullptr: write raw fp32 partial tiles to ws[split][M][N] instead of C
 };
 
 template <int BN>
@@ -60,10 +65,27 @@ __device__ __forceinline__ float apply_act(float v, int act) {
     return v;
 }
 
+struct TileCoord {
+    int m0, n0, kb0, kb1, split;
+};
+// tile -> (m fastest, then n, then k-split)
+__device__ __forceinline__ TileCoord tile_coord(int tile, int m_tiles, int n_tiles, int BN, int k_blocks, int splits) {
+    TileCoord t;
+    const int mn = m_tiles * n_tiles;
+    t.split = tile / mn;
+    const int r = tile - t.split * mn;
+    t.m0 = (r % m_tiles) * BLOCK_M;
+    t.n0 = (r / m_tiles) * BN;
+    const int per = (k_blocks + splits - 1) / splits;
+    t.kb0 = t.split * per;
+    t.kb1 = t.kb0 + per < k_blocks ? t.kb0 + per : k_blocks;
+    return t;
+}
+
 template <bool A_MN, bool B_MN, int BN>
 __global__ void __launch_bounds__(kNumThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, int M, int N,
-                 int K, Epilogue ep) {
+                 int K, int splits, Epilogue ep) {
     using C = Cfg<BN>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -88,7 +110,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&tmem_full[i], 1);
-            mbar_init(&tmem_empty[i], 4);  // one arrive per epilogue warp
+            mbar_init(&tmem_empty[i], kEpiWarps);  // one arrive per epilogue warp
         }
         fence_barrier_init();
     }
@@ -100,7 +122,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 
     const int m_tiles = (M + BLOCK_M - 1) / BLOCK_M;
     const int n_tiles = (N + BN - 1) / BN;
-    const int num_tiles = m_tiles * n_tiles;
+    const int num_tiles = m_tiles * n_tiles * splits;
     const int k_blocks = (K + BLOCK_K - 1) / BLOCK_K;
 
     if (warp == 0) {
@@ -109,27 +131,26 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             int stage = 0;
             uint32_t phase = 0;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                const int m0 = (tile % m_tiles) * BLOCK_M;
-                const int n0 = (tile / m_tiles) * BN;
-                for (int kb = 0; kb < k_blocks; ++kb) {
+                const TileCoord t = tile_coord(tile, m_tiles, n_tiles, BN, k_blocks, splits);
+                for (int kb = t.kb0; kb < t.kb1; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     uint8_t* sa = smem + stage * C::kStageBytes;
                     uint8_t* sb = sa + C::kABytes;
                     mbar_arrive_expect_tx(&full_bar[stage], C::kStageBytes);
                     const int k0 = kb * BLOCK_K;
                     if (!A_MN) {
-                        tma_load_2d(sa, &tmap_a, &full_bar[stage], k0, m0);
+                        tma_load_2d(sa, &tmap_a, &full_bar[stage], k0, t.m0);
                     } else {
 #pragma unroll
                         for (int j = 0; j < BLOCK_M / 64; ++j)
-                            tma_load_2d(sa + j * 8192, &tmap_a, &full_bar[stage], m0 + 64 * j, k0);
+                            tma_load_2d(sa + j * 8192, &tmap_a, &full_bar[stage], t.m0 + 64 * j, k0);
                     }
                     if (!B_MN) {
-                        tma_load_2d(sb, &tmap_b, &full_bar[stage], k0, n0);
+                        tma_load_2d(sb, &tmap_b, &full_bar[stage], k0, t.n0);
                     } else {
 #pragma unroll
                         for (int j = 0; j < BN / 64; ++j)
-                            tma_load_2d(sb + j * 8192, &tmap_b, &full_bar[stage], n0 + 64 * j, k0);
+                            tma_load_2d(sb + j * 8192, &tmap_b, &full_bar[stage], t.n0 + 64 * j, k0);
                     }
                     if (++stage == C::kStages) { stage = 0; phase ^= 1; }
                 }
@@ -144,10 +165,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             int acc = 0;
             uint32_t acc_phase = 0;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const TileCoord t = tile_coord(tile, m_tiles, n_tiles, BN, k_blocks, splits);
                 mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_base + acc * BN;
-                for (int kb = 0; kb < k_blocks; ++kb) {
+                for (int kb = t.kb0; kb < t.kb1; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
                     const uint32_t sa = smem_u32(smem + stage * C::kStageBytes);
@@ -158,7 +180,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                                                  : umma_smem_desc(sa + kk * (UMMA_K * 2), 16, 1024);
                         const uint64_t db = B_MN ? umma_smem_desc(sb + kk * (UMMA_K * 128), 8192, 1024)
                                                  : umma_smem_desc(sb + kk * (UMMA_K * 2), 16, 1024);
-                        umma_bf16(tmem_d, da, db, idesc, (kb | kk) != 0 ? 1u : 0u);
+                        umma_bf16(tmem_d, da, db, idesc, (kb > t.kb0 || kk != 0) ? 1u : 0u);
                     }
                     umma_commit(&empty_bar[stage]);  // smem slot reusable once these MMAs retire
                     if (++stage == C::kStages) { stage = 0; phase ^= 1; }
@@ -168,8 +190,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             }
         }
     } else {
-        // ===================== epilogue (warps 2..5) =====================
-        const int quarter = warp & 3;  // TMEM lane quarter this warp may access
+        // ===================== epilogue (warps 2..9) =====================
+        const int quarter = warp & 3;          // TMEM lane quarter this warp may access
+        const int half = (warp - 2) >> 2;      // which of the two warps sharing the quarter
         int acc = 0;
         uint32_t acc_phase = 0;
         const bool do_drop = ep.dropout_p > 0.f && ep.rng != nullptr;
@@ -182,89 +205,142 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             keep_scale = 1.f / (1.f - ep.dropout_p);
         }
         const float alpha = ep.alpha * (ep.alpha_dev ? __ldg(ep.alpha_dev) : 1.f);
-        const bool vec_ok_c = ep.c_fp32 ? ((ep.ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(ep.C) & 15) == 0)
-                                        : ((ep.ldc & 7) == 0 && (reinterpret_cast<uintptr_t>(ep.C) & 15) == 0);
+        const bool vec_c = ep.c_fp32 ? ((ep.ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(ep.C) & 15) == 0)
+                                     : ((ep.ldc & 7) == 0 && (reinterpret_cast<uintptr_t>(ep.C) & 15) == 0);
+        const bool vec_bias = ep.bias && (reinterpret_cast<uintptr_t>(ep.bias) & 15) == 0;
+        const bool vec_aux = ep.aux_mode && (ep.ldaux & 7) == 0 && (reinterpret_cast<uintptr_t>(ep.aux) & 15) == 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-            const int m0 = (tile % m_tiles) * BLOCK_M;
-            const int n0 = (tile / m_tiles) * BN;
+            const TileCoord t = tile_coord(tile, m_tiles, n_tiles, BN, k_blocks, splits);
             mbar_wait(&tmem_full[acc], acc_phase);
             tc_fence_after();
-            const int row = m0 + quarter * 32 + lane;
+            const int row = t.m0 + quarter * 32 + lane;
             const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BN;
 #pragma unroll 1
-            for (int c = 0; c < BN; c += 32) {
-                if (n0 + c >= N) break;  // warp-uniform
+            for (int c = half * 32; c < BN; c += 64) {
+                if (t.n0 + c >= N) break;  // warp-uniform
                 uint32_t r[32];
                 tmem_ld_32x32b_x32(taddr + c, r);
                 tmem_ld_wait();
-                if (row < M) {
-                    const int col0 = n0 + c;
-                    float v[32];
+                if (row >= M) continue;
+                const int col0 = t.n0 + c;
+                const bool full = col0 + 32 <= N;
+                if (ep.splitk_ws) {  // raw partial sums; the reduce kernel applies alpha and the store mode
+                    float* out = ep.splitk_ws + ((long long)t.split * M + row) * N + col0;
+                    if (full && (N & 3) == 0) {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * alpha;
-                    if (ep.bias) {
+                        for (int j = 0; j < 32; j += 4)
+                            *reinterpret_cast<uint4*>(out + j) = make_uint4(r[j], r[j + 1], r[j + 2], r[j + 3]);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (col0 + j < N) out[j] = __uint_as_float(r[j]);
+                    }
+                    continue;
+                }
+                float v[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * alpha;
+                if (ep.bias) {
+                    if (full && vec_bias) {
+                        const float4* b4 = reinterpret_cast<const float4*>(ep.bias + col0);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 b = __ldg(b4 + j);
+                            v[4 * j] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
+                        }
+                    } else {
 #pragma unroll
                         for (int j = 0; j < 32; ++j)
                             if (col0 + j < N) v[j] += __ldg(ep.bias + col0 + j);
                     }
-                    if (ep.act) {
+                }
+                if (ep.act) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], ep.act);
-                    }
-                    if (do_drop) {
-                        const uint64_t base = static_cast<uint64_t>(row) * static_cast<uint64_t>(N) + col0;
+                    for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], ep.act);
+                }
+                if (do_drop) {
+                    // element index row*N + col; N % 4 == 0 and col0 % 4 == 0 make each group of 4 share one hash
+                    const uint64_t base = static_cast<uint64_t>(row) * static_cast<uint64_t>(N) + col0;
+                    if ((N & 3) == 0) {
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4) {
+                            const uint64_t bits = rng_bits4(key, (base + j) >> 2);
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                const uint32_t rr = static_cast<uint32_t>(bits >> (q * 16)) & 0xFFFFu;
+                                v[j + q] = rr >= thr16 ? v[j + q] * keep_scale : 0.f;
+                            }
+                        }
+                    } else {
 #pragma unroll
                         for (int j = 0; j < 32; ++j)
                             v[j] = rng_keep(key, base + j, thr16) ? v[j] * keep_scale : 0.f;
                     }
-                    if (ep.aux_mode) {
-                        const __nv_bfloat16* ax = ep.aux + static_cast<long long>(row) * ep.ldaux + col0;
+                }
+                if (ep.aux_mode) {
+                    const __nv_bfloat16* ax = ep.aux + static_cast<long long>(row) * ep.ldaux + col0;
+                    float a[32];
+                    if (full && vec_aux) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            if (col0 + j < N) {
-                                const float a = __bfloat162float(ax[j]);
-                                if (ep.aux_mode == 1) v[j] = a > 0.f ? v[j] * ep.aux_scale : 0.f;
-                                else if (ep.aux_mode == 2) v[j] += a;
-                                else v[j] *= a * (1.f - a);
+                        for (int j = 0; j < 4; ++j) {
+                            const uint4 u = __ldg(reinterpret_cast<const uint4*>(ax) + j);
+                            const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                const float2 f = __bfloat1622float2(h[q]);
+                                a[8 * j + 2 * q] = f.x;
+                                a[8 * j + 2 * q + 1] = f.y;
                             }
-                        }
-                    }
-                    const bool full = col0 + 32 <= N;
-                    if (ep.c_fp32) {
-                        float* out = reinterpret_cast<float*>(ep.C) + static_cast<long long>(row) * ep.ldc + col0;
-                        if (full && vec_ok_c) {
-#pragma unroll
-                            for (int j = 0; j < 32; j += 4) {
-                                float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-                                if (ep.accumulate) {
-                                    const float4 old = *reinterpret_cast<const float4*>(out + j);
-                                    o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
-                                }
-                                *reinterpret_cast<float4*>(out + j) = o;
-                            }
-                        } else {
-#pragma unroll
-                            for (int j = 0; j < 32; ++j)
-                                if (col0 + j < N) out[j] = ep.accumulate ? out[j] + v[j] : v[j];
                         }
                     } else {
-                        __nv_bfloat16* out =
-                            reinterpret_cast<__nv_bfloat16*>(ep.C) + static_cast<long long>(row) * ep.ldc + col0;
-                        if (full && vec_ok_c) {
 #pragma unroll
-                            for (int j = 0; j < 32; j += 8) {
-                                uint4 o;
-                                o.x = pack_bf16x2(v[j], v[j + 1]);
-                                o.y = pack_bf16x2(v[j + 2], v[j + 3]);
-                                o.z = pack_bf16x2(v[j + 4], v[j + 5]);
-                                o.w = pack_bf16x2(v[j + 6], v[j + 7]);
-                                *reinterpret_cast<uint4*>(out + j) = o;
+                        for (int j = 0; j < 32; ++j) a[j] = col0 + j < N ? __bfloat162float(ax[j]) : 0.f;
+                    }
+                    if (ep.aux_mode == 1) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] = a[j] > 0.f ? v[j] * ep.aux_scale : 0.f;
+                    } else if (ep.aux_mode == 2) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] += a[j];
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] *= a[j] * (1.f - a[j]);
+                    }
+                }
+                if (ep.c_fp32) {
+                    float* out = reinterpret_cast<float*>(ep.C) + static_cast<long long>(row) * ep.ldc + col0;
+                    if (full && vec_c) {
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4) {
+                            float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                            if (ep.accumulate) {
+                                const float4 old = *reinterpret_cast<const float4*>(out + j);
+                                o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
                             }
-                        } else {
-#pragma unroll
-                            for (int j = 0; j < 32; ++j)
-                                if (col0 + j < N) out[j] = __float2bfloat16(v[j]);
+                            *reinterpret_cast<float4*>(out + j) = o;
                         }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (col0 + j < N) out[j] = ep.accumulate ? out[j] + v[j] : v[j];
+                    }
+                } else {
+                    __nv_bfloat16* out =
+                        reinterpret_cast<__nv_bfloat16*>(ep.C) + static_cast<long long>(row) * ep.ldc + col0;
+                    if (full && vec_c) {
+#pragma unroll
+                        for (int j = 0; j < 32; j += 8) {
+                            uint4 o;
+                            o.x = pack_bf16x2(v[j], v[j + 1]);
+                            o.y = pack_bf16x2(v[j + 2], v[j + 3]);
+                            o.z = pack_bf16x2(v[j + 4], v[j + 5]);
+                            o.w = pack_bf16x2(v[j + 6], v[j + 7]);
+                            *reinterpret_cast<uint4*>(out + j) = o;
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (col0 + j < N) out[j] = __float2bfloat16(v[j]);
                     }
                 }
             }
@@ -280,6 +356,26 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     if (warp == 2) {
         tc_fence_after();
         tmem_dealloc<C::kTmemCols>(tmem_base);
+    }
+}
+
+// Second stage of split-K: C = alpha * sum_s ws[s]  (fixed order), fp32 or bf16 store, optional accumulate.
+__global__ void __launch_bounds__(256)
+splitk_reduce_kernel(const float* __restrict__ ws, int splits, long long mn, int N, void* __restrict__ Cp,
+                     long long ldc, int c_fp32, int accumulate, float alpha, const float* __restrict__ alpha_dev) {
+    const float a = alpha * (alpha_dev ? *alpha_dev : 1.f);
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < mn; i += stride) {
+        float s = 0.f;
+        for (int k = 0; k < splits; ++k) s += ws[(long long)k * mn + i];
+        s *= a;
+        const long long row = i / N, col = i - row * N;
+        if (c_fp32) {
+            float* o = reinterpret_cast<float*>(Cp) + row * ldc + col;
+            *o = accumulate ? *o + s : s;
+        } else {
+            reinterpret_cast<__nv_bfloat16*>(Cp)[row * ldc + col] = __float2bfloat16(s);
+        }
     }
 }
 
@@ -336,7 +432,7 @@ gemm_simt_kernel(const __nv_bfloat16* __restrict__ A, long long lda, int a_mn, c
 }
 
 template <bool A_MN, bool B_MN, int BN>
-static int launch(const b200ml_gemm_args* g, const Epilogue& ep, cudaStream_t stream) {
+static int launch(const b200ml_gemm_args* g, Epilogue ep, int splits, cudaStream_t stream) {
     using C = Cfg<BN>;
     CUtensorMap ta, tb;
     {
@@ -361,19 +457,28 @@ static int launch(const b200ml_gemm_args* g, const Epilogue& ep, cudaStream_t st
         attr_set = true;
     }
     const int m_tiles = (g->M + BLOCK_M - 1) / BLOCK_M, n_tiles = (g->N + BN - 1) / BN;
-    const int tiles = m_tiles * n_tiles;
+    const int tiles = m_tiles * n_tiles * splits;
     const int grid = tiles < sm_count() ? tiles : sm_count();
-    kern<<<grid, kNumThreads, C::kSmemBytes, stream>>>(ta, tb, g->M, g->N, g->K, ep);
+    if (splits > 1) ep.splitk_ws = reinterpret_cast<float*>(g->workspace);
+    kern<<<grid, kNumThreads, C::kSmemBytes, stream>>>(ta, tb, g->M, g->N, g->K, splits, ep);
     B200_CHECK_CUDA(cudaGetLastError());
+    if (splits > 1) {
+        const long long mn = (long long)g->M * g->N;
+        long long blocks = (mn + 255) / 256;
+        if (blocks > 4LL * sm_count()) blocks = 4LL * sm_count();
+        splitk_reduce_kernel<<<(int)blocks, 256, 0, stream>>>(ep.splitk_ws, splits, mn, g->N, g->C, g->ldc, g->c_fp32,
+                                                              g->accumulate, g->alpha, g->alpha_dev);
+        B200_CHECK_CUDA(cudaGetLastError());
+    }
     return 0;
 }
 
 template <int BN>
-static int dispatch_major(const b200ml_gemm_args* g, const Epilogue& ep, cudaStream_t s) {
-    if (!g->a_mn_major && !g->b_mn_major) return launch<false, false, BN>(g, ep, s);
-    if (!g->a_mn_major && g->b_mn_major) return launch<false, true, BN>(g, ep, s);
-    if (g->a_mn_major && !g->b_mn_major) return launch<true, false, BN>(g, ep, s);
-    return launch<true, true, BN>(g, ep, s);
+static int dispatch_major(const b200ml_gemm_args* g, const Epilogue& ep, int splits, cudaStream_t s) {
+    if (!g->a_mn_major && !g->b_mn_major) return launch<false, false, BN>(g, ep, splits, s);
+    if (!g->a_mn_major && g->b_mn_major) return launch<false, true, BN>(g, ep, splits, s);
+    if (g->a_mn_major && !g->b_mn_major) return launch<true, false, BN>(g, ep, splits, s);
+    return launch<true, true, BN>(g, ep, splits, s);
 }
 
 }  // namespace gemm
@@ -391,6 +496,7 @@ extern "C" int b200ml_gemm_bf16(const b200ml_gemm_args* g, cudaStream_t stream) 
     ep.aux_mode = g->aux ? g->aux_mode : 0; ep.aux_scale = g->aux_scale; ep.alpha = g->alpha; ep.alpha_dev = g->alpha_dev;
     ep.accumulate = g->accumulate; ep.dropout_p = g->dropout_p;
     ep.rng = reinterpret_cast<const RngState*>(g->rng_state); ep.rng_site = g->rng_site;
+    ep.splitk_ws = nullptr;
 
     const bool tma_ok = (g->lda % 8 == 0) && (g->ldb % 8 == 0) && ((reinterpret_cast<uintptr_t>(g->A) & 15) == 0) &&
                         ((reinterpret_cast<uintptr_t>(g->B) & 15) == 0) && g->force_simt == 0;
@@ -402,20 +508,38 @@ extern "C" int b200ml_gemm_bf16(const b200ml_gemm_args* g, cudaStream_t stream) 
         B200_CHECK_CUDA(cudaGetLastError());
         return 0;
     }
-    // Tile-N choice: widest tile that still gives every SM work; narrow N uses the narrow tile.
+    const int sms = sm_count();
+    const long long m_tiles = (g->M + BLOCK_M - 1) / BLOCK_M;
+    const int k_blocks = (g->K + BLOCK_K - 1) / BLOCK_K;
+    // Tile-N: minimise waves x tile width (an MMA-bound tile costs ~BN); ties go to the wider tile (less A re-reading).
     int bn = g->tile_n;
     if (bn != 64 && bn != 128 && bn != 256) {
-        const long long m_tiles = (g->M + BLOCK_M - 1) / BLOCK_M;
-        const int sms = sm_count();
-        if (g->N <= 64) bn = 64;
-        else if (g->N <= 128) bn = 128;
-        else {
-            bn = 256;
-            if (m_tiles * ((g->N + 255) / 256) < 2LL * sms) bn = 128;
-            if (bn == 128 && m_tiles * ((g->N + 127) / 128) < sms) bn = 64;
+        long long best = -1;
+        const int cands[3] = {256, 128, 64};
+        for (int ci = 0; ci < 3; ++ci) {
+            const int c = cands[ci];
+            if (c > 64 && g->N <= c / 2) continue;  // do not pad a narrow N to a wide tile
+            const long long tiles = m_tiles * ((g->N + c - 1) / c);
+            const long long cost = ((tiles + sms - 1) / sms) * c;
+            if (best < 0 || cost < best) { best = cost; bn = c; }
         }
     }
-    if (bn == 256) return dispatch_major<256>(g, ep, stream);
-    if (bn == 128) return dispatch_major<128>(g, ep, stream);
-    return dispatch_major<64>(g, ep, stream);
+    // Split-K: only for the plain epilogue, when the output tiles cannot fill the machine and K is long.
+    int splits = 1;
+    const bool plain = !g->bias && !g->act && !ep.aux_mode && g->dropout_p <= 0.f;
+    const long long tiles_mn = m_tiles * ((g->N + bn - 1) / bn);
+    if (plain && g->workspace && g->split_k != 1 && k_blocks >= 8) {
+        int want = g->split_k > 1 ? g->split_k : (tiles_mn * 2 <= sms ? (int)(sms / tiles_mn) : 1);
+        if (want > k_blocks / 4) want = k_blocks / 4;
+        if (want > 32) want = 32;
+        while (want > 1 && (size_t)want * g->M * g->N * sizeof(float) > g->workspace_bytes) --want;
+        if (want > 1) {
+            const int per = (k_blocks + want - 1) / want;
+            want = (k_blocks + per - 1) / per;  // no empty splits
+            splits = want;
+        }
+    }
+    if (bn == 256) return dispatch_major<256>(g, ep, splits, stream);
+    if (bn == 128) return dispatch_major<128>(g, ep, splits, stream);
+    return dispatch_major<64>(g, ep, splits, stream);
 }

@@ -11,6 +11,7 @@
 #include "../../include/b200ml.h"
 #include "../common/host.h"
 #include "../common/ptx.cuh"
+#include "../common/reduce.cuh"
 #include "../common/rng.cuh"
 
 namespace b200 {
@@ -214,25 +215,6 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
     }
 }
 
-// Stage 2: fixed-order sum over the per-CTA partials.
-__global__ void ln_bwd_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dgamma,
-                                     float* __restrict__ dbeta, int nblocks, int d, int accumulate) {
-    const int col = blockIdx.x * blockDim.x + threadIdx.x;
-    if (col >= d) return;
-    float g = 0.f, b = 0.f;
-    for (int i = 0; i < nblocks; ++i) {
-        g += partial[((long long)i * 2) * d + col];
-        b += partial[((long long)i * 2 + 1) * d + col];
-    }
-    if (accumulate) {
-        dgamma[col] += g;
-        dbeta[col] += b;
-    } else {
-        dgamma[col] = g;
-        dbeta[col] = b;
-    }
-}
-
 static int bwd_grid(int rows) {
     int g = (rows + kWarpsPerBlock - 1) / kWarpsPerBlock;
     const int cap = 2 * sm_count();
@@ -280,9 +262,9 @@ int b200ml_layernorm_bwd(const void* dy, const void* z, const float* mean, const
         (const __nv_bfloat16*)dy, (const __nv_bfloat16*)z, mean, rstd, gamma, (__nv_bfloat16*)dz, (__nv_bfloat16*)da,
         (float*)scratch, rows, d, dropout_p, (const b200::RngState*)rng_state, rng_site);
     B200_CHECK_CUDA(cudaGetLastError());
-    ln_bwd_reduce_kernel<<<(d + 127) / 128, 128, 0, stream>>>((const float*)scratch, dgamma, dbeta, grid, d,
-                                                               accumulate);
-    B200_CHECK_CUDA(cudaGetLastError());
+    // stage 2: fixed-order sum over the per-CTA partial rows ([grid][2*d]: dgamma | dbeta)
+    B200_CHECK_CUDA(b200::launch_reduce_partials((const float*)scratch, grid, 2 * d, d, dgamma, dbeta, accumulate,
+                                                 stream));
     return 0;
 }
 

@@ -8,6 +8,7 @@
 #include "../common/host.h"
 #include "../common/optim.cuh"
 #include "../common/ptx.cuh"
+#include "../common/reduce.cuh"
 #include "../common/rng.cuh"
 
 namespace b200 {
@@ -51,25 +52,42 @@ __global__ void cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat1
         dst[i] = __float2bfloat16(src[i]);
 }
 
-// partial[split][col] = sum over this split's rows of x[row][col]
-__global__ void __launch_bounds__(128)
+// partial[split][col] = sum over this split's rows of x[row][col].  One CTA = 64 columns (a lane owns two adjacent
+// columns -> 128-byte coalesced row segments) x 8 warps striding over the split's rows.
+__global__ void __launch_bounds__(256)
 colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, int rows, int cols, int rows_per_split,
-                      float* __restrict__ partial) {
-    const int col = blockIdx.x * 128 + threadIdx.x;
-    if (col >= cols) return;
+                      int vec2_ok, float* __restrict__ partial) {
+    __shared__ float red[8][64];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int col = blockIdx.x * 64 + lane * 2;
     const int r0 = blockIdx.y * rows_per_split;
     const int r1 = min(rows, r0 + rows_per_split);
-    float s = 0.f;
-    for (int r = r0; r < r1; ++r) s += __bfloat162float(x[(long long)r * ldx + col]);
-    partial[(long long)blockIdx.y * cols + col] = s;
-}
-__global__ void colsum_reduce_kernel(const float* __restrict__ partial, int splits, int cols, float* __restrict__ out,
-                                     int accumulate) {
-    const int col = blockIdx.x * blockDim.x + threadIdx.x;
-    if (col >= cols) return;
-    float s = 0.f;
-    for (int i = 0; i < splits; ++i) s += partial[(long long)i * cols + col];
-    out[col] = accumulate ? out[col] + s : s;
+    float s0 = 0.f, s1 = 0.f;
+    if (vec2_ok && col + 1 < cols) {
+#pragma unroll 8
+        for (int r = r0 + warp; r < r1; r += 8) {
+            const float2 t = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(x + (long long)r * ldx + col));
+            s0 += t.x;
+            s1 += t.y;
+        }
+    } else {
+        for (int r = r0 + warp; r < r1; r += 8) {
+            if (col < cols) s0 += __bfloat162float(x[(long long)r * ldx + col]);
+            if (col + 1 < cols) s1 += __bfloat162float(x[(long long)r * ldx + col + 1]);
+        }
+    }
+    red[warp][lane * 2] = s0;
+    red[warp][lane * 2 + 1] = s1;
+    __syncthreads();
+    if (threadIdx.x < 64) {
+        const int c = blockIdx.x * 64 + threadIdx.x;
+        if (c < cols) {
+            float t = 0.f;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) t += red[w][threadIdx.x];
+            partial[(long long)blockIdx.y * cols + c] = t;
+        }
+    }
 }
 
 __global__ void counters_advance_kernel(RngState* rng, int* step) {
@@ -98,9 +116,9 @@ __global__ void argmax_accuracy_kernel(const T* __restrict__ logits, long long l
 }
 
 static int colsum_splits(int rows, int cols) {
-    const int col_blocks = (cols + 127) / 128;
-    int splits = (2 * sm_count() + col_blocks - 1) / col_blocks;
-    if (splits > rows) splits = rows;
+    const int col_blocks = (cols + 63) / 64;
+    int splits = (4 * sm_count() + col_blocks - 1) / col_blocks;
+    if (splits > (rows + 31) / 32) splits = (rows + 31) / 32;  // at least 32 rows per split
     if (splits < 1) splits = 1;
     if (splits > 256) splits = 256;
     return splits;
@@ -156,11 +174,13 @@ int b200ml_colsum_bf16(const void* x, long long ldx, int rows, int cols, float* 
     const int splits = colsum_splits(rows, cols);
     B200_REQUIRE(scratch_bytes >= (size_t)splits * cols * sizeof(float), "colsum: scratch too small");
     const int rps = (rows + splits - 1) / splits;
-    dim3 grid((cols + 127) / 128, splits);
-    colsum_partial_kernel<<<grid, 128, 0, stream>>>((const __nv_bfloat16*)x, ldx, rows, cols, rps, (float*)scratch);
+    dim3 grid((cols + 63) / 64, splits);
+    const int vec2_ok = (ldx % 2 == 0) && ((reinterpret_cast<uintptr_t>(x) & 3) == 0);
+    colsum_partial_kernel<<<grid, 256, 0, stream>>>((const __nv_bfloat16*)x, ldx, rows, cols, rps, vec2_ok,
+                                                    (float*)scratch);
     B200_CHECK_CUDA(cudaGetLastError());
-    colsum_reduce_kernel<<<(cols + 127) / 128, 128, 0, stream>>>((const float*)scratch, splits, cols, out, accumulate);
-    B200_CHECK_CUDA(cudaGetLastError());
+    B200_CHECK_CUDA(b200::launch_reduce_partials((const float*)scratch, splits, cols, cols, out, nullptr, accumulate,
+                                                 stream));
     return 0;
 }
 

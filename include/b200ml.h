@@ -50,6 +50,8 @@ typedef struct {
     float dropout_p; const void* rng_state; unsigned rng_site;
     int tile_n;      /* 0 = auto, or 64 / 128 / 256 */
     int force_simt;  /* testing: run the SIMT fallback */
+    int split_k;     /* 0 = auto, 1 = never, n > 1 = request n K-splits (plain epilogue only; needs workspace) */
+    void* workspace; size_t workspace_bytes; /* fp32 scratch for split-K partial tiles (optional) */
 } b200ml_gemm_args;
 int b200ml_gemm_bf16(const b200ml_gemm_args* args, cudaStream_t stream);
 

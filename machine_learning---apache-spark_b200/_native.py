@@ -39,6 +39,8 @@ class GemmArgs(C.Structure):
         ("dropout_p", C.c_float), ("rng_state", C.c_void_p), ("rng_site", C.c_uint),
         ("tile_n", C.c_int),
         ("force_simt", C.c_int),
+        ("split_k", C.c_int),
+        ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
     ]
 
 

@@ -118,3 +118,23 @@ def test_linear_chain_grads_match_torch():
         for g, r in zip(got, (xr, w1r, b1r, w2r, b2r)):
             rel = (g - r.grad).norm() / (r.grad.norm() + 1e-6)
             assert rel < 0.03, f"{act}: rel grad err {rel}"
+
+
+@pytest.mark.parametrize("split_k", [0, 4, 7])
+def test_gemm_split_k_wgrad_shape(split_k):
+    """wgrad of a small Linear: few output tiles, long reduction -> split-K slabs + deterministic reduce."""
+    from b200ml.ops.gemm import gemm
+    torch.manual_seed(4)
+    rows, N, K = 6400, 512, 512
+    dy = (torch.randn(rows, N, device="cuda") * 0.1).to(torch.bfloat16)
+    x = torch.randn(rows, K, device="cuda").to(torch.bfloat16)
+    ref = dy.float().cpu().t() @ x.float().cpu()
+    out = gemm(dy, x, a_mn=True, b_mn=True, out_dtype=torch.float32, split_k=split_k)
+    _check(out, ref, rows)
+    out2 = gemm(dy, x, a_mn=True, b_mn=True, out_dtype=torch.float32, split_k=split_k)
+    assert torch.equal(out, out2)                                  # deterministic
+    acc = torch.ones(N, K, device="cuda")
+    gemm(dy, x, a_mn=True, b_mn=True, out=acc, accumulate=True, split_k=split_k, alpha=0.5)
+    _check(acc, 0.5 * ref + 1, rows)
+    o16 = gemm(dy, x, a_mn=True, b_mn=True, split_k=split_k)
+    _check(o16, ref, rows, tol_scale=2.0)
