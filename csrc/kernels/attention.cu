@@ -85,9 +85,13 @@ struct SmemLayout {  // offsets from the 1024-aligned base; see kernels for alia
 
 // ------------------------------------------------------------------------------------------------ forward
 // smem: [Q 16K][K 32K][P-extra 16K][V 32K] ; P (4 x 16 KB tiles) aliases Q+K+extra once S has been computed.
-constexpr int kFwdSmem = 16384 + 32768 + 16384 + 32768 + 1024 + 128;
+// 8 warps: warps w and w+4 share TMEM lane quarter w%4 (rows 32(w%4)..+31 of the tile) and take alternate 32-column
+// chunks, so the softmax of one row is split over two threads (partials exchanged through smem).
+constexpr int kThreads = 256;
+constexpr int kXchg = 2 * 2 * TILE * 4;  // two float[2][128] exchange arrays
+constexpr int kFwdSmem = 16384 + 32768 + 16384 + 32768 + 1024 + 128 + kXchg;
 
-__global__ void __launch_bounds__(128, 2)
+__global__ void __launch_bounds__(kThreads, 2)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tk,
                 const __grid_constant__ CUtensorMap tv, Operand q, Operand k, Operand v, Operand o,
                 float* __restrict__ lse, int H, int Sq, int Skv, int skv_pad, float scale, int mask_mode) {
@@ -99,8 +103,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
     uint8_t* sP = smem;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 16384 + 32768 + 16384 + 32768);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
+    float* x_max = reinterpret_cast<float*>(bars + 8);   // [2][128]
+    float* x_sum = x_max + 2 * TILE;                     // [2][128]
 
-    const int tid = threadIdx.x, warp = tid >> 5;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int quarter = warp & 3, half = warp >> 2;
+    const int r = quarter * 32 + lane;  // row inside the tile == TMEM lane
     const int q0 = blockIdx.x * TILE, h = blockIdx.y, b = blockIdx.z;
     if (tid == 0) {
         mbar_init(&bars[0], 1);
@@ -127,44 +135,50 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
     mbar_wait(&bars[1], 0);
     tc_fence_after();
 
-    const int qrow = q0 + tid;
-    const uint32_t trow = tmem + (static_cast<uint32_t>(warp * 32) << 16);
+    const int qrow = q0 + r;
+    const uint32_t trow = tmem + (static_cast<uint32_t>(quarter * 32) << 16);
     const float sc = scale * kLog2e;
-    // pass 1: row maximum (log2 domain)
+    // pass 1: row maximum (log2 domain) over this thread's chunks
     float mx = -INFINITY;
-    for (int c = 0; c < skv_pad; c += 32) {
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(trow + c, r);
+    for (int c = half * 32; c < skv_pad; c += 64) {
+        uint32_t rg[32];
+        tmem_ld_32x32b_x32(trow + c, rg);
         tmem_ld_wait();
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
             const int kc = c + j;
-            const float x = __uint_as_float(r[j]) * sc + bias_of(mask_mode, qrow, kc) * kLog2e;
+            const float x = __uint_as_float(rg[j]) * sc + bias_of(mask_mode, qrow, kc) * kLog2e;
             if (kc < Skv) mx = fmaxf(mx, x);
         }
     }
+    x_max[half * TILE + r] = mx;
+    __syncthreads();
+    mx = fmaxf(mx, x_max[(half ^ 1) * TILE + r]);
     if (mx == -INFINITY) mx = 0.f;
-    // pass 2: probabilities -> smem (bf16), row sum.  All threads passed bars[1], so Q/K smem is dead: P may alias it.
+    // pass 2: probabilities -> smem (bf16), row sum.  The S MMA has completed (bars[1]), so Q/K smem is dead: P may
+    // alias it.
     float sum = 0.f;
-    for (int c = 0; c < skv_pad; c += 32) {
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(trow + c, r);
+    for (int c = half * 32; c < skv_pad; c += 64) {
+        uint32_t rg[32];
+        tmem_ld_32x32b_x32(trow + c, rg);
         tmem_ld_wait();
         float p[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
             const int kc = c + j;
-            const float x = __uint_as_float(r[j]) * sc + bias_of(mask_mode, qrow, kc) * kLog2e;
+            const float x = __uint_as_float(rg[j]) * sc + bias_of(mask_mode, qrow, kc) * kLog2e;
             float e = kc < Skv ? exp2f(x - mx) : 0.f;
             e = __bfloat162float(__float2bfloat16(e));  // the value the tensor core will see
             p[j] = e;
             sum += e;
         }
-        store_row_chunk32(sP, TILE * 128, tid, c, p);
+        store_row_chunk32(sP, TILE * 128, r, c, p);
     }
+    x_sum[half * TILE + r] = sum;
     tc_fence_before();
     fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the tensor core (async proxy)
     __syncthreads();
+    sum += x_sum[(half ^ 1) * TILE + r];
     if (tid == 0) {
         tc_fence_after();
         mma_tiles_x_mn(tmem, smem_u32(sP), smem_u32(sV), skv_pad);  // O overwrites the first 64 columns of S
@@ -175,25 +189,23 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
     const float inv = 1.f / sum;
     {
         __nv_bfloat16* out = o.ptr + ((long long)b * Sq + qrow) * o.ld + o.col0 + h * o.head_stride;
+        const int c = half * 32;  // each half writes 32 of the 64 output columns
+        uint32_t rg[32];
+        tmem_ld_32x32b_x32(trow + c, rg);  // .sync.aligned: executed by the whole warp, stores are predicated
+        tmem_ld_wait();
+        if (qrow < Sq) {
 #pragma unroll
-        for (int c = 0; c < HD; c += 32) {
-            uint32_t r[32];
-            tmem_ld_32x32b_x32(trow + c, r);  // .sync.aligned: executed by the whole warp, stores are predicated
-            tmem_ld_wait();
-            if (qrow < Sq) {
-#pragma unroll
-                for (int j = 0; j < 32; j += 8) {
-                    uint4 u;
-                    u.x = pack_bf16x2(__uint_as_float(r[j]) * inv, __uint_as_float(r[j + 1]) * inv);
-                    u.y = pack_bf16x2(__uint_as_float(r[j + 2]) * inv, __uint_as_float(r[j + 3]) * inv);
-                    u.z = pack_bf16x2(__uint_as_float(r[j + 4]) * inv, __uint_as_float(r[j + 5]) * inv);
-                    u.w = pack_bf16x2(__uint_as_float(r[j + 6]) * inv, __uint_as_float(r[j + 7]) * inv);
-                    *reinterpret_cast<uint4*>(out + c + j) = u;
-                }
+            for (int j = 0; j < 32; j += 8) {
+                uint4 u;
+                u.x = pack_bf16x2(__uint_as_float(rg[j]) * inv, __uint_as_float(rg[j + 1]) * inv);
+                u.y = pack_bf16x2(__uint_as_float(rg[j + 2]) * inv, __uint_as_float(rg[j + 3]) * inv);
+                u.z = pack_bf16x2(__uint_as_float(rg[j + 4]) * inv, __uint_as_float(rg[j + 5]) * inv);
+                u.w = pack_bf16x2(__uint_as_float(rg[j + 6]) * inv, __uint_as_float(rg[j + 7]) * inv);
+                *reinterpret_cast<uint4*>(out + c + j) = u;
             }
+            // natural-log LSE of the biased, scaled scores
+            if (half == 0) lse[((long long)b * H + h) * Sq + qrow] = (mx + log2f(sum)) / kLog2e;
         }
-        // natural-log LSE of the biased, scaled scores
-        if (qrow < Sq) lse[((long long)b * H + h) * Sq + qrow] = (mx + log2f(sum)) / kLog2e;
     }
     tc_fence_before();
     __syncthreads();
@@ -207,7 +219,37 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
 // smem: [Q 16K][dO 16K][V 32K][K 32K] ; dS (4 x 16 KB tiles) aliases Q+dO+V after S and dP are in TMEM.
 constexpr int kBwdQSmem = 16384 + 16384 + 32768 + 32768 + 1024 + 128;
 
-__global__ void __launch_bounds__(128, 1)
+__device__ __forceinline__ float row_dot64(const __nv_bfloat16* a, const __nv_bfloat16* b) {
+    const uint4* pa = reinterpret_cast<const uint4*>(a);
+    const uint4* pb = reinterpret_cast<const uint4*>(b);
+    float d = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const uint4 x = pa[i], y = pb[i];
+        const __nv_bfloat162* hx = reinterpret_cast<const __nv_bfloat162*>(&x);
+        const __nv_bfloat162* hy = reinterpret_cast<const __nv_bfloat162*>(&y);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float2 u = __bfloat1622float2(hx[j]), w = __bfloat1622float2(hy[j]);
+            d += u.x * w.x + u.y * w.y;
+        }
+    }
+    return d;
+}
+
+__device__ __forceinline__ void store_row32_bf16(__nv_bfloat16* out, const uint32_t (&r)[32]) {
+#pragma unroll
+    for (int j = 0; j < 32; j += 8) {
+        uint4 u;
+        u.x = pack_bf16x2(__uint_as_float(r[j]), __uint_as_float(r[j + 1]));
+        u.y = pack_bf16x2(__uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+        u.z = pack_bf16x2(__uint_as_float(r[j + 4]), __uint_as_float(r[j + 5]));
+        u.w = pack_bf16x2(__uint_as_float(r[j + 6]), __uint_as_float(r[j + 7]));
+        *reinterpret_cast<uint4*>(out + j) = u;
+    }
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
 attn_bwd_q_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tdo,
                   const __grid_constant__ CUtensorMap tk, const __grid_constant__ CUtensorMap tv, Operand q, Operand k,
                   Operand v, Operand o, Operand dout, Operand dq, const float* __restrict__ lse, int H, int Sq, int Skv,
@@ -222,7 +264,9 @@ attn_bwd_q_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 98304);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
 
-    const int tid = threadIdx.x, warp = tid >> 5;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int quarter = warp & 3, half = warp >> 2;
+    const int r = quarter * 32 + lane;
     const int q0 = blockIdx.x * TILE, h = blockIdx.y, b = blockIdx.z;
     if (tid == 0) {
         mbar_init(&bars[0], 1);
@@ -248,32 +292,19 @@ attn_bwd_q_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
         mma_k64(tmem + 256, smem_u32(sdO), smem_u32(sV), skv_pad);   // dP  -> cols [256, 512)
         umma_commit(&bars[1]);
     }
-    // D = rowsum(dO ∘ O) for this thread's query row, from global (two 128-byte rows)
-    const int qrow = q0 + tid;
+    // D = rowsum(dO ∘ O) for this thread's query row, from global (two 128-byte rows); both halves compute it
+    const int qrow = q0 + r;
     float D = 0.f, l2 = 0.f;
     if (qrow < Sq) {
-        const uint4* po = reinterpret_cast<const uint4*>(o.ptr + ((long long)b * Sq + qrow) * o.ld + o.col0 +
-                                                         h * o.head_stride);
-        const uint4* pd = reinterpret_cast<const uint4*>(dout.ptr + ((long long)b * Sq + qrow) * dout.ld + dout.col0 +
-                                                         h * dout.head_stride);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const uint4 a = po[i], c = pd[i];
-            const __nv_bfloat162* ha = reinterpret_cast<const __nv_bfloat162*>(&a);
-            const __nv_bfloat162* hc = reinterpret_cast<const __nv_bfloat162*>(&c);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const float2 x = __bfloat1622float2(ha[j]), y = __bfloat1622float2(hc[j]);
-                D += x.x * y.x + x.y * y.y;
-            }
-        }
+        D = row_dot64(o.ptr + ((long long)b * Sq + qrow) * o.ld + o.col0 + h * o.head_stride,
+                      dout.ptr + ((long long)b * Sq + qrow) * dout.ld + dout.col0 + h * dout.head_stride);
         l2 = lse[((long long)b * H + h) * Sq + qrow] * kLog2e;
     }
     mbar_wait(&bars[1], 0);
     tc_fence_after();
-    const uint32_t trow = tmem + (static_cast<uint32_t>(warp * 32) << 16);
+    const uint32_t trow = tmem + (static_cast<uint32_t>(quarter * 32) << 16);
     const float sc = scale * kLog2e;
-    for (int c = 0; c < skv_pad; c += 32) {
+    for (int c = half * 32; c < skv_pad; c += 64) {
         uint32_t rs[32], rp[32];
         tmem_ld_32x32b_x32(trow + c, rs);
         tmem_ld_32x32b_x32(trow + 256 + c, rp);
@@ -287,7 +318,7 @@ attn_bwd_q_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
             const float p = ok ? exp2f(x - l2) : 0.f;
             ds[j] = ok ? p * (__uint_as_float(rp[j]) - D) * scale : 0.f;
         }
-        store_row_chunk32(sdS, TILE * 128, tid, c, ds);
+        store_row_chunk32(sdS, TILE * 128, r, c, ds);
     }
     tc_fence_before();
     fence_proxy_async_smem();
@@ -299,23 +330,13 @@ attn_bwd_q_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
     }
     mbar_wait(&bars[2], 0);
     tc_fence_after();
-    __nv_bfloat16* out = dq.ptr + ((long long)b * Sq + qrow) * dq.ld + dq.col0 + h * dq.head_stride;
-#pragma unroll
-    for (int c = 0; c < HD; c += 32) {
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(trow + c, r);
+    {
+        __nv_bfloat16* out = dq.ptr + ((long long)b * Sq + qrow) * dq.ld + dq.col0 + h * dq.head_stride;
+        const int c = half * 32;
+        uint32_t rg[32];
+        tmem_ld_32x32b_x32(trow + c, rg);
         tmem_ld_wait();
-        if (qrow < Sq) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-                uint4 u;
-                u.x = pack_bf16x2(__uint_as_float(r[j]), __uint_as_float(r[j + 1]));
-                u.y = pack_bf16x2(__uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
-                u.z = pack_bf16x2(__uint_as_float(r[j + 4]), __uint_as_float(r[j + 5]));
-                u.w = pack_bf16x2(__uint_as_float(r[j + 6]), __uint_as_float(r[j + 7]));
-                *reinterpret_cast<uint4*>(out + c + j) = u;
-            }
-        }
+        if (qrow < Sq) store_row32_bf16(out + c, rg);
     }
     tc_fence_before();
     __syncthreads();
@@ -330,7 +351,7 @@ attn_bwd_q_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
 // dead by the time Pᵀ is written.
 constexpr int kBwdKVSmem = 65536 + 65536 + 32768 + 32768 + 2048 + 1024 + 128;
 
-__global__ void __launch_bounds__(128, 1)
+__global__ void __launch_bounds__(kThreads, 1)
 attn_bwd_kv_kernel(const __grid_constant__ CUtensorMap tk, const __grid_constant__ CUtensorMap tv,
                    const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tdo, Operand q, Operand k,
                    Operand v, Operand o, Operand dout, Operand dk, Operand dv, const float* __restrict__ lse, int H,
@@ -348,7 +369,9 @@ attn_bwd_kv_kernel(const __grid_constant__ CUtensorMap tk, const __grid_constant
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 196608 + 2048);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
 
-    const int tid = threadIdx.x, warp = tid >> 5;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int quarter = warp & 3, half = warp >> 2;
+    const int r = quarter * 32 + lane;
     const int k0 = blockIdx.x * TILE, h = blockIdx.y, b = blockIdx.z;
     if (tid == 0) {
         mbar_init(&bars[0], 1);
@@ -375,24 +398,12 @@ attn_bwd_kv_kernel(const __grid_constant__ CUtensorMap tk, const __grid_constant
         umma_commit(&bars[1]);
     }
     // per-query statistics for every query row of this (b, h): lse and D = rowsum(dO ∘ O)
-    for (int qr = tid; qr < MAXS; qr += 128) {
+    {
+        const int qr = tid;  // kThreads == MAXS
         float D = 0.f, l2 = 0.f;
         if (qr < Sq) {
-            const uint4* po = reinterpret_cast<const uint4*>(o.ptr + ((long long)b * Sq + qr) * o.ld + o.col0 +
-                                                             h * o.head_stride);
-            const uint4* pd = reinterpret_cast<const uint4*>(dout.ptr + ((long long)b * Sq + qr) * dout.ld +
-                                                             dout.col0 + h * dout.head_stride);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const uint4 a = po[i], c = pd[i];
-                const __nv_bfloat162* ha = reinterpret_cast<const __nv_bfloat162*>(&a);
-                const __nv_bfloat162* hc = reinterpret_cast<const __nv_bfloat162*>(&c);
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const float2 x = __bfloat1622float2(ha[j]), y = __bfloat1622float2(hc[j]);
-                    D += x.x * y.x + x.y * y.y;
-                }
-            }
+            D = row_dot64(o.ptr + ((long long)b * Sq + qr) * o.ld + o.col0 + h * o.head_stride,
+                          dout.ptr + ((long long)b * Sq + qr) * dout.ld + dout.col0 + h * dout.head_stride);
             l2 = lse[((long long)b * H + h) * Sq + qr] * kLog2e;
         }
         s_lse[qr] = l2;
@@ -401,10 +412,10 @@ attn_bwd_kv_kernel(const __grid_constant__ CUtensorMap tk, const __grid_constant
     __syncthreads();
     mbar_wait(&bars[1], 0);
     tc_fence_after();
-    const int krow = k0 + tid;
-    const uint32_t trow = tmem + (static_cast<uint32_t>(warp * 32) << 16);
+    const int krow = k0 + r;
+    const uint32_t trow = tmem + (static_cast<uint32_t>(quarter * 32) << 16);
     const float sc = scale * kLog2e;
-    for (int c = 0; c < sq_pad; c += 32) {
+    for (int c = half * 32; c < sq_pad; c += 64) {
         uint32_t rs[32], rp[32];
         tmem_ld_32x32b_x32(trow + c, rs);
         tmem_ld_32x32b_x32(trow + 256 + c, rp);
@@ -419,8 +430,8 @@ attn_bwd_kv_kernel(const __grid_constant__ CUtensorMap tk, const __grid_constant
             pt[j] = p;
             ds[j] = ok ? p * (__uint_as_float(rp[j]) - s_D[qc]) * scale : 0.f;
         }
-        store_row_chunk32(sPt, TILE * 128, tid, c, pt);
-        store_row_chunk32(sdSt, TILE * 128, tid, c, ds);
+        store_row_chunk32(sPt, TILE * 128, r, c, pt);
+        store_row_chunk32(sdSt, TILE * 128, r, c, ds);
     }
     tc_fence_before();
     fence_proxy_async_smem();
@@ -437,23 +448,11 @@ attn_bwd_kv_kernel(const __grid_constant__ CUtensorMap tk, const __grid_constant
     for (int which = 0; which < 2; ++which) {
         const Operand& dst = which == 0 ? dv : dk;
         __nv_bfloat16* out = dst.ptr + ((long long)b * Skv + krow) * dst.ld + dst.col0 + h * dst.head_stride;
-#pragma unroll
-        for (int c = 0; c < HD; c += 32) {
-            uint32_t r[32];
-            tmem_ld_32x32b_x32(trow + which * 64 + c, r);
-            tmem_ld_wait();
-            if (krow < Skv) {
-#pragma unroll
-                for (int j = 0; j < 32; j += 8) {
-                    uint4 u;
-                    u.x = pack_bf16x2(__uint_as_float(r[j]), __uint_as_float(r[j + 1]));
-                    u.y = pack_bf16x2(__uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
-                    u.z = pack_bf16x2(__uint_as_float(r[j + 4]), __uint_as_float(r[j + 5]));
-                    u.w = pack_bf16x2(__uint_as_float(r[j + 6]), __uint_as_float(r[j + 7]));
-                    *reinterpret_cast<uint4*>(out + c + j) = u;
-                }
-            }
-        }
+        const int c = half * 32;
+        uint32_t rg[32];
+        tmem_ld_32x32b_x32(trow + which * 64 + c, rg);
+        tmem_ld_wait();
+        if (krow < Skv) store_row32_bf16(out + c, rg);
     }
     tc_fence_before();
     __syncthreads();
@@ -511,7 +510,7 @@ int b200ml_attn_fwd(const b200ml_attn_operand* q, const b200ml_attn_operand* k, 
         attr = true;
     }
     dim3 grid((Sq + TILE - 1) / TILE, H, B);
-    attn_fwd_kernel<<<grid, 128, kFwdSmem, stream>>>(tq, tk, tv, dev_op(q), dev_op(k), dev_op(v), dev_op(out), lse, H,
+    attn_fwd_kernel<<<grid, kThreads, kFwdSmem, stream>>>(tq, tk, tv, dev_op(q), dev_op(k), dev_op(v), dev_op(out), lse, H,
                                                      Sq, Skv, skv_pad, scale, mask_mode);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
@@ -544,7 +543,7 @@ int b200ml_attn_bwd(const b200ml_attn_operand* q, const b200ml_attn_operand* k, 
             head_tmap(&tk, k, B, Skv, H, skv_pad) || head_tmap(&tv, v, B, Skv, H, skv_pad))
             return -1;
         dim3 grid((Sq + TILE - 1) / TILE, H, B);
-        attn_bwd_q_kernel<<<grid, 128, kBwdQSmem, stream>>>(tq, tdo, tk, tv, dev_op(q), dev_op(k), dev_op(v),
+        attn_bwd_q_kernel<<<grid, kThreads, kBwdQSmem, stream>>>(tq, tdo, tk, tv, dev_op(q), dev_op(k), dev_op(v),
                                                             dev_op(out), dev_op(dout), dev_op(dq), lse, H, Sq, Skv,
                                                             skv_pad, scale, mask_mode);
         B200_CHECK_CUDA(cudaGetLastError());
@@ -555,7 +554,7 @@ int b200ml_attn_bwd(const b200ml_attn_operand* q, const b200ml_attn_operand* k, 
             head_tmap(&tq, q, B, Sq, H, sq_pad) || head_tmap(&tdo, dout, B, Sq, H, sq_pad))
             return -1;
         dim3 grid((Skv + TILE - 1) / TILE, H, B);
-        attn_bwd_kv_kernel<<<grid, 128, kBwdKVSmem, stream>>>(tk, tv, tq, tdo, dev_op(q), dev_op(k), dev_op(v),
+        attn_bwd_kv_kernel<<<grid, kThreads, kBwdKVSmem, stream>>>(tk, tv, tq, tdo, dev_op(q), dev_op(k), dev_op(v),
                                                               dev_op(out), dev_op(dout), dev_op(dk), dev_op(dv), lse, H,
                                                               Sq, Skv, sq_pad, scale, mask_mode);
         B200_CHECK_CUDA(cudaGetLastError());
