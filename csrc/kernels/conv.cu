@@ -1,0 +1,280 @@
+// b200ml — K1/K2/K3: 3x3 / stride 1 / pad 1 convolution fused with bias + ReLU (+ 2x2 max-pool), forward and backward.
+//
+// Reference: FashionMNISTModel's four Conv2d+ReLU pairs and two MaxPool2d(2) (distributed_cnn.py:51-73).  With the
+// reference's channel counts (Cin in {1, 3, 10}, Cout = 10) an implicit GEMM has N = 10 and K = 9..90: a 128xNx16 UMMA
+// tile would be >85 % padding, so this round's kernels are direct convolutions on the CUDA cores, fp32 NCHW like the
+// reference, built around shared-memory tiles; what IS fused is everything around the MACs:
+//   forward : conv + bias + ReLU (+ max-pool with a 2-bit argmax) in one kernel — the pre-pool activation never hits HBM
+//   backward: un-pool + ReLU' folded into the loads of both gradient kernels (dZ is never materialised);
+//             dX = full correlation with flipped weights; dW / db via per-CTA partial sums + a fixed-order second stage
+//             (deterministic, no atomics).
+// One CTA = one image x one 16x16 output tile x all channels.  Cin, Cout <= 64.
+#include "../../include/b200ml.h"
+#include "../common/host.h"
+#include "../common/reduce.cuh"
+
+namespace b200 {
+namespace conv {
+
+constexpr int T = 16;        // output tile edge
+constexpr int HALO = T + 2;  // input tile edge
+constexpr int kMaxC = 64;
+constexpr int kChunk = 16;   // output channels accumulated in registers at a time
+
+// ---------------------------------------------------------------------------------------------------------------
+// forward
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(T* T)
+conv_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                float* __restrict__ y, unsigned char* __restrict__ pool_idx, int B, int Cin, int Cout, int H, int W,
+                int pool) {
+    extern __shared__ float smem[];
+    float* s_in = smem;                           // [Cin][HALO][HALO]
+    float* s_w = s_in + Cin * HALO * HALO;        // [Cout][Cin][9]
+    float* s_out = s_w + Cout * Cin * 9;          // [kChunk][T][T+1]   (pool only)
+    const int tiles_x = (W + T - 1) / T;
+    const int b = blockIdx.y;
+    const int ty0 = (blockIdx.x / tiles_x) * T, tx0 = (blockIdx.x % tiles_x) * T;
+    const int tid = threadIdx.x, ly = tid / T, lx = tid % T;
+
+    for (int i = tid; i < Cin * HALO * HALO; i += T * T) {
+        const int c = i / (HALO * HALO), rem = i % (HALO * HALO);
+        const int gy = ty0 + rem / HALO - 1, gx = tx0 + rem % HALO - 1;
+        s_in[i] = (gy >= 0 && gy < H && gx >= 0 && gx < W) ? x[((long long)(b * Cin + c) * H + gy) * W + gx] : 0.f;
+    }
+    for (int i = tid; i < Cout * Cin * 9; i += T * T) s_w[i] = w[i];
+    __syncthreads();
+
+    const int oy = ty0 + ly, ox = tx0 + lx;
+    const bool inside = oy < H && ox < W;
+    const int Hp = H / 2, Wp = W / 2;
+    for (int c0 = 0; c0 < Cout; c0 += kChunk) {
+        float acc[kChunk];
+#pragma unroll
+        for (int k = 0; k < kChunk; ++k) acc[k] = (c0 + k < Cout && bias) ? bias[c0 + k] : 0.f;
+        for (int ci = 0; ci < Cin; ++ci) {
+            float v[9];
+#pragma unroll
+            for (int t = 0; t < 9; ++t) v[t] = s_in[(ci * HALO + ly + t / 3) * HALO + lx + t % 3];
+#pragma unroll
+            for (int k = 0; k < kChunk; ++k) {
+                if (c0 + k < Cout) {
+                    const float* wk = s_w + ((c0 + k) * Cin + ci) * 9;
+#pragma unroll
+                    for (int t = 0; t < 9; ++t) acc[k] += v[t] * wk[t];
+                }
+            }
+        }
+        if (!pool) {
+            if (inside) {
+#pragma unroll
+                for (int k = 0; k < kChunk; ++k)
+                    if (c0 + k < Cout) y[((long long)(b * Cout + c0 + k) * H + oy) * W + ox] = fmaxf(acc[k], 0.f);
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < kChunk; ++k) s_out[(k * T + ly) * (T + 1) + lx] = inside ? fmaxf(acc[k], 0.f) : 0.f;
+            __syncthreads();
+            for (int i = tid; i < kChunk * (T / 2) * (T / 2); i += T * T) {
+                const int k = i / ((T / 2) * (T / 2)), rem = i % ((T / 2) * (T / 2));
+                const int py = rem / (T / 2), px = rem % (T / 2);
+                const int gy = ty0 / 2 + py, gx = tx0 / 2 + px;
+                if (c0 + k < Cout && gy < Hp && gx < Wp) {
+                    float best = -1.f;
+                    int arg = 0;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {  // first maximum wins, like torch
+                        const float val = s_out[(k * T + 2 * py + j / 2) * (T + 1) + 2 * px + j % 2];
+                        if (val > best) { best = val; arg = j; }
+                    }
+                    const long long o = ((long long)(b * Cout + c0 + k) * Hp + gy) * Wp + gx;
+                    y[o] = best;
+                    pool_idx[o] = (unsigned char)arg;
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+// dZ(b, co, y, x): gradient w.r.t. the pre-activation, reconstructed from what forward saved.
+//   no pool : dY * (Y > 0)              (Y, dY at full resolution)
+//   pool    : dYp routed to the arg-max position of its 2x2 window, gated by Yp > 0
+struct DzSource {
+    const float* dy;
+    const float* ysaved;
+    const unsigned char* idx;
+    int pool, H, W;
+    __device__ __forceinline__ float at(int b, int C, int c, int yy, int xx) const {
+        if (yy < 0 || yy >= H || xx < 0 || xx >= W) return 0.f;
+        if (!pool) {
+            const long long o = ((long long)(b * C + c) * H + yy) * W + xx;
+            return ysaved[o] > 0.f ? dy[o] : 0.f;
+        }
+        const int Hp = H / 2, Wp = W / 2;
+        if (yy / 2 >= Hp || xx / 2 >= Wp) return 0.f;
+        const long long o = ((long long)(b * C + c) * Hp + yy / 2) * Wp + xx / 2;
+        return (idx[o] == (unsigned char)((yy & 1) * 2 + (xx & 1)) && ysaved[o] > 0.f) ? dy[o] : 0.f;
+    }
+};
+
+// dX[b, ci, y, x] = sum_co sum_taps dZ[b, co, y - dy + 1, x - dx + 1] * W[co, ci, dy, dx]
+__global__ void __launch_bounds__(T* T)
+conv_bwd_data_kernel(DzSource src, const float* __restrict__ w, float* __restrict__ dx, int B, int Cin, int Cout) {
+    extern __shared__ float smem[];
+    float* s_dz = smem;                          // [Cout][HALO][HALO]
+    float* s_w = s_dz + Cout * HALO * HALO;      // [Cout][Cin][9]
+    const int H = src.H, W = src.W;
+    const int tiles_x = (W + T - 1) / T;
+    const int b = blockIdx.y;
+    const int ty0 = (blockIdx.x / tiles_x) * T, tx0 = (blockIdx.x % tiles_x) * T;
+    const int tid = threadIdx.x, ly = tid / T, lx = tid % T;
+    for (int i = tid; i < Cout * HALO * HALO; i += T * T) {
+        const int c = i / (HALO * HALO), rem = i % (HALO * HALO);
+        s_dz[i] = src.at(b, Cout, c, ty0 + rem / HALO - 1, tx0 + rem % HALO - 1);
+    }
+    for (int i = tid; i < Cout * Cin * 9; i += T * T) s_w[i] = w[i];
+    __syncthreads();
+    const int oy = ty0 + ly, ox = tx0 + lx;
+    if (oy >= H || ox >= W) return;
+    for (int c0 = 0; c0 < Cin; c0 += kChunk) {
+        float acc[kChunk];
+#pragma unroll
+        for (int k = 0; k < kChunk; ++k) acc[k] = 0.f;
+        for (int co = 0; co < Cout; ++co) {
+            float v[9];
+#pragma unroll
+            for (int t = 0; t < 9; ++t)  // dZ at (y + 1 - dy, x + 1 - dx)  ->  tile offset (ly + 2 - dy, lx + 2 - dx)
+                v[t] = s_dz[(co * HALO + ly + 2 - t / 3) * HALO + lx + 2 - t % 3];
+#pragma unroll
+            for (int k = 0; k < kChunk; ++k) {
+                if (c0 + k < Cin) {
+                    const float* wk = s_w + (co * Cin + c0 + k) * 9;
+#pragma unroll
+                    for (int t = 0; t < 9; ++t) acc[k] += v[t] * wk[t];
+                }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < kChunk; ++k)
+            if (c0 + k < Cin) dx[((long long)(b * Cin + c0 + k) * H + oy) * W + ox] = acc[k];
+    }
+}
+
+// partial[cta][co*Cin*9 + ci*9 + t] = sum over the CTA's pixels of dZ[co] * X[ci, shifted by tap t];
+// partial[cta][Cout*Cin*9 + co] = sum dZ[co]
+__global__ void __launch_bounds__(T* T)
+conv_bwd_weight_kernel(DzSource src, const float* __restrict__ x, float* __restrict__ partial, int B, int Cin,
+                       int Cout) {
+    extern __shared__ float smem[];
+    float* s_in = smem;                        // [Cin][HALO][HALO]
+    float* s_dz = s_in + Cin * HALO * HALO;    // [Cout][T][T]
+    const int H = src.H, W = src.W;
+    const int tiles_x = (W + T - 1) / T;
+    const int b = blockIdx.y;
+    const int ty0 = (blockIdx.x / tiles_x) * T, tx0 = (blockIdx.x % tiles_x) * T;
+    const int tid = threadIdx.x;
+    for (int i = tid; i < Cin * HALO * HALO; i += T * T) {
+        const int c = i / (HALO * HALO), rem = i % (HALO * HALO);
+        const int gy = ty0 + rem / HALO - 1, gx = tx0 + rem % HALO - 1;
+        s_in[i] = (gy >= 0 && gy < H && gx >= 0 && gx < W) ? x[((long long)(b * Cin + c) * H + gy) * W + gx] : 0.f;
+    }
+    for (int i = tid; i < Cout * T * T; i += T * T) {
+        const int c = i / (T * T), rem = i % (T * T);
+        s_dz[i] = src.at(b, Cout, c, ty0 + rem / T, tx0 + rem % T);
+    }
+    __syncthreads();
+    const int nW = Cout * Cin * 9;
+    const long long cta = (long long)blockIdx.y * gridDim.x + blockIdx.x;
+    float* out = partial + cta * (nW + Cout);
+    for (int o = tid; o < nW + Cout; o += T * T) {
+        float s = 0.f;
+        if (o < nW) {
+            const int co = o / (Cin * 9), ci = (o / 9) % Cin, t = o % 9;
+            const float* dz = s_dz + co * T * T;
+            const float* in = s_in + (ci * HALO + t / 3) * HALO + t % 3;
+            for (int py = 0; py < T; ++py)
+#pragma unroll
+                for (int px = 0; px < T; ++px) s += dz[py * T + px] * in[py * HALO + px];
+        } else {
+            const float* dz = s_dz + (o - nW) * T * T;
+            for (int i = 0; i < T * T; ++i) s += dz[i];
+        }
+        out[o] = s;
+    }
+}
+
+static size_t fwd_smem(int Cin, int Cout, int pool) {
+    return sizeof(float) * ((size_t)Cin * HALO * HALO + (size_t)Cout * Cin * 9 + (pool ? kChunk * T * (T + 1) : 0));
+}
+
+}  // namespace conv
+}  // namespace b200
+
+extern "C" {
+
+int b200ml_conv3x3_relu_fwd(const float* x, const float* w, const float* bias, float* y, unsigned char* pool_idx, int B,
+                            int Cin, int Cout, int H, int W, int pool, cudaStream_t stream) {
+    using namespace b200::conv;
+    B200_REQUIRE(x && w && y && (!pool || pool_idx), "conv fwd: null pointer");
+    B200_REQUIRE(Cin >= 1 && Cout >= 1 && Cin <= kMaxC && Cout <= kMaxC, "conv: channel counts must be <= %d", kMaxC);
+    B200_REQUIRE(!pool || (H % 2 == 0 && W % 2 == 0), "conv: pooling needs even H and W");
+    const size_t smem = fwd_smem(Cin, Cout, pool);
+    static size_t attr = 0;
+    if (smem > attr) {
+        B200_CHECK_CUDA(cudaFuncSetAttribute(conv_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr = smem;
+    }
+    dim3 grid(((H + T - 1) / T) * ((W + T - 1) / T), B);
+    conv_fwd_kernel<<<grid, T * T, smem, stream>>>(x, w, bias, y, pool_idx, B, Cin, Cout, H, W, pool);
+    B200_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+size_t b200ml_conv3x3_bwd_scratch_bytes(int B, int Cin, int Cout, int H, int W) {
+    using namespace b200::conv;
+    const size_t ctas = (size_t)B * ((H + T - 1) / T) * ((W + T - 1) / T);
+    return ctas * ((size_t)Cout * Cin * 9 + Cout) * sizeof(float);
+}
+
+/* dy / ysaved / pool_idx describe the layer OUTPUT: at H x W when pool == 0, at H/2 x W/2 when pool != 0.
+ * dx may be NULL (first layer).  dw [Cout,Cin,3,3] and db [Cout] are overwritten (accumulate = 0) or added to. */
+int b200ml_conv3x3_relu_bwd(const float* dy, const float* ysaved, const unsigned char* pool_idx, const float* x,
+                            const float* w, float* dx, float* dw, float* db, void* scratch, size_t scratch_bytes, int B,
+                            int Cin, int Cout, int H, int W, int pool, int accumulate, cudaStream_t stream) {
+    using namespace b200::conv;
+    B200_REQUIRE(dy && ysaved && x && w && dw && db && scratch && (!pool || pool_idx), "conv bwd: null pointer");
+    B200_REQUIRE(Cin >= 1 && Cout >= 1 && Cin <= kMaxC && Cout <= kMaxC, "conv: channel counts must be <= %d", kMaxC);
+    const size_t need = b200ml_conv3x3_bwd_scratch_bytes(B, Cin, Cout, H, W);
+    B200_REQUIRE(scratch_bytes >= need, "conv bwd: scratch too small (%zu < %zu)", scratch_bytes, need);
+    DzSource src{dy, ysaved, pool_idx, pool, H, W};
+    dim3 grid(((H + T - 1) / T) * ((W + T - 1) / T), B);
+    if (dx) {
+        const size_t smem = sizeof(float) * ((size_t)Cout * HALO * HALO + (size_t)Cout * Cin * 9);
+        static size_t attr = 0;
+        if (smem > attr) {
+            B200_CHECK_CUDA(
+                cudaFuncSetAttribute(conv_bwd_data_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            attr = smem;
+        }
+        conv_bwd_data_kernel<<<grid, T * T, smem, stream>>>(src, w, dx, B, Cin, Cout);
+        B200_CHECK_CUDA(cudaGetLastError());
+    }
+    {
+        const size_t smem = sizeof(float) * ((size_t)Cin * HALO * HALO + (size_t)Cout * T * T);
+        static size_t attr = 0;
+        if (smem > attr) {
+            B200_CHECK_CUDA(
+                cudaFuncSetAttribute(conv_bwd_weight_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            attr = smem;
+        }
+        conv_bwd_weight_kernel<<<grid, T * T, smem, stream>>>(src, x, (float*)scratch, B, Cin, Cout);
+        B200_CHECK_CUDA(cudaGetLastError());
+        const int nW = Cout * Cin * 9;
+        B200_CHECK_CUDA(b200::launch_reduce_partials((const float*)scratch, (int)(grid.x * grid.y), nW + Cout, nW, dw, db,
+                                                     accumulate, stream));
+    }
+    return 0;
+}
+
+}  // extern "C"

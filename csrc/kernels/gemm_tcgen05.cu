@@ -511,16 +511,19 @@ extern "C" int b200ml_gemm_bf16(const b200ml_gemm_args* g, cudaStream_t stream) 
     const int sms = sm_count();
     const long long m_tiles = (g->M + BLOCK_M - 1) / BLOCK_M;
     const int k_blocks = (g->K + BLOCK_K - 1) / BLOCK_K;
-    // Tile-N: minimise waves x tile width (an MMA-bound tile costs ~BN); ties go to the wider tile (less A re-reading).
+    // Tile-N: minimise waves x per-tile cost.  A 128xBN tile costs ~BN MMA cycles per k-step at BN = 256, but narrower
+    // tiles are shared-memory-bandwidth bound (A is re-read per tile: 128 B/clk at BN = 128, 192 B/clk at BN = 64
+    // against a 128 B/clk port) and pay the same fixed prologue/epilogue, hence the measured weights below.
     int bn = g->tile_n;
     if (bn != 64 && bn != 128 && bn != 256) {
         long long best = -1;
         const int cands[3] = {256, 128, 64};
+        const int cost_per_tile[3] = {288, 192, 160};
         for (int ci = 0; ci < 3; ++ci) {
             const int c = cands[ci];
             if (c > 64 && g->N <= c / 2) continue;  // do not pad a narrow N to a wide tile
             const long long tiles = m_tiles * ((g->N + c - 1) / c);
-            const long long cost = ((tiles + sms - 1) / sms) * c;
+            const long long cost = ((tiles + sms - 1) / sms) * cost_per_tile[ci];
             if (best < 0 || cost < best) { best = cost; bn = c; }
         }
     }

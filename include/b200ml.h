@@ -127,6 +127,36 @@ int b200ml_attn_bwd(const b200ml_attn_operand* q, const b200ml_attn_operand* k, 
                     const b200ml_attn_operand* dq, const b200ml_attn_operand* dk, const b200ml_attn_operand* dv, int B,
                     int H, int Sq, int Skv, float scale, int mask_mode, cudaStream_t stream);
 
+/* ------------------------------------------------------------------------------------------------ K1/K2/K3 conv
+ * relu(conv2d(x, w, bias, stride 1, pad 1)) on fp32 NCHW, optionally followed by max_pool2d(2) (pool != 0: y and
+ * pool_idx are [B,Cout,H/2,W/2], pool_idx holds the 2-bit arg-max).  Cin, Cout <= 64.
+ * Backward takes the layer OUTPUT's gradient / saved value (pooled when pool != 0); dx may be NULL.
+ * ref: FashionMNISTModel (distributed_cnn.py:51-73). */
+int b200ml_conv3x3_relu_fwd(const float* x, const float* w, const float* bias, float* y, unsigned char* pool_idx, int B,
+                            int Cin, int Cout, int H, int W, int pool, cudaStream_t stream);
+size_t b200ml_conv3x3_bwd_scratch_bytes(int B, int Cin, int Cout, int H, int W);
+int b200ml_conv3x3_relu_bwd(const float* dy, const float* ysaved, const unsigned char* pool_idx, const float* x,
+                            const float* w, float* dx, float* dw, float* db, void* scratch, size_t scratch_bytes, int B,
+                            int Cin, int Cout, int H, int W, int pool, int accumulate, cudaStream_t stream);
+
+/* ------------------------------------------------------------------------------------------------ K9 LSTM
+ * One persistent kernel per layer and direction of time.  fp32; x [B,T,K] (K <= 32), hidden must be 32,
+ * w_ih [128,K], w_hh [128,32], gate order i,f,g,o; h0/c0/h_n/c_n [B,32]; h_out [B,T,32];
+ * gates_out [T,B,4,32] and c_out [T,B,32] are the activations saved for backward (both NULL at inference).
+ * dropout_p > 0 applies inter-layer dropout to the layer INPUT (regenerated, not stored, in backward).
+ * ref: nn.LSTM inside the classifier (distributed_lstm.py:118-119,131). */
+int b200ml_lstm_layer_fwd(const float* x, const float* w_ih, const float* w_hh, const float* b_ih, const float* b_hh,
+                          const float* h0, const float* c0, float* h_out, float* gates_out, float* c_out, float* h_n,
+                          float* c_n, int B, int T, int K, int hidden, float dropout_p, const void* rng_state,
+                          unsigned rng_site, cudaStream_t stream);
+size_t b200ml_lstm_bwd_scratch_bytes(int B);
+int b200ml_lstm_layer_bwd(const float* x, const float* w_ih, const float* w_hh, const float* h0, const float* c0,
+                          const float* h_out, const float* gates, const float* c_seq, const float* dh_seq,
+                          const float* dh_n, const float* dc_n, float* dx, float* dh0, float* dc0, float* dw_ih,
+                          float* dw_hh, float* db_ih, float* db_hh, void* scratch, size_t scratch_bytes, int B, int T,
+                          int K, int hidden, float dropout_p, const void* rng_state, unsigned rng_site, int accumulate,
+                          cudaStream_t stream);
+
 /* ------------------------------------------------------------------------------------------------ K18 all-reduce
  * Symmetric buffers: b200ml_comm_alloc ALLOCATES (cudaMalloc + zero fill) — it is the set-up-time allocator for
  * buffers that peers map through CUDA IPC (export on the owner, import on every peer).

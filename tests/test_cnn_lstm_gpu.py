@@ -1,0 +1,118 @@
+"""conv3x3+ReLU(+pool) and persistent LSTM kernels vs PyTorch (fp32)."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel(a, b):
+    a, b = a.float().cpu(), b.float().cpu()
+    return ((a - b).norm() / (b.norm() + 1e-12)).item()
+
+
+@pytest.mark.parametrize("B,Cin,Cout,HW,pool", [(4, 1, 10, 28, False), (4, 10, 10, 28, True), (3, 3, 10, 32, False),
+                                                (2, 10, 10, 14, True), (2, 7, 13, 20, True), (1, 64, 64, 16, False)])
+def test_conv3x3_relu_pool(B, Cin, Cout, HW, pool):
+    from b200ml.ops.conv import conv3x3_relu
+    torch.manual_seed(0)
+    x = torch.randn(B, Cin, HW, HW, device="cuda", requires_grad=True)
+    w = (torch.randn(Cout, Cin, 3, 3, device="cuda") * 0.3).requires_grad_()
+    b = (torch.randn(Cout, device="cuda") * 0.1).requires_grad_()
+    y = conv3x3_relu(x, w, b, pool=pool)
+    g = torch.randn_like(y)
+    (y * g).sum().backward()
+    xr, wr, br = [t.detach().cpu().requires_grad_() for t in (x, w, b)]
+    yr = F.relu(F.conv2d(xr, wr, br, padding=1))
+    if pool:
+        yr = F.max_pool2d(yr, 2)
+    (yr * g.cpu()).sum().backward()
+    assert _rel(y, yr) < 1e-5
+    assert _rel(x.grad, xr.grad) < 1e-4
+    assert _rel(w.grad, wr.grad) < 1e-4
+    assert _rel(b.grad, br.grad) < 1e-4
+
+
+@pytest.mark.parametrize("B,T,E", [(32, 128, 32), (5, 17, 32), (40, 9, 20)])
+def test_lstm_matches_torch(B, T, E):
+    from b200ml.ops.lstm import lstm_forward
+    torch.manual_seed(0)
+    ref = torch.nn.LSTM(E, 32, num_layers=2, batch_first=True, dropout=0.0)
+    mine = [getattr(ref, n).detach().clone().cuda().requires_grad_() for n in ref._flat_weights_names]
+    x = torch.randn(B, T, E, device="cuda", requires_grad=True)
+    h0 = (torch.randn(2, B, 32, device="cuda") * 0.1).requires_grad_()
+    c0 = (torch.randn(2, B, 32, device="cuda") * 0.1).requires_grad_()
+    out, hn, cn = lstm_forward(x, h0, c0, mine, 2, 0.0, 11)
+    g = torch.randn_like(out)
+    ((out * g).sum() + hn.sum() * 0.5 + cn.sum() * 0.25).backward()
+    xr, h0r, c0r = [t.detach().cpu().requires_grad_() for t in (x, h0, c0)]
+    outr, (hnr, cnr) = ref(xr, (h0r, c0r))
+    ((outr * g.cpu()).sum() + hnr.sum() * 0.5 + cnr.sum() * 0.25).backward()
+    assert _rel(out, outr) < 1e-4
+    assert _rel(hn, hnr) < 1e-4 and _rel(cn, cnr) < 1e-4
+    assert _rel(x.grad, xr.grad) < 1e-3
+    assert _rel(h0.grad, h0r.grad) < 1e-3 and _rel(c0.grad, c0r.grad) < 1e-3
+    for m, n in zip(mine, ref._flat_weights_names):
+        assert _rel(m.grad, getattr(ref, n).grad) < 1e-3, n
+
+
+def test_lstm_dropout_mask_consistency():
+    """Inter-layer dropout: forward mask and backward mask must be the same draw (gradient check by finite difference
+    is impossible with fresh masks, so compare two identical backward passes and the zero pattern)."""
+    from b200ml.ops.lstm import lstm_forward
+    from b200ml.utils.rng import DeviceCounters
+    DeviceCounters.get("cuda").seed(3)
+    torch.manual_seed(0)
+    ref = torch.nn.LSTM(32, 32, num_layers=2, batch_first=True)
+    w = [getattr(ref, n).detach().clone().cuda().requires_grad_() for n in ref._flat_weights_names]
+    x = torch.randn(8, 12, 32, device="cuda", requires_grad=True)
+    z = torch.zeros(2, 8, 32, device="cuda")
+    outs = []
+    for _ in range(2):
+        for t in w + [x]:
+            t.grad = None
+        out, _, _ = lstm_forward(x, z, z, w, 2, 0.5, 21)
+        out.sum().backward()
+        outs.append((out.detach().clone(), x.grad.clone(), w[0].grad.clone()))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    out_nodrop, _, _ = lstm_forward(x, z, z, w, 2, 0.0, 21)
+    assert not torch.allclose(out_nodrop, outs[0][0])
+
+
+def test_models_on_gpu_match_reference_classes(reference_dir):
+    import ast
+    import os
+    from b200ml.models import FashionMNISTModel, LSTM, Multilayer_perceptor
+
+    def extract(path, cls):
+        src = open(os.path.join(reference_dir, path)).read()
+        tree = ast.parse(src)
+        node = next(n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == cls)
+        ns = {"torch": torch, "nn": torch.nn}
+        exec(compile(ast.Module([node], []), path, "exec"), ns)
+        return ns[cls]
+
+    torch.manual_seed(0)
+    RefCNN = extract("pytorch_cnn.py", "FashionMNISTModel")
+    r = RefCNN(1, 10, 10)
+    m = FashionMNISTModel(1, 10, 10).cuda()
+    m.load_state_dict(r.state_dict(), strict=True)
+    x = torch.randn(8, 1, 28, 28)
+    assert _rel(m(x.cuda()), r(x)) < 2e-2          # classifier Linear runs in bf16
+    RefMLP = extract("pytorch_multilayer_perceptron.py", "Multilayer_perceptor")
+    r = RefMLP()
+    m = Multilayer_perceptor().cuda()
+    m.load_state_dict(r.state_dict(), strict=True)
+    x = torch.randn(30, 4)
+    assert _rel(m(x.cuda()), r(x)) < 2e-2
+    RefLSTM = extract("pytorch_lstm.py", "LSTM")
+    ns_vocab = {"0": 0}
+    RefLSTM.__init__.__globals__["vocab"] = ns_vocab
+    r = RefLSTM(500, 32, 32, 4).eval()
+    m = LSTM(500, 32, 32, 4).cuda().eval()
+    m.load_state_dict(r.state_dict(), strict=True)
+    tok = torch.randint(0, 500, (6, 20))
+    z = torch.zeros(2, 6, 32)
+    o1, h1, c1 = r(tok, z, z)
+    o2, h2, c2 = m(tok.cuda(), z.cuda(), z.cuda())
+    assert _rel(o2, o1) < 3e-2 and _rel(h2, h1) < 2e-2
