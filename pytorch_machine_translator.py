@@ -1,0 +1,120 @@
+"""EN→DE seq2seq translator training — the reference's ``pytorch_machine_translator.py`` on b200ml.
+
+Same pipeline: tokenise → vocab (4 specials first, min_freq 1) → VocabTransform/AddToken/Truncate(199)/AddToken/
+ToTensor/PadTransform(200) → Transformer(d 512, ffn 1024, 8 heads, 1+1 layers, S 200) → CrossEntropy(ignore_index=0,
+'none') + masked mean → Adam(1e-3); loss every step, time every 100 batches.  Multi30k and the spacy models need a
+network, so the corpus is the synthetic Multi30k-shaped one (b200ml.data.synthetic) unless ``B200ML_MULTI30K`` points
+at a TSV of ``english<TAB>german`` lines.
+
+Beyond the reference (BASELINE.json config 4): run it under ``torchrun --nproc-per-node N`` (or with
+``--conf spark.executor.instances=N``) and it trains data-parallel in bf16 through the fused all-reduce engine.
+Quirks kept/fixed are listed in SURVEY §9 (Q11–Q16): masks behave as in the reference by default
+(``B200ML_MASK_MODE=causal`` for the intended ones); tensors are moved to the model's device; the 100-batch timer resets.
+"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+
+import torch  # noqa: E402
+from torch.utils.data import DataLoader  # noqa: E402
+from torch.utils.data.distributed import DistributedSampler  # noqa: E402
+
+from b200ml.data import text as T  # noqa: E402
+from b200ml.data.synthetic import SyntheticParallelCorpus  # noqa: E402
+from b200ml.ops.loss import linear_cross_entropy  # noqa: E402
+from b200ml.parallel.engine import DataParallelEngine  # noqa: E402
+from b200ml.utils import script as S  # noqa: E402
+from transformer import Transformer  # noqa: E402
+
+
+def load_corpus():
+    path = os.environ.get("B200ML_MULTI30K")
+    if path and os.path.isfile(path):
+        with open(path, encoding="utf-8") as fh:
+            return [tuple(line.rstrip("\n").split("\t")[:2]) for line in fh if "\t" in line]
+    return SyntheticParallelCorpus(n=320 if S.quick() else 2900, vocab_words=400 if S.quick() else 3000)
+
+
+def create_look_ahead_mask(size):
+    mask = torch.tril(torch.ones(size, size)) == 0
+    return mask.unsqueeze(0).unsqueeze(0)
+
+
+def main():
+    device, rank, world = S.init_worker()
+    train_dataset = load_corpus()
+    de_tokenizer = T.get_tokenizer("spacy", language="de_core_news_sm")
+    en_tokenizer = T.get_tokenizer("spacy", language="en_core_web_sm")
+    specials = ["<pad>", "<sos>", "<eos>", "<unk>"]
+    en_vocab = T.build_vocab_from_iterator((en_tokenizer(s) for s, _ in train_dataset), min_freq=1, specials=specials)
+    en_vocab.set_default_index(en_vocab["<unk>"])
+    de_vocab = T.build_vocab_from_iterator((de_tokenizer(t) for _, t in train_dataset), min_freq=1, specials=specials)
+    de_vocab.set_default_index(de_vocab["<unk>"])
+
+    def make_transform(vocab):
+        return T.Sequential(T.VocabTransform(vocab), T.AddToken(1, begin=True), T.Truncate(199), T.AddToken(2, begin=False),
+                            T.ToTensor(padding_value=0), T.PadTransform(max_length=200, pad_value=0))
+
+    en_text_transform, de_text_transform = make_transform(en_vocab), make_transform(de_vocab)
+
+    # hyper-parameters (pytorch_machine_translator.py:108-117)
+    d_model, ffn_hidden, num_heads, drop_prob, num_layers = 512, 1024, 8, 0.1, 1
+    max_sequence_length, batch_size = 200, 32
+    epochs = S.env_int("B200ML_EPOCHS", 1)
+    if S.quick():
+        d_model, ffn_hidden, num_heads = 128, 256, 2
+    model = Transformer(d_model, ffn_hidden, num_heads, drop_prob, num_layers, max_sequence_length, len(de_vocab),
+                        en_vocab, de_vocab, mask_mode=os.environ.get("B200ML_MASK_MODE", "reference")).to(device)
+    model.train()
+    engine = DataParallelEngine(model, optimizer="adam", lr=0.001)
+    sampler = DistributedSampler(train_dataset, num_replicas=world, rank=rank, shuffle=True) if world > 1 else None
+    loader = DataLoader(train_dataset, batch_size=batch_size, shuffle=sampler is None, sampler=sampler, drop_last=True)
+    max_steps = S.env_int("B200ML_STEPS", 6 if S.quick() else 10 ** 9)
+
+    total = S.DeviceTimer(device).start()
+    for epoch in range(epochs):
+        if sampler is not None:
+            sampler.set_epoch(epoch)
+        window = S.DeviceTimer(device).start()
+        for batch_idx, (src, trg) in enumerate(loader):
+            if batch_idx >= max_steps:
+                break
+            src_tensor = en_text_transform([en_tokenizer(s) for s in src]).to(device)
+            trg_tensor = de_text_transform([de_tokenizer(t) for t in trg]).to(device)
+            padding_mask_x = (src_tensor != en_vocab["<pad>"]).unsqueeze(1).unsqueeze(2)
+            look_ahead_mask = create_look_ahead_mask(trg_tensor.size(1)).to(device)
+            engine.zero_grad()
+            hidden = model(src_tensor, trg_tensor, padding_mask_x, look_ahead_mask, look_ahead_mask, return_hidden=True)
+            # head Linear + CrossEntropy(ignore_index=0) + masked mean as one fused node
+            loss = linear_cross_entropy(hidden, model.linear.weight, model.linear.bias, trg_tensor,
+                                        ignore_index=de_vocab["<pad>"])
+            loss.backward()
+            engine.step()
+            if rank == 0 and (batch_idx % 100 == 0 or S.quick()):
+                print(f"Iteration {batch_idx} : {loss.item()}")
+            if batch_idx > 1 and batch_idx % 100 == 0:
+                secs = S.max_over_ranks(window.elapsed(), device)
+                if rank == 0:
+                    print(f"Training time of 100 batches  is : {secs}")
+                    S.log_json(rank, step=batch_idx, loss=float(loss), samples_per_s=100 * batch_size * world / secs)
+                window = S.DeviceTimer(device).start()
+    secs = S.max_over_ranks(total.elapsed(), device)
+    if rank == 0:
+        print(f"Total Training time is : {secs}")
+    engine.close()
+    S.finish_worker()
+    return model
+
+
+if __name__ == "__main__":
+    n = 1
+    for i, a in enumerate(sys.argv):
+        if a == "--conf" and i + 1 < len(sys.argv) and sys.argv[i + 1].startswith("spark.executor.instances="):
+            n = int(sys.argv[i + 1].split("=", 1)[1])
+    if n > 1 and "RANK" not in os.environ:
+        from b200ml.spark import TorchDistributor
+
+        TorchDistributor(num_processes=n, local_mode=True, use_gpu=torch.cuda.is_available()).run(main)
+    else:
+        main()
