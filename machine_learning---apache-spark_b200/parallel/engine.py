@@ -53,6 +53,7 @@ class DataParallelEngine:
             sym_alloc = SymmetricAllocator(self.device)
         self.flat = FlatParams(params, allocator=sym_alloc)
         self.counters = DeviceCounters.get(self.device)
+        self.step_tensor = torch.zeros(1, dtype=torch.int32, device=self.device)  # this engine's optimizer step
         self.m = torch.zeros_like(self.flat.flat_p) if self.kind == 2 else None
         self.v = torch.zeros_like(self.flat.flat_p) if self.kind == 2 else None
         self.launches_in_capture = 0
@@ -123,16 +124,16 @@ class DataParallelEngine:
     def _reduce_and_update(self, start: int, n: int) -> None:
         if self.comm is not None:
             self.comm.allreduce_update(start, n, self.kind, self.lr, self.betas, self.eps, self.weight_decay,
-                                       self.counters.opt_step)
+                                       self.step_tensor)
             return
         g = self.flat.flat_g[start:start + n]
         dist.all_reduce(g, group=self.pg)
         optim_step_flat(self.flat.flat_p, self.flat.flat_g, self.m, self.v, self.flat.flat_w16, self.kind, self.lr,
-                        self.betas, self.eps, self.weight_decay, self.counters.opt_step, 1.0 / self.world, start, n)
+                        self.betas, self.eps, self.weight_decay, self.step_tensor, 1.0 / self.world, start, n)
 
     # ------------------------------------------------------------------------------------------------ step API
     def begin_step(self) -> None:
-        self.counters.advance(rng=True, opt=True)
+        self.counters.advance(rng=True, opt_tensor=self.step_tensor)
         self.flat.zero_accumulating_slots()
         for b, (_, _, ids) in enumerate(self.buckets):
             self._pending[b] = len(ids)
@@ -142,7 +143,7 @@ class DataParallelEngine:
         self._in_step = False
         if self.world == 1 or not self.sync_gradients:
             optim_step_flat(self.flat.flat_p, self.flat.flat_g, self.m, self.v, self.flat.flat_w16, self.kind, self.lr,
-                            self.betas, self.eps, self.weight_decay, self.counters.opt_step)
+                            self.betas, self.eps, self.weight_decay, self.step_tensor)
             return
         # parameters that never reported (unused in this forward) still need their bucket processed
         for b in range(len(self.buckets)):
@@ -187,10 +188,10 @@ class DataParallelEngine:
         return float(h.item())
 
     def state_dict(self):
-        return {"step": int(self.counters.opt_step.item()), "m": self.m, "v": self.v, "kind": self.kind}
+        return {"step": int(self.step_tensor.item()), "m": self.m, "v": self.v, "kind": self.kind}
 
     def load_state_dict(self, sd) -> None:
-        self.counters.opt_step.fill_(sd["step"])
+        self.step_tensor.fill_(sd["step"])
         if self.m is not None and sd.get("m") is not None:
             self.m.copy_(sd["m"])
             self.v.copy_(sd["v"])

@@ -42,17 +42,20 @@ class DeviceCounters:
         self.rng[0] = seed
         self.rng[1] = 0
 
-    def advance(self, rng: bool = True, opt: bool = False) -> None:
+    def advance(self, rng: bool = True, opt: bool = False, opt_tensor=None) -> None:
+        """One one-thread kernel bumps the dropout step and (optionally) an optimizer step counter — the caller's own
+        ``opt_tensor`` (each engine/optimizer counts its own steps) or the shared ``opt_step``."""
+        step = opt_tensor if opt_tensor is not None else (self.opt_step if opt else None)
         if self.device.type == "cuda":
             lib = _native.load()
             _native.check(lib.b200ml_counters_advance(self.rng.data_ptr() if rng else None,
-                                                      self.opt_step.data_ptr() if opt else None,
+                                                      None if step is None else step.data_ptr(),
                                                       _native.stream_ptr()), "counters_advance")
         else:
             if rng:
                 self.rng[1] += 1
-            if opt:
-                self.opt_step += 1
+            if step is not None:
+                step += 1
 
 
 def manual_seed(seed: int, device=None) -> None:

@@ -14,7 +14,7 @@ def _launch(cases, nproc, port, env_extra=None, timeout=600):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
            "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "dist_worker.py"), *cases]
     r = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=timeout, cwd=ROOT)
-    assert r.returncode == 0, r.stdout[-3000:] + "\n" + r.stderr[-3000:]
+    assert r.returncode == 0, r.stdout[-6000:] + "\n" + "\n".join(l for l in r.stderr.splitlines() if "rank" in l or "Error" in l)[-8000:]
     return r.stdout
 
 
