@@ -269,3 +269,79 @@ int b200ml_layernorm_bwd(const void* dy, const void* z, const float* mean, const
 }
 
 }  // extern "C"
+
+// ================================================================================================================
+// LayerNorm backward for callers that cannot hand us (or make) a device allocation.
+//
+// Who that is: a host application whose device memory is owned by its own pool and which forbids cudaMalloc/cudaFree
+// once it is initialised (an allocation may fail because the pool already holds the rest of HBM, and cudaMalloc /
+// cudaFree synchronise the whole device, which a latency-bound training or serving loop cannot afford); and plain
+// C / FFI callers that link this library without PyTorch and therefore have no caching allocator to carve a workspace
+// from.  For them the per-CTA partial sums of dgamma/dbeta live in a file-scope device array that is part of the
+// library image: every GPU that loads libb200ml.so carries these ~2.3 MiB until the process exits.
+//
+// Limits: d <= 1024 and d % 8 == 0 (as for b200ml_layernorm_bwd); at most kNoAllocMaxCtas CTAs are used, so on a GPU
+// with more than 148 SMs this variant launches a smaller grid than the scratch-taking one (same results up to fp32
+// summation order).  Anything else is refused with an error, nothing is truncated silently.
+// ================================================================================================================
+namespace b200 {
+namespace ln {
+
+constexpr int kNoAllocMaxCtas = 296;                 // 2 CTAs per SM on a 148-SM B200
+constexpr int kNoAllocMaxD = kMaxChunks * 256;       // 1024
+constexpr size_t kNoAllocFloats = (size_t)kNoAllocMaxCtas * 2 * kNoAllocMaxD;
+
+// In HOST code this name is only a handle for cudaGetSymbolAddress — it is not a device address and must never be
+// passed to a kernel directly.
+static __device__ __align__(256) float g_ln_bwd_scratch[kNoAllocFloats];
+
+// One look-up per device, made with that device current; later calls reuse the cached address.
+static int noalloc_scratch_ptr(float** out) {
+    static float* cache[64] = {nullptr};
+    int dev = -1;
+    B200_CHECK_CUDA(cudaGetDevice(&dev));
+    B200_REQUIRE(dev >= 0 && dev < 64, "layernorm_bwd_noalloc: device index %d out of range", dev);
+    if (cache[dev] == nullptr) {
+        float* p = nullptr;
+        B200_CHECK_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_ln_bwd_scratch));
+        B200_REQUIRE(p != nullptr, "layernorm_bwd_noalloc: cudaGetSymbolAddress returned a null address");
+        cache[dev] = p;
+    }
+    *out = cache[dev];
+    return 0;
+}
+
+}  // namespace ln
+}  // namespace b200
+
+extern "C" {
+
+size_t b200ml_layernorm_bwd_noalloc_max_d(void) { return b200::ln::kNoAllocMaxD; }
+
+int b200ml_layernorm_bwd_noalloc(const void* dy, const void* z, const float* mean, const float* rstd,
+                                 const float* gamma, void* dz, void* da, float* dgamma, float* dbeta, int rows, int d,
+                                 float dropout_p, const void* rng_state, unsigned rng_site, int accumulate,
+                                 cudaStream_t stream) {
+    using namespace b200::ln;
+    B200_REQUIRE(dy && z && mean && rstd && gamma && dz && dgamma && dbeta, "layernorm_bwd_noalloc: null pointer");
+    B200_REQUIRE(d > 0 && d % 8 == 0, "layernorm_bwd_noalloc: d=%d must be a positive multiple of 8", d);
+    B200_REQUIRE(d <= kNoAllocMaxD,
+                 "layernorm_bwd_noalloc: d=%d exceeds the built-in scratch (max d = %d); use b200ml_layernorm_bwd with "
+                 "caller-provided scratch instead",
+                 d, kNoAllocMaxD);
+    if (rows <= 0) return 0;
+    float* scratch = nullptr;
+    if (noalloc_scratch_ptr(&scratch)) return -1;  // first call on a device resolves the symbol address
+    int grid = bwd_grid(rows);
+    if (grid > kNoAllocMaxCtas) grid = kNoAllocMaxCtas;
+    // Stage 1 overwrites rows [0, grid) x 2d of the scratch completely, stage 2 reads exactly those: nothing in the
+    // shared array has to start at zero, whatever an earlier call left behind.
+    ln_bwd_kernel<<<grid, kWarpsPerBlock * 32, 0, stream>>>(
+        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)z, mean, rstd, gamma, (__nv_bfloat16*)dz, (__nv_bfloat16*)da,
+        scratch, rows, d, dropout_p, (const b200::RngState*)rng_state, rng_site);
+    B200_CHECK_CUDA(cudaGetLastError());
+    B200_CHECK_CUDA(b200::launch_reduce_partials(scratch, grid, 2 * d, d, dgamma, dbeta, accumulate, stream));
+    return 0;
+}
+
+}  // extern "C"

@@ -69,6 +69,25 @@ int b200ml_layernorm_bwd(const void* dy, const void* z, const float* mean, const
                          int d, float dropout_p, const void* rng_state, unsigned rng_site, int accumulate,
                          cudaStream_t stream);
 
+/* LayerNorm backward WITHOUT caller scratch and without any allocation (no counterpart in the reference; added for
+ * hosts that may not allocate).  Same arguments and results as b200ml_layernorm_bwd minus (scratch, scratch_bytes): the
+ * per-CTA partial sums of dgamma/dbeta go to a ~2.3 MiB array that is compiled into the library and lives on every GPU
+ * that loads it until the process exits.  Meant for callers whose device memory is owned by their own pool and who
+ * must not call cudaMalloc/cudaFree after start-up (the call can fail when the pool holds the rest of HBM, and it
+ * synchronises the device), and for C/FFI callers with no allocator to borrow a workspace from.
+ *   - limit: d % 8 == 0 and d <= b200ml_layernorm_bwd_noalloc_max_d() (1024); larger d is refused with an error —
+ *     use the scratch-taking entry point for it.  rows is unlimited.
+ *   - the FIRST call on each device looks up the array's device address (cudaGetSymbolAddress, with that device
+ *     current); make that first call before any stream capture begins.
+ *   - all calls on a device share the one array.  Nothing in it needs clearing between calls (each call overwrites
+ *     what it later reads), but two calls whose kernels overlap in time on the same GPU — different streams, or
+ *     several host threads — race on it: serialise them on one stream or with events. */
+size_t b200ml_layernorm_bwd_noalloc_max_d(void);
+int b200ml_layernorm_bwd_noalloc(const void* dy, const void* z, const float* mean, const float* rstd,
+                                 const float* gamma, void* dz, void* da, float* dgamma, float* dbeta, int rows, int d,
+                                 float dropout_p, const void* rng_state, unsigned rng_site, int accumulate,
+                                 cudaStream_t stream);
+
 /* ------------------------------------------------------------------------------------------------ K7/K8 embedding
  * ref: transformer.py:27-62 (sinusoidal PE + embedding + dropout), distributed_lstm.py:115,128 (padding_idx). */
 int b200ml_pe_table(float* pe, int S, int d, cudaStream_t stream);
