@@ -111,20 +111,12 @@ allreduce_update_kernel(Peers c, long long start, long long n, OptimSpec o, floa
     }
     const long long nvec = (hi - lo) / 4;
     const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
-        const long long e = start + lo + i * 4;
-        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-        for (int r = 0; r < kMaxRanks; ++r) {
-            if (r < c.world) {
-                const float4 t = ld_peer_f4(c.g[r] + e);
-                acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
-            }
-        }
+    // the update for one float4 of reduced gradient
+    auto apply = [&](long long e, float4 acc) {
         acc.x *= inv_world; acc.y *= inv_world; acc.z *= inv_world; acc.w *= inv_world;
         if (o.kind == 0) {
             *reinterpret_cast<float4*>(out + e) = acc;
-            continue;
+            return;
         }
         float4 p = *reinterpret_cast<const float4*>(c.p[c.rank] + e);
         if (o.kind == 2) {
@@ -155,6 +147,32 @@ allreduce_update_kernel(Peers c, long long start, long long n, OptimSpec o, floa
             *reinterpret_cast<float4*>(c.p[c.rank] + e) = p;
             *reinterpret_cast<uint2*>(c.w16[c.rank] + e) = pb;
         }
+    };
+    // Two float4 per thread per trip: all 2 x world peer loads are issued before the first add, which doubles the
+    // bytes in flight per CTA (NVLink round trips are ~2-3 us; bandwidth needs ~2 MB outstanding per GPU).
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += 2 * stride) {
+        const long long e0 = start + lo + i * 4;
+        const bool two = i + stride < nvec;
+        const long long e1 = two ? e0 + stride * 4 : e0;
+        float4 t0[kMaxRanks], t1[kMaxRanks];
+#pragma unroll
+        for (int r = 0; r < kMaxRanks; ++r)
+            if (r < c.world) t0[r] = ld_peer_f4(c.g[r] + e0);
+        if (two) {
+#pragma unroll
+            for (int r = 0; r < kMaxRanks; ++r)
+                if (r < c.world) t1[r] = ld_peer_f4(c.g[r] + e1);
+        }
+        float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
+#pragma unroll
+        for (int r = 0; r < kMaxRanks; ++r) {  // fixed rank order => the same bits on every rank
+            if (r < c.world) {
+                a0.x += t0[r].x; a0.y += t0[r].y; a0.z += t0[r].z; a0.w += t0[r].w;
+                if (two) { a1.x += t1[r].x; a1.y += t1[r].y; a1.z += t1[r].z; a1.w += t1[r].w; }
+            }
+        }
+        apply(e0, a0);
+        if (two) apply(e1, a1);
     }
     // peers are done reading my gradients and (two-shot) done writing my weights
     cross_barrier(c, 1, epoch);
@@ -221,8 +239,8 @@ int b200ml_allreduce_update(const b200ml_comm* cm, long long start, long long n,
     bool two = algo == 2 || (algo == 0 && kind != 0 && n * 4 > (512 << 10));
     if (kind == 0) two = false;
     const long long work = two ? (n / cm->world + 3) / 4 : n / 4;
-    long long blocks = (work + kThreads * 4 - 1) / (kThreads * 4);
-    int cap = max_blocks > 0 ? max_blocks : 64;
+    long long blocks = (work + kThreads * 8 - 1) / (kThreads * 8);
+    int cap = max_blocks > 0 ? max_blocks : 96;
     if (cap > kMaxBlocks) cap = kMaxBlocks;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
