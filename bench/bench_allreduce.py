@@ -57,13 +57,15 @@ def main():
         for label, algo in (("oneshot", 1), ("twoshot", 2)):
             if algo == 1 and nbytes > (64 << 20):
                 continue
-            for blocks in ((0,) if nbytes < (1 << 20) else (32, 64, 128)):
-                comm.max_blocks = blocks
-                ms = timed(lambda: comm.allreduce_update(0, flat.numel, 1, 1e-3, (0.9, 0.999), 1e-8, 0.0, step,
-                                                         algo=algo), iters, dev)
-                key = f"fused_{label}_sgd" + (f"_b{blocks}" if blocks else "")
-                row[key + "_us"] = ms * 1e3
-                row[key + "_busGBs"] = 2 * (world - 1) / world * nbytes / (ms * 1e-3) / 1e9
+            for blocks in ((0,) if nbytes < (1 << 20) else (64, 148, 296)):
+                for push in ((1,) if algo == 1 else (1, 0)):
+                    comm.max_blocks = blocks
+                    comm.push_master = push
+                    ms = timed(lambda: comm.allreduce_update(0, flat.numel, 1, 1e-3, (0.9, 0.999), 1e-8, 0.0, step,
+                                                             algo=algo), iters, dev)
+                    key = f"fused_{label}_sgd" + (f"_b{blocks}" if blocks else "") + ("" if push else "_bf16push")
+                    row[key + "_us"] = ms * 1e3
+                    row[key + "_busGBs"] = 2 * (world - 1) / world * nbytes / (ms * 1e-3) / 1e9
         g = flat.flat_g
 
         def nccl_step():

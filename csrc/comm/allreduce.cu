@@ -22,7 +22,7 @@ namespace b200 {
 namespace comm {
 
 constexpr int kMaxRanks = 8;
-constexpr int kMaxBlocks = 128;
+constexpr int kMaxBlocks = 320;
 constexpr int kThreads = 512;
 
 struct Peers {

@@ -180,7 +180,7 @@ int b200ml_lstm_layer_bwd(const float* x, const float* w_ih, const float* w_hh, 
  * Symmetric buffers: b200ml_comm_alloc ALLOCATES (cudaMalloc + zero fill) — it is the set-up-time allocator for
  * buffers that peers map through CUDA IPC (export on the owner, import on every peer).
  * b200ml_allreduce_update: grads[r] / params[r] / w16[r] / signals[r] are rank r's flat gradient (fp32), master
- * weight (fp32), working weight (bf16) and signal-pad (2*128*8 uint32, zero-initialised) buffers as mapped in THIS
+ * weight (fp32), working weight (bf16) and signal-pad (2*320*8 uint32, zero-initialised) buffers as mapped in THIS
  * process; counter is a local zero-initialised uint32[2].  Elements [start, start+n) are summed over ranks in rank
  * order, divided by world, and (kind 1 SGD / 2 Adam) applied to the weights; kind 0 writes the mean to `out`.
  * algo: 0 auto, 1 one-shot, 2 two-shot.  Every rank must issue the same sequence of calls.

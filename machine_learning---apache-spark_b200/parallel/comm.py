@@ -17,7 +17,7 @@ import torch.distributed as dist
 from .. import _native, _native_ext
 
 MAX_RANKS = 8
-SIGNAL_WORDS = 2 * 128 * 8
+SIGNAL_WORDS = 2 * 320 * 8
 
 
 class CommStruct(C.Structure):
@@ -134,6 +134,10 @@ class FusedAllReduce:
                     self._imported.append(p)
                     arr[r] = p
         self.cs.counter = self.counter.data_ptr()
+        # torch views of the peers' fp32 master buffers (for the on-demand pull of slices this rank does not own)
+        self.peer_p = [flat.flat_p if r == self.rank else
+                       torch.as_tensor(_RawCuda(self.cs.params[r], flat.numel, "<f4"), device=dev)
+                       for r in range(self.world)]
         self.push_master = 1
         self.max_blocks = 0
         torch.cuda.synchronize(dev)
@@ -147,6 +151,21 @@ class FusedAllReduce:
             None if self.m is None else self.m.data_ptr(), None if self.v is None else self.v.data_ptr(),
             None if out is None else out.data_ptr(), self.push_master, self.max_blocks, _native.stream_ptr()),
             "allreduce_update")
+
+    def pull_master(self, start: int, n: int) -> None:
+        """Refresh the fp32 master values of [start, start+n) that other ranks own (two-shot buckets updated with
+        push_master = 0).  One-sided peer reads; the owners' values are final once our own last all-reduce kernel
+        has returned, because that kernel's closing barrier waits for every rank's update."""
+        n4 = (n + 3) // 4 * 4
+        if n4 * 4 <= (512 << 10):
+            return  # such a bucket takes the one-shot path: every rank already updated all of it locally
+        per = ((n4 // 4 + self.world - 1) // self.world) * 4
+        for r in range(self.world):
+            if r == self.rank:
+                continue
+            lo, hi = per * r, min(per * r + per, n4)
+            if hi > lo:
+                self.flat.flat_p[start + lo:start + hi].copy_(self.peer_p[r][start + lo:start + hi])
 
     def close(self) -> None:
         lib = _native.load()

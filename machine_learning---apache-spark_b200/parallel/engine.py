@@ -12,6 +12,13 @@ Per step:
 
 Rank 0's parameters are broadcast at construction (what DDP's constructor does); gradients are
 averaged (sum / world), so N ranks with batch B reproduce one rank with batch N·B.
+
+Weight traffic in the fused two-shot path: the GEMMs and the embedding gather only ever read the bf16 working copy of
+nn.Linear / nn.Embedding weights (99.9 % of the Transformer's parameters), so for those buckets the slice owner pushes
+just the bf16 values to its peers (2 B/param instead of 6) and keeps the fp32 master of its slice to itself; the other
+ranks' fp32 views of such slices are refreshed on demand (``sync_master``: a one-sided pull over the same peer mappings,
+run automatically before ``state_dict()``).  Biases, LayerNorm / conv / LSTM parameters are read in fp32 by their
+kernels and stay fully replicated.
 """
 from __future__ import annotations
 
@@ -19,6 +26,7 @@ import os
 
 import torch
 import torch.distributed as dist
+from torch import nn
 
 from .. import _native
 from ..ops.optim import KINDS, optim_step_flat
@@ -29,7 +37,7 @@ from .flat import FlatParams
 class DataParallelEngine:
     def __init__(self, module, optimizer: str = "sgd", lr: float = 1e-2, betas=(0.9, 0.999), eps: float = 1e-8,
                  weight_decay: float = 0.0, allreduce: str = "auto", bucket_mb: float = 25.0,
-                 process_group=None, sync_gradients: bool = True):
+                 process_group=None, sync_gradients: bool = True, push_master="auto"):
         self.module = module
         self.kind = KINDS[optimizer]
         self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
@@ -51,7 +59,20 @@ class DataParallelEngine:
             from .comm import SymmetricAllocator
 
             sym_alloc = SymmetricAllocator(self.device)
-        self.flat = FlatParams(params, allocator=sym_alloc)
+
+        # parameters whose kernels read only the bf16 working copy (nn.Linear / nn.Embedding weights) go first
+        if push_master == "auto":
+            push_master = os.environ.get("B200ML_PUSH_MASTER", "auto")
+        self._bf16_push = mode == "fused" and str(push_master) in ("auto", "0", "False", "false")
+        w16_only = set()
+        if self._bf16_push:
+            for m in module.modules():
+                if isinstance(m, (nn.Linear, nn.Embedding)):
+                    w16_only.add(id(m.weight))
+        order = ([i for i, p in enumerate(params) if id(p) in w16_only] +
+                 [i for i, p in enumerate(params) if id(p) not in w16_only])
+        n_w16 = sum(1 for p in params if id(p) in w16_only)
+        self.flat = FlatParams(params, allocator=sym_alloc, order=order)
         self.counters = DeviceCounters.get(self.device)
         self.step_tensor = torch.zeros(1, dtype=torch.int32, device=self.device)  # this engine's optimizer step
         self.m = torch.zeros_like(self.flat.flat_p) if self.kind == 2 else None
@@ -63,23 +84,26 @@ class DataParallelEngine:
             dist.broadcast(self.flat.flat_p, src=0, group=self.pg)
             self.flat.refresh_working_copy()
 
-        # buckets: contiguous ranges of the flat buffer, in registration order; gradients become ready roughly in
-        # reverse order, so the LAST bucket completes first.
+        # buckets: contiguous ranges of the flat buffer; gradients become ready roughly in reverse registration
+        # order, so within each group the LAST bucket completes first.  (start, numel, [param indices], bf16_push)
         cap = max(int(bucket_mb * (1 << 20) / 4), 1)
-        self.buckets = []  # (start, numel, [param indices])
-        start, cur, idxs = 0, 0, []
-        for i, p in enumerate(self.flat.params):
-            o, n = self.flat.slot(i)
-            end = (self.flat.offsets[i + 1] if i + 1 < len(self.flat.params) else self.flat.numel)
-            idxs.append(i)
-            cur = end - start
-            if cur >= cap:
-                self.buckets.append((start, cur, idxs))
-                start, idxs = end, []
-        if idxs:
-            self.buckets.append((start, self.flat.numel - start, idxs))
+        self.buckets = []
+        n_params = len(self.flat.params)
+        for lo_i, hi_i, bf16_push in ((0, n_w16, True), (n_w16, n_params, False)):
+            if hi_i <= lo_i:
+                continue
+            group_end = self.flat.offsets[hi_i] if hi_i < n_params else self.flat.numel
+            start, idxs = self.flat.offsets[lo_i], []
+            for i in range(lo_i, hi_i):
+                end = self.flat.offsets[i + 1] if i + 1 < hi_i else group_end
+                idxs.append(i)
+                if end - start >= cap:
+                    self.buckets.append((start, end - start, idxs, bf16_push))
+                    start, idxs = end, []
+            if idxs:
+                self.buckets.append((start, group_end - start, idxs, bf16_push))
         self._bucket_of = {}
-        for b, (_, _, ids) in enumerate(self.buckets):
+        for b, (_, _, ids, _) in enumerate(self.buckets):
             for i in ids:
                 self._bucket_of[i] = b
         self._pending = [0] * len(self.buckets)
@@ -89,12 +113,16 @@ class DataParallelEngine:
         self.allreduce_mode = mode
         self.comm = None
         self.comm_stream = None
+        self._master_stale = False
         if self.world > 1 and self.sync_gradients:
             if mode == "fused":
                 from .comm import FusedAllReduce
 
                 self.comm = FusedAllReduce(self.flat, self.m, self.v, self.pg, allocator=sym_alloc)
-                self.allreduce_mode = "fused:" + self.comm.transport
+                self.allreduce_mode = "fused:" + self.comm.transport + (":bf16push" if self._bf16_push else "")
+                if self._bf16_push:
+                    # model.state_dict() on any rank first pulls the fp32 slices it does not own
+                    module.register_state_dict_pre_hook(lambda *a, **k: self.sync_master())
             if self.device.type == "cuda":
                 self.comm_stream = torch.cuda.Stream(device=self.device, priority=-1)
         self._in_step = False
@@ -113,16 +141,17 @@ class DataParallelEngine:
     def _bucket_ready(self, b: int) -> None:
         if self.world == 1 or not self.sync_gradients:
             return  # single fused optimizer launch in finish_step
-        start, n, _ = self.buckets[b]
         if self.comm_stream is not None:
             self.comm_stream.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(self.comm_stream):
-                self._reduce_and_update(start, n)
+                self._reduce_and_update(b)
         else:
-            self._reduce_and_update(start, n)
+            self._reduce_and_update(b)
 
-    def _reduce_and_update(self, start: int, n: int) -> None:
+    def _reduce_and_update(self, b: int) -> None:
+        start, n, _, bf16_push = self.buckets[b]
         if self.comm is not None:
+            self.comm.push_master = 0 if (bf16_push and self._bf16_push) else 1
             self.comm.allreduce_update(start, n, self.kind, self.lr, self.betas, self.eps, self.weight_decay,
                                        self.step_tensor)
             return
@@ -135,7 +164,7 @@ class DataParallelEngine:
     def begin_step(self) -> None:
         self.counters.advance(rng=True, opt_tensor=self.step_tensor)
         self.flat.zero_accumulating_slots()
-        for b, (_, _, ids) in enumerate(self.buckets):
+        for b, (_, _, ids, _) in enumerate(self.buckets):
             self._pending[b] = len(ids)
         self._in_step = True
 
@@ -152,6 +181,7 @@ class DataParallelEngine:
                 self._bucket_ready(b)
         if self.comm_stream is not None:
             torch.cuda.current_stream().wait_stream(self.comm_stream)
+        self._master_stale = self._bf16_push and self.comm is not None
 
     # torch.optim-flavoured aliases so the entry scripts read like the reference loops
     def zero_grad(self, set_to_none: bool = True) -> None:
@@ -176,8 +206,23 @@ class DataParallelEngine:
         return g
 
     # ------------------------------------------------------------------------------------------------ utilities
+    def sync_master(self) -> None:
+        """Make every fp32 master parameter current on THIS rank (no-op unless the bf16-only push is active).
+        One-sided: pulls the slices other ranks own through the peer mappings; safe to call on a single rank."""
+        if self.comm is None or not self._bf16_push:
+            return
+        if not self._master_stale and self._graph is None:
+            return
+        torch.cuda.current_stream().synchronize()
+        for start, n, _, bf16_push in self.buckets:
+            if bf16_push:
+                self.comm.pull_master(start, n)
+        torch.cuda.current_stream().synchronize()
+        self._master_stale = False
+
     def weights_hash(self) -> float:
         """Cheap rank-divergence check: every rank must hold bit-identical master weights."""
+        self.sync_master()
         h = self.flat.flat_p.double().sum()
         if self.world > 1:
             lo, hi = h.clone(), h.clone()
@@ -198,6 +243,7 @@ class DataParallelEngine:
 
     def close(self) -> None:
         if self.comm is not None:
+            self.sync_master()
             self.comm.close()
             self.comm = None
         for p in self.flat.params:
