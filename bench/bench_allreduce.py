@@ -66,6 +66,27 @@ def main():
                     key = f"fused_{label}_sgd" + (f"_b{blocks}" if blocks else "") + ("" if push else "_bf16push")
                     row[key + "_us"] = ms * 1e3
                     row[key + "_busGBs"] = 2 * (world - 1) / world * nbytes / (ms * 1e-3) / 1e9
+        comm.close()
+        # NVLS variant (needs torch symmetric memory + multicast support)
+        try:
+            from b200ml.parallel.comm import SymmMemAllocator, make_allocator
+            alloc2 = make_allocator(dev)
+            if isinstance(alloc2, SymmMemAllocator) and nbytes >= (1 << 20):
+                p2 = torch.randn(n, device=dev).requires_grad_()
+                flat2 = FlatParams([p2], allocator=alloc2)
+                comm2 = FusedAllReduce(flat2, None, None, None, allocator=alloc2)
+                flat2.flat_g.normal_()
+                for blocks in (64, 148, 296):
+                    for push in (1, 0):
+                        comm2.max_blocks, comm2.push_master = blocks, push
+                        ms = timed(lambda: comm2.allreduce_update(0, flat2.numel, 1, 1e-3, (0.9, 0.999), 1e-8, 0.0, step,
+                                                                  algo=3), iters, dev)
+                        key = f"fused_nvls_sgd_b{blocks}" + ("" if push else "_bf16push")
+                        row[key + "_us"] = ms * 1e3
+                        row[key + "_busGBs"] = 2 * (world - 1) / world * nbytes / (ms * 1e-3) / 1e9
+                comm2.close()
+        except Exception as e:  # noqa: BLE001
+            row["nvls_error"] = str(e)[:200]
         g = flat.flat_g
 
         def nccl_step():
@@ -78,7 +99,6 @@ def main():
         ms = timed(lambda: dist.all_reduce(g), iters, dev)
         row["nccl_only_us"] = ms * 1e3
         row["nccl_only_busGBs"] = 2 * (world - 1) / world * nbytes / (ms * 1e-3) / 1e9
-        comm.close()
         if rank == 0:
             print(json.dumps(row), flush=True)
         rows.append(row)

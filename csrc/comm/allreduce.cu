@@ -32,6 +32,9 @@ struct Peers {
     __nv_bfloat16* w16[kMaxRanks];
     uint32_t* sig[kMaxRanks];  // [2][kMaxBlocks][kMaxRanks] per rank
     uint32_t* counter;         // local: [0] epoch, [1] CTA ticket
+    float* mc_g;               // NVLS multicast addresses of the same buffers (null when not available)
+    float* mc_p;
+    __nv_bfloat16* mc_w16;
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -179,6 +182,96 @@ allreduce_update_kernel(Peers c, long long start, long long n, OptimSpec o, floa
     finish_epoch(c, epoch);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// NVLS variant (NVSwitch multicast objects): the reduce-scatter half is ONE multimem.ld_reduce per 16 bytes — the
+// switch adds the N copies and returns the sum, so a GPU receives n/N instead of (N-1)n/N bytes — and the all-gather
+// half is ONE multimem.st per 16 bytes that the switch fans out to every GPU.  Same two-shot ownership as above, so
+// the optimizer still runs once per element and every rank ends up with the same bits.
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float4 mc_ld_reduce_f4(const float* mc) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "l"(mc)
+                 : "memory");
+    return v;
+}
+__device__ __forceinline__ void mc_st_f4(void* mc, float4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y),
+                 "f"(v.z), "f"(v.w)
+                 : "memory");
+}
+
+// `start`, `n` multiples of 8 elements (32 bytes of fp32 / 16 bytes of bf16 per thread-trip).
+__global__ void __launch_bounds__(kThreads)
+allreduce_nvls_kernel(Peers c, long long start, long long n, OptimSpec o, float* __restrict__ m,
+                      float* __restrict__ v, float* __restrict__ out, int push_master) {
+    const uint32_t epoch = c.counter[0] + 1;
+    cross_barrier(c, 0, epoch);
+    const float inv_world = 1.f / (float)c.world;
+    AdamCorr corr = {0.f, 0.f};
+    if (o.kind == 2) corr = adam_corr(o);
+    const long long per = (n / 8 + c.world - 1) / c.world * 8;
+    long long lo = per * c.rank;
+    if (lo > n) lo = n;
+    const long long hi = lo + per < n ? lo + per : n;
+    const long long nvec = (hi - lo) / 8;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+        const long long e = start + lo + i * 8;
+        float4 a[2];
+        a[0] = mc_ld_reduce_f4(c.mc_g + e);
+        a[1] = mc_ld_reduce_f4(c.mc_g + e + 4);
+        float4 pw[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            float4 acc = a[h];
+            acc.x *= inv_world; acc.y *= inv_world; acc.z *= inv_world; acc.w *= inv_world;
+            const long long eh = e + 4 * h;
+            if (o.kind == 0) {
+                pw[h] = acc;
+                continue;
+            }
+            float4 p = *reinterpret_cast<const float4*>(c.p[c.rank] + eh);
+            if (o.kind == 2) {
+                float4 mm = *reinterpret_cast<const float4*>(m + eh);
+                float4 vv = *reinterpret_cast<const float4*>(v + eh);
+                p.x = adam_update(p.x, acc.x, mm.x, vv.x, o, corr);
+                p.y = adam_update(p.y, acc.y, mm.y, vv.y, o, corr);
+                p.z = adam_update(p.z, acc.z, mm.z, vv.z, o, corr);
+                p.w = adam_update(p.w, acc.w, mm.w, vv.w, o, corr);
+                *reinterpret_cast<float4*>(m + eh) = mm;
+                *reinterpret_cast<float4*>(v + eh) = vv;
+            } else {
+                p.x = sgd_update(p.x, acc.x, o);
+                p.y = sgd_update(p.y, acc.y, o);
+                p.z = sgd_update(p.z, acc.z, o);
+                p.w = sgd_update(p.w, acc.w, o);
+            }
+            pw[h] = p;
+        }
+        if (o.kind == 0) {  // plain all-reduce: every rank needs the mean -> multicast it into everyone's `out`?  `out`
+            // is a private buffer, so the owner writes its slice locally and the caller all-gathers; not used by the
+            // engine (kind 0 goes through the one-shot P2P kernel).
+            *reinterpret_cast<float4*>(out + e) = pw[0];
+            *reinterpret_cast<float4*>(out + e + 4) = pw[1];
+            continue;
+        }
+        if (push_master) {
+            mc_st_f4(c.mc_p + e, pw[0]);
+            mc_st_f4(c.mc_p + e + 4, pw[1]);
+        } else {
+            *reinterpret_cast<float4*>(c.p[c.rank] + e) = pw[0];
+            *reinterpret_cast<float4*>(c.p[c.rank] + e + 4) = pw[1];
+        }
+        const uint2 b0 = pack4_bf16(pw[0]), b1 = pack4_bf16(pw[1]);
+        mc_st_f4(c.mc_w16 + e, make_float4(__uint_as_float(b0.x), __uint_as_float(b0.y), __uint_as_float(b1.x),
+                                           __uint_as_float(b1.y)));
+    }
+    cross_barrier(c, 1, epoch);
+    finish_epoch(c, epoch);
+}
+
 }  // namespace comm
 }  // namespace b200
 
@@ -234,6 +327,9 @@ int b200ml_allreduce_update(const b200ml_comm* cm, long long start, long long n,
         c.sig[r] = r < cm->world ? cm->signals[r] : nullptr;
     }
     c.counter = cm->counter;
+    c.mc_g = cm->mc_grads;
+    c.mc_p = cm->mc_params;
+    c.mc_w16 = reinterpret_cast<__nv_bfloat16*>(cm->mc_w16);
     OptimSpec o{kind, lr, beta1, beta2, eps, weight_decay, step_dev};
     // two-shot pays two NVLink round trips but moves (N-1)/N of the bytes once; one-shot moves (N-1)x the bytes.
     bool two = algo == 2 || (algo == 0 && kind != 0 && n * 4 > (512 << 10));
@@ -244,7 +340,12 @@ int b200ml_allreduce_update(const b200ml_comm* cm, long long start, long long n,
     if (cap > kMaxBlocks) cap = kMaxBlocks;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-    if (two)
+    const bool nvls = (algo == 3 || (algo == 0 && two)) && kind != 0 && c.mc_g && c.mc_w16 && (c.mc_p || !push_master) &&
+                      start % 8 == 0 && n % 8 == 0;
+    B200_REQUIRE(algo != 3 || nvls, "allreduce: NVLS requested but multicast addresses / 8-element alignment missing");
+    if (nvls)
+        allreduce_nvls_kernel<<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, out, push_master);
+    else if (two)
         allreduce_update_kernel<true><<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, out, push_master);
     else
         allreduce_update_kernel<false><<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, out, push_master);

@@ -22,7 +22,8 @@ SIGNAL_WORDS = 2 * 320 * 8
 
 class CommStruct(C.Structure):
     _fields_ = [("world", C.c_int), ("rank", C.c_int), ("grads", C.c_void_p * 8), ("params", C.c_void_p * 8),
-                ("w16", C.c_void_p * 8), ("signals", C.c_void_p * 8), ("counter", C.c_void_p)]
+                ("w16", C.c_void_p * 8), ("signals", C.c_void_p * 8), ("counter", C.c_void_p),
+                ("mc_grads", C.c_void_p), ("mc_params", C.c_void_p), ("mc_w16", C.c_void_p)]
 
 
 vp, i, ll, f = C.c_void_p, C.c_int, C.c_longlong, C.c_float
@@ -99,15 +100,61 @@ class SymmetricAllocator:
         return b.tensor
 
 
+class SymmMemAllocator:
+    """Flat buffers from torch.distributed._symmetric_memory (CUDA VMM allocations that can additionally be bound to an
+    NVSwitch multicast object).  Used when NVLS is wanted; peer and multicast addresses come from the rendezvous
+    handles instead of CUDA IPC."""
+
+    def __init__(self, device):
+        import torch.distributed._symmetric_memory as symm_mem
+
+        self._sm = symm_mem
+        self.device = torch.device(device)
+        self.tensors: dict[str, torch.Tensor] = {}
+        self.handles: dict = {}
+
+    def __call__(self, name: str, numel: int, dtype) -> torch.Tensor:
+        t = self._sm.empty(numel, dtype=dtype, device=self.device)
+        t.zero_()
+        self.tensors[name] = t
+        return t
+
+    def rendezvous(self, group) -> None:
+        for name, t in self.tensors.items():
+            self.handles[name] = self._sm.rendezvous(t, group if group is not None else dist.group.WORLD)
+
+
+def make_allocator(device, group=None):
+    """NVLS-capable symmetric memory when B200ML_NVLS != 0 and torch can provide it, else cudaMalloc + CUDA IPC."""
+    import os
+
+    if os.environ.get("B200ML_NVLS", "1") != "0":
+        try:
+            alloc = SymmMemAllocator(device)
+            probe = alloc("_probe", 1024, torch.float32)
+            h = alloc._sm.rendezvous(probe, group if group is not None else dist.group.WORLD)
+            ok = bool(getattr(h, "multicast_ptr", 0))
+            del alloc.tensors["_probe"]
+            if ok:
+                return alloc
+        except Exception as e:  # noqa: BLE001
+            if os.environ.get("B200ML_DEBUG"):
+                print(f"[b200ml] symmetric-memory/NVLS unavailable: {e}")
+    return SymmetricAllocator(device)
+
+
 class FusedAllReduce:
     """Peer-pointer tables + launcher for b200ml_allreduce_update."""
 
     transport = "p2p-ipc"
 
     def __init__(self, flat, m, v, group=None, allocator: SymmetricAllocator | None = None):
+        self.flat, self.m, self.v, self.group = flat, m, v, group
+        if isinstance(allocator, SymmMemAllocator):
+            self._init_symm_mem(allocator)
+            return
         assert allocator is not None and {"flat_p", "flat_g", "flat_w16"} <= set(allocator.buffers), \
             "fused all-reduce needs FlatParams built on a SymmetricAllocator"
-        self.flat, self.m, self.v, self.group = flat, m, v, group
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
         assert self.world <= MAX_RANKS, f"fused all-reduce supports up to {MAX_RANKS} ranks per node"
@@ -143,6 +190,44 @@ class FusedAllReduce:
         torch.cuda.synchronize(dev)
         dist.barrier(group=group)  # nobody launches before every mapping exists
 
+    def _init_symm_mem(self, allocator: "SymmMemAllocator") -> None:
+        """Peer + multicast addresses from torch symmetric-memory rendezvous handles (NVLS path)."""
+        flat, group = self.flat, self.group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        assert self.world <= MAX_RANKS
+        dev = flat.device
+        self.alloc = allocator
+        self.signals_t = allocator("signals", SIGNAL_WORDS, torch.int32)
+        self.counter = torch.zeros(2, dtype=torch.int32, device=dev)
+        allocator.rendezvous(group)
+        h = allocator.handles
+        self._imported = []
+        self.cs = CommStruct()
+        self.cs.world, self.cs.rank = self.world, self.rank
+        table = {"flat_g": self.cs.grads, "flat_p": self.cs.params, "flat_w16": self.cs.w16, "signals": self.cs.signals}
+        for key, arr in table.items():
+            ptrs = list(h[key].buffer_ptrs)
+            off = int(getattr(h[key], "offset", 0) or 0)
+            for r in range(self.world):
+                arr[r] = ptrs[r] + off
+            assert arr[self.rank] == allocator.tensors[key].data_ptr(), "symmetric-memory offset mismatch"
+        self.cs.counter = self.counter.data_ptr()
+
+        def mc(key):
+            p = int(getattr(h[key], "multicast_ptr", 0) or 0)
+            return (p + int(getattr(h[key], "offset", 0) or 0)) if p else None
+
+        self.cs.mc_grads, self.cs.mc_params, self.cs.mc_w16 = mc("flat_g"), mc("flat_p"), mc("flat_w16")
+        self.transport = "symm-mem+nvls" if self.cs.mc_grads and self.cs.mc_w16 else "symm-mem"
+        self.peer_p = [flat.flat_p if r == self.rank else
+                       torch.as_tensor(_RawCuda(self.cs.params[r], flat.numel, "<f4"), device=dev)
+                       for r in range(self.world)]
+        self.push_master = 1
+        self.max_blocks = 0
+        torch.cuda.synchronize(dev)
+        dist.barrier(group=group)
+
     def allreduce_update(self, start, n, kind, lr, betas, eps, weight_decay, step_tensor, out=None, algo: int = 0):
         lib = _native.load()
         n4 = (n + 3) // 4 * 4  # slots are 64-element aligned, so rounding up stays inside the bucket
@@ -159,7 +244,8 @@ class FusedAllReduce:
         n4 = (n + 3) // 4 * 4
         if n4 * 4 <= (512 << 10):
             return  # such a bucket takes the one-shot path: every rank already updated all of it locally
-        per = ((n4 // 4 + self.world - 1) // self.world) * 4
+        gran = 8 if (self.cs.mc_grads and self.cs.mc_w16 and start % 8 == 0 and n4 % 8 == 0) else 4  # NVLS: 8-wide
+        per = ((n4 // gran + self.world - 1) // self.world) * gran
         for r in range(self.world):
             if r == self.rank:
                 continue

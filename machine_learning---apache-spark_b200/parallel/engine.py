@@ -56,9 +56,9 @@ class DataParallelEngine:
                 mode = "gloo"
         sym_alloc = None
         if mode == "fused":
-            from .comm import SymmetricAllocator
+            from .comm import make_allocator
 
-            sym_alloc = SymmetricAllocator(self.device)
+            sym_alloc = make_allocator(self.device, self.pg)
 
         # parameters whose kernels read only the bf16 working copy (nn.Linear / nn.Embedding weights) go first
         if push_master == "auto":

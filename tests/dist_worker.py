@@ -130,7 +130,45 @@ def case_allreduce_raw(rank, world, dev, mode):
     print(f"[rank {rank}] allreduce_raw ok")
 
 
-CASES = {"dp_equals_big_batch": case_dp_equals_big_batch, "fused_matches_nccl": case_fused_matches_nccl,
+def case_allreduce_nvls(rank, world, dev, mode):
+    """NVLS (multimem.ld_reduce / multimem.st) two-shot update vs torch.distributed.all_reduce; skipped when the box has
+    no multicast support."""
+    from b200ml.parallel.comm import FusedAllReduce, SymmMemAllocator, make_allocator
+    from b200ml.parallel.flat import FlatParams
+    alloc = make_allocator(dev)
+    if not isinstance(alloc, SymmMemAllocator):
+        print(f"[rank {rank}] allreduce_nvls skipped (no multicast)")
+        return
+    torch.manual_seed(rank)
+    ps = [torch.randn(1024, 333, device=dev).requires_grad_(), torch.randn(4099, device=dev).requires_grad_()]
+    flat = FlatParams(ps, allocator=alloc)
+    dist.broadcast(flat.flat_p, src=0)
+    flat.refresh_working_copy()
+    comm = FusedAllReduce(flat, None, None, None, allocator=alloc)
+    assert "nvls" in comm.transport, comm.transport
+    step = torch.ones(1, dtype=torch.int32, device=dev)
+    for push in (1, 0):
+        flat.flat_g.copy_(torch.randn(flat.numel, device=dev))
+        expect = flat.flat_g.clone()
+        dist.all_reduce(expect)
+        expect /= world
+        p0 = flat.flat_p.clone()
+        comm.push_master = push
+        comm.allreduce_update(0, flat.numel, 1, 0.5, (0.9, 0.999), 1e-8, 0.0, step, algo=3)
+        torch.cuda.synchronize()
+        dist.barrier()
+        want = p0 - 0.5 * expect
+        assert (flat.flat_w16.float() - want).abs().max().item() < 0.05, "bf16 working copy"
+        if not push:
+            comm.pull_master(0, flat.numel)
+            torch.cuda.synchronize()
+        assert (flat.flat_p - want).abs().max().item() < 1e-4, f"push={push}"
+        dist.barrier()
+    comm.close()
+    print(f"[rank {rank}] allreduce_nvls ok")
+
+
+CASES = {"allreduce_nvls": case_allreduce_nvls, "dp_equals_big_batch": case_dp_equals_big_batch, "fused_matches_nccl": case_fused_matches_nccl,
          "allreduce_raw": case_allreduce_raw}
 
 if __name__ == "__main__":

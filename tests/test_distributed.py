@@ -26,5 +26,5 @@ def test_dp_engine_gloo_world2():
 @pytest.mark.gpu
 @pytest.mark.multigpu
 def test_fused_allreduce_two_gpus():
-    out = _launch(["allreduce_raw", "fused_matches_nccl", "dp_equals_big_batch"], 2, 29612)
+    out = _launch(["allreduce_raw", "allreduce_nvls", "fused_matches_nccl", "dp_equals_big_batch"], 2, 29612)
     assert out.count("allreduce_raw ok") == 2 and out.count("fused_matches_nccl ok") == 2
