@@ -54,10 +54,10 @@ def main():
         nbytes = flat.numel * 4
         iters = 200 if nbytes < (1 << 20) else 30
         row = {"name": name, "bytes": nbytes, "world": world}
-        for label, algo in (("oneshot", 1), ("twoshot", 2)):
+        for label, algo in (("oneshot", 1), ("twoshot", 2), ("push", 4)):
             if algo == 1 and nbytes > (64 << 20):
                 continue
-            for blocks in ((0,) if nbytes < (1 << 20) else (64, 148, 296)):
+            for blocks in ((0,) if nbytes < (1 << 20) else (64, 148, 296) if algo != 1 else (148,)):
                 for push in ((1,) if algo == 1 else (1, 0)):
                     comm.max_blocks = blocks
                     comm.push_master = push

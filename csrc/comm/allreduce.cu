@@ -32,6 +32,7 @@ struct Peers {
     __nv_bfloat16* w16[kMaxRanks];
     uint32_t* sig[kMaxRanks];  // [2][kMaxBlocks][kMaxRanks] per rank
     uint32_t* counter;         // local: [0] epoch, [1] CTA ticket
+    float* stage[kMaxRanks];   // per-rank staging buffers for the push variant (same size/layout as g; may be null)
     float* mc_g;               // NVLS multicast addresses of the same buffers (null when not available)
     float* mc_p;
     __nv_bfloat16* mc_w16;
@@ -47,7 +48,9 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
 }
 __device__ __forceinline__ float4 ld_peer_f4(const float* p) {
     float4 v;
-    asm volatile("ld.global.relaxed.sys.v4.f32 {%0, %1, %2, %3}, [%4];"
+    // .cg: bypass L1 (a peer line cached there in the previous step would be stale); visibility of the peers' writes is
+    // established by the acquire on the barrier flags + bar.sync, so the data loads themselves can be weak
+    asm volatile("ld.global.cg.v4.f32 {%0, %1, %2, %3}, [%4];"
                  : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
                  : "l"(p)
                  : "memory");
@@ -272,6 +275,99 @@ allreduce_nvls_kernel(Peers c, long long start, long long n, OptimSpec o, float*
     finish_epoch(c, epoch);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Push variant of the two-shot update.  Measured on B200: peer STORES run at NVLink line rate (~770 GB/s) while the
+// load-based pull above tops out near 320 GB/s, so here the reduce-scatter half is done with stores: every rank writes
+// the slices it does not own into their owners' staging buffers, one barrier, then each owner sums its own slice and
+// the N-1 staged copies from LOCAL memory in rank order (same bits everywhere), runs the optimizer and pushes the new
+// weights.  No opening barrier is needed: a staging region is only rewritten after the closing barrier of the previous
+// call that used it.  Staging region of source r in owner s for bucket [start, start+n): start + j*per, j = r - (r>s).
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+allreduce_push_kernel(Peers c, long long start, long long n, OptimSpec o, float* __restrict__ m,
+                      float* __restrict__ v, int push_master) {
+    const uint32_t epoch = c.counter[0] + 1;
+    const float inv_world = 1.f / (float)c.world;
+    AdamCorr corr = {0.f, 0.f};
+    if (o.kind == 2) corr = adam_corr(o);
+    const long long per = (n / 4 + c.world - 1) / c.world * 4;   // slice length (elements, multiple of 4)
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const long long tid0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const float* g_local = c.g[c.rank];
+
+    // phase 1: scatter my gradient slices to their owners (remote 16-byte stores)
+#pragma unroll 1
+    for (int s = 0; s < c.world; ++s) {
+        if (s == c.rank) continue;
+        const long long lo = per * s;
+        if (lo >= n) break;
+        const long long len = (lo + per < n ? per : n - lo) / 4;
+        const int j = c.rank - (c.rank > s ? 1 : 0);
+        float* dst = c.stage[s] + start + (long long)j * per;
+        const float* src = g_local + start + lo;
+        for (long long i = tid0; i < len; i += 2 * stride) {
+            const float4 a = *reinterpret_cast<const float4*>(src + i * 4);
+            const bool two = i + stride < len;
+            float4 b = a;
+            if (two) b = *reinterpret_cast<const float4*>(src + (i + stride) * 4);
+            *reinterpret_cast<float4*>(dst + i * 4) = a;
+            if (two) *reinterpret_cast<float4*>(dst + (i + stride) * 4) = b;
+        }
+    }
+    cross_barrier(c, 0, epoch);  // every slice destined to me has landed
+
+    // phase 2: reduce my slice from local memory, update, push the new weights
+    long long lo = per * c.rank;
+    if (lo > n) lo = n;
+    const long long hi = lo + per < n ? lo + per : n;
+    const long long nvec = (hi - lo) / 4;
+    const float* st = c.stage[c.rank] + start;
+    for (long long i = tid0; i < nvec; i += stride) {
+        const long long e = start + lo + i * 4;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int r = 0; r < kMaxRanks; ++r) {
+            if (r < c.world) {
+                float4 t;
+                if (r == c.rank) {
+                    t = *reinterpret_cast<const float4*>(g_local + e);
+                } else {
+                    const int j = r - (r > c.rank ? 1 : 0);
+                    t = __ldcg(reinterpret_cast<const float4*>(st + (long long)j * per + i * 4));  // written by a peer
+                }
+                acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+            }
+        }
+        acc.x *= inv_world; acc.y *= inv_world; acc.z *= inv_world; acc.w *= inv_world;
+        float4 p = *reinterpret_cast<const float4*>(c.p[c.rank] + e);
+        if (o.kind == 2) {
+            float4 mm = *reinterpret_cast<const float4*>(m + e);
+            float4 vv = *reinterpret_cast<const float4*>(v + e);
+            p.x = adam_update(p.x, acc.x, mm.x, vv.x, o, corr);
+            p.y = adam_update(p.y, acc.y, mm.y, vv.y, o, corr);
+            p.z = adam_update(p.z, acc.z, mm.z, vv.z, o, corr);
+            p.w = adam_update(p.w, acc.w, mm.w, vv.w, o, corr);
+            *reinterpret_cast<float4*>(m + e) = mm;
+            *reinterpret_cast<float4*>(v + e) = vv;
+        } else {
+            p.x = sgd_update(p.x, acc.x, o);
+            p.y = sgd_update(p.y, acc.y, o);
+            p.z = sgd_update(p.z, acc.z, o);
+            p.w = sgd_update(p.w, acc.w, o);
+        }
+        const uint2 pb = pack4_bf16(p);
+#pragma unroll
+        for (int r = 0; r < kMaxRanks; ++r) {
+            if (r < c.world) {
+                if (push_master || r == c.rank) *reinterpret_cast<float4*>(c.p[r] + e) = p;
+                *reinterpret_cast<uint2*>(c.w16[r] + e) = pb;
+            }
+        }
+    }
+    cross_barrier(c, 1, epoch);  // weights have landed everywhere; staging regions are free again
+    finish_epoch(c, epoch);
+}
+
 }  // namespace comm
 }  // namespace b200
 
@@ -327,6 +423,7 @@ int b200ml_allreduce_update(const b200ml_comm* cm, long long start, long long n,
         c.sig[r] = r < cm->world ? cm->signals[r] : nullptr;
     }
     c.counter = cm->counter;
+    for (int r = 0; r < kMaxRanks; ++r) c.stage[r] = r < cm->world ? cm->stage[r] : nullptr;
     c.mc_g = cm->mc_grads;
     c.mc_p = cm->mc_params;
     c.mc_w16 = reinterpret_cast<__nv_bfloat16*>(cm->mc_w16);
@@ -343,7 +440,11 @@ int b200ml_allreduce_update(const b200ml_comm* cm, long long start, long long n,
     const bool nvls = (algo == 3 || (algo == 0 && two)) && kind != 0 && c.mc_g && c.mc_w16 && (c.mc_p || !push_master) &&
                       start % 8 == 0 && n % 8 == 0;
     B200_REQUIRE(algo != 3 || nvls, "allreduce: NVLS requested but multicast addresses / 8-element alignment missing");
-    if (nvls)
+    const bool push = (algo == 4 || (algo == 0 && two)) && kind != 0 && c.stage[0] != nullptr && cm->world > 1;
+    B200_REQUIRE(algo != 4 || push, "allreduce: push variant requested but no staging buffers were registered");
+    if (push && algo != 3)
+        allreduce_push_kernel<<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, push_master);
+    else if (nvls)
         allreduce_nvls_kernel<<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, out, push_master);
     else if (two)
         allreduce_update_kernel<true><<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, out, push_master);

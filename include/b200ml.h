@@ -183,7 +183,8 @@ int b200ml_lstm_layer_bwd(const float* x, const float* w_ih, const float* w_hh, 
  * weight (fp32), working weight (bf16) and signal-pad (2*320*8 uint32, zero-initialised) buffers as mapped in THIS
  * process; counter is a local zero-initialised uint32[2].  Elements [start, start+n) are summed over ranks in rank
  * order, divided by world, and (kind 1 SGD / 2 Adam) applied to the weights; kind 0 writes the mean to `out`.
- * algo: 0 auto, 1 one-shot, 2 two-shot, 3 NVLS (multimem.ld_reduce / multimem.st; auto picks it for large buckets when
+ * algo: 0 auto, 1 one-shot, 2 two-shot (pull), 4 two-shot (push through the staging buffers; auto prefers it for large
+ * buckets when staging is registered), 3 NVLS (multimem.ld_reduce / multimem.st; auto picks it for large buckets when
  * the multicast addresses are set).  Every rank must issue the same sequence of calls.
  * ref: DDP bucket all-reduce + optimizer.step (distributed_cnn.py:156,181-183). */
 typedef struct {
@@ -193,6 +194,7 @@ typedef struct {
     void* w16[8];
     unsigned* signals[8];
     unsigned* counter;
+    float* stage[8];   /* optional staging buffers (one per rank, same size as grads) for the store-based "push" two-shot */
     float* mc_grads;   /* NVLS multicast addresses of the gradient / master / bf16 buffers, or NULL */
     float* mc_params;
     void* mc_w16;

@@ -23,6 +23,7 @@ SIGNAL_WORDS = 2 * 320 * 8
 class CommStruct(C.Structure):
     _fields_ = [("world", C.c_int), ("rank", C.c_int), ("grads", C.c_void_p * 8), ("params", C.c_void_p * 8),
                 ("w16", C.c_void_p * 8), ("signals", C.c_void_p * 8), ("counter", C.c_void_p),
+                ("stage", C.c_void_p * 8),
                 ("mc_grads", C.c_void_p), ("mc_params", C.c_void_p), ("mc_w16", C.c_void_p)]
 
 
@@ -124,11 +125,17 @@ class SymmMemAllocator:
             self.handles[name] = self._sm.rendezvous(t, group if group is not None else dist.group.WORLD)
 
 
+def use_staging() -> bool:
+    import os
+
+    return os.environ.get("B200ML_AR_PUSH", "1") != "0"
+
+
 def make_allocator(device, group=None):
     """NVLS-capable symmetric memory when B200ML_NVLS != 0 and torch can provide it, else cudaMalloc + CUDA IPC."""
     import os
 
-    if os.environ.get("B200ML_NVLS", "1") != "0":
+    if os.environ.get("B200ML_NVLS", "0") == "1":  # opt-in: the P2P two-shot kernel measured faster at 2 and 8 GPUs
         try:
             alloc = SymmMemAllocator(device)
             probe = alloc("_probe", 1024, torch.float32)
@@ -162,8 +169,12 @@ class FusedAllReduce:
         self.alloc = allocator
         self.signals = SymmetricBuffer(SIGNAL_WORDS, torch.int32, dev)
         self.counter = torch.zeros(2, dtype=torch.int32, device=dev)
+        # staging for the store-based reduce-scatter (peer stores run at NVLink line rate, peer loads do not)
+        self.stage = SymmetricBuffer(flat.numel, torch.float32, dev) if use_staging() else None
         mine = {k: b.export() for k, b in allocator.buffers.items()}
         mine["signals"] = self.signals.export()
+        if self.stage is not None:
+            mine["stage"] = self.stage.export()
         gathered = [None] * self.world
         dist.all_gather_object(gathered, mine, group=group)
         self._imported = []
@@ -172,6 +183,9 @@ class FusedAllReduce:
         table = {"flat_g": self.cs.grads, "flat_p": self.cs.params, "flat_w16": self.cs.w16, "signals": self.cs.signals}
         local = {"flat_g": allocator.buffers["flat_g"].ptr, "flat_p": allocator.buffers["flat_p"].ptr,
                  "flat_w16": allocator.buffers["flat_w16"].ptr, "signals": self.signals.ptr}
+        if self.stage is not None:
+            table["stage"] = self.cs.stage
+            local["stage"] = self.stage.ptr
         for r in range(self.world):
             for key, arr in table.items():
                 if r == self.rank:

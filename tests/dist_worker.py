@@ -111,7 +111,7 @@ def case_allreduce_raw(rank, world, dev, mode):
     flat.refresh_working_copy()
     comm = FusedAllReduce(flat, None, None, None, allocator=alloc)
     step = torch.ones(1, dtype=torch.int32, device=dev)
-    for algo in (1, 2):
+    for algo in (1, 2, 4):
         flat.flat_g.copy_(torch.randn(flat.numel, device=dev))
         expect = flat.flat_g.clone()
         dist.all_reduce(expect)
