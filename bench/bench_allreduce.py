@@ -10,6 +10,8 @@ import json
 import os
 import sys
 
+os.environ.setdefault("B200ML_AR_PUSH", "1")  # the benchmark measures every variant, including the opt-in ones
+
 import torch
 import torch.distributed as dist
 
@@ -70,20 +72,24 @@ def main():
         # NVLS variant (needs torch symmetric memory + multicast support)
         try:
             from b200ml.parallel.comm import SymmMemAllocator, make_allocator
+            os.environ["B200ML_NVLS"] = "1"
             alloc2 = make_allocator(dev)
             if isinstance(alloc2, SymmMemAllocator) and nbytes >= (1 << 20):
                 p2 = torch.randn(n, device=dev).requires_grad_()
                 flat2 = FlatParams([p2], allocator=alloc2)
                 comm2 = FusedAllReduce(flat2, None, None, None, allocator=alloc2)
                 flat2.flat_g.normal_()
-                for blocks in (64, 148, 296):
-                    for push in (1, 0):
-                        comm2.max_blocks, comm2.push_master = blocks, push
-                        ms = timed(lambda: comm2.allreduce_update(0, flat2.numel, 1, 1e-3, (0.9, 0.999), 1e-8, 0.0, step,
-                                                                  algo=3), iters, dev)
-                        key = f"fused_nvls_sgd_b{blocks}" + ("" if push else "_bf16push")
-                        row[key + "_us"] = ms * 1e3
-                        row[key + "_busGBs"] = 2 * (world - 1) / world * nbytes / (ms * 1e-3) / 1e9
+                for lab2, algo2 in (("nvls", 3), ("vmm_twoshot", 2), ("vmm_push", 4)):
+                    if algo2 == 4 and not comm2.cs.stage[0]:
+                        continue
+                    for blocks in (148, 296):
+                        for push in (1, 0):
+                            comm2.max_blocks, comm2.push_master = blocks, push
+                            ms = timed(lambda: comm2.allreduce_update(0, flat2.numel, 1, 1e-3, (0.9, 0.999), 1e-8, 0.0,
+                                                                      step, algo=algo2), iters, dev)
+                            key = f"fused_{lab2}_sgd_b{blocks}" + ("" if push else "_bf16push")
+                            row[key + "_us"] = ms * 1e3
+                            row[key + "_busGBs"] = 2 * (world - 1) / world * nbytes / (ms * 1e-3) / 1e9
                 comm2.close()
         except Exception as e:  # noqa: BLE001
             row["nvls_error"] = str(e)[:200]

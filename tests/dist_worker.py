@@ -5,6 +5,8 @@
 import os
 import sys
 
+os.environ.setdefault("B200ML_AR_PUSH", "1")  # exercise the staging (push) variant too
+
 import torch
 import torch.distributed as dist
 
