@@ -12,7 +12,7 @@ reduce_partials_kernel(const float* __restrict__ partial, int n_rows, int cols, 
                        float* __restrict__ out1, int accumulate) {
     __shared__ float red[8][33];
     const int c = threadIdx.x & 31, g = threadIdx.x >> 5;
-    const int col = blockIdx.x * 32 + c;
+    const int col = blockIdx.x * 32 + c;  // one warp-wide column group per CTA keeps the CTA count (= cols/32) high
     float s = 0.f;
     if (col < cols) {
 #pragma unroll 4

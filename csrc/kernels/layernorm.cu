@@ -73,10 +73,15 @@ ln_fwd_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restri
             const long long off = (long long)row * d + col;
             if (a) unpack8(*reinterpret_cast<const uint4*>(a + off), av);
             if (x) unpack8(*reinterpret_cast<const uint4*>(x + off), xv);
+            uint64_t bits[2] = {0, 0};
+            if (drop) {  // off is a multiple of 8: two groups of four elements, one hash each
+                bits[0] = rng_bits4(key, (uint64_t)off >> 2);
+                bits[1] = rng_bits4(key, ((uint64_t)off >> 2) + 1);
+            }
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
                 float t = a ? av[j] : 0.f;
-                if (drop) t = rng_keep(key, (uint64_t)off + j, thr) ? t * ks : 0.f;
+                if (drop) t = ((uint32_t)(bits[j >> 2] >> ((j & 3) * 16)) & 0xFFFFu) >= thr ? t * ks : 0.f;
                 if (x) t += xv[j];
                 // round to the stored precision so backward (which reads z in bf16) sees the same statistics
                 t = __bfloat162float(__float2bfloat16(t));
@@ -190,8 +195,12 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
                 for (int j = 0; j < 8; ++j) o[j] = rs * (gy[c][j] - s1 - xh[c][j] * s2);
                 *reinterpret_cast<uint4*>(dz + off) = pack8(o);
                 if (drop) {
+                    const uint64_t b0 = rng_bits4(key, (uint64_t)off >> 2), b1 = rng_bits4(key, ((uint64_t)off >> 2) + 1);
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) o[j] = rng_keep(key, (uint64_t)off + j, thr) ? o[j] * ks : 0.f;
+                    for (int j = 0; j < 8; ++j) {
+                        const uint64_t bb = j < 4 ? b0 : b1;
+                        o[j] = ((uint32_t)(bb >> ((j & 3) * 16)) & 0xFFFFu) >= thr ? o[j] * ks : 0.f;
+                    }
                     *reinterpret_cast<uint4*>(da + off) = pack8(o);
                 }
             }
@@ -217,7 +226,7 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
 
 static int bwd_grid(int rows) {
     int g = (rows + kWarpsPerBlock - 1) / kWarpsPerBlock;
-    const int cap = 2 * sm_count();
+    const int cap = 4 * sm_count();  // ~1-2 rows per warp: the row loop is latency-bound, parallelism hides it
     return g < cap ? g : cap;
 }
 
