@@ -16,6 +16,7 @@ are kept exactly.
 from __future__ import annotations
 
 import math
+import os
 
 import torch
 from torch import nn
@@ -230,9 +231,14 @@ class DecoderLayer(nn.Module):
         self._sites = (new_site(), new_site(), new_site())
         self.mask_mode = "reference"
 
-    def forward(self, x, y, self_attention_mask=None, cross_attention_mask=None):
+    def forward_self(self, y, self_attention_mask=None):
+        """Self-attention sub-layer: the part of the decoder layer that does not depend on the encoder output."""
         a = self.self_attention(y, mask=self_attention_mask, mask_mode=self.mask_mode, decoder=True)
-        y = self.layer_norm1(a, y, self.dropout1.p, self._sites[0])
+        return self.layer_norm1(a, y, self.dropout1.p, self._sites[0])
+
+    def forward(self, x, y, self_attention_mask=None, cross_attention_mask=None, self_done: bool = False):
+        if not self_done:
+            y = self.forward_self(y, self_attention_mask)
         c = self.encoder_decoder_attention(x, y, mask=cross_attention_mask, mask_mode=self.mask_mode)
         y = self.layer_norm2(c, y, self.dropout2.p, self._sites[1])
         f = self.ffn(y)
@@ -240,10 +246,10 @@ class DecoderLayer(nn.Module):
 
 
 class SequentialDecoder(nn.Sequential):
-    def forward(self, *inputs):
+    def forward(self, *inputs, first_self_done: bool = False):
         x, y, self_attention_mask, cross_attention_mask = inputs
-        for module in self._modules.values():
-            y = module(x, y, self_attention_mask, cross_attention_mask)
+        for i, module in enumerate(self._modules.values()):
+            y = module(x, y, self_attention_mask, cross_attention_mask, self_done=(first_self_done and i == 0))
         return y
 
 
@@ -254,9 +260,16 @@ class Decoder(nn.Module):
         self.layers = SequentialDecoder(*[DecoderLayer(d_model, ffn_hidden, num_heads, drop_prob)
                                           for _ in range(num_layers)])
 
-    def forward(self, x, y, self_attention_mask=None, cross_attention_mask=None):
+    def forward_pre(self, y, self_attention_mask=None):
+        """Everything of the decoder that can run before (= concurrently with) the encoder: target embedding and the
+        first layer's self-attention sub-layer."""
         y = self.sentence_embedding(y)
-        return self.layers(x, y, self_attention_mask, cross_attention_mask)
+        return self.layers[0].forward_self(y, self_attention_mask)
+
+    def forward(self, x, y, self_attention_mask=None, cross_attention_mask=None, pre_done: bool = False):
+        if not pre_done:
+            y = self.sentence_embedding(y)
+        return self.layers(x, y, self_attention_mask, cross_attention_mask, first_self_done=pre_done)
 
 
 class Transformer(nn.Module):
@@ -270,6 +283,9 @@ class Transformer(nn.Module):
         self.linear = nn.Linear(d_model, de_vocab_size)
         self.device = get_device()
         self.set_mask_mode(mask_mode)
+        # run the decoder's encoder-independent prefix on a second stream (forward, and therefore backward too)
+        self.overlap_streams = os.environ.get("B200ML_OVERLAP_STREAMS", "1") != "0"
+        self._dec_stream = None
 
     def set_mask_mode(self, mode: str) -> None:
         assert mode in ("reference", "causal")
@@ -280,8 +296,20 @@ class Transformer(nn.Module):
 
     def forward(self, x, y, encoder_self_attention_mask=None, decoder_self_attention_mask=None,
                 decoder_cross_attention_mask=None, return_hidden: bool = False):
-        x = self.encoder(x, encoder_self_attention_mask)
-        out = self.decoder(x, y, decoder_self_attention_mask, decoder_cross_attention_mask)
+        if self.overlap_streams and x.is_cuda and len(self.decoder.layers) > 0:
+            if self._dec_stream is None:
+                self._dec_stream = torch.cuda.Stream(device=x.device)
+            cur = torch.cuda.current_stream()
+            self._dec_stream.wait_stream(cur)
+            with torch.cuda.stream(self._dec_stream):
+                y_pre = self.decoder.forward_pre(y, decoder_self_attention_mask)
+            x = self.encoder(x, encoder_self_attention_mask)
+            cur.wait_stream(self._dec_stream)
+            y_pre.record_stream(cur)
+            out = self.decoder(x, y_pre, decoder_self_attention_mask, decoder_cross_attention_mask, pre_done=True)
+        else:
+            x = self.encoder(x, encoder_self_attention_mask)
+            out = self.decoder(x, y, decoder_self_attention_mask, decoder_cross_attention_mask)
         if return_hidden:
             return out
         return _linear(out, self.linear.weight, self.linear.bias)

@@ -104,7 +104,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     g.force_simt = int(force_simt)
     g.split_k = split_k
     if split_k != 1 and bias is None and not act and not (aux is not None and aux_mode) and dropout_p <= 0:
-        ws = workspace.get("gemm_splitk", SPLITK_WORKSPACE_BYTES, a.device)
+        ws = workspace.get(f"gemm_splitk@{_native.stream_ptr()}", SPLITK_WORKSPACE_BYTES, a.device)  # one per stream
         g.workspace, g.workspace_bytes = ws.data_ptr(), ws.numel()
     _native.check(lib.b200ml_gemm_bf16(C.byref(g), _native.stream_ptr()), "gemm_bf16")
     return out
@@ -121,7 +121,7 @@ def colsum(x: torch.Tensor, out: torch.Tensor | None = None, accumulate: bool = 
         return out
     lib = _native.load()
     nbytes = lib.b200ml_colsum_scratch_bytes(rows, cols)
-    ws = workspace.get("colsum", nbytes, x.device)
+    ws = workspace.get(f"colsum@{_native.stream_ptr()}", nbytes, x.device)  # one per stream
     _native.check(lib.b200ml_colsum_bf16(x.data_ptr(), x.stride(0), rows, cols, out.data_ptr(), int(accumulate),
                                          ws.data_ptr(), ws.numel(), _native.stream_ptr()), "colsum")
     return out
@@ -150,6 +150,29 @@ def working_copy(param: torch.Tensor) -> torch.Tensor:
     return w16
 
 
+class GradSideStream:
+    """Parameter-gradient kernels (wgrad GEMMs, bias column sums) are leaves of the backward graph: nothing else in
+    backward consumes them.  The engine lets them run on this side stream so they overlap the dgrad / attention /
+    LayerNorm chain (small grids leave SMs idle); inside a captured CUDA graph the two streams become parallel branches.
+    Tensors the side kernels read are kept alive here until the engine has joined the streams."""
+
+    def __init__(self, device):
+        self.stream = torch.cuda.Stream(device=device)
+        self.keep: list = []
+        self.active = False
+
+    def run(self, fn, *args) -> None:
+        cur = torch.cuda.current_stream()
+        self.stream.wait_stream(cur)
+        with torch.cuda.stream(self.stream):
+            fn(*args)
+        self.keep.append(fn)  # the closure owns references to the gradient / activation tensors it reads
+
+    def join(self) -> None:
+        torch.cuda.current_stream().wait_stream(self.stream)
+        self.keep.clear()
+
+
 def deliver_grad(param: torch.Tensor, compute, shape) -> torch.Tensor | None:
     """Produce a parameter gradient.  With a DP engine the gradient is written straight into the parameter's slot of
     the flat bucket (``param._b200_grad``) and the engine is told the slot is ready — autograd sees ``None``.
@@ -157,7 +180,11 @@ def deliver_grad(param: torch.Tensor, compute, shape) -> torch.Tensor | None:
     slot = getattr(param, "_b200_grad", None)
     if slot is not None and slot.device == param.device:
         acc = bool(getattr(param, "_b200_grad_accumulate", False))
-        compute(slot.view(shape), acc)
+        side = getattr(param, "_b200_side", None)
+        if side is not None and side.active and slot.is_cuda:
+            side.run(compute, slot.view(shape), acc)
+        else:
+            compute(slot.view(shape), acc)
         ready = getattr(param, "_b200_ready", None)
         if ready is not None:
             ready()

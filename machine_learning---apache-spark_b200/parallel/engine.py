@@ -107,8 +107,16 @@ class DataParallelEngine:
             for i in ids:
                 self._bucket_of[i] = b
         self._pending = [0] * len(self.buckets)
+        self._events = [dict() for _ in self.buckets]
+        # side stream for the parameter-gradient kernels (ops/gemm.py GradSideStream)
+        self.side = None
+        if self.device.type == "cuda" and os.environ.get("B200ML_WGRAD_STREAM", "1") != "0":
+            from ..ops.gemm import GradSideStream
+
+            self.side = GradSideStream(self.device)
         for i, p in enumerate(self.flat.params):
             p._b200_ready = self._make_ready(i)
+            p._b200_side = self.side
 
         self.allreduce_mode = mode
         self.comm = None
@@ -125,6 +133,11 @@ class DataParallelEngine:
                     module.register_state_dict_pre_hook(lambda *a, **k: self.sync_master())
             if self.device.type == "cuda":
                 self.comm_stream = torch.cuda.Stream(device=self.device, priority=-1)
+        # single GPU: the per-bucket optimizer launches also run on a side stream, overlapping the rest of backward
+        self._local_overlap = (self.world == 1 and self.device.type == "cuda" and self.sync_gradients and
+                               os.environ.get("B200ML_OPT_OVERLAP", "1") != "0")
+        if self._local_overlap:
+            self.comm_stream = torch.cuda.Stream(device=self.device)
         self._in_step = False
 
     # ------------------------------------------------------------------------------------------------ bucket events
@@ -133,16 +146,29 @@ class DataParallelEngine:
             if not self._in_step:
                 return
             b = self._bucket_of[i]
+            if self.comm_stream is not None:
+                # gradients of one bucket may be produced on several streams (backward runs each node on the stream of
+                # its forward; wgrads run on the side stream): remember the latest point of each
+                cur = torch.cuda.current_stream()
+                ev = torch.cuda.Event()
+                ev.record(cur)
+                self._events[b][cur.cuda_stream] = ev
+                if self.side is not None and self.side.active:
+                    ev2 = torch.cuda.Event()
+                    ev2.record(self.side.stream)
+                    self._events[b][self.side.stream.cuda_stream] = ev2
             self._pending[b] -= 1
             if self._pending[b] == 0:
                 self._bucket_ready(b)
         return ready
 
     def _bucket_ready(self, b: int) -> None:
-        if self.world == 1 or not self.sync_gradients:
+        if (self.world == 1 and not self._local_overlap) or not self.sync_gradients:
             return  # single fused optimizer launch in finish_step
         if self.comm_stream is not None:
             self.comm_stream.wait_stream(torch.cuda.current_stream())
+            for ev in self._events[b].values():
+                self.comm_stream.wait_event(ev)
             with torch.cuda.stream(self.comm_stream):
                 self._reduce_and_update(b)
         else:
@@ -155,6 +181,10 @@ class DataParallelEngine:
             self.comm.allreduce_update(start, n, self.kind, self.lr, self.betas, self.eps, self.weight_decay,
                                        self.step_tensor)
             return
+        if self.world == 1:
+            optim_step_flat(self.flat.flat_p, self.flat.flat_g, self.m, self.v, self.flat.flat_w16, self.kind, self.lr,
+                            self.betas, self.eps, self.weight_decay, self.step_tensor, 1.0, start, n)
+            return
         g = self.flat.flat_g[start:start + n]
         dist.all_reduce(g, group=self.pg)
         optim_step_flat(self.flat.flat_p, self.flat.flat_g, self.m, self.v, self.flat.flat_w16, self.kind, self.lr,
@@ -166,11 +196,18 @@ class DataParallelEngine:
         self.flat.zero_accumulating_slots()
         for b, (_, _, ids, _) in enumerate(self.buckets):
             self._pending[b] = len(ids)
+            self._events[b].clear()
         self._in_step = True
+        if self.side is not None:
+            self.side.active = True
 
     def finish_step(self) -> None:
         self._in_step = False
-        if self.world == 1 or not self.sync_gradients:
+        if self.side is not None:
+            self.side.active = False
+            if self.comm_stream is None or not self.sync_gradients:
+                self.side.join()
+        if (self.world == 1 and not self._local_overlap) or not self.sync_gradients:
             optim_step_flat(self.flat.flat_p, self.flat.flat_g, self.m, self.v, self.flat.flat_w16, self.kind, self.lr,
                             self.betas, self.eps, self.weight_decay, self.step_tensor)
             return
@@ -181,6 +218,8 @@ class DataParallelEngine:
                 self._bucket_ready(b)
         if self.comm_stream is not None:
             torch.cuda.current_stream().wait_stream(self.comm_stream)
+        if self.side is not None:
+            self.side.join()
         self._master_stale = self._bf16_push and self.comm is not None
 
     # torch.optim-flavoured aliases so the entry scripts read like the reference loops
@@ -248,3 +287,4 @@ class DataParallelEngine:
             self.comm = None
         for p in self.flat.params:
             p._b200_ready = None
+            p._b200_side = None
