@@ -44,12 +44,16 @@ __device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
     return u;
 }
 
-// a: sublayer output (may be null => z = x), x: residual (may be null => z = dropout(a))
+// a: sublayer output (may be null => z = x), x: residual (may be null => z = dropout(a)).
+// kChunks = ceil(d / 256) as a template parameter: the per-lane register arrays scale with it, and d = 512 (the
+// Transformer) must not pay the register footprint (=> occupancy) of d = 1024.
+template <int kChunks>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 ln_fwd_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ x,
               const float* __restrict__ gamma, const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
               __nv_bfloat16* __restrict__ z_out, float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows,
               int d, float eps, float p, const RngState* __restrict__ rng, uint32_t site) {
+    constexpr int kMaxChunks = kChunks;  // shadows the namespace-level maximum inside this kernel
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int row = blockIdx.x * kWarpsPerBlock + warp;
     if (row >= rows) return;
@@ -132,11 +136,13 @@ ln_fwd_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restri
 }
 
 // Stage 1: each CTA walks rows (grid-stride), writes dz / d_a, and leaves per-CTA partial dgamma/dbeta in scratch.
+template <int kChunks>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ z,
               const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ gamma,
               __nv_bfloat16* __restrict__ dz, __nv_bfloat16* __restrict__ da, float* __restrict__ partial, int rows,
               int d, float p, const RngState* __restrict__ rng, uint32_t site) {
+    constexpr int kMaxChunks = kChunks;
     __shared__ float red[kWarpsPerBlock][kMaxChunks * 256];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const bool drop = p > 0.f && rng != nullptr && da != nullptr;
@@ -224,6 +230,19 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
     }
 }
 
+template <typename... Args>
+static void launch_ln_fwd(int d, int grid, cudaStream_t stream, Args... args) {
+    if (d <= 256) ln_fwd_kernel<1><<<grid, kWarpsPerBlock * 32, 0, stream>>>(args...);
+    else if (d <= 512) ln_fwd_kernel<2><<<grid, kWarpsPerBlock * 32, 0, stream>>>(args...);
+    else ln_fwd_kernel<4><<<grid, kWarpsPerBlock * 32, 0, stream>>>(args...);
+}
+template <typename... Args>
+static void launch_ln_bwd(int d, int grid, cudaStream_t stream, Args... args) {
+    if (d <= 256) ln_bwd_kernel<1><<<grid, kWarpsPerBlock * 32, 0, stream>>>(args...);
+    else if (d <= 512) ln_bwd_kernel<2><<<grid, kWarpsPerBlock * 32, 0, stream>>>(args...);
+    else ln_bwd_kernel<4><<<grid, kWarpsPerBlock * 32, 0, stream>>>(args...);
+}
+
 static int bwd_grid(int rows) {
     int g = (rows + kWarpsPerBlock - 1) / kWarpsPerBlock;
     const int cap = 4 * sm_count();  // ~1-2 rows per warp: the row loop is latency-bound, parallelism hides it
@@ -244,7 +263,7 @@ int b200ml_layernorm_fwd(const void* a, const void* x, const float* gamma, const
                  kMaxChunks * 256);
     if (rows <= 0) return 0;
     const int grid = (rows + kWarpsPerBlock - 1) / kWarpsPerBlock;
-    ln_fwd_kernel<<<grid, kWarpsPerBlock * 32, 0, stream>>>(
+    launch_ln_fwd(d, grid, stream,
         (const __nv_bfloat16*)a, (const __nv_bfloat16*)x, gamma, beta, (__nv_bfloat16*)y, (__nv_bfloat16*)z_out, mean,
         rstd, rows, d, eps, dropout_p, (const b200::RngState*)rng_state, rng_site);
     B200_CHECK_CUDA(cudaGetLastError());
@@ -267,7 +286,7 @@ int b200ml_layernorm_bwd(const void* dy, const void* z, const float* mean, const
     const int grid = bwd_grid(rows);
     B200_REQUIRE(scratch_bytes >= (size_t)grid * 2 * d * sizeof(float), "layernorm_bwd: scratch too small (%zu < %zu)",
                  scratch_bytes, (size_t)grid * 2 * d * sizeof(float));
-    ln_bwd_kernel<<<grid, kWarpsPerBlock * 32, 0, stream>>>(
+    launch_ln_bwd(d, grid, stream,
         (const __nv_bfloat16*)dy, (const __nv_bfloat16*)z, mean, rstd, gamma, (__nv_bfloat16*)dz, (__nv_bfloat16*)da,
         (float*)scratch, rows, d, dropout_p, (const b200::RngState*)rng_state, rng_site);
     B200_CHECK_CUDA(cudaGetLastError());
@@ -345,7 +364,7 @@ int b200ml_layernorm_bwd_noalloc(const void* dy, const void* z, const float* mea
     if (grid > kNoAllocMaxCtas) grid = kNoAllocMaxCtas;
     // Stage 1 overwrites rows [0, grid) x 2d of the scratch completely, stage 2 reads exactly those: nothing in the
     // shared array has to start at zero, whatever an earlier call left behind.
-    ln_bwd_kernel<<<grid, kWarpsPerBlock * 32, 0, stream>>>(
+    launch_ln_bwd(d, grid, stream,
         (const __nv_bfloat16*)dy, (const __nv_bfloat16*)z, mean, rstd, gamma, (__nv_bfloat16*)dz, (__nv_bfloat16*)da,
         scratch, rows, d, dropout_p, (const b200::RngState*)rng_state, rng_site);
     B200_CHECK_CUDA(cudaGetLastError());

@@ -10,8 +10,12 @@ from __future__ import annotations
 
 import torch
 
+import os
+
 from .. import _native
 from .gemm import colsum, deliver_grad, gemm, working_copy
+
+HEAD_CHUNK_BYTES = int(float(os.environ.get("B200ML_HEAD_CHUNK_MB", "64")) * (1 << 20))
 
 
 def _xent_native(logits, ld, targets, V, ignore_index, write_grad=True):
@@ -79,12 +83,36 @@ class _LinearCrossEntropy(torch.autograd.Function):
             h2 = h2.to(torch.bfloat16).contiguous()
             w16 = working_copy(weight)
             ld = (V + 7) // 8 * 8  # TMA needs 16-byte row pitch
-            logits = torch.empty(rows, ld, dtype=torch.bfloat16, device=h.device)
-            gemm(h2, w16, out=logits, bias=None if bias is None else bias.detach(), n_logical=V)
-            loss, _ = _xent_native(logits, ld, t, V, ignore_index)
-            ctx.save_for_backward(h2, logits)  # logits now hold d(loss)/d(logits)
+            dev = h.device
+            lib = _native.load()
+            st = _native.stream_ptr()
+            logits = torch.empty(rows, ld, dtype=torch.bfloat16, device=dev)
+            inv = torch.empty(2, dtype=torch.float32, device=dev)
+            row_loss = torch.empty(rows, dtype=torch.float32, device=dev)
+            loss = torch.empty(1, dtype=torch.float32, device=dev)
+            need_grad = h.requires_grad or weight.requires_grad
+            _native.check(lib.b200ml_xent_count(t.data_ptr(), rows, ignore_index, inv.data_ptr(), st), "xent_count")
+            # Row chunks sized to stay L2-resident (126 MB): the GEMM writes a chunk of logits, the loss kernel reads it
+            # twice and overwrites it with the gradient, and the input-gradient GEMM consumes that gradient — all before
+            # the chunk is evicted, so the [rows, V] matrix makes one trip to HBM instead of four.
+            chunk_rows = max(128, (HEAD_CHUNK_BYTES // (ld * 2)) // 128 * 128)
+            dh = torch.empty(rows, d, dtype=torch.bfloat16, device=dev) if (need_grad and h.requires_grad) else None
+            b_ = None if bias is None else bias.detach()
+            for r0 in range(0, rows, chunk_rows):
+                r1 = min(rows, r0 + chunk_rows)
+                lg = logits[r0:r1]
+                gemm(h2[r0:r1], w16, out=lg, bias=b_, n_logical=V)
+                _native.check(lib.b200ml_xent_fwd_bwd(lg.data_ptr(), 0, ld, t[r0:r1].data_ptr(),
+                                                      row_loss[r0:r1].data_ptr(), inv.data_ptr(), 0.0, r1 - r0, V,
+                                                      ignore_index, int(need_grad), st), "xent_fwd_bwd")
+                if dh is not None:
+                    gemm(lg[:, :V], w16, b_mn=True, out=dh[r0:r1])  # d(loss)/dh for an upstream gradient of 1
+            _native.check(lib.b200ml_loss_reduce(row_loss.data_ptr(), rows, inv.data_ptr(), 0.0, loss.data_ptr(), st),
+                          "loss_reduce")
+            ctx.save_for_backward(h2, logits, dh if dh is not None else h2.new_empty(0))
             ctx.V = V
-            return loss
+            ctx.has_dh = dh is not None
+            return loss[0]
         zf = h2.float() @ weight.float().t()
         if bias is not None:
             zf = zf + bias.float()
@@ -94,13 +122,14 @@ class _LinearCrossEntropy(torch.autograd.Function):
         picked = zf.gather(1, t.clamp(0, V - 1).unsqueeze(1)).squeeze(1)
         loss = ((lse - picked) * valid).sum() / cnt
         g = (torch.softmax(zf, -1) - torch.nn.functional.one_hot(t.clamp(0, V - 1), V)) * valid.unsqueeze(1) / cnt
-        ctx.save_for_backward(h2, g)
+        ctx.save_for_backward(h2, g, h2.new_empty(0))
         ctx.V = V
+        ctx.has_dh = False
         return loss
 
     @staticmethod
     def backward(ctx, gout):
-        h2, g = ctx.saved_tensors
+        h2, g, dh_pre = ctx.saved_tensors
         weight, bias = ctx.params
         V = ctx.V
         d = weight.shape[1]
@@ -109,8 +138,11 @@ class _LinearCrossEntropy(torch.autograd.Function):
             gv = g[:, :V]
             dh = None
             if ctx.needs_input_grad[0]:
-                dh = gemm(gv, working_copy(weight), b_mn=True, alpha_dev=gdev)
-                dh = dh.reshape(ctx.h_shape).to(ctx.h_dtype)
+                if ctx.has_dh:   # computed chunk-wise in forward while the gradient chunk was L2-resident
+                    dh = (dh_pre * gdev.to(dh_pre.dtype)).reshape(ctx.h_shape).to(ctx.h_dtype)
+                else:
+                    dh = gemm(gv, working_copy(weight), b_mn=True, alpha_dev=gdev)
+                    dh = dh.reshape(ctx.h_shape).to(ctx.h_dtype)
             dw = db = None
             if weight.requires_grad:
                 dw = deliver_grad(weight, lambda out, acc: gemm(gv, h2, a_mn=True, b_mn=True, out=out, accumulate=acc,
