@@ -47,6 +47,7 @@ struct Epilogue {
     const RngState* rng;
     uint32_t rng_site;
     float* splitk_ws;        // != nullptr: write raw fp32 partial tiles to ws[split][M][N] instead of C
+    int tma_store;           // bf16 C through smem staging + cp.async.bulk.tensor stores (needs tmap_c)
 };
 
 template <int BN>
@@ -56,7 +57,11 @@ struct Cfg {
     static constexpr int kBBytes = BN * BLOCK_K * 2;
     static constexpr int kStageBytes = kABytes + kBBytes;
     static constexpr int kTmemCols = 2 * BN;  // double-buffered accumulator
-    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+    // epilogue staging: one 32-row x 64-col bf16 slab (4 KB, 128B-swizzled) per epilogue warp for the TMA store path
+    static constexpr int kCStageBytes = BN >= 128 ? kEpiWarps * 4096 : 0;
+    static constexpr int kBiasBytes = 1024;  // BN floats
+    static constexpr int kSmemBytes =
+        kStages * kStageBytes + kCStageBytes + kBiasBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
 __device__ __forceinline__ float apply_act(float v, int act) {
@@ -84,12 +89,14 @@ __device__ __forceinline__ TileCoord tile_coord(int tile, int m_tiles, int n_til
 
 template <bool A_MN, bool B_MN, int BN>
 __global__ void __launch_bounds__(kNumThreads, 1)
-gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, int M, int N,
-                 int K, int splits, Epilogue ep) {
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                 const __grid_constant__ CUtensorMap tmap_c, int M, int N, int K, int splits, Epilogue ep) {
     using C = Cfg<BN>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+    uint8_t* stage_c = smem + C::kStages * C::kStageBytes;                       // 1024-aligned
+    float* s_bias = reinterpret_cast<float*>(stage_c + C::kCStageBytes);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(stage_c + C::kCStageBytes + C::kBiasBytes);
     uint64_t* full_bar = bars;
     uint64_t* empty_bar = bars + C::kStages;
     uint64_t* tmem_full = bars + 2 * C::kStages;
@@ -102,6 +109,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmap_a);
         tma_prefetch_desc(&tmap_b);
+        if (ep.tma_store) tma_prefetch_desc(&tmap_c);
     }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < C::kStages; ++i) {
@@ -193,6 +201,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         // ===================== epilogue (warps 2..9) =====================
         const int quarter = warp & 3;          // TMEM lane quarter this warp may access
         const int half = (warp - 2) >> 2;      // which of the two warps sharing the quarter
+        const int etid = threadIdx.x - 64;     // 0..255 among the epilogue threads
         int acc = 0;
         uint32_t acc_phase = 0;
         const bool do_drop = ep.dropout_p > 0.f && ep.rng != nullptr;
@@ -207,140 +216,180 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const float alpha = ep.alpha * (ep.alpha_dev ? __ldg(ep.alpha_dev) : 1.f);
         const bool vec_c = ep.c_fp32 ? ((ep.ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(ep.C) & 15) == 0)
                                      : ((ep.ldc & 7) == 0 && (reinterpret_cast<uintptr_t>(ep.C) & 15) == 0);
-        const bool vec_bias = ep.bias && (reinterpret_cast<uintptr_t>(ep.bias) & 15) == 0;
         const bool vec_aux = ep.aux_mode && (ep.ldaux & 7) == 0 && (reinterpret_cast<uintptr_t>(ep.aux) & 15) == 0;
+        const bool use_tma_store = C::kCStageBytes > 0 && ep.tma_store != 0;
+        uint8_t* my_stage = stage_c + (warp - 2) * 4096;
+
+        // fused math on 32 consecutive accumulator columns of one row (ct = column offset inside the tile)
+        auto epi_math = [&](float (&v)[32], const uint32_t (&r)[32], int row, int col0, int ct) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * alpha;
+            if (ep.bias) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] += s_bias[ct + j];  // smem broadcast; zero beyond N
+            }
+            if (ep.act) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], ep.act);
+            }
+            if (do_drop) {
+                // element index row*N + col; N % 4 == 0 and col0 % 4 == 0 make each group of 4 share one hash
+                const uint64_t base = static_cast<uint64_t>(row) * static_cast<uint64_t>(N) + col0;
+                if ((N & 3) == 0) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) {
+                        const uint64_t bits = rng_bits4(key, (base + j) >> 2);
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            const uint32_t rr = static_cast<uint32_t>(bits >> (q * 16)) & 0xFFFFu;
+                            v[j + q] = rr >= thr16 ? v[j + q] * keep_scale : 0.f;
+                        }
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = rng_keep(key, base + j, thr16) ? v[j] * keep_scale : 0.f;
+                }
+            }
+            if (ep.aux_mode && row < M) {
+                const __nv_bfloat16* ax = ep.aux + static_cast<long long>(row) * ep.ldaux + col0;
+                float a[32];
+                if (col0 + 32 <= N && vec_aux) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const uint4 u = __ldg(reinterpret_cast<const uint4*>(ax) + j);
+                        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            const float2 f = __bfloat1622float2(h[q]);
+                            a[8 * j + 2 * q] = f.x;
+                            a[8 * j + 2 * q + 1] = f.y;
+                        }
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) a[j] = col0 + j < N ? __bfloat162float(ax[j]) : 0.f;
+                }
+                if (ep.aux_mode == 1) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = a[j] > 0.f ? v[j] * ep.aux_scale : 0.f;
+                } else if (ep.aux_mode == 2) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] += a[j];
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] *= a[j] * (1.f - a[j]);
+                }
+            }
+        };
+
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
             const TileCoord t = tile_coord(tile, m_tiles, n_tiles, BN, k_blocks, splits);
+            if (ep.bias) {  // stage this tile's bias slice once (overlaps the MMA of this tile)
+                named_bar_sync(1, kEpiWarps * 32);  // everyone is done with the previous tile's slice
+                if (etid < BN) s_bias[etid] = t.n0 + etid < N ? __ldg(ep.bias + t.n0 + etid) : 0.f;
+                named_bar_sync(1, kEpiWarps * 32);
+            }
             mbar_wait(&tmem_full[acc], acc_phase);
             tc_fence_after();
             const int row = t.m0 + quarter * 32 + lane;
             const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BN;
+            if (use_tma_store) {
+                // this warp owns columns [half*BN/2, (half+1)*BN/2) of the tile, in 64-column slabs
+                const int cbase = half * (BN / 2);
 #pragma unroll 1
-            for (int c = half * 32; c < BN; c += 64) {
-                if (t.n0 + c >= N) break;  // warp-uniform
-                uint32_t r[32];
-                tmem_ld_32x32b_x32(taddr + c, r);
-                tmem_ld_wait();
-                if (row >= M) continue;
-                const int col0 = t.n0 + c;
-                const bool full = col0 + 32 <= N;
-                if (ep.splitk_ws) {  // raw partial sums; the reduce kernel applies alpha and the store mode
-                    float* out = ep.splitk_ws + ((long long)t.split * M + row) * N + col0;
-                    if (full && (N & 3) == 0) {
+                for (int g = 0; g < BN / 2; g += 64) {
+                    const int c = cbase + g;
+                    if (t.n0 + c >= N) break;  // warp-uniform
+                    uint32_t r0[32], r1[32];
+                    tmem_ld_32x32b_x32(taddr + c, r0);
+                    tmem_ld_32x32b_x32(taddr + c + 32, r1);
+                    tmem_ld_wait();
+                    float v0[32], v1[32];
+                    epi_math(v0, r0, row, t.n0 + c, c);
+                    epi_math(v1, r1, row, t.n0 + c + 32, c + 32);
+                    if (lane == 0) tma_store_wait_read<0>();  // previous slab has left this warp's staging buffer
+                    __syncwarp();
 #pragma unroll
-                        for (int j = 0; j < 32; j += 4)
-                            *reinterpret_cast<uint4*>(out + j) = make_uint4(r[j], r[j + 1], r[j + 2], r[j + 3]);
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            if (col0 + j < N) out[j] = __uint_as_float(r[j]);
+                    for (int j = 0; j < 4; ++j) {
+                        uint4 o;
+                        o.x = pack_bf16x2(v0[8 * j], v0[8 * j + 1]);
+                        o.y = pack_bf16x2(v0[8 * j + 2], v0[8 * j + 3]);
+                        o.z = pack_bf16x2(v0[8 * j + 4], v0[8 * j + 5]);
+                        o.w = pack_bf16x2(v0[8 * j + 6], v0[8 * j + 7]);
+                        *reinterpret_cast<uint4*>(my_stage + swz128_offset(lane, j)) = o;
+                        o.x = pack_bf16x2(v1[8 * j], v1[8 * j + 1]);
+                        o.y = pack_bf16x2(v1[8 * j + 2], v1[8 * j + 3]);
+                        o.z = pack_bf16x2(v1[8 * j + 4], v1[8 * j + 5]);
+                        o.w = pack_bf16x2(v1[8 * j + 6], v1[8 * j + 7]);
+                        *reinterpret_cast<uint4*>(my_stage + swz128_offset(lane, 4 + j)) = o;
                     }
-                    continue;
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) {
+                        tma_store_2d(&tmap_c, my_stage, t.n0 + c, t.m0 + quarter * 32);  // edges clipped by TMA
+                        tma_store_commit();
+                    }
                 }
-                float v[32];
+            } else {
+#pragma unroll 1
+                for (int c = half * 32; c < BN; c += 64) {
+                    if (t.n0 + c >= N) break;  // warp-uniform
+                    uint32_t r[32];
+                    tmem_ld_32x32b_x32(taddr + c, r);
+                    tmem_ld_wait();
+                    if (row >= M) continue;
+                    const int col0 = t.n0 + c;
+                    const bool full = col0 + 32 <= N;
+                    if (ep.splitk_ws) {  // raw partial sums; the reduce kernel applies alpha and the store mode
+                        float* out = ep.splitk_ws + ((long long)t.split * M + row) * N + col0;
+                        if (full && (N & 3) == 0) {
 #pragma unroll
-                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * alpha;
-                if (ep.bias) {
-                    if (full && vec_bias) {
-                        const float4* b4 = reinterpret_cast<const float4*>(ep.bias + col0);
+                            for (int j = 0; j < 32; j += 4)
+                                *reinterpret_cast<uint4*>(out + j) = make_uint4(r[j], r[j + 1], r[j + 2], r[j + 3]);
+                        } else {
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const float4 b = __ldg(b4 + j);
-                            v[4 * j] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
+                            for (int j = 0; j < 32; ++j)
+                                if (col0 + j < N) out[j] = __uint_as_float(r[j]);
                         }
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            if (col0 + j < N) v[j] += __ldg(ep.bias + col0 + j);
+                        continue;
                     }
-                }
-                if (ep.act) {
+                    float v[32];
+                    epi_math(v, r, row, col0, c);
+                    if (ep.c_fp32) {
+                        float* out = reinterpret_cast<float*>(ep.C) + static_cast<long long>(row) * ep.ldc + col0;
+                        if (full && vec_c) {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], ep.act);
-                }
-                if (do_drop) {
-                    // element index row*N + col; N % 4 == 0 and col0 % 4 == 0 make each group of 4 share one hash
-                    const uint64_t base = static_cast<uint64_t>(row) * static_cast<uint64_t>(N) + col0;
-                    if ((N & 3) == 0) {
-#pragma unroll
-                        for (int j = 0; j < 32; j += 4) {
-                            const uint64_t bits = rng_bits4(key, (base + j) >> 2);
-#pragma unroll
-                            for (int q = 0; q < 4; ++q) {
-                                const uint32_t rr = static_cast<uint32_t>(bits >> (q * 16)) & 0xFFFFu;
-                                v[j + q] = rr >= thr16 ? v[j + q] * keep_scale : 0.f;
+                            for (int j = 0; j < 32; j += 4) {
+                                float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                                if (ep.accumulate) {
+                                    const float4 old = *reinterpret_cast<const float4*>(out + j);
+                                    o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
+                                }
+                                *reinterpret_cast<float4*>(out + j) = o;
                             }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (col0 + j < N) out[j] = ep.accumulate ? out[j] + v[j] : v[j];
                         }
                     } else {
+                        __nv_bfloat16* out =
+                            reinterpret_cast<__nv_bfloat16*>(ep.C) + static_cast<long long>(row) * ep.ldc + col0;
+                        if (full && vec_c) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            v[j] = rng_keep(key, base + j, thr16) ? v[j] * keep_scale : 0.f;
-                    }
-                }
-                if (ep.aux_mode) {
-                    const __nv_bfloat16* ax = ep.aux + static_cast<long long>(row) * ep.ldaux + col0;
-                    float a[32];
-                    if (full && vec_aux) {
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            const uint4 u = __ldg(reinterpret_cast<const uint4*>(ax) + j);
-                            const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
-#pragma unroll
-                            for (int q = 0; q < 4; ++q) {
-                                const float2 f = __bfloat1622float2(h[q]);
-                                a[8 * j + 2 * q] = f.x;
-                                a[8 * j + 2 * q + 1] = f.y;
+                            for (int j = 0; j < 32; j += 8) {
+                                uint4 o;
+                                o.x = pack_bf16x2(v[j], v[j + 1]);
+                                o.y = pack_bf16x2(v[j + 2], v[j + 3]);
+                                o.z = pack_bf16x2(v[j + 4], v[j + 5]);
+                                o.w = pack_bf16x2(v[j + 6], v[j + 7]);
+                                *reinterpret_cast<uint4*>(out + j) = o;
                             }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (col0 + j < N) out[j] = __float2bfloat16(v[j]);
                         }
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) a[j] = col0 + j < N ? __bfloat162float(ax[j]) : 0.f;
-                    }
-                    if (ep.aux_mode == 1) {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] = a[j] > 0.f ? v[j] * ep.aux_scale : 0.f;
-                    } else if (ep.aux_mode == 2) {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] += a[j];
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] *= a[j] * (1.f - a[j]);
-                    }
-                }
-                if (ep.c_fp32) {
-                    float* out = reinterpret_cast<float*>(ep.C) + static_cast<long long>(row) * ep.ldc + col0;
-                    if (full && vec_c) {
-#pragma unroll
-                        for (int j = 0; j < 32; j += 4) {
-                            float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-                            if (ep.accumulate) {
-                                const float4 old = *reinterpret_cast<const float4*>(out + j);
-                                o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
-                            }
-                            *reinterpret_cast<float4*>(out + j) = o;
-                        }
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            if (col0 + j < N) out[j] = ep.accumulate ? out[j] + v[j] : v[j];
-                    }
-                } else {
-                    __nv_bfloat16* out =
-                        reinterpret_cast<__nv_bfloat16*>(ep.C) + static_cast<long long>(row) * ep.ldc + col0;
-                    if (full && vec_c) {
-#pragma unroll
-                        for (int j = 0; j < 32; j += 8) {
-                            uint4 o;
-                            o.x = pack_bf16x2(v[j], v[j + 1]);
-                            o.y = pack_bf16x2(v[j + 2], v[j + 3]);
-                            o.z = pack_bf16x2(v[j + 4], v[j + 5]);
-                            o.w = pack_bf16x2(v[j + 6], v[j + 7]);
-                            *reinterpret_cast<uint4*>(out + j) = o;
-                        }
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            if (col0 + j < N) out[j] = __float2bfloat16(v[j]);
                     }
                 }
             }
@@ -349,6 +398,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             if (lane == 0) mbar_arrive(&tmem_empty[acc]);
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
+        if (use_tma_store && lane == 0) tma_store_wait_all<0>();  // global writes done before the CTA retires
     }
 
     tc_fence_before();
@@ -450,6 +500,15 @@ static int launch(const b200ml_gemm_args* g, Epilogue ep, int splits, cudaStream
         else       { dims[0] = g->N; dims[1] = g->K; box[0] = 64; box[1] = BLOCK_K; }
         if (make_tmap_bf16(&tb, g->B, 2, dims, strides, box)) return -1;
     }
+    CUtensorMap tc = ta;  // placeholder when the TMA-store epilogue is off
+    ep.tma_store = 0;
+    if (C::kCStageBytes > 0 && splits == 1 && !g->c_fp32 && !g->accumulate && (g->ldc % 8 == 0) &&
+        ((reinterpret_cast<uintptr_t>(g->C) & 15) == 0) && g->epilogue_direct == 0) {
+        uint64_t dims[2] = {(uint64_t)g->N, (uint64_t)g->M}, strides[2] = {2, (uint64_t)g->ldc * 2};
+        uint32_t box[2] = {64, 32};
+        if (make_tmap_bf16(&tc, g->C, 2, dims, strides, box)) return -1;
+        ep.tma_store = 1;
+    }
     auto kern = gemm_bf16_kernel<A_MN, B_MN, BN>;
     static bool attr_set = false;  // per instantiation
     if (!attr_set) {
@@ -460,7 +519,7 @@ static int launch(const b200ml_gemm_args* g, Epilogue ep, int splits, cudaStream
     const int tiles = m_tiles * n_tiles * splits;
     const int grid = tiles < sm_count() ? tiles : sm_count();
     if (splits > 1) ep.splitk_ws = reinterpret_cast<float*>(g->workspace);
-    kern<<<grid, kNumThreads, C::kSmemBytes, stream>>>(ta, tb, g->M, g->N, g->K, splits, ep);
+    kern<<<grid, kNumThreads, C::kSmemBytes, stream>>>(ta, tb, tc, g->M, g->N, g->K, splits, ep);
     B200_CHECK_CUDA(cudaGetLastError());
     if (splits > 1) {
         const long long mn = (long long)g->M * g->N;
@@ -497,6 +556,7 @@ extern "C" int b200ml_gemm_bf16(const b200ml_gemm_args* g, cudaStream_t stream) 
     ep.accumulate = g->accumulate; ep.dropout_p = g->dropout_p;
     ep.rng = reinterpret_cast<const RngState*>(g->rng_state); ep.rng_site = g->rng_site;
     ep.splitk_ws = nullptr;
+    ep.tma_store = 0;
 
     const bool tma_ok = (g->lda % 8 == 0) && (g->ldb % 8 == 0) && ((reinterpret_cast<uintptr_t>(g->A) & 15) == 0) &&
                         ((reinterpret_cast<uintptr_t>(g->B) & 15) == 0) && g->force_simt == 0;

@@ -52,6 +52,7 @@ typedef struct {
     int force_simt;  /* testing: run the SIMT fallback */
     int split_k;     /* 0 = auto, 1 = never, n > 1 = request n K-splits (plain epilogue only; needs workspace) */
     void* workspace; size_t workspace_bytes; /* fp32 scratch for split-K partial tiles (optional) */
+    int epilogue_direct; /* testing: 1 = register->global stores even where the TMA-store epilogue applies */
 } b200ml_gemm_args;
 int b200ml_gemm_bf16(const b200ml_gemm_args* args, cudaStream_t stream);
 

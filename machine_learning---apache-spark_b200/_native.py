@@ -41,6 +41,7 @@ class GemmArgs(C.Structure):
         ("force_simt", C.c_int),
         ("split_k", C.c_int),
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
+        ("epilogue_direct", C.c_int),
     ]
 
 

@@ -138,3 +138,26 @@ def test_gemm_split_k_wgrad_shape(split_k):
     _check(acc, 0.5 * ref + 1, rows)
     o16 = gemm(dy, x, a_mn=True, b_mn=True, split_k=split_k)
     _check(o16, ref, rows, tol_scale=2.0)
+
+
+@pytest.mark.parametrize("M,N,K", [(6400, 1536, 512), (200, 19214, 512), (333, 200, 128), (128, 136, 64)])
+def test_gemm_tma_store_epilogue_matches_direct(M, N, K):
+    """bf16 outputs leave through swizzled smem + cp.async.bulk.tensor stores; the register->global path is the oracle
+    (edges in M and N, padded leading dimension, bias + ReLU + residual epilogue)."""
+    from b200ml.ops.gemm import gemm
+    torch.manual_seed(5)
+    a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
+    b = (torch.randn(N, K, device="cuda") * 0.2).to(torch.bfloat16)
+    bias = torch.randn(N, device="cuda")
+    ld = (N + 7) // 8 * 8 + 8
+    aux = torch.randn(M, ld, device="cuda").to(torch.bfloat16)
+    outs = []
+    for direct in (False, True):
+        out = torch.full((M, ld), 7.0, dtype=torch.bfloat16, device="cuda")
+        gemm(a, b, out=out, bias=bias, act="relu", aux=aux, aux_mode=2, n_logical=N, epilogue_direct=direct)
+        outs.append(out)
+    torch.cuda.synchronize()
+    assert torch.equal(outs[0][:, :N], outs[1][:, :N])
+    assert (outs[0][:, N:] == 7.0).all()            # padding columns untouched
+    ref = torch.relu(a.float() @ b.float().t() + bias) + aux[:, :N].float()
+    _check(outs[0][:, :N], ref.cpu(), K, tol_scale=2.0)
