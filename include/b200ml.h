@@ -160,22 +160,24 @@ int b200ml_conv3x3_relu_bwd(const float* dy, const float* ysaved, const unsigned
                             int Cin, int Cout, int H, int W, int pool, int accumulate, cudaStream_t stream);
 
 /* ------------------------------------------------------------------------------------------------ K9 LSTM
- * One persistent kernel per layer and direction of time.  fp32; x [B,T,K] (K <= 32), hidden must be 32,
- * w_ih [128,K], w_hh [128,32], gate order i,f,g,o; h0/c0/h_n/c_n [B,32]; h_out [B,T,32];
- * gates_out [T,B,4,32] and c_out [T,B,32] are the activations saved for backward (both NULL at inference).
- * dropout_p > 0 applies inter-layer dropout to the layer INPUT (regenerated, not stored, in backward).
+ * The sequential part of one LSTM layer as a persistent kernel per direction of time (hidden must be 32, fp32):
+ *   forward : pre [B,T,128] = X·W_ihᵀ + b_ih + b_hh (hoisted GEMM) -> h_out [B,T,32], h_n, c_n [B,32];
+ *             gates_out [B,T,128] (i,f,g,o after their nonlinearity) and c_out [B,T,32] are saved for backward
+ *             (both NULL at inference).
+ *   backward: dh_seq [B,T,32] (may be NULL), dh_n / dc_n -> dg_out [B,T,128] bf16 (pre-activation gate gradients, the
+ *             operand of the hoisted dW_ih / dW_hh / dX / db GEMMs), dh0, dc0.
+ * b200ml_dropout_cast / _bwd: (inter-layer) dropout + fp32->bf16 cast and its backward with the mask regenerated.
  * ref: nn.LSTM inside the classifier (distributed_lstm.py:118-119,131). */
-int b200ml_lstm_layer_fwd(const float* x, const float* w_ih, const float* w_hh, const float* b_ih, const float* b_hh,
-                          const float* h0, const float* c0, float* h_out, float* gates_out, float* c_out, float* h_n,
-                          float* c_n, int B, int T, int K, int hidden, float dropout_p, const void* rng_state,
-                          unsigned rng_site, cudaStream_t stream);
-size_t b200ml_lstm_bwd_scratch_bytes(int B);
-int b200ml_lstm_layer_bwd(const float* x, const float* w_ih, const float* w_hh, const float* h0, const float* c0,
-                          const float* h_out, const float* gates, const float* c_seq, const float* dh_seq,
-                          const float* dh_n, const float* dc_n, float* dx, float* dh0, float* dc0, float* dw_ih,
-                          float* dw_hh, float* db_ih, float* db_hh, void* scratch, size_t scratch_bytes, int B, int T,
-                          int K, int hidden, float dropout_p, const void* rng_state, unsigned rng_site, int accumulate,
-                          cudaStream_t stream);
+int b200ml_lstm_rec_fwd(const float* pre, const float* w_hh, const float* h0, const float* c0, float* h_out,
+                        float* gates_out, float* c_out, float* h_n, float* c_n, int B, int T, int hidden,
+                        cudaStream_t stream);
+int b200ml_lstm_rec_bwd(const float* w_hh, const float* c0, const float* gates, const float* c_seq,
+                        const float* dh_seq, const float* dh_n, const float* dc_n, void* dg_out_bf16, float* dh0,
+                        float* dc0, int B, int T, int hidden, cudaStream_t stream);
+int b200ml_dropout_cast(const float* x, void* out_bf16, long long n, float p, const void* rng_state, unsigned rng_site,
+                        cudaStream_t stream);
+int b200ml_dropout_bwd(const void* g, int g_fp32, float* dx, long long n, float p, const void* rng_state,
+                       unsigned rng_site, cudaStream_t stream);
 
 /* ------------------------------------------------------------------------------------------------ K18 all-reduce
  * Symmetric buffers: b200ml_comm_alloc ALLOCATES (cudaMalloc + zero fill) — it is the set-up-time allocator for

@@ -1,4 +1,11 @@
-"""Autograd wrapper of the persistent LSTM layer kernels (csrc/kernels/lstm.cu)."""
+"""Stacked LSTM on the GPU (csrc/kernels/lstm.cu + the tcgen05 GEMM).
+
+Per layer, forward:   x16 = dropout(x).bf16  ->  pre = x16·W_ihᵀ + (b_ih + b_hh)   [one GEMM over all B·T rows]
+                      ->  persistent recurrence kernel (h_t = cell(pre_t + h_{t-1}·W_hhᵀ), fp32)
+           backward:  persistent reverse recurrence -> dG [B·T, 128] (bf16)
+                      ->  dW_ih = dGᵀ·x16,  dW_hh = dGᵀ·H_prev,  db = colsum(dG),  dX = dG·W_ih   [hoisted GEMMs]
+Reference: nn.LSTM(E, 32, num_layers=2, batch_first=True, dropout=0.5) (distributed_lstm.py:118-119,131).
+"""
 from __future__ import annotations
 
 import ctypes as C
@@ -6,13 +13,14 @@ import ctypes as C
 import torch
 
 from .. import _native, _native_ext
-from ..utils import workspace
 from ..utils.rng import DeviceCounters
+from .gemm import colsum, deliver_grad, gemm
 
-vp, i, f, sz, u = C.c_void_p, C.c_int, C.c_float, C.c_size_t, C.c_uint
-_native_ext.register("b200ml_lstm_layer_fwd", [vp] * 12 + [i, i, i, i, f, vp, u, vp])
-_native_ext.register("b200ml_lstm_bwd_scratch_bytes", [i], size_t_return=True)
-_native_ext.register("b200ml_lstm_layer_bwd", [vp] * 19 + [sz, i, i, i, i, f, vp, u, i, vp])
+vp, i, f, ll, u = C.c_void_p, C.c_int, C.c_float, C.c_longlong, C.c_uint
+_native_ext.register("b200ml_lstm_rec_fwd", [vp] * 9 + [i, i, i, vp])
+_native_ext.register("b200ml_lstm_rec_bwd", [vp] * 10 + [i, i, i, vp])
+_native_ext.register("b200ml_dropout_cast", [vp, vp, ll, f, vp, u, vp])
+_native_ext.register("b200ml_dropout_bwd", [vp, i, vp, ll, f, vp, u, vp])
 
 
 class _LSTMStack(torch.autograd.Function):
@@ -22,33 +30,39 @@ class _LSTMStack(torch.autograd.Function):
         dev = x.device
         B, T, _ = x.shape
         H = weights[1].shape[1]
+        st = _native.stream_ptr()
         x = x.float().contiguous()
         h0 = h0.float().contiguous()
         c0 = c0.float().contiguous()
         rng = DeviceCounters.get(dev).rng.data_ptr() if dropout_p > 0 else None
+        need_grad = any(w.requires_grad for w in weights) or x.requires_grad
         inp = x
         saved = []
         h_n = torch.empty(num_layers, B, H, dtype=torch.float32, device=dev)
         c_n = torch.empty(num_layers, B, H, dtype=torch.float32, device=dev)
-        need_grad = any(w.requires_grad for w in weights) or x.requires_grad
         for layer in range(num_layers):
-            w_ih, w_hh, b_ih, b_hh = [w.detach().float().contiguous() for w in weights[4 * layer:4 * layer + 4]]
+            w_ih, w_hh, b_ih, b_hh = weights[4 * layer:4 * layer + 4]
             K = inp.shape[2]
-            h_out = torch.empty(B, T, H, dtype=torch.float32, device=dev)
-            gates = torch.empty(T, B, 4, H, dtype=torch.float32, device=dev) if need_grad else None
-            c_seq = torch.empty(T, B, H, dtype=torch.float32, device=dev) if need_grad else None
             p = dropout_p if layer > 0 else 0.0
-            _native.check(lib.b200ml_lstm_layer_fwd(
-                inp.data_ptr(), w_ih.data_ptr(), w_hh.data_ptr(), b_ih.data_ptr(), b_hh.data_ptr(),
-                h0[layer].data_ptr(), c0[layer].data_ptr(), h_out.data_ptr(), _native.ptr(gates), _native.ptr(c_seq),
-                h_n[layer].data_ptr(), c_n[layer].data_ptr(), B, T, K, H, p, rng if p > 0 else None, site + layer,
-                _native.stream_ptr()), "lstm_layer_fwd")
-            saved.append((inp, w_ih, w_hh, h_out, gates, c_seq, p))
+            x16 = torch.empty(B * T, K, dtype=torch.bfloat16, device=dev)
+            _native.check(lib.b200ml_dropout_cast(inp.data_ptr(), x16.data_ptr(), B * T * K, p, rng if p > 0 else None,
+                                                  site + layer, st), "dropout_cast")
+            w_ih16 = w_ih.detach().to(torch.bfloat16)
+            bias = (b_ih.detach().float() + b_hh.detach().float()).contiguous()
+            pre = gemm(x16, w_ih16, bias=bias, out_dtype=torch.float32)          # [B*T, 4H]
+            w_hh32 = w_hh.detach().float().contiguous()
+            h_out = torch.empty(B, T, H, dtype=torch.float32, device=dev)
+            gates = torch.empty(B, T, 4 * H, dtype=torch.float32, device=dev) if need_grad else None
+            c_seq = torch.empty(B, T, H, dtype=torch.float32, device=dev) if need_grad else None
+            _native.check(lib.b200ml_lstm_rec_fwd(pre.data_ptr(), w_hh32.data_ptr(), h0[layer].data_ptr(),
+                                                  c0[layer].data_ptr(), h_out.data_ptr(), _native.ptr(gates),
+                                                  _native.ptr(c_seq), h_n[layer].data_ptr(), c_n[layer].data_ptr(), B,
+                                                  T, H, st), "lstm_rec_fwd")
+            saved.append((x16, w_ih16, w_hh32, h_out, gates, c_seq, p, K))
             inp = h_out
         ctx.saved = saved
         ctx.state = (h0, c0, num_layers, site, B, T, H)
         ctx.weights = weights
-        ctx.mark_non_differentiable()
         return inp, h_n, c_n
 
     @staticmethod
@@ -57,8 +71,8 @@ class _LSTMStack(torch.autograd.Function):
         h0, c0, num_layers, site, B, T, H = ctx.state
         weights = ctx.weights
         dev = d_out.device
+        st = _native.stream_ptr()
         rngp = DeviceCounters.get(dev).rng.data_ptr()
-        ws = workspace.get("lstm_bwd", lib.b200ml_lstm_bwd_scratch_bytes(B), dev)
         d_seq = d_out.float().contiguous()
         d_hn = None if d_hn is None else d_hn.float().contiguous()
         d_cn = None if d_cn is None else d_cn.float().contiguous()
@@ -67,37 +81,40 @@ class _LSTMStack(torch.autograd.Function):
         grads = [None] * len(weights)
         dx = None
         for layer in range(num_layers - 1, -1, -1):
-            inp, w_ih, w_hh, h_out, gates, c_seq, p = ctx.saved[layer]
-            K = inp.shape[2]
-            prm = weights[4 * layer:4 * layer + 4]
-            slots = [getattr(w, "_b200_grad", None) for w in prm]
-            direct = all(s is not None for s in slots)
-            if direct:
-                outs = slots
-                acc = int(bool(getattr(prm[0], "_b200_grad_accumulate", False)))
-            else:
-                outs = [torch.empty(w.numel(), dtype=torch.float32, device=dev) for w in prm]
-                acc = 0
-            need_dx = layer > 0 or ctx.needs_input_grad[0]
-            dx = torch.empty(B, T, K, dtype=torch.float32, device=dev) if need_dx else None
-            _native.check(lib.b200ml_lstm_layer_bwd(
-                inp.data_ptr(), w_ih.data_ptr(), w_hh.data_ptr(), h0[layer].data_ptr(), c0[layer].data_ptr(),
-                h_out.data_ptr(), gates.data_ptr(), c_seq.data_ptr(), _native.ptr(d_seq),
+            x16, w_ih16, w_hh32, h_out, gates, c_seq, p, K = ctx.saved[layer]
+            w_ih, w_hh, b_ih, b_hh = weights[4 * layer:4 * layer + 4]
+            dg = torch.empty(B * T, 4 * H, dtype=torch.bfloat16, device=dev)
+            _native.check(lib.b200ml_lstm_rec_bwd(
+                w_hh32.data_ptr(), c0[layer].data_ptr(), gates.data_ptr(), c_seq.data_ptr(), _native.ptr(d_seq),
                 None if d_hn is None else d_hn[layer].data_ptr(), None if d_cn is None else d_cn[layer].data_ptr(),
-                _native.ptr(dx), dh0[layer].data_ptr(), dc0[layer].data_ptr(), outs[0].data_ptr(), outs[1].data_ptr(),
-                outs[2].data_ptr(), outs[3].data_ptr(), ws.data_ptr(), ws.numel(), B, T, K, H, p,
-                rngp if p > 0 else None, site + layer, acc, _native.stream_ptr()), "lstm_layer_bwd")
-            if direct:
-                for w in prm:
-                    ready = getattr(w, "_b200_ready", None)
-                    if ready is not None:
-                        ready()
+                dg.data_ptr(), dh0[layer].data_ptr(), dc0[layer].data_ptr(), B, T, H, st), "lstm_rec_bwd")
+            # input gradient first (reads W_ih), then the parameter gradients (may release their bucket)
+            need_dx = layer > 0 or ctx.needs_input_grad[0]
+            if need_dx:
+                dxd = gemm(dg, w_ih16, b_mn=True, out_dtype=torch.float32)       # d(dropped input) [B*T, K]
+                if p > 0:
+                    dx = torch.empty(B, T, K, dtype=torch.float32, device=dev)
+                    _native.check(lib.b200ml_dropout_bwd(dxd.data_ptr(), 1, dx.data_ptr(), B * T * K, p, rngp,
+                                                         site + layer, st), "dropout_bwd")
+                else:
+                    dx = dxd.view(B, T, K)
             else:
-                for j, w in enumerate(prm):
-                    grads[4 * layer + j] = outs[j].view_as(w)
+                dx = None
+            hprev16 = torch.cat([h0[layer].unsqueeze(1), h_out[:, :-1, :]], dim=1).reshape(B * T, H).to(torch.bfloat16)
+            if w_ih.requires_grad:
+                grads[4 * layer] = deliver_grad(w_ih, lambda out, acc, g=dg, a=x16: gemm(
+                    g, a, a_mn=True, b_mn=True, out=out, accumulate=acc), (4 * H, K))
+            if w_hh.requires_grad:
+                grads[4 * layer + 1] = deliver_grad(w_hh, lambda out, acc, g=dg, a=hprev16: gemm(
+                    g, a, a_mn=True, b_mn=True, out=out, accumulate=acc), (4 * H, H))
+            for j, b in ((2, b_ih), (3, b_hh)):
+                if b.requires_grad:
+                    grads[4 * layer + j] = deliver_grad(b, lambda out, acc, g=dg: colsum(g, out=out, accumulate=acc),
+                                                        (4 * H,))
             d_seq = dx
         return (dx if ctx.needs_input_grad[0] else None, dh0, dc0, None, None, None, *grads)
 
 
 def lstm_forward(x, h0, c0, weights, num_layers, dropout_p, site):
+    assert weights[1].shape[1] == 32, "the LSTM kernels are specialised for hidden_size 32 (the reference value)"
     return _LSTMStack.apply(x, h0, c0, num_layers, dropout_p, site, *weights)
