@@ -25,7 +25,12 @@ constexpr int kThreads = 512;
 
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }
 
+__device__ __forceinline__ float tanhf_(float x) { return 1.f - 2.f / (1.f + __expf(2.f * x)); }
+
 // pre: [B][T][G] (input projection + both biases); gates_out: [B][T][G] activations; c_out: [B][T][H]; h_out: [B][T][H]
+// Phase A (gate pre-activations): thread = (gate row r, 8 batch rows), W_hh row in registers, h broadcast from smem.
+// Phase B (cell update):          thread = (hidden unit = lane, 2 batch rows): every global access of a warp is one
+//                                 128-byte line (32 consecutive units of one (b, t)).
 __global__ void __launch_bounds__(kThreads)
 lstm_rec_fwd_kernel(const float* __restrict__ pre, const float* __restrict__ w_hh, const float* __restrict__ h0,
                     const float* __restrict__ c0, float* __restrict__ h_out, float* __restrict__ gates_out,
@@ -34,18 +39,15 @@ lstm_rec_fwd_kernel(const float* __restrict__ pre, const float* __restrict__ w_h
     __shared__ float s_g[G][BT + 1];                 // gate activations, [gate row][batch]
     const int tid = threadIdx.x;
     const int b0 = blockIdx.x * BT;
-    // phase A mapping: gate row r, 8 batch rows
-    const int r = tid & (G - 1), bq = tid >> 7;
+    const int r = tid & (G - 1), bq = tid >> 7;      // phase A
     float w[H];
 #pragma unroll
     for (int k = 0; k < H; ++k) w[k] = w_hh[r * H + k];
-    // phase B mapping: batch row lb, units u0 and u0 + 16
-    const int lb = tid & 31, u0 = tid >> 5;
-    const int gb = b0 + lb;
+    const int u = tid & 31, bg = tid >> 5;           // phase B: unit u, batch rows bg and bg + 16
     float c[2];
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
-        const int u = u0 + 16 * j;
+        const int lb = bg + 16 * j, gb = b0 + lb;
         c[j] = (c0 && gb < B) ? c0[(long long)gb * H + u] : 0.f;
         s_h[lb][u] = (h0 && gb < B) ? h0[(long long)gb * H + u] : 0.f;
     }
@@ -61,7 +63,7 @@ lstm_rec_fwd_kernel(const float* __restrict__ pre, const float* __restrict__ w_h
         float acc[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[j] = pnext[j];
-        if (t + 1 < T) {  // prefetch the next step's input projection
+        if (t + 1 < T) {  // prefetch the next step's input projection (128 consecutive floats per batch row)
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
                 const int b = b0 + bq * 8 + j;
@@ -78,14 +80,14 @@ lstm_rec_fwd_kernel(const float* __restrict__ pre, const float* __restrict__ w_h
         }
         const bool is_g = (r >> 5) == 2;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) s_g[r][bq * 8 + j] = is_g ? tanhf(acc[j]) : sigmoidf_(acc[j]);
+        for (int j = 0; j < 8; ++j) s_g[r][bq * 8 + j] = is_g ? tanhf_(acc[j]) : sigmoidf_(acc[j]);
         __syncthreads();
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
-            const int u = u0 + 16 * j;
+            const int lb = bg + 16 * j, gb = b0 + lb;
             const float ig = s_g[u][lb], fg = s_g[H + u][lb], gg = s_g[2 * H + u][lb], og = s_g[3 * H + u][lb];
             c[j] = fg * c[j] + ig * gg;
-            const float hn = og * tanhf(c[j]);
+            const float hn = og * tanhf_(c[j]);
             s_h[lb][u] = hn;
             if (gb < B) {
                 const long long bt = (long long)gb * T + t;
@@ -101,10 +103,10 @@ lstm_rec_fwd_kernel(const float* __restrict__ pre, const float* __restrict__ w_h
         }
         __syncthreads();
     }
-    if (gb < B) {
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {
-            const int u = u0 + 16 * j;
+    for (int j = 0; j < 2; ++j) {
+        const int lb = bg + 16 * j, gb = b0 + lb;
+        if (gb < B) {
             if (h_n) h_n[(long long)gb * H + u] = s_h[lb][u];
             if (c_n) c_n[(long long)gb * H + u] = c[j];
         }
@@ -112,6 +114,7 @@ lstm_rec_fwd_kernel(const float* __restrict__ pre, const float* __restrict__ w_h
 }
 
 // Backward recurrence: produces dG [B][T][G] (pre-activation gate gradients, bf16 for the hoisted GEMMs) and dh0/dc0.
+// Thread = (hidden unit / k index = lane, 2 batch rows) in both phases.
 __global__ void __launch_bounds__(kThreads)
 lstm_rec_bwd_kernel(const float* __restrict__ w_hh, const float* __restrict__ c0, const float* __restrict__ gates,
                     const float* __restrict__ c_seq, const float* __restrict__ dh_seq, const float* __restrict__ dh_n,
@@ -122,26 +125,24 @@ lstm_rec_bwd_kernel(const float* __restrict__ w_hh, const float* __restrict__ c0
     __shared__ float s_dh[BT][H + 1];                // dh_{t} flowing back through time
     const int tid = threadIdx.x;
     const int b0 = blockIdx.x * BT;
-    const int lb = tid & 31, u0 = tid >> 5;
-    const int gb = b0 + lb;
+    const int u = tid & 31, bg = tid >> 5;
     for (int i = tid; i < G * H; i += kThreads) s_wt[i % H][i / H] = w_hh[i];
     float dc[2];
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
-        const int u = u0 + 16 * j;
+        const int lb = bg + 16 * j, gb = b0 + lb;
         dc[j] = (dc_n && gb < B) ? dc_n[(long long)gb * H + u] : 0.f;
         s_dh[lb][u] = (dh_n && gb < B) ? dh_n[(long long)gb * H + u] : 0.f;
     }
     __syncthreads();
 
     for (int t = T - 1; t >= 0; --t) {
-        // cell backward for (batch row lb, units u0, u0+16)
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
-            const int u = u0 + 16 * j;
+            const int lb = bg + 16 * j, gb = b0 + lb;
             float ig = 0.f, fg = 0.f, gg = 0.f, og = 0.f, ct = 0.f, cp = 0.f, dh = s_dh[lb][u];
+            const long long bt = (long long)gb * T + t;
             if (gb < B) {
-                const long long bt = (long long)gb * T + t;
                 ig = gates[bt * G + u];
                 fg = gates[bt * G + H + u];
                 gg = gates[bt * G + 2 * H + u];
@@ -150,7 +151,7 @@ lstm_rec_bwd_kernel(const float* __restrict__ w_hh, const float* __restrict__ c0
                 cp = t > 0 ? c_seq[(bt - 1) * H + u] : (c0 ? c0[(long long)gb * H + u] : 0.f);
                 if (dh_seq) dh += dh_seq[bt * H + u];
             }
-            const float tc = tanhf(ct);
+            const float tc = tanhf_(ct);
             const float d = dc[j] + dh * og * (1.f - tc * tc);
             const float di = d * gg * ig * (1.f - ig), df = d * cp * fg * (1.f - fg), dgg = d * ig * (1.f - gg * gg),
                         dog = dh * tc * og * (1.f - og);
@@ -160,7 +161,6 @@ lstm_rec_bwd_kernel(const float* __restrict__ w_hh, const float* __restrict__ c0
             s_dg[lb][3 * H + u] = dog;
             dc[j] = d * fg;
             if (gb < B) {
-                const long long bt = (long long)gb * T + t;
                 dg_out[bt * G + u] = __float2bfloat16(di);
                 dg_out[bt * G + H + u] = __float2bfloat16(df);
                 dg_out[bt * G + 2 * H + u] = __float2bfloat16(dgg);
@@ -168,25 +168,25 @@ lstm_rec_bwd_kernel(const float* __restrict__ w_hh, const float* __restrict__ c0
             }
         }
         __syncthreads();
-        // dh_{t-1}[b][k] = sum_r dG[b][r] * W_hh[r][k]   for k = u0, u0 + 16
+        // dh_{t-1}[b][k = u] = sum_r dG[b][r] * W_hh[r][k]   for this thread's two batch rows
         float a0 = 0.f, a1 = 0.f;
 #pragma unroll 8
         for (int r4 = 0; r4 < G; r4 += 4) {
-            const float4 d4 = *reinterpret_cast<const float4*>(&s_dg[lb][r4]);
-            const float4 w0 = *reinterpret_cast<const float4*>(&s_wt[u0][r4]);        // broadcast
-            const float4 w1 = *reinterpret_cast<const float4*>(&s_wt[u0 + 16][r4]);   // broadcast
-            a0 += d4.x * w0.x + d4.y * w0.y + d4.z * w0.z + d4.w * w0.w;
-            a1 += d4.x * w1.x + d4.y * w1.y + d4.z * w1.z + d4.w * w1.w;
+            const float4 wv = *reinterpret_cast<const float4*>(&s_wt[u][r4]);
+            const float4 d0 = *reinterpret_cast<const float4*>(&s_dg[bg][r4]);        // broadcast
+            const float4 d1 = *reinterpret_cast<const float4*>(&s_dg[bg + 16][r4]);   // broadcast
+            a0 += d0.x * wv.x + d0.y * wv.y + d0.z * wv.z + d0.w * wv.w;
+            a1 += d1.x * wv.x + d1.y * wv.y + d1.z * wv.z + d1.w * wv.w;
         }
         __syncthreads();  // everyone has consumed s_dh / s_dg of this step
-        s_dh[lb][u0] = a0;
-        s_dh[lb][u0 + 16] = a1;
+        s_dh[bg][u] = a0;
+        s_dh[bg + 16][u] = a1;
         __syncthreads();
     }
-    if (gb < B) {
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {
-            const int u = u0 + 16 * j;
+    for (int j = 0; j < 2; ++j) {
+        const int lb = bg + 16 * j, gb = b0 + lb;
+        if (gb < B) {
             if (dh0) dh0[(long long)gb * H + u] = s_dh[lb][u];
             if (dc0) dc0[(long long)gb * H + u] = dc[j];
         }

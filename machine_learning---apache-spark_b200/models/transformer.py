@@ -27,6 +27,7 @@ from ..ops.embedding import positional_encoding_table
 from ..ops.gemm import linear as _linear
 from ..ops.gemm import mlp_chain as _mlp_chain
 from ..ops.norm import layernorm_residual as _ln_res
+from ..utils import workspace as _workspace
 from ..utils.rng import new_site
 
 
@@ -299,6 +300,7 @@ class Transformer(nn.Module):
         if self.overlap_streams and x.is_cuda and len(self.decoder.layers) > 0:
             if self._dec_stream is None:
                 self._dec_stream = torch.cuda.Stream(device=x.device)
+                _workspace.register_stream(self._dec_stream, 2)
             cur = torch.cuda.current_stream()
             self._dec_stream.wait_stream(cur)
             with torch.cuda.stream(self._dec_stream):

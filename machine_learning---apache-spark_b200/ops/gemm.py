@@ -106,7 +106,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     g.split_k = split_k
     g.epilogue_direct = int(epilogue_direct)
     if split_k != 1 and bias is None and not act and not (aux is not None and aux_mode) and dropout_p <= 0:
-        ws = workspace.get(f"gemm_splitk@{_native.stream_ptr()}", SPLITK_WORKSPACE_BYTES, a.device)  # one per stream
+        ws = workspace.get(f"gemm_splitk@{workspace.lane()}", SPLITK_WORKSPACE_BYTES, a.device)  # one per stream lane
         g.workspace, g.workspace_bytes = ws.data_ptr(), ws.numel()
     _native.check(lib.b200ml_gemm_bf16(C.byref(g), _native.stream_ptr()), "gemm_bf16")
     return out
@@ -123,7 +123,7 @@ def colsum(x: torch.Tensor, out: torch.Tensor | None = None, accumulate: bool = 
         return out
     lib = _native.load()
     nbytes = lib.b200ml_colsum_scratch_bytes(rows, cols)
-    ws = workspace.get(f"colsum@{_native.stream_ptr()}", nbytes, x.device)  # one per stream
+    ws = workspace.get(f"colsum@{workspace.lane()}", nbytes, x.device)  # one per stream lane
     _native.check(lib.b200ml_colsum_bf16(x.data_ptr(), x.stride(0), rows, cols, out.data_ptr(), int(accumulate),
                                          ws.data_ptr(), ws.numel(), _native.stream_ptr()), "colsum")
     return out
@@ -160,6 +160,7 @@ class GradSideStream:
 
     def __init__(self, device):
         self.stream = torch.cuda.Stream(device=device)
+        workspace.register_stream(self.stream, 1)
         self.keep: list = []
         self.active = False
 

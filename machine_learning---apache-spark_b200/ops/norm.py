@@ -68,7 +68,7 @@ class _LayerNormResidual(torch.autograd.Function):
             da = torch.empty_like(z) if ctx.p > 0 else None
             lib = _native.load()
             nbytes = lib.b200ml_layernorm_bwd_scratch_bytes(rows, d)
-            ws = workspace.get(f"ln_bwd@{_native.stream_ptr()}", nbytes, z.device)  # one per stream
+            ws = workspace.get(f"ln_bwd@{workspace.lane()}", nbytes, z.device)  # one per stream lane
             rng = DeviceCounters.get(z.device).rng.data_ptr() if ctx.p > 0 else None
             slot_g = getattr(gamma, "_b200_grad", None)
             slot_b = getattr(beta, "_b200_grad", None)

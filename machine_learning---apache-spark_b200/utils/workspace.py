@@ -8,6 +8,17 @@ from __future__ import annotations
 import torch
 
 _cache: dict = {}
+_lanes: dict = {}   # cuda stream pointer -> small lane id
+
+
+def register_stream(stream, lane: int) -> None:
+    """Give a long-lived side stream its own set of scratch buffers.  Streams that are never registered (the default
+    stream, a CUDA-graph capture stream) share lane 0 — they never run concurrently with each other."""
+    _lanes[stream.cuda_stream] = lane
+
+
+def lane() -> int:
+    return _lanes.get(torch.cuda.current_stream().cuda_stream, 0) if torch.cuda.is_available() else 0
 
 
 def get(name: str, nbytes: int, device) -> torch.Tensor:
