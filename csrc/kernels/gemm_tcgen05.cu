@@ -435,13 +435,15 @@ splitk_reduce_kernel(const float* __restrict__ ws, int splits, long long mn, int
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 gemm_simt_kernel(const __nv_bfloat16* __restrict__ A, long long lda, int a_mn, const __nv_bfloat16* __restrict__ B,
-                 long long ldb, int b_mn, int M, int N, int K, Epilogue ep) {
+                 long long ldb, int b_mn, int M, int N, int K, int k_per_split, Epilogue ep) {
     __shared__ float sa[16][17];
     __shared__ float sb[16][17];
     const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
     const int row = blockIdx.y * 16 + ty, col = blockIdx.x * 16 + tx;
     float acc = 0.f;
-    for (int k0 = 0; k0 < K; k0 += 16) {
+    const int k_begin = blockIdx.z * k_per_split;   // split-K over gridDim.z (long-K, tiny-MN weight gradients)
+    if (k_begin + k_per_split < K) K = k_begin + k_per_split;
+    for (int k0 = k_begin; k0 < K; k0 += 16) {
         {
             const int r = blockIdx.y * 16 + ty, k = k0 + tx;
             float v = 0.f;
@@ -460,6 +462,10 @@ gemm_simt_kernel(const __nv_bfloat16* __restrict__ A, long long lda, int a_mn, c
         __syncthreads();
     }
     if (row >= M || col >= N) return;
+    if (ep.splitk_ws) {  // raw partial; splitk_reduce_kernel applies alpha / accumulate
+        ep.splitk_ws[((long long)blockIdx.z * M + row) * N + col] = acc;
+        return;
+    }
     float v = acc * ep.alpha * (ep.alpha_dev ? *ep.alpha_dev : 1.f);
     if (ep.bias) v += ep.bias[col];
     v = apply_act(v, ep.act);
@@ -562,10 +568,33 @@ extern "C" int b200ml_gemm_bf16(const b200ml_gemm_args* g, cudaStream_t stream) 
                         ((reinterpret_cast<uintptr_t>(g->B) & 15) == 0) && g->force_simt == 0;
     if (!tma_ok) {
         dim3 grid((g->N + 15) / 16, (g->M + 15) / 16);
+        const long long ctas = (long long)grid.x * grid.y;
+        const bool plain_ep = !g->bias && !g->act && !ep.aux_mode && g->dropout_p <= 0.f;
+        int splits = 1;
+        if (plain_ep && g->workspace && g->split_k != 1 && g->K >= 512 && ctas * 2 <= sm_count()) {
+            splits = (int)(2LL * sm_count() / ctas);
+            if (splits > g->K / 64) splits = g->K / 64;
+            while (splits > 1 && (size_t)splits * g->M * g->N * sizeof(float) > g->workspace_bytes) --splits;
+        }
+        int k_per = g->K;
+        if (splits > 1) {
+            k_per = ((g->K + splits - 1) / splits + 15) / 16 * 16;
+            splits = (g->K + k_per - 1) / k_per;
+            grid.z = splits;
+            ep.splitk_ws = reinterpret_cast<float*>(g->workspace);
+        }
         gemm_simt_kernel<<<grid, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(g->A), g->lda, g->a_mn_major,
                                                    reinterpret_cast<const __nv_bfloat16*>(g->B), g->ldb,
-                                                   g->b_mn_major, g->M, g->N, g->K, ep);
+                                                   g->b_mn_major, g->M, g->N, g->K, k_per, ep);
         B200_CHECK_CUDA(cudaGetLastError());
+        if (splits > 1) {
+            const long long mn = (long long)g->M * g->N;
+            long long blocks = (mn + 255) / 256;
+            if (blocks > 4LL * sm_count()) blocks = 4LL * sm_count();
+            splitk_reduce_kernel<<<(int)blocks, 256, 0, stream>>>(ep.splitk_ws, splits, mn, g->N, g->C, g->ldc,
+                                                                  g->c_fp32, g->accumulate, g->alpha, g->alpha_dev);
+            B200_CHECK_CUDA(cudaGetLastError());
+        }
         return 0;
     }
     const int sms = sm_count();

@@ -6,10 +6,16 @@
 // Everything that is NOT sequential is hoisted out of the time loop into tcgen05 GEMMs over all B*T rows at once
 // (ops/lstm_native.py):  forward  pre = X·W_ihᵀ + (b_ih + b_hh);  backward  dW_ih = dGᵀ·X, dW_hh = dGᵀ·H_prev,
 // dX = dG·W_ih, db = colsum(dG).  What remains sequential — h_t = cell(pre_t + h_{t-1}·W_hhᵀ) forward, and
-// dG_t / dh_{t-1} = dG_t·W_hh backward — runs in ONE persistent kernel per layer and direction (this file): a CTA owns
-// 32 batch rows for the whole sequence, W_hh lives in registers / shared memory, h and c never leave the chip, each
-// step is a 128x32x32 product per CTA plus the cell update between two CTA barriers.  fp32 throughout the recurrence,
-// so no rounding error accumulates over time.  hidden_size must be 32 (the reference value).
+// dG_t / dh_{t-1} = dG_t·W_hh backward — runs in ONE persistent kernel per layer and direction (this file).
+//
+// The recurrence is a latency chain of T dependent steps, so the design minimises the length of one step rather than
+// throughput: ONE WARP owns one batch row for the whole sequence.  Lane u owns hidden unit u: it keeps the four W_hh rows
+// (forward) / the W_hh column (backward) it needs in 128 registers, its c / dc / dh state in registers, and exchanges
+// the 32-float h (or 128-float dG) vector with the other lanes through a warp-private shared-memory line — the only
+// synchronisation in a step is __syncwarp, there is no CTA barrier in the loop.  Every global access of a warp is a
+// whole 128-byte line (32 consecutive units of one (b, t)) and the next step's operands are prefetched into registers
+// while the current step computes.  fp32 throughout the recurrence, so no rounding error accumulates over time.
+// hidden_size must be 32 (the reference value).
 #include "../../include/b200ml.h"
 #include "../common/host.h"
 #include "../common/ptx.cuh"
@@ -18,179 +24,145 @@
 namespace b200 {
 namespace lstm {
 
-constexpr int H = 32;        // hidden size
+constexpr int H = 32;        // hidden size == warp width
 constexpr int G = 4 * H;     // gate rows
-constexpr int BT = 32;       // batch rows per CTA
-constexpr int kThreads = 512;
+constexpr int kWarps = 4;    // batch rows (warps) per CTA
+constexpr int kThreads = kWarps * 32;
 
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }
 
 __device__ __forceinline__ float tanhf_(float x) { return 1.f - 2.f / (1.f + __expf(2.f * x)); }
 
 // pre: [B][T][G] (input projection + both biases); gates_out: [B][T][G] activations; c_out: [B][T][H]; h_out: [B][T][H]
-// Phase A (gate pre-activations): thread = (gate row r, 8 batch rows), W_hh row in registers, h broadcast from smem.
-// Phase B (cell update):          thread = (hidden unit = lane, 2 batch rows): every global access of a warp is one
-//                                 128-byte line (32 consecutive units of one (b, t)).
 __global__ void __launch_bounds__(kThreads)
 lstm_rec_fwd_kernel(const float* __restrict__ pre, const float* __restrict__ w_hh, const float* __restrict__ h0,
                     const float* __restrict__ c0, float* __restrict__ h_out, float* __restrict__ gates_out,
                     float* __restrict__ c_out, float* __restrict__ h_n, float* __restrict__ c_n, int B, int T) {
-    __shared__ __align__(16) float s_h[BT][H + 4];   // h_{t-1} per batch row
-    __shared__ float s_g[G][BT + 1];                 // gate activations, [gate row][batch]
-    const int tid = threadIdx.x;
-    const int b0 = blockIdx.x * BT;
-    const int r = tid & (G - 1), bq = tid >> 7;      // phase A
-    float w[H];
+    __shared__ __align__(16) float s_h[kWarps][H];   // h_{t-1} of this warp's batch row
+    const int u = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int b = blockIdx.x * kWarps + wid;
+    if (b >= B) return;  // whole warp; no CTA-wide barrier below
+    float wi[H], wf[H], wg[H], wo[H];
 #pragma unroll
-    for (int k = 0; k < H; ++k) w[k] = w_hh[r * H + k];
-    const int u = tid & 31, bg = tid >> 5;           // phase B: unit u, batch rows bg and bg + 16
-    float c[2];
-#pragma unroll
-    for (int j = 0; j < 2; ++j) {
-        const int lb = bg + 16 * j, gb = b0 + lb;
-        c[j] = (c0 && gb < B) ? c0[(long long)gb * H + u] : 0.f;
-        s_h[lb][u] = (h0 && gb < B) ? h0[(long long)gb * H + u] : 0.f;
+    for (int k4 = 0; k4 < H; k4 += 4) {
+        const float4 a = *reinterpret_cast<const float4*>(w_hh + (0 * H + u) * H + k4);
+        const float4 f = *reinterpret_cast<const float4*>(w_hh + (1 * H + u) * H + k4);
+        const float4 g = *reinterpret_cast<const float4*>(w_hh + (2 * H + u) * H + k4);
+        const float4 o = *reinterpret_cast<const float4*>(w_hh + (3 * H + u) * H + k4);
+        wi[k4] = a.x, wi[k4 + 1] = a.y, wi[k4 + 2] = a.z, wi[k4 + 3] = a.w;
+        wf[k4] = f.x, wf[k4 + 1] = f.y, wf[k4 + 2] = f.z, wf[k4 + 3] = f.w;
+        wg[k4] = g.x, wg[k4 + 1] = g.y, wg[k4 + 2] = g.z, wg[k4 + 3] = g.w;
+        wo[k4] = o.x, wo[k4 + 1] = o.y, wo[k4 + 2] = o.z, wo[k4 + 3] = o.w;
     }
-    float pnext[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-        const int b = b0 + bq * 8 + j;
-        pnext[j] = (b < B && T > 0) ? pre[((long long)b * T) * G + r] : 0.f;
-    }
-    __syncthreads();
+    float c = c0 ? c0[(long long)b * H + u] : 0.f;
+    s_h[wid][u] = h0 ? h0[(long long)b * H + u] : 0.f;
+    const float* pb = pre + (long long)b * T * G;
+    float pi = pb[u], pf = pb[H + u], pg = pb[2 * H + u], po = pb[3 * H + u];
+    float hn = 0.f;
+    __syncwarp();
 
     for (int t = 0; t < T; ++t) {
-        float acc[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] = pnext[j];
-        if (t + 1 < T) {  // prefetch the next step's input projection (128 consecutive floats per batch row)
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const int b = b0 + bq * 8 + j;
-                pnext[j] = b < B ? pre[((long long)b * T + t + 1) * G + r] : 0.f;
-            }
+        float ai = pi, af = pf, ag = pg, ao = po;
+        if (t + 1 < T) {  // prefetch the next step's input projection (four 128-byte lines)
+            const float* pn = pb + (long long)(t + 1) * G;
+            pi = pn[u], pf = pn[H + u], pg = pn[2 * H + u], po = pn[3 * H + u];
         }
 #pragma unroll
         for (int k4 = 0; k4 < H; k4 += 4) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const float4 hv = *reinterpret_cast<const float4*>(&s_h[bq * 8 + j][k4]);  // warp-wide broadcast
-                acc[j] += hv.x * w[k4] + hv.y * w[k4 + 1] + hv.z * w[k4 + 2] + hv.w * w[k4 + 3];
-            }
+            const float4 hv = *reinterpret_cast<const float4*>(&s_h[wid][k4]);  // warp-wide broadcast
+            ai += hv.x * wi[k4] + hv.y * wi[k4 + 1] + hv.z * wi[k4 + 2] + hv.w * wi[k4 + 3];
+            af += hv.x * wf[k4] + hv.y * wf[k4 + 1] + hv.z * wf[k4 + 2] + hv.w * wf[k4 + 3];
+            ag += hv.x * wg[k4] + hv.y * wg[k4 + 1] + hv.z * wg[k4 + 2] + hv.w * wg[k4 + 3];
+            ao += hv.x * wo[k4] + hv.y * wo[k4 + 1] + hv.z * wo[k4 + 2] + hv.w * wo[k4 + 3];
         }
-        const bool is_g = (r >> 5) == 2;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) s_g[r][bq * 8 + j] = is_g ? tanhf_(acc[j]) : sigmoidf_(acc[j]);
-        __syncthreads();
-#pragma unroll
-        for (int j = 0; j < 2; ++j) {
-            const int lb = bg + 16 * j, gb = b0 + lb;
-            const float ig = s_g[u][lb], fg = s_g[H + u][lb], gg = s_g[2 * H + u][lb], og = s_g[3 * H + u][lb];
-            c[j] = fg * c[j] + ig * gg;
-            const float hn = og * tanhf_(c[j]);
-            s_h[lb][u] = hn;
-            if (gb < B) {
-                const long long bt = (long long)gb * T + t;
-                h_out[bt * H + u] = hn;
-                if (gates_out) {
-                    gates_out[bt * G + u] = ig;
-                    gates_out[bt * G + H + u] = fg;
-                    gates_out[bt * G + 2 * H + u] = gg;
-                    gates_out[bt * G + 3 * H + u] = og;
-                    c_out[bt * H + u] = c[j];
-                }
-            }
-        }
-        __syncthreads();
-    }
-#pragma unroll
-    for (int j = 0; j < 2; ++j) {
-        const int lb = bg + 16 * j, gb = b0 + lb;
-        if (gb < B) {
-            if (h_n) h_n[(long long)gb * H + u] = s_h[lb][u];
-            if (c_n) c_n[(long long)gb * H + u] = c[j];
+        const float ig = sigmoidf_(ai), fg = sigmoidf_(af), gg = tanhf_(ag), og = sigmoidf_(ao);
+        c = fg * c + ig * gg;
+        hn = og * tanhf_(c);
+        __syncwarp();          // every lane has read h_{t-1}
+        s_h[wid][u] = hn;
+        __syncwarp();
+        const long long bt = (long long)b * T + t;
+        h_out[bt * H + u] = hn;
+        if (gates_out) {
+            gates_out[bt * G + u] = ig;
+            gates_out[bt * G + H + u] = fg;
+            gates_out[bt * G + 2 * H + u] = gg;
+            gates_out[bt * G + 3 * H + u] = og;
+            c_out[bt * H + u] = c;
         }
     }
+    if (h_n) h_n[(long long)b * H + u] = s_h[wid][u];
+    if (c_n) c_n[(long long)b * H + u] = c;
 }
 
 // Backward recurrence: produces dG [B][T][G] (pre-activation gate gradients, bf16 for the hoisted GEMMs) and dh0/dc0.
-// Thread = (hidden unit / k index = lane, 2 batch rows) in both phases.
+// Lane u holds dh[u], dc[u] and column u of W_hh; dh_{t-1}[u] = sum_r dG_t[r] * W_hh[r][u].
 __global__ void __launch_bounds__(kThreads)
 lstm_rec_bwd_kernel(const float* __restrict__ w_hh, const float* __restrict__ c0, const float* __restrict__ gates,
                     const float* __restrict__ c_seq, const float* __restrict__ dh_seq, const float* __restrict__ dh_n,
                     const float* __restrict__ dc_n, __nv_bfloat16* __restrict__ dg_out, float* __restrict__ dh0,
                     float* __restrict__ dc0, int B, int T) {
-    __shared__ __align__(16) float s_wt[H][G + 4];   // W_hh transposed: [k][gate row]
-    __shared__ __align__(16) float s_dg[BT][G + 4];  // gate gradients of this step, [batch][gate row]
-    __shared__ float s_dh[BT][H + 1];                // dh_{t} flowing back through time
-    const int tid = threadIdx.x;
-    const int b0 = blockIdx.x * BT;
-    const int u = tid & 31, bg = tid >> 5;
-    for (int i = tid; i < G * H; i += kThreads) s_wt[i % H][i / H] = w_hh[i];
-    float dc[2];
+    __shared__ __align__(16) float s_dg[kWarps][G];  // gate gradients of this step for this warp's batch row
+    const int u = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int b = blockIdx.x * kWarps + wid;
+    if (b >= B) return;
+    float wc[G];                                     // W_hh[:, u]
 #pragma unroll
-    for (int j = 0; j < 2; ++j) {
-        const int lb = bg + 16 * j, gb = b0 + lb;
-        dc[j] = (dc_n && gb < B) ? dc_n[(long long)gb * H + u] : 0.f;
-        s_dh[lb][u] = (dh_n && gb < B) ? dh_n[(long long)gb * H + u] : 0.f;
-    }
-    __syncthreads();
+    for (int r = 0; r < G; ++r) wc[r] = w_hh[r * H + u];
+    float dc = dc_n ? dc_n[(long long)b * H + u] : 0.f;
+    float dh = dh_n ? dh_n[(long long)b * H + u] : 0.f;
+    const float* gb = gates + (long long)b * T * G;
+    const float* cb = c_seq + (long long)b * T * H;
+    const float* db = dh_seq ? dh_seq + (long long)b * T * H : nullptr;
+    const float c_init = c0 ? c0[(long long)b * H + u] : 0.f;
+    // operands of step T-1
+    const float* gt = gb + (long long)(T - 1) * G;
+    float ig = gt[u], fg = gt[H + u], gg = gt[2 * H + u], og = gt[3 * H + u];
+    float ct = cb[(long long)(T - 1) * H + u];
+    float cp = T > 1 ? cb[(long long)(T - 2) * H + u] : c_init;
+    float ds = db ? db[(long long)(T - 1) * H + u] : 0.f;
 
     for (int t = T - 1; t >= 0; --t) {
-#pragma unroll
-        for (int j = 0; j < 2; ++j) {
-            const int lb = bg + 16 * j, gb = b0 + lb;
-            float ig = 0.f, fg = 0.f, gg = 0.f, og = 0.f, ct = 0.f, cp = 0.f, dh = s_dh[lb][u];
-            const long long bt = (long long)gb * T + t;
-            if (gb < B) {
-                ig = gates[bt * G + u];
-                fg = gates[bt * G + H + u];
-                gg = gates[bt * G + 2 * H + u];
-                og = gates[bt * G + 3 * H + u];
-                ct = c_seq[bt * H + u];
-                cp = t > 0 ? c_seq[(bt - 1) * H + u] : (c0 ? c0[(long long)gb * H + u] : 0.f);
-                if (dh_seq) dh += dh_seq[bt * H + u];
-            }
-            const float tc = tanhf_(ct);
-            const float d = dc[j] + dh * og * (1.f - tc * tc);
-            const float di = d * gg * ig * (1.f - ig), df = d * cp * fg * (1.f - fg), dgg = d * ig * (1.f - gg * gg),
-                        dog = dh * tc * og * (1.f - og);
-            s_dg[lb][u] = di;
-            s_dg[lb][H + u] = df;
-            s_dg[lb][2 * H + u] = dgg;
-            s_dg[lb][3 * H + u] = dog;
-            dc[j] = d * fg;
-            if (gb < B) {
-                dg_out[bt * G + u] = __float2bfloat16(di);
-                dg_out[bt * G + H + u] = __float2bfloat16(df);
-                dg_out[bt * G + 2 * H + u] = __float2bfloat16(dgg);
-                dg_out[bt * G + 3 * H + u] = __float2bfloat16(dog);
-            }
+        // prefetch the operands of step t-1 while this step computes
+        float nig = 0.f, nfg = 0.f, ngg = 0.f, nog = 0.f, ncp = c_init, nds = 0.f;
+        if (t > 0) {
+            const float* gn = gb + (long long)(t - 1) * G;
+            nig = gn[u], nfg = gn[H + u], ngg = gn[2 * H + u], nog = gn[3 * H + u];
+            if (t > 1) ncp = cb[(long long)(t - 2) * H + u];
+            if (db) nds = db[(long long)(t - 1) * H + u];
         }
-        __syncthreads();
-        // dh_{t-1}[b][k = u] = sum_r dG[b][r] * W_hh[r][k]   for this thread's two batch rows
-        float a0 = 0.f, a1 = 0.f;
-#pragma unroll 8
+        const float dht = dh + ds;
+        const float tc = tanhf_(ct);
+        const float d = dc + dht * og * (1.f - tc * tc);
+        const float di = d * gg * ig * (1.f - ig), df = d * cp * fg * (1.f - fg), dgg = d * ig * (1.f - gg * gg),
+                    dog = dht * tc * og * (1.f - og);
+        dc = d * fg;
+        s_dg[wid][u] = di;
+        s_dg[wid][H + u] = df;
+        s_dg[wid][2 * H + u] = dgg;
+        s_dg[wid][3 * H + u] = dog;
+        __syncwarp();
+        __nv_bfloat16* dgo = dg_out + ((long long)b * T + t) * G;
+        dgo[u] = __float2bfloat16(di);
+        dgo[H + u] = __float2bfloat16(df);
+        dgo[2 * H + u] = __float2bfloat16(dgg);
+        dgo[3 * H + u] = __float2bfloat16(dog);
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
         for (int r4 = 0; r4 < G; r4 += 4) {
-            const float4 wv = *reinterpret_cast<const float4*>(&s_wt[u][r4]);
-            const float4 d0 = *reinterpret_cast<const float4*>(&s_dg[bg][r4]);        // broadcast
-            const float4 d1 = *reinterpret_cast<const float4*>(&s_dg[bg + 16][r4]);   // broadcast
-            a0 += d0.x * wv.x + d0.y * wv.y + d0.z * wv.z + d0.w * wv.w;
-            a1 += d1.x * wv.x + d1.y * wv.y + d1.z * wv.z + d1.w * wv.w;
+            const float4 dv = *reinterpret_cast<const float4*>(&s_dg[wid][r4]);   // warp-wide broadcast
+            a0 += dv.x * wc[r4];
+            a1 += dv.y * wc[r4 + 1];
+            a2 += dv.z * wc[r4 + 2];
+            a3 += dv.w * wc[r4 + 3];
         }
-        __syncthreads();  // everyone has consumed s_dh / s_dg of this step
-        s_dh[bg][u] = a0;
-        s_dh[bg + 16][u] = a1;
-        __syncthreads();
+        dh = (a0 + a1) + (a2 + a3);
+        __syncwarp();  // every lane has consumed s_dg of this step
+        ct = cp;
+        ig = nig, fg = nfg, gg = ngg, og = nog, cp = ncp, ds = nds;
     }
-#pragma unroll
-    for (int j = 0; j < 2; ++j) {
-        const int lb = bg + 16 * j, gb = b0 + lb;
-        if (gb < B) {
-            if (dh0) dh0[(long long)gb * H + u] = s_dh[lb][u];
-            if (dc0) dc0[(long long)gb * H + u] = dc[j];
-        }
-    }
+    if (dh0) dh0[(long long)b * H + u] = dh;
+    if (dc0) dc0[(long long)b * H + u] = dc;
 }
 
 // out_bf16[i] = dropout(x[i]) — the (inter-layer) dropout + cast that feeds the hoisted input-projection GEMM
@@ -246,7 +218,7 @@ int b200ml_lstm_rec_fwd(const float* pre, const float* w_hh, const float* h0, co
     B200_REQUIRE(hidden == H, "lstm: hidden_size must be %d (got %d)", H, hidden);
     B200_REQUIRE((gates_out == nullptr) == (c_out == nullptr), "lstm_rec_fwd: gates_out and c_out go together");
     if (B <= 0 || T <= 0) return 0;
-    lstm_rec_fwd_kernel<<<(B + BT - 1) / BT, kThreads, 0, stream>>>(pre, w_hh, h0, c0, h_out, gates_out, c_out, h_n,
+    lstm_rec_fwd_kernel<<<(B + kWarps - 1) / kWarps, kThreads, 0, stream>>>(pre, w_hh, h0, c0, h_out, gates_out, c_out, h_n,
                                                                     c_n, B, T);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
@@ -259,7 +231,7 @@ int b200ml_lstm_rec_bwd(const float* w_hh, const float* c0, const float* gates, 
     B200_REQUIRE(w_hh && gates && c_seq && dg_out_bf16, "lstm_rec_bwd: null pointer");
     B200_REQUIRE(hidden == H, "lstm: hidden_size must be %d (got %d)", H, hidden);
     if (B <= 0 || T <= 0) return 0;
-    lstm_rec_bwd_kernel<<<(B + BT - 1) / BT, kThreads, 0, stream>>>(w_hh, c0, gates, c_seq, dh_seq, dh_n, dc_n,
+    lstm_rec_bwd_kernel<<<(B + kWarps - 1) / kWarps, kThreads, 0, stream>>>(w_hh, c0, gates, c_seq, dh_seq, dh_n, dc_n,
                                                                     (__nv_bfloat16*)dg_out_bf16, dh0, dc0, B, T);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;

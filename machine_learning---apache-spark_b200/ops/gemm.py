@@ -163,16 +163,20 @@ class GradSideStream:
         workspace.register_stream(self.stream, 1)
         self.keep: list = []
         self.active = False
+        self.used = False  # has work been queued since the last join (i.e. is the stream part of the current step/capture)
 
     def run(self, fn, *args) -> None:
         cur = torch.cuda.current_stream()
         self.stream.wait_stream(cur)
         with torch.cuda.stream(self.stream):
             fn(*args)
+        self.used = True
         self.keep.append(fn)  # the closure owns references to the gradient / activation tensors it reads
 
     def join(self) -> None:
-        torch.cuda.current_stream().wait_stream(self.stream)
+        if self.used:
+            torch.cuda.current_stream().wait_stream(self.stream)
+        self.used = False
         self.keep.clear()
 
 

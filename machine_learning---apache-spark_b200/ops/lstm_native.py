@@ -37,7 +37,7 @@ class _LSTMStack(torch.autograd.Function):
         rng = DeviceCounters.get(dev).rng.data_ptr() if dropout_p > 0 else None
         need_grad = any(w.requires_grad for w in weights) or x.requires_grad
         inp = x
-        saved = []
+        saved, meta = [], []
         h_n = torch.empty(num_layers, B, H, dtype=torch.float32, device=dev)
         c_n = torch.empty(num_layers, B, H, dtype=torch.float32, device=dev)
         for layer in range(num_layers):
@@ -58,9 +58,13 @@ class _LSTMStack(torch.autograd.Function):
                                                   c0[layer].data_ptr(), h_out.data_ptr(), _native.ptr(gates),
                                                   _native.ptr(c_seq), h_n[layer].data_ptr(), c_n[layer].data_ptr(), B,
                                                   T, H, st), "lstm_rec_fwd")
-            saved.append((x16, w_ih16, w_hh32, h_out, gates, c_seq, p, K))
+            saved += [x16, w_ih16, w_hh32, h_out, gates, c_seq]
+            meta.append((p, K))
             inp = h_out
-        ctx.saved = saved
+        # save_for_backward (not attributes): the last h_out is also an output of this node, and an attribute reference
+        # to it would form a cycle node -> output -> grad_fn that only the garbage collector can break
+        ctx.save_for_backward(*saved)
+        ctx.meta = meta
         ctx.state = (h0, c0, num_layers, site, B, T, H)
         ctx.weights = weights
         return inp, h_n, c_n
@@ -70,6 +74,7 @@ class _LSTMStack(torch.autograd.Function):
         lib = _native.load()
         h0, c0, num_layers, site, B, T, H = ctx.state
         weights = ctx.weights
+        saved = ctx.saved_tensors
         dev = d_out.device
         st = _native.stream_ptr()
         rngp = DeviceCounters.get(dev).rng.data_ptr()
@@ -81,7 +86,8 @@ class _LSTMStack(torch.autograd.Function):
         grads = [None] * len(weights)
         dx = None
         for layer in range(num_layers - 1, -1, -1):
-            x16, w_ih16, w_hh32, h_out, gates, c_seq, p, K = ctx.saved[layer]
+            x16, w_ih16, w_hh32, h_out, gates, c_seq = saved[6 * layer:6 * layer + 6]
+            p, K = ctx.meta[layer]
             w_ih, w_hh, b_ih, b_hh = weights[4 * layer:4 * layer + 4]
             dg = torch.empty(B * T, 4 * H, dtype=torch.bfloat16, device=dev)
             _native.check(lib.b200ml_lstm_rec_bwd(

@@ -22,6 +22,7 @@ kernels and stay fully replicated.
 """
 from __future__ import annotations
 
+import gc
 import os
 
 import torch
@@ -153,7 +154,7 @@ class DataParallelEngine:
                 ev = torch.cuda.Event()
                 ev.record(cur)
                 self._events[b][cur.cuda_stream] = ev
-                if self.side is not None and self.side.active:
+                if self.side is not None and self.side.active and self.side.used:
                     ev2 = torch.cuda.Event()
                     ev2.record(self.side.stream)
                     self._events[b][self.side.stream.cuda_stream] = ev2
@@ -235,6 +236,10 @@ class DataParallelEngine:
         assert self.device.type == "cuda"
         if self.world > 1 and self.comm is None:
             return None  # NCCL baseline path stays eager
+        # Autograd nodes left over from eager warm-up steps (reference cycles awaiting the collector) would keep their
+        # AccumulateGrad nodes - created on the warm-up stream - alive, and backward under capture would then try to
+        # synchronise the capture stream with that uncaptured stream.
+        gc.collect()
         torch.cuda.synchronize()
         n0 = _native.launches()
         g = torch.cuda.CUDAGraph()

@@ -50,6 +50,23 @@ def test_gemm_simt_matches():
     assert (o1 - o2).abs().max().item() < 1e-2
 
 
+def test_gemm_simt_split_k_weight_gradient_shape():
+    """dW[4, 32] = dZᵀ[4, 4128]·X[4128, 32]: lda = 4 is not TMA-describable and K is long -> SIMT with split-K."""
+    from b200ml.ops.gemm import gemm
+    torch.manual_seed(11)
+    K, M, N = 4128 + 5, 4, 32
+    a = torch.randn(K, M, device="cuda").to(torch.bfloat16)
+    b = torch.randn(K, N, device="cuda").to(torch.bfloat16)
+    ref = _ref(a, b, True, True)
+    out = gemm(a, b, a_mn=True, b_mn=True, out_dtype=torch.float32)
+    _check(out, ref, K)
+    acc = torch.ones(M, N, device="cuda")
+    gemm(a, b, a_mn=True, b_mn=True, out=acc, accumulate=True, alpha=0.5)
+    _check(acc, 1.0 + 0.5 * ref, K)
+    one = gemm(a, b, a_mn=True, b_mn=True, out_dtype=torch.float32, split_k=1)
+    _check(one, ref, K)
+
+
 def test_gemm_epilogues():
     from b200ml.ops.gemm import gemm
     torch.manual_seed(2)
