@@ -29,6 +29,19 @@ def main():
         out = torch.empty(6400, 19216, dtype=torch.bfloat16, device="cuda")
         for _ in range(3):
             gemm(a, b, out=out, bias=bias, n_logical=19214)
+    elif what == "gemm_wgrad":
+        # weight-gradient shapes (both operands MN-major, K = B*S = 6400) and a long-K NN shape at the narrow tile
+        a = torch.randn(6400, 1536, device="cuda").to(torch.bfloat16)
+        b = torch.randn(6400, 512, device="cuda").to(torch.bfloat16)
+        out = torch.empty(1536, 512, device="cuda")
+        a2 = torch.randn(6400, 4096, device="cuda").to(torch.bfloat16)
+        b2 = torch.randn(512, 4096, device="cuda").to(torch.bfloat16)
+        for _ in range(2):
+            gemm(a, b, a_mn=True, b_mn=True, out=out, tile_n=64, split_k=1)
+            gemm(a, b, a_mn=True, b_mn=True, out=out, tile_n=256, split_k=1)
+            gemm(a, b, a_mn=True, b_mn=True, out=out, tile_n=128)
+            gemm(a2, b2, tile_n=64)
+            gemm(a2, b2, tile_n=256)
     else:
         a = torch.randn(6400, 512, device="cuda").to(torch.bfloat16)
         b = torch.randn(1024, 512, device="cuda").to(torch.bfloat16)
