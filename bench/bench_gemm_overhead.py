@@ -35,14 +35,20 @@ def timed(fn):
 def main():
     torch.manual_seed(0)
     shapes = [(6400, 512, K, False, False) for K in (64, 256, 512, 1024, 2048, 4096)]
+    shapes += [(6400, 19214, 512, False, False), (6400, 512, 19214, False, True), (19214, 512, 6400, True, True),
+               (8192, 8192, 8192, False, False)]
     shapes += [(512, 512, 6400, True, True), (1536, 512, 6400, True, True), (1024, 512, 6400, True, True),
                (6400, 1536, 512, False, False), (6400, 512, 1536, False, True)]
     for M, N, K, a_mn, b_mn in shapes:
-        a = torch.randn((K, M) if a_mn else (M, K), device="cuda").to(torch.bfloat16)
-        b = torch.randn((K, N) if b_mn else (N, K), device="cuda").to(torch.bfloat16)
-        out = torch.empty(M, N, dtype=torch.float32 if a_mn else torch.bfloat16, device="cuda")
+        r8 = lambda v: (v + 7) // 8 * 8  # TMA needs 16-byte row pitches: pad the leading dimension, view the logical part
+        a = torch.randn((K, r8(M)) if a_mn else (M, r8(K)), device="cuda").to(torch.bfloat16)
+        a = a[:, :M] if a_mn else a[:, :K]
+        b = torch.randn((K, r8(N)) if b_mn else (N, r8(K)), device="cuda").to(torch.bfloat16)
+        b = b[:, :N] if b_mn else b[:, :K]
+        ldc = (N + 7) // 8 * 8
+        out = torch.empty(M, ldc, dtype=torch.float32 if a_mn else torch.bfloat16, device="cuda")[:, :N]
         row = f"M={M:5d} N={N:5d} K={K:5d} {'T' if a_mn else 'N'}{'T' if b_mn else 'N'}"
-        for tn in (0, 64, 128, 256):
+        for tn in (0, 128, 256, 512):
             t = timed(lambda: gemm(a, b, a_mn=a_mn, b_mn=b_mn, out=out, tile_n=tn))
             row += f"  bn{tn}: {t:6.2f}us"
         if a_mn:

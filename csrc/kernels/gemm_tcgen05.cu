@@ -16,6 +16,8 @@
 // into an fp32 workspace slab, a second kernel sums the slabs in fixed order (deterministic, no atomics).
 // Reference ops covered: every nn.Linear in the reference (transformer.py:71-72,107-108,177-179,272;
 // distributed_multilayer_perceptron.py:47-53 at the 784-dim preset) with its ReLU / Sigmoid / Dropout neighbours.
+#include <cstdlib>
+
 #include "../../include/b200ml.h"
 #include "../common/host.h"
 #include "../common/ptx.cuh"
@@ -28,6 +30,7 @@ constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 64;  // 64 bf16 = 128 B = one swizzle row
 constexpr int UMMA_K = 16;
 constexpr int kEpiWarps = 8;
+constexpr int kPairTileCost = 250;  // relative cost of one 256 x 256 pair tile per wave (a 128 x 256 tile: 288)
 constexpr int kNumThreads = 64 + kEpiWarps * 32;  // 10 warps
 
 struct Epilogue {
@@ -48,13 +51,18 @@ struct Epilogue {
     uint32_t rng_site;
     float* splitk_ws;        // != nullptr: write raw fp32 partial tiles to ws[split][M][N] instead of C
     int tma_store;           // bf16 C through smem staging + cp.async.bulk.tensor stores (needs tmap_c)
+    int debug;               // B200ML_GEMM_DEBUG (timing experiments only, results are garbage): 1 = no TMA loads, 2 = no MMAs
 };
 
-template <int BN>
+// kCtas == 2: a CTA pair (cluster of two on one TPC) computes a 256 x BN tile with tcgen05.mma.cta_group::2; each CTA
+// stages its own 128 rows of A and BN/2 columns of B, so the operand bytes per CTA per k-block drop from 48 KB to 32 KB
+// (BN = 256) for the same MMA time - these GEMMs are bound by the L2 -> SM fabric, not by the tensor pipe.
+template <int BN, int kCtas = 1>
 struct Cfg {
-    static constexpr int kStages = BN == 256 ? 4 : (BN == 128 ? 6 : 8);
+    static constexpr int kBRows = BN / kCtas;  // N extent of B staged by one CTA
+    static constexpr int kStages = kCtas == 2 ? 6 : (BN == 256 ? 4 : (BN == 128 ? 6 : 8));
     static constexpr int kABytes = BLOCK_M * BLOCK_K * 2;
-    static constexpr int kBBytes = BN * BLOCK_K * 2;
+    static constexpr int kBBytes = kBRows * BLOCK_K * 2;
     static constexpr int kStageBytes = kABytes + kBBytes;
     static constexpr int kTmemCols = 2 * BN;  // double-buffered accumulator
     // epilogue staging: one 32-row x 64-col bf16 slab (4 KB, 128B-swizzled) per epilogue warp for the TMA store path
@@ -73,25 +81,36 @@ __device__ __forceinline__ float apply_act(float v, int act) {
 struct TileCoord {
     int m0, n0, kb0, kb1, split;
 };
-// tile -> (m fastest, then n, then k-split)
-__device__ __forceinline__ TileCoord tile_coord(int tile, int m_tiles, int n_tiles, int BN, int k_blocks, int splits) {
+// tile -> (m fastest inside a band of kGroupM m-tiles, then n, then the next band, then k-split).  One wave of CTAs then
+// covers a roughly square patch of C, so the A and B panels it streams stay L2-resident (matters once A alone
+// approaches the 126 MB L2, e.g. 8192^3); with m_tiles <= kGroupM this is plain m-fastest order.
+constexpr int kGroupM = 16;
+__device__ __forceinline__ TileCoord tile_coord(int tile, int m_tiles, int n_tiles, int BN, int k_blocks, int splits,
+                                               int block_m = BLOCK_M) {
     TileCoord t;
     const int mn = m_tiles * n_tiles;
     t.split = tile / mn;
     const int r = tile - t.split * mn;
-    t.m0 = (r % m_tiles) * BLOCK_M;
-    t.n0 = (r / m_tiles) * BN;
+    const int band = kGroupM * BLOCK_M / block_m;           // 16 single tiles or 8 pair tiles = 2048 rows
+    const int per_band = band * n_tiles;
+    const int first_m = (r / per_band) * band;
+    const int in_band = r - (r / per_band) * per_band;
+    const int rows = m_tiles - first_m < band ? m_tiles - first_m : band;
+    t.m0 = (first_m + in_band % rows) * block_m;
+    t.n0 = (in_band / rows) * BN;
     const int per = (k_blocks + splits - 1) / splits;
     t.kb0 = t.split * per;
     t.kb1 = t.kb0 + per < k_blocks ? t.kb0 + per : k_blocks;
     return t;
 }
 
-template <bool A_MN, bool B_MN, int BN>
+template <bool A_MN, bool B_MN, int BN, int kCtas>
 __global__ void __launch_bounds__(kNumThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const __grid_constant__ CUtensorMap tmap_c, int M, int N, int K, int splits, Epilogue ep) {
-    using C = Cfg<BN>;
+    using C = Cfg<BN, kCtas>;
+    constexpr int kTileM = BLOCK_M * kCtas;
+    const uint32_t cta_rank = kCtas == 2 ? cluster_ctarank() : 0u;  // rank 0 of a pair issues the MMAs
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* stage_c = smem + C::kStages * C::kStageBytes;                       // 1024-aligned
@@ -118,47 +137,68 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&tmem_full[i], 1);
-            mbar_init(&tmem_empty[i], kEpiWarps);  // one arrive per epilogue warp
+            mbar_init(&tmem_empty[i], kEpiWarps * kCtas);  // one arrive per epilogue warp (of both CTAs of a pair)
         }
         fence_barrier_init();
     }
-    if (warp == 2) tmem_alloc<C::kTmemCols>(tmem_ptr_smem);
+    if (warp == 2) {
+        if (kCtas == 2) tmem_alloc_2sm<C::kTmemCols>(tmem_ptr_smem);
+        else tmem_alloc<C::kTmemCols>(tmem_ptr_smem);
+    }
     tc_fence_before();
-    __syncthreads();
+    if (kCtas == 2) cluster_sync_all();  // the peer's barriers must be initialised before anything signals them
+    else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr_smem;
 
-    const int m_tiles = (M + BLOCK_M - 1) / BLOCK_M;
+    const int m_tiles = (M + kTileM - 1) / kTileM;
     const int n_tiles = (N + BN - 1) / BN;
     const int num_tiles = m_tiles * n_tiles * splits;
     const int k_blocks = (K + BLOCK_K - 1) / BLOCK_K;
+    const int first_tile = blockIdx.x / kCtas, tile_step = gridDim.x / kCtas;  // both CTAs of a pair walk the same tiles
 
     if (warp == 0) {
         // ===================== TMA producer =====================
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                const TileCoord t = tile_coord(tile, m_tiles, n_tiles, BN, k_blocks, splits);
+            for (int tile = first_tile; tile < num_tiles; tile += tile_step) {
+                const TileCoord t = tile_coord(tile, m_tiles, n_tiles, BN, k_blocks, splits, kTileM);
+                const int my_m0 = t.m0 + cta_rank * BLOCK_M;     // this CTA's 128 rows of A / of the output
+                const int my_n0 = t.n0 + cta_rank * C::kBRows;   // this CTA's share of B's columns
                 for (int kb = t.kb0; kb < t.kb1; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     uint8_t* sa = smem + stage * C::kStageBytes;
                     uint8_t* sb = sa + C::kABytes;
-                    mbar_arrive_expect_tx(&full_bar[stage], C::kStageBytes);
+                    // pair: both CTAs' loads complete on the leader's barrier, which expects the bytes of both
+                    uint32_t bar2 = 0;
+                    if (ep.debug & 1) {  // handshake-only experiment: signal the stage without loading anything
+                        if (kCtas == 1 || cta_rank == 0) mbar_arrive(&full_bar[stage]);
+                        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+                        continue;
+                    }
+                    if (kCtas == 2) {
+                        bar2 = mapa_shared(smem_u32(&full_bar[stage]), 0);
+                        if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * C::kStageBytes);
+                    } else {
+                        mbar_arrive_expect_tx(&full_bar[stage], C::kStageBytes);
+                    }
+                    auto load = [&](uint8_t* dst, const CUtensorMap* map, int c0, int c1) {
+                        if (kCtas == 2) tma_load_2d_2sm(dst, map, bar2, c0, c1);
+                        else tma_load_2d(dst, map, &full_bar[stage], c0, c1);
+                    };
                     const int k0 = kb * BLOCK_K;
                     if (!A_MN) {
-                        tma_load_2d(sa, &tmap_a, &full_bar[stage], k0, t.m0);
+                        load(sa, &tmap_a, k0, my_m0);
                     } else {
 #pragma unroll
-                        for (int j = 0; j < BLOCK_M / 64; ++j)
-                            tma_load_2d(sa + j * 8192, &tmap_a, &full_bar[stage], t.m0 + 64 * j, k0);
+                        for (int j = 0; j < BLOCK_M / 64; ++j) load(sa + j * 8192, &tmap_a, my_m0 + 64 * j, k0);
                     }
                     if (!B_MN) {
-                        tma_load_2d(sb, &tmap_b, &full_bar[stage], k0, t.n0);
+                        load(sb, &tmap_b, k0, my_n0);
                     } else {
 #pragma unroll
-                        for (int j = 0; j < BN / 64; ++j)
-                            tma_load_2d(sb + j * 8192, &tmap_b, &full_bar[stage], t.n0 + 64 * j, k0);
+                        for (int j = 0; j < C::kBRows / 64; ++j) load(sb + j * 8192, &tmap_b, my_n0 + 64 * j, k0);
                     }
                     if (++stage == C::kStages) { stage = 0; phase ^= 1; }
                 }
@@ -166,14 +206,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, BN, A_MN, B_MN);
+        if (lane == 0 && cta_rank == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(kTileM, BN, A_MN, B_MN);
             int stage = 0;
             uint32_t phase = 0;
             int acc = 0;
             uint32_t acc_phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                const TileCoord t = tile_coord(tile, m_tiles, n_tiles, BN, k_blocks, splits);
+            for (int tile = first_tile; tile < num_tiles; tile += tile_step) {
+                const TileCoord t = tile_coord(tile, m_tiles, n_tiles, BN, k_blocks, splits, kTileM);
                 mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_base + acc * BN;
@@ -184,16 +224,22 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     const uint32_t sb = sa + C::kABytes;
 #pragma unroll
                     for (int kk = 0; kk < BLOCK_K / UMMA_K; ++kk) {
+                        if (ep.debug & 2) break;
                         const uint64_t da = A_MN ? umma_smem_desc(sa + kk * (UMMA_K * 128), 8192, 1024)
                                                  : umma_smem_desc(sa + kk * (UMMA_K * 2), 16, 1024);
                         const uint64_t db = B_MN ? umma_smem_desc(sb + kk * (UMMA_K * 128), 8192, 1024)
                                                  : umma_smem_desc(sb + kk * (UMMA_K * 2), 16, 1024);
-                        umma_bf16(tmem_d, da, db, idesc, (kb > t.kb0 || kk != 0) ? 1u : 0u);
+                        if (kCtas == 2) umma_bf16_2sm(tmem_d, da, db, idesc, (kb > t.kb0 || kk != 0) ? 1u : 0u);
+                        else umma_bf16(tmem_d, da, db, idesc, (kb > t.kb0 || kk != 0) ? 1u : 0u);
                     }
-                    umma_commit(&empty_bar[stage]);  // smem slot reusable once these MMAs retire
+                    // smem slot reusable once these MMAs retire (pair: in both CTAs)
+                    if (kCtas == 2) umma_commit_2sm(&empty_bar[stage], 3);
+                    else umma_commit(&empty_bar[stage]);
                     if (++stage == C::kStages) { stage = 0; phase ^= 1; }
                 }
-                umma_commit(&tmem_full[acc]);  // accumulator complete
+                // accumulator complete (pair: each CTA's epilogue drains its own 128 TMEM lanes)
+                if (kCtas == 2) umma_commit_2sm(&tmem_full[acc], 3);
+                else umma_commit(&tmem_full[acc]);
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
             }
         }
@@ -282,8 +328,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             }
         };
 
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-            const TileCoord t = tile_coord(tile, m_tiles, n_tiles, BN, k_blocks, splits);
+        for (int tile = first_tile; tile < num_tiles; tile += tile_step) {
+            TileCoord t = tile_coord(tile, m_tiles, n_tiles, BN, k_blocks, splits, kTileM);
+            t.m0 += cta_rank * BLOCK_M;  // this CTA's rows
             if (ep.bias) {  // stage this tile's bias slice once (overlaps the MMA of this tile)
                 named_bar_sync(1, kEpiWarps * 32);  // everyone is done with the previous tile's slice
                 if (etid < BN) s_bias[etid] = t.n0 + etid < N ? __ldg(ep.bias + t.n0 + etid) : 0.f;
@@ -395,17 +442,22 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+            if (lane == 0) {
+                if (kCtas == 1 || cta_rank == 0) mbar_arrive(&tmem_empty[acc]);
+                else mbar_arrive_cluster(mapa_shared(smem_u32(&tmem_empty[acc]), 0));  // the leader owns the barrier
+            }
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
         if (use_tma_store && lane == 0) tma_store_wait_all<0>();  // global writes done before the CTA retires
     }
 
     tc_fence_before();
-    __syncthreads();
+    if (kCtas == 2) cluster_sync_all();  // the peer may still be reading operands / signalling barriers of this CTA
+    else __syncthreads();
     if (warp == 2) {
         tc_fence_after();
-        tmem_dealloc<C::kTmemCols>(tmem_base);
+        if (kCtas == 2) tmem_dealloc_2sm<C::kTmemCols>(tmem_base);
+        else tmem_dealloc<C::kTmemCols>(tmem_base);
     }
 }
 
@@ -487,9 +539,9 @@ gemm_simt_kernel(const __nv_bfloat16* __restrict__ A, long long lda, int a_mn, c
     }
 }
 
-template <bool A_MN, bool B_MN, int BN>
+template <bool A_MN, bool B_MN, int BN, int kCtas>
 static int launch(const b200ml_gemm_args* g, Epilogue ep, int splits, cudaStream_t stream) {
-    using C = Cfg<BN>;
+    using C = Cfg<BN, kCtas>;
     CUtensorMap ta, tb;
     {
         // K-major: dims {K, rows}; MN-major: dims {rows(MN), K}
@@ -502,7 +554,7 @@ static int launch(const b200ml_gemm_args* g, Epilogue ep, int splits, cudaStream
     {
         uint64_t dims[2], strides[2] = {2, (uint64_t)g->ldb * 2};
         uint32_t box[2];
-        if (!B_MN) { dims[0] = g->K; dims[1] = g->N; box[0] = 64; box[1] = BN; }
+        if (!B_MN) { dims[0] = g->K; dims[1] = g->N; box[0] = 64; box[1] = C::kBRows; }
         else       { dims[0] = g->N; dims[1] = g->K; box[0] = 64; box[1] = BLOCK_K; }
         if (make_tmap_bf16(&tb, g->B, 2, dims, strides, box)) return -1;
     }
@@ -515,17 +567,34 @@ static int launch(const b200ml_gemm_args* g, Epilogue ep, int splits, cudaStream
         if (make_tmap_bf16(&tc, g->C, 2, dims, strides, box)) return -1;
         ep.tma_store = 1;
     }
-    auto kern = gemm_bf16_kernel<A_MN, B_MN, BN>;
+    auto kern = gemm_bf16_kernel<A_MN, B_MN, BN, kCtas>;
     static bool attr_set = false;  // per instantiation
     if (!attr_set) {
         B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
         attr_set = true;
     }
-    const int m_tiles = (g->M + BLOCK_M - 1) / BLOCK_M, n_tiles = (g->N + BN - 1) / BN;
-    const int tiles = m_tiles * n_tiles * splits;
-    const int grid = tiles < sm_count() ? tiles : sm_count();
+    const int m_tiles = (g->M + BLOCK_M * kCtas - 1) / (BLOCK_M * kCtas), n_tiles = (g->N + BN - 1) / BN;
+    const int tiles = m_tiles * n_tiles * splits;       // per CTA (kCtas == 1) or per CTA pair
+    const int slots = sm_count() / kCtas;
+    const int grid = (tiles < slots ? tiles : slots) * kCtas;
     if (splits > 1) ep.splitk_ws = reinterpret_cast<float*>(g->workspace);
-    kern<<<grid, kNumThreads, C::kSmemBytes, stream>>>(ta, tb, tc, g->M, g->N, g->K, splits, ep);
+    if (kCtas == 1) {
+        kern<<<grid, kNumThreads, C::kSmemBytes, stream>>>(ta, tb, tc, g->M, g->N, g->K, splits, ep);
+    } else {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(grid);
+        cfg.blockDim = dim3(kNumThreads);
+        cfg.dynamicSmemBytes = C::kSmemBytes;
+        cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;  // a pair = cluster of two CTAs (same TPC)
+        attr[0].val.clusterDim.x = 2;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, g->M, g->N, g->K, splits, ep));
+    }
     B200_CHECK_CUDA(cudaGetLastError());
     if (splits > 1) {
         const long long mn = (long long)g->M * g->N;
@@ -538,12 +607,12 @@ static int launch(const b200ml_gemm_args* g, Epilogue ep, int splits, cudaStream
     return 0;
 }
 
-template <int BN>
+template <int BN, int kCtas>
 static int dispatch_major(const b200ml_gemm_args* g, const Epilogue& ep, int splits, cudaStream_t s) {
-    if (!g->a_mn_major && !g->b_mn_major) return launch<false, false, BN>(g, ep, splits, s);
-    if (!g->a_mn_major && g->b_mn_major) return launch<false, true, BN>(g, ep, splits, s);
-    if (g->a_mn_major && !g->b_mn_major) return launch<true, false, BN>(g, ep, splits, s);
-    return launch<true, true, BN>(g, ep, splits, s);
+    if (!g->a_mn_major && !g->b_mn_major) return launch<false, false, BN, kCtas>(g, ep, splits, s);
+    if (!g->a_mn_major && g->b_mn_major) return launch<false, true, BN, kCtas>(g, ep, splits, s);
+    if (g->a_mn_major && !g->b_mn_major) return launch<true, false, BN, kCtas>(g, ep, splits, s);
+    return launch<true, true, BN, kCtas>(g, ep, splits, s);
 }
 
 }  // namespace gemm
@@ -563,6 +632,8 @@ extern "C" int b200ml_gemm_bf16(const b200ml_gemm_args* g, cudaStream_t stream) 
     ep.rng = reinterpret_cast<const RngState*>(g->rng_state); ep.rng_site = g->rng_site;
     ep.splitk_ws = nullptr;
     ep.tma_store = 0;
+    static const int debug_flags = [] { const char* e = getenv("B200ML_GEMM_DEBUG"); return e ? atoi(e) : 0; }();
+    ep.debug = debug_flags;
 
     const bool tma_ok = (g->lda % 8 == 0) && (g->ldb % 8 == 0) && ((reinterpret_cast<uintptr_t>(g->A) & 15) == 0) &&
                         ((reinterpret_cast<uintptr_t>(g->B) & 15) == 0) && g->force_simt == 0;
@@ -603,11 +674,19 @@ extern "C" int b200ml_gemm_bf16(const b200ml_gemm_args* g, cudaStream_t stream) 
     // Tile-N: minimise waves x per-tile cost.  A 128xBN tile costs ~BN MMA cycles per k-step at BN = 256, but narrower
     // tiles are shared-memory-bandwidth bound (A is re-read per tile: 128 B/clk at BN = 128, 192 B/clk at BN = 64
     // against a 128 B/clk port) and pay the same fixed prologue/epilogue, hence the measured weights below.
+    // tile_n: 64 / 128 / 256 force a single-CTA tile width, 512 forces the CTA-pair 256 x 256 tile, anything else = auto
     int bn = g->tile_n;
-    if (bn != 64 && bn != 128 && bn != 256) {
+    int ctas = 1;
+    if (bn == 512) { bn = 256; ctas = 2; }
+    else if (bn != 64 && bn != 128 && bn != 256) {
         long long best = -1;
         const int cands[3] = {256, 128, 64};
-        const int cost_per_tile[3] = {288, 192, 160};
+        // Measured (bench/bench_gemm_debug.py, loads switched off): a 128 x N x 16 UMMA with A in shared memory takes
+        // ~128 cycles for every N <= 256 (the 4 KB A slice is re-read per instruction), so a k-block costs ~0.26 us at
+        // every tile width.  Short K: the epilogue / fixed share still favours narrow tiles when that saves a wave.
+        // Long K: wide tiles win outright; 128 keeps enough tiles for a moderate split-K.
+        const int cost_short[3] = {288, 192, 160}, cost_long[3] = {288, 240, 250};
+        const int* cost_per_tile = k_blocks >= 32 ? cost_long : cost_short;
         for (int ci = 0; ci < 3; ++ci) {
             const int c = cands[ci];
             if (c > 64 && g->N <= c / 2) continue;  // do not pad a narrow N to a wide tile
@@ -615,13 +694,22 @@ extern "C" int b200ml_gemm_bf16(const b200ml_gemm_args* g, cudaStream_t stream) 
             const long long cost = ((tiles + sms - 1) / sms) * cost_per_tile[ci];
             if (best < 0 || cost < best) { best = cost; bn = c; }
         }
+        // CTA pair: same MMA time per SM, two thirds of the operand traffic; worth it once every pair has work
+        if (g->N > 128 && g->M > BLOCK_M) {
+            const long long tiles2 = ((g->M + 2 * BLOCK_M - 1) / (2 * BLOCK_M)) * ((g->N + 255) / 256);
+            const long long cost2 = ((tiles2 + sms / 2 - 1) / (sms / 2)) * kPairTileCost;
+            // the pair start-up (cluster launch, cluster barriers) costs ~1.2 us: needs several waves or a long K loop
+            const bool enough = tiles2 >= 4 * (sms / 2) || (k_blocks >= 48 && tiles2 >= sms / 4);
+            if (enough && cost2 <= best) { best = cost2; bn = 256; ctas = 2; }
+        }
     }
     // Split-K: only for the plain epilogue, when the output tiles cannot fill the machine and K is long.
     int splits = 1;
     const bool plain = !g->bias && !g->act && !ep.aux_mode && g->dropout_p <= 0.f;
-    const long long tiles_mn = m_tiles * ((g->N + bn - 1) / bn);
+    const long long tiles_mn = (ctas == 2 ? (g->M + 2 * BLOCK_M - 1) / (2 * BLOCK_M) : m_tiles) * ((g->N + bn - 1) / bn);
     if (plain && g->workspace && g->split_k != 1 && k_blocks >= 8) {
-        int want = g->split_k > 1 ? g->split_k : (tiles_mn * 2 <= sms ? (int)(sms / tiles_mn) : 1);
+        const int slots = sms / ctas;
+        int want = g->split_k > 1 ? g->split_k : (tiles_mn * 2 <= slots ? (int)(slots / tiles_mn) : 1);
         if (want > k_blocks / 4) want = k_blocks / 4;
         if (want > 32) want = 32;
         while (want > 1 && (size_t)want * g->M * g->N * sizeof(float) > g->workspace_bytes) --want;
@@ -631,7 +719,8 @@ extern "C" int b200ml_gemm_bf16(const b200ml_gemm_args* g, cudaStream_t stream) 
             splits = want;
         }
     }
-    if (bn == 256) return dispatch_major<256>(g, ep, splits, stream);
-    if (bn == 128) return dispatch_major<128>(g, ep, splits, stream);
-    return dispatch_major<64>(g, ep, splits, stream);
+    if (ctas == 2) return dispatch_major<256, 2>(g, ep, splits, stream);
+    if (bn == 256) return dispatch_major<256, 1>(g, ep, splits, stream);
+    if (bn == 128) return dispatch_major<128, 1>(g, ep, splits, stream);
+    return dispatch_major<64, 1>(g, ep, splits, stream);
 }

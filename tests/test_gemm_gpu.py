@@ -22,6 +22,8 @@ def _check(out, ref, K, tol_scale=1.0):
 @pytest.mark.parametrize("M,N,K,tile_n", [
     (128, 64, 64, 64), (256, 128, 128, 128), (384, 512, 192, 256), (200, 136, 72, 0), (1000, 264, 520, 0),
     (6400, 512, 512, 0),
+    # tile_n = 512: CTA-pair (cta_group::2) 256 x 256 tiles, incl. ragged M / N / K and more tiles than pairs
+    (256, 256, 64, 512), (512, 512, 192, 512), (1000, 264, 520, 512), (5000, 2048, 136, 512), (200, 136, 72, 512),
 ])
 def test_gemm_layouts(a_mn, b_mn, M, N, K, tile_n):
     from b200ml.ops.gemm import gemm
@@ -65,6 +67,27 @@ def test_gemm_simt_split_k_weight_gradient_shape():
     _check(acc, 1.0 + 0.5 * ref, K)
     one = gemm(a, b, a_mn=True, b_mn=True, out_dtype=torch.float32, split_k=1)
     _check(one, ref, K)
+
+
+def test_gemm_pair_epilogue_and_split_k():
+    """CTA-pair path with the fused epilogue (bias + ReLU, bf16 TMA store), fp32 accumulate, and split-K."""
+    from b200ml.ops.gemm import gemm
+    torch.manual_seed(5)
+    M, N, K = 1300, 1000, 256
+    a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
+    b = (torch.randn(N, K, device="cuda") * 0.1).to(torch.bfloat16)
+    bias = torch.randn(N, device="cuda")
+    ref = torch.relu(_ref(a, b, False, False) + bias.cpu())
+    _check(gemm(a, b, bias=bias, act="relu", tile_n=512), ref, K, tol_scale=2.0)
+    _check(gemm(a, b, bias=bias, act="relu", tile_n=512, out_dtype=torch.float32), ref, K)
+    # long K, few tiles -> split-K over pairs
+    K2 = 6400
+    a2 = torch.randn(K2, 512, device="cuda").to(torch.bfloat16)
+    b2 = torch.randn(K2, 512, device="cuda").to(torch.bfloat16)
+    ref2 = _ref(a2, b2, True, True)
+    acc = torch.ones(512, 512, device="cuda")
+    gemm(a2, b2, a_mn=True, b_mn=True, out=acc, accumulate=True, tile_n=512)
+    _check(acc, 1.0 + ref2, K2)
 
 
 def test_gemm_epilogues():
