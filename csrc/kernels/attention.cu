@@ -16,6 +16,8 @@
 //   bwd_q  : S, dP = dO·Vᵀ -> dS = P∘(dP − D)·scale -> dQ = dS·K
 //   bwd_kv : Sᵀ = K·Qᵀ, dPᵀ = V·dOᵀ (this CTA owns 128 keys) -> Pᵀ, dSᵀ -> dV = Pᵀ·dO, dK = dSᵀ·Q
 // No atomics, every gradient element is written exactly once => bit-reproducible.
+#include <cstdlib>
+
 #include "../../include/b200ml.h"
 #include "../common/host.h"
 #include "../common/ptx.cuh"
@@ -462,6 +464,225 @@ attn_bwd_kv_kernel(const __grid_constant__ CUtensorMap tk, const __grid_constant
     }
 }
 
+// ------------------------------------------------------------------------------------------------ backward, fused
+// One CTA per (batch, head) computes dQ, dK and dV together, so S and dP are formed once (the two kernels above each
+// recompute them) and Q / K / V / dO are read from HBM once.  The sequence is cut into 128 x 128 blocks (q tile i,
+// key tile j); per block:   S = Q_i·K_jᵀ, dP = dO_i·V_jᵀ (TMEM)  ->  P, dS (registers -> bf16 smem)  ->
+// dV_j += Pᵀ·dO_i,  dK_j += dSᵀ·Q_i,  dQ_i += dS·K_j   with Pᵀ / dSᵀ consumed as MN-major A operands from the same
+// bytes.  The S / dP products of block n+1 are issued before the three accumulation products of block n, so the
+// exponentials of block n+1 overlap the tensor work of block n.
+// smem: [Q 32K][dO 32K][K 32K][V 32K][P 32K][dS 32K][lse 1K][D 1K]      TMEM: S 128 | dP 128 | dQ_0 64 | dQ_1 64 | dV 64 | dK 64
+constexpr int kBwdFusedSmem = 6 * 32768 + 2048 + 1024 + 128;
+
+__device__ __forceinline__ float ex2_approx(float x) {  // 2^x, one MUFU; -inf -> 0
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+// P and dS of 32 consecutive keys of one query row, packed to bf16 pairs.  No range masks: rows / keys outside the
+// sequence are zero in shared memory (TMA zero fill + the tail clear at kernel start), which makes their S, dP and
+// therefore dS exactly harmless, and TMEM columns beyond the live keys only reach gradient rows that are never stored.
+template <int MODE>
+__device__ __forceinline__ void bwd_chunk(const uint32_t (&rs)[32], const uint32_t (&rp)[32], int qrow, int kc0, float sc,
+                                          float nl2, float D, float scale, uint32_t (&pp)[16], uint32_t (&pd)[16]) {
+#pragma unroll
+    for (int e = 0; e < 32; e += 2) {
+        float pv[2], dv[2];
+#pragma unroll
+        for (int t = 0; t < 2; ++t) {
+            const int kc = kc0 + e + t;
+            float x = fmaf(__uint_as_float(rs[e + t]), sc, nl2);
+            if (MODE == 1) x += kc < qrow ? kLog2e : 0.f;
+            if (MODE == 2) x = kc > qrow ? -INFINITY : x;
+            pv[t] = ex2_approx(x);
+            dv[t] = pv[t] * scale * (__uint_as_float(rp[e + t]) - D);
+        }
+        pp[e >> 1] = pack_bf16x2(pv[0], pv[1]);
+        pd[e >> 1] = pack_bf16x2(dv[0], dv[1]);
+    }
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tdo,
+                      const __grid_constant__ CUtensorMap tk, const __grid_constant__ CUtensorMap tv, Operand q,
+                      Operand k, Operand v, Operand o, Operand dout, Operand dq, Operand dk, Operand dv,
+                      const float* __restrict__ lse, int H, int Sq, int Skv, int sq_pad, int skv_pad, float scale,
+                      int mask_mode) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sQ = smem;
+    uint8_t* sdO = smem + 32768;
+    uint8_t* sK = smem + 2 * 32768;
+    uint8_t* sV = smem + 3 * 32768;
+    uint8_t* sP = smem + 4 * 32768;
+    uint8_t* sdS = smem + 5 * 32768;
+    float* s_lse = reinterpret_cast<float*>(smem + 6 * 32768);
+    float* s_D = s_lse + MAXS;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 6 * 32768 + 2048);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int quarter = warp & 3, half = warp >> 2;
+    const int r = quarter * 32 + lane;  // row inside a 128-row tile == TMEM lane
+    const int h = blockIdx.y, b = blockIdx.z;
+    if (tid == 0) {
+        mbar_init(&bars[0], 1);  // operands landed
+        mbar_init(&bars[1], 1);  // S / dP of a block complete
+        mbar_init(&bars[2], 1);  // accumulation products of a block complete (P / dS smem reusable)
+        fence_barrier_init();
+    }
+    if (warp == 0) tmem_alloc<512>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+    const uint32_t tS = tmem, tdP = tmem + 128, tdQ = tmem + 256, tdV = tmem + 384, tdK = tmem + 448;
+    const int nqt = (Sq + TILE - 1) / TILE, nkt = (Skv + TILE - 1) / TILE;
+    const int nblocks = nqt * nkt;
+    // padded (multiple of 16) number of live rows in q tile i / key tile j: rows beyond were never written by TMA
+    auto nq_of = [&](int i) { return sq_pad - TILE * i < TILE ? sq_pad - TILE * i : TILE; };
+    auto nk_of = [&](int j) { return skv_pad - TILE * j < TILE ? skv_pad - TILE * j : TILE; };
+
+    auto issue_scores = [&](int i, int j) {  // S = Q_i·K_jᵀ, dP = dO_i·V_jᵀ
+        mma_k64(tS, smem_u32(sQ) + i * 16384, smem_u32(sK) + j * 16384, nk_of(j));
+        mma_k64(tdP, smem_u32(sdO) + i * 16384, smem_u32(sV) + j * 16384, nk_of(j));
+        umma_commit(&bars[1]);
+    };
+    auto issue_accum = [&](int i, int j) {
+        const uint32_t id_t = umma_idesc_bf16(TILE, HD, true, true);    // A = Pᵀ / dSᵀ (MN-major), B MN-major
+        const uint32_t id_n = umma_idesc_bf16(TILE, HD, false, true);   // A = dS (K-major), B MN-major
+        const uint32_t p0 = smem_u32(sP), s0 = smem_u32(sdS);
+        const uint32_t do_i = smem_u32(sdO) + i * 16384, q_i = smem_u32(sQ) + i * 16384, k_j = smem_u32(sK) + j * 16384;
+        const int qs = nq_of(i) >> 4, ks = nk_of(j) >> 4;
+        for (int kk = 0; kk < qs; ++kk)   // dV_j += Pᵀ·dO_i  (reduction over the q rows of tile i)
+            umma_bf16(tdV, umma_smem_desc(p0 + kk * 2048, 16384, 1024), umma_smem_desc(do_i + kk * 2048, 8192, 1024),
+                      id_t, (i > 0 || kk > 0) ? 1u : 0u);
+        for (int kk = 0; kk < qs; ++kk)   // dK_j += dSᵀ·Q_i
+            umma_bf16(tdK, umma_smem_desc(s0 + kk * 2048, 16384, 1024), umma_smem_desc(q_i + kk * 2048, 8192, 1024),
+                      id_t, (i > 0 || kk > 0) ? 1u : 0u);
+        for (int kk = 0; kk < ks; ++kk)   // dQ_i += dS·K_j  (reduction over the keys of tile j)
+            umma_bf16(tdQ + 64 * i, umma_smem_desc(s0 + (kk >> 2) * 16384 + (kk & 3) * 32, 16, 1024),
+                      umma_smem_desc(k_j + kk * 2048, 8192, 1024), id_n, (j > 0 || kk > 0) ? 1u : 0u);
+        umma_commit(&bars[2]);
+    };
+
+    {   // rows the TMA boxes do not cover (beyond the 16-padded sequence, up to the tile edge) must read as zero
+        const int q_tail = (nqt * TILE - sq_pad) * 8, k_tail = (nkt * TILE - skv_pad) * 8;  // in 16-byte units
+        const uint4 z = make_uint4(0, 0, 0, 0);
+        for (int x = tid; x < q_tail; x += kThreads) {
+            reinterpret_cast<uint4*>(sQ + sq_pad * 128)[x] = z;
+            reinterpret_cast<uint4*>(sdO + sq_pad * 128)[x] = z;
+        }
+        for (int x = tid; x < k_tail; x += kThreads) {
+            reinterpret_cast<uint4*>(sK + skv_pad * 128)[x] = z;
+            reinterpret_cast<uint4*>(sV + skv_pad * 128)[x] = z;
+        }
+        fence_proxy_async_smem();
+        __syncthreads();
+    }
+    if (tid == 0) {
+        mbar_arrive_expect_tx(&bars[0], 2 * sq_pad * 128 + 2 * skv_pad * 128);
+        tma_load_3d(sQ, &tq, &bars[0], q.col0 + h * q.head_stride, 0, b);
+        tma_load_3d(sdO, &tdo, &bars[0], dout.col0 + h * dout.head_stride, 0, b);
+        tma_load_3d(sK, &tk, &bars[0], k.col0 + h * k.head_stride, 0, b);
+        tma_load_3d(sV, &tv, &bars[0], v.col0 + h * v.head_stride, 0, b);
+        mbar_wait(&bars[0], 0);
+        tc_fence_after();
+        issue_scores(0, 0);
+    }
+    {   // per-query statistics: lse (log2 domain) and D = rowsum(dO ∘ O); thread t owns query row t
+        const int qr = tid;  // kThreads == MAXS
+        float D = 0.f, l2 = 0.f;
+        if (qr < Sq) {
+            D = row_dot64(o.ptr + ((long long)b * Sq + qr) * o.ld + o.col0 + h * o.head_stride,
+                          dout.ptr + ((long long)b * Sq + qr) * dout.ld + dout.col0 + h * dout.head_stride);
+            l2 = lse[((long long)b * H + h) * Sq + qr] * kLog2e;
+        }
+        s_lse[qr] = l2;
+        s_D[qr] = D;
+    }
+    __syncthreads();
+
+    const uint32_t trow = static_cast<uint32_t>(quarter * 32) << 16;
+    const float sc = scale * kLog2e;
+    auto write_out = [&](uint32_t tcol, const Operand& dst, int row, int limit) {  // 32 of the 64 columns per thread
+        uint32_t rg[32];
+        tmem_ld_32x32b_x32(trow + tcol + half * 32, rg);
+        tmem_ld_wait();
+        if (row < limit) {
+            __nv_bfloat16* out = dst.ptr + ((long long)b * limit + row) * dst.ld + dst.col0 + h * dst.head_stride;
+            store_row32_bf16(out + half * 32, rg);
+        }
+    };
+
+    int n = 0;
+    for (int j = 0; j < nkt; ++j) {
+        for (int i = 0; i < nqt; ++i, ++n) {
+            mbar_wait(&bars[1], n & 1);
+            tc_fence_after();
+            const int qrow = TILE * i + r;
+            const float nl2 = -s_lse[qrow], D = s_D[qrow];
+            uint32_t pp[2][16], pd[2][16];  // bf16x2-packed P and dS of this thread's 64 columns
+#pragma unroll
+            for (int cc = 0; cc < 2; ++cc) {
+                const int c = half * 64 + cc * 32;
+                uint32_t rs[32], rp[32];
+                tmem_ld_32x32b_x32(tS + trow + c, rs);
+                tmem_ld_32x32b_x32(tdP + trow + c, rp);
+                tmem_ld_wait();
+                const int kc0 = TILE * j + c;
+                if (mask_mode == 1) bwd_chunk<1>(rs, rp, qrow, kc0, sc, nl2, D, scale, pp[cc], pd[cc]);
+                else if (mask_mode == 2) bwd_chunk<2>(rs, rp, qrow, kc0, sc, nl2, D, scale, pp[cc], pd[cc]);
+                else bwd_chunk<0>(rs, rp, qrow, kc0, sc, nl2, D, scale, pp[cc], pd[cc]);
+            }
+            if (n > 0) {  // the accumulation products of the previous block have consumed P / dS
+                mbar_wait(&bars[2], (n - 1) & 1);
+                tc_fence_after();
+                if (i == 0) {  // ... and they completed dV / dK of the previous key tile
+                    write_out(384, dv, TILE * (j - 1) + r, Skv);
+                    write_out(448, dk, TILE * (j - 1) + r, Skv);
+                }
+            }
+            {
+                const uint32_t bp = smem_u32(sP) + half * 16384, bd = smem_u32(sdS) + half * 16384;
+#pragma unroll
+                for (int cc = 0; cc < 2; ++cc)
+#pragma unroll
+                    for (int c4 = 0; c4 < 4; ++c4) {
+                        const uint32_t off = swz128_offset(r, cc * 4 + c4);
+                        sts128(bp + off, pp[cc][4 * c4], pp[cc][4 * c4 + 1], pp[cc][4 * c4 + 2], pp[cc][4 * c4 + 3]);
+                        sts128(bd + off, pd[cc][4 * c4], pd[cc][4 * c4 + 1], pd[cc][4 * c4 + 2], pd[cc][4 * c4 + 3]);
+                    }
+            }
+            tc_fence_before();
+            fence_proxy_async_smem();
+            __syncthreads();
+            if (tid == 0) {
+                tc_fence_after();
+                if (n + 1 < nblocks) {
+                    const int i2 = i + 1 < nqt ? i + 1 : 0, j2 = i + 1 < nqt ? j : j + 1;
+                    issue_scores(i2, j2);
+                }
+                issue_accum(i, j);
+            }
+        }
+    }
+    mbar_wait(&bars[2], (n - 1) & 1);
+    tc_fence_after();
+    write_out(384, dv, TILE * (nkt - 1) + r, Skv);
+    write_out(448, dk, TILE * (nkt - 1) + r, Skv);
+    for (int i = 0; i < nqt; ++i) write_out(256 + 64 * i, dq, TILE * i + r, Sq);
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        tmem_dealloc<512>(tmem);
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ host
 static int head_tmap(CUtensorMap* m, const b200ml_attn_operand* op, int B, int S, int H, int box_rows) {
     // dims: {columns reachable by any head, S, B}
@@ -529,6 +750,26 @@ int b200ml_attn_bwd(const b200ml_attn_operand* q, const b200ml_attn_operand* k, 
     B200_REQUIRE(Sq >= 1 && Skv >= 1 && Sq <= MAXS && Skv <= MAXS, "attention bwd: need S <= %d (got %d, %d)", MAXS, Sq,
                  Skv);
     const int skv_pad = (Skv + 15) / 16 * 16, sq_pad = (Sq + 15) / 16 * 16;
+    // B200ML_ATTN_BWD=split keeps the two-kernel backward (dQ, then dK/dV); default is the fused single kernel
+    static const bool split = [] { const char* e = getenv("B200ML_ATTN_BWD"); return e && e[0] == 's'; }();
+    if (!split) {
+        static bool attr_f = false;
+        if (!attr_f) {
+            B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 kBwdFusedSmem + 1024));
+            attr_f = true;
+        }
+        CUtensorMap tq, tdo, tk, tv;
+        if (head_tmap(&tq, q, B, Sq, H, sq_pad) || head_tmap(&tdo, dout, B, Sq, H, sq_pad) ||
+            head_tmap(&tk, k, B, Skv, H, skv_pad) || head_tmap(&tv, v, B, Skv, H, skv_pad))
+            return -1;
+        dim3 grid(1, H, B);
+        attn_bwd_fused_kernel<<<grid, kThreads, kBwdFusedSmem + 1024, stream>>>(
+            tq, tdo, tk, tv, dev_op(q), dev_op(k), dev_op(v), dev_op(out), dev_op(dout), dev_op(dq), dev_op(dk), dev_op(dv),
+            lse, H, Sq, Skv, sq_pad, skv_pad, scale, mask_mode);
+        B200_CHECK_CUDA(cudaGetLastError());
+        return 0;
+    }
     static bool attr = false;
     if (!attr) {
         B200_CHECK_CUDA(

@@ -29,7 +29,7 @@ def test_self_attention(mask_mode, B, H, S):
 
 
 @pytest.mark.parametrize("mask_mode", ["reference", "none"])
-@pytest.mark.parametrize("Sq,Skv", [(200, 200), (72, 136)])
+@pytest.mark.parametrize("Sq,Skv", [(200, 200), (72, 136), (200, 40), (130, 256)])
 def test_cross_attention(mask_mode, Sq, Skv):
     from b200ml.ops.attention import attention, attention_reference
     torch.manual_seed(1)
