@@ -7,6 +7,7 @@ import torch
 from torch.profiler import ProfilerActivity, profile
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+os.environ.setdefault("B200ML_PDL", "0")  # early-launched kernels would be charged for the time they spend waiting
 os.environ.setdefault("B200ML_WGRAD_STREAM", "0")
 os.environ.setdefault("B200ML_OVERLAP_STREAMS", "0")
 os.environ.setdefault("B200ML_OPT_OVERLAP", "0")

@@ -2,6 +2,7 @@
 // sums `n_rows` partial rows of `cols` floats in a fixed order.  32 columns x 8 row-groups per CTA, so the long
 // dimension is walked by 8 threads per column instead of one.
 #pragma once
+#include "pdl.cuh"
 #include <cuda_runtime.h>
 
 namespace b200 {
@@ -10,6 +11,8 @@ namespace b200 {
 static __global__ void __launch_bounds__(256)
 reduce_partials_kernel(const float* __restrict__ partial, int n_rows, int cols, int split_col, float* __restrict__ out0,
                        float* __restrict__ out1, int accumulate) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
     __shared__ float red[8][33];
     const int c = threadIdx.x & 31, g = threadIdx.x >> 5;
     const int col = blockIdx.x * 32 + c;  // one warp-wide column group per CTA keeps the CTA count (= cols/32) high
@@ -31,7 +34,7 @@ reduce_partials_kernel(const float* __restrict__ partial, int n_rows, int cols, 
 
 static inline cudaError_t launch_reduce_partials(const float* partial, int n_rows, int cols, int split_col, float* out0,
                                           float* out1, int accumulate, cudaStream_t stream) {
-    reduce_partials_kernel<<<(cols + 31) / 32, 256, 0, stream>>>(partial, n_rows, cols, split_col, out0, out1,
+    b200::pdl(reduce_partials_kernel, dim3((cols + 31) / 32), dim3(256), 0, stream)(partial, n_rows, cols, split_col, out0, out1,
                                                                  accumulate);
     return cudaGetLastError();
 }

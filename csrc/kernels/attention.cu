@@ -16,6 +16,7 @@
 //   bwd_q  : S, dP = dO·Vᵀ -> dS = P∘(dP − D)·scale -> dQ = dS·K
 //   bwd_kv : Sᵀ = K·Qᵀ, dPᵀ = V·dOᵀ (this CTA owns 128 keys) -> Pᵀ, dSᵀ -> dV = Pᵀ·dO, dK = dSᵀ·Q
 // No atomics, every gradient element is written exactly once => bit-reproducible.
+#include "../common/pdl.cuh"
 #include <cstdlib>
 
 #include "../../include/b200ml.h"
@@ -97,6 +98,8 @@ __global__ void __launch_bounds__(kThreads, 2)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tk,
                 const __grid_constant__ CUtensorMap tv, Operand q, Operand k, Operand v, Operand o,
                 float* __restrict__ lse, int H, int Sq, int Skv, int skv_pad, float scale, int mask_mode) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sQ = smem;
@@ -256,6 +259,8 @@ attn_bwd_q_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
                   const __grid_constant__ CUtensorMap tk, const __grid_constant__ CUtensorMap tv, Operand q, Operand k,
                   Operand v, Operand o, Operand dout, Operand dq, const float* __restrict__ lse, int H, int Sq, int Skv,
                   int skv_pad, float scale, int mask_mode) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sQ = smem;
@@ -358,6 +363,8 @@ attn_bwd_kv_kernel(const __grid_constant__ CUtensorMap tk, const __grid_constant
                    const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tdo, Operand q, Operand k,
                    Operand v, Operand o, Operand dout, Operand dk, Operand dv, const float* __restrict__ lse, int H,
                    int Sq, int Skv, int sq_pad, float scale, int mask_mode) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sK = smem;
@@ -511,6 +518,8 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
                       Operand k, Operand v, Operand o, Operand dout, Operand dq, Operand dk, Operand dv,
                       const float* __restrict__ lse, int H, int Sq, int Skv, int sq_pad, int skv_pad, float scale,
                       int mask_mode) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sQ = smem;
@@ -731,7 +740,7 @@ int b200ml_attn_fwd(const b200ml_attn_operand* q, const b200ml_attn_operand* k, 
         attr = true;
     }
     dim3 grid((Sq + TILE - 1) / TILE, H, B);
-    attn_fwd_kernel<<<grid, kThreads, kFwdSmem, stream>>>(tq, tk, tv, dev_op(q), dev_op(k), dev_op(v), dev_op(out), lse, H,
+    b200::pdl(attn_fwd_kernel, dim3(grid), dim3(kThreads), kFwdSmem, stream)(tq, tk, tv, dev_op(q), dev_op(k), dev_op(v), dev_op(out), lse, H,
                                                      Sq, Skv, skv_pad, scale, mask_mode);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
@@ -764,7 +773,7 @@ int b200ml_attn_bwd(const b200ml_attn_operand* q, const b200ml_attn_operand* k, 
             head_tmap(&tk, k, B, Skv, H, skv_pad) || head_tmap(&tv, v, B, Skv, H, skv_pad))
             return -1;
         dim3 grid(1, H, B);
-        attn_bwd_fused_kernel<<<grid, kThreads, kBwdFusedSmem + 1024, stream>>>(
+        b200::pdl(attn_bwd_fused_kernel, dim3(grid), dim3(kThreads), kBwdFusedSmem + 1024, stream)(
             tq, tdo, tk, tv, dev_op(q), dev_op(k), dev_op(v), dev_op(out), dev_op(dout), dev_op(dq), dev_op(dk), dev_op(dv),
             lse, H, Sq, Skv, sq_pad, skv_pad, scale, mask_mode);
         B200_CHECK_CUDA(cudaGetLastError());
@@ -784,7 +793,7 @@ int b200ml_attn_bwd(const b200ml_attn_operand* q, const b200ml_attn_operand* k, 
             head_tmap(&tk, k, B, Skv, H, skv_pad) || head_tmap(&tv, v, B, Skv, H, skv_pad))
             return -1;
         dim3 grid((Sq + TILE - 1) / TILE, H, B);
-        attn_bwd_q_kernel<<<grid, kThreads, kBwdQSmem, stream>>>(tq, tdo, tk, tv, dev_op(q), dev_op(k), dev_op(v),
+        b200::pdl(attn_bwd_q_kernel, dim3(grid), dim3(kThreads), kBwdQSmem, stream)(tq, tdo, tk, tv, dev_op(q), dev_op(k), dev_op(v),
                                                             dev_op(out), dev_op(dout), dev_op(dq), lse, H, Sq, Skv,
                                                             skv_pad, scale, mask_mode);
         B200_CHECK_CUDA(cudaGetLastError());
@@ -795,7 +804,7 @@ int b200ml_attn_bwd(const b200ml_attn_operand* q, const b200ml_attn_operand* k, 
             head_tmap(&tq, q, B, Sq, H, sq_pad) || head_tmap(&tdo, dout, B, Sq, H, sq_pad))
             return -1;
         dim3 grid((Skv + TILE - 1) / TILE, H, B);
-        attn_bwd_kv_kernel<<<grid, kThreads, kBwdKVSmem, stream>>>(tk, tv, tq, tdo, dev_op(q), dev_op(k), dev_op(v),
+        b200::pdl(attn_bwd_kv_kernel, dim3(grid), dim3(kThreads), kBwdKVSmem, stream)(tk, tv, tq, tdo, dev_op(q), dev_op(k), dev_op(v),
                                                               dev_op(out), dev_op(dout), dev_op(dk), dev_op(dv), lse, H,
                                                               Sq, Skv, sq_pad, scale, mask_mode);
         B200_CHECK_CUDA(cudaGetLastError());

@@ -9,6 +9,7 @@
 //             dX = full correlation with flipped weights; dW / db via per-CTA partial sums + a fixed-order second stage
 //             (deterministic, no atomics).
 // One CTA = one image x one 16x16 output tile x all channels.  Cin, Cout <= 64.
+#include "../common/pdl.cuh"
 #include "../../include/b200ml.h"
 #include "../common/host.h"
 #include "../common/reduce.cuh"
@@ -28,6 +29,8 @@ __global__ void __launch_bounds__(T* T)
 conv_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                 float* __restrict__ y, unsigned char* __restrict__ pool_idx, int B, int Cin, int Cout, int H, int W,
                 int pool) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
     extern __shared__ float smem[];
     float* s_in = smem;                           // [Cin][HALO][HALO]
     float* s_w = s_in + Cin * HALO * HALO;        // [Cout][Cin][9]
@@ -121,6 +124,8 @@ struct DzSource {
 // dX[b, ci, y, x] = sum_co sum_taps dZ[b, co, y - dy + 1, x - dx + 1] * W[co, ci, dy, dx]
 __global__ void __launch_bounds__(T* T)
 conv_bwd_data_kernel(DzSource src, const float* __restrict__ w, float* __restrict__ dx, int B, int Cin, int Cout) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
     extern __shared__ float smem[];
     float* s_dz = smem;                          // [Cout][HALO][HALO]
     float* s_w = s_dz + Cout * HALO * HALO;      // [Cout][Cin][9]
@@ -166,6 +171,8 @@ conv_bwd_data_kernel(DzSource src, const float* __restrict__ w, float* __restric
 __global__ void __launch_bounds__(T* T)
 conv_bwd_weight_kernel(DzSource src, const float* __restrict__ x, float* __restrict__ partial, int B, int Cin,
                        int Cout) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
     extern __shared__ float smem[];
     float* s_in = smem;                        // [Cin][HALO][HALO]
     float* s_dz = s_in + Cin * HALO * HALO;    // [Cout][T][T]
@@ -226,7 +233,7 @@ int b200ml_conv3x3_relu_fwd(const float* x, const float* w, const float* bias, f
         attr = smem;
     }
     dim3 grid(((H + T - 1) / T) * ((W + T - 1) / T), B);
-    conv_fwd_kernel<<<grid, T * T, smem, stream>>>(x, w, bias, y, pool_idx, B, Cin, Cout, H, W, pool);
+    b200::pdl(conv_fwd_kernel, dim3(grid), dim3(T * T), smem, stream, 3)(x, w, bias, y, pool_idx, B, Cin, Cout, H, W, pool);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
@@ -257,7 +264,7 @@ int b200ml_conv3x3_relu_bwd(const float* dy, const float* ysaved, const unsigned
                 cudaFuncSetAttribute(conv_bwd_data_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             attr = smem;
         }
-        conv_bwd_data_kernel<<<grid, T * T, smem, stream>>>(src, w, dx, B, Cin, Cout);
+        b200::pdl(conv_bwd_data_kernel, dim3(grid), dim3(T * T), smem, stream, 3)(src, w, dx, B, Cin, Cout);
         B200_CHECK_CUDA(cudaGetLastError());
     }
     {
@@ -268,7 +275,7 @@ int b200ml_conv3x3_relu_bwd(const float* dy, const float* ysaved, const unsigned
                 cudaFuncSetAttribute(conv_bwd_weight_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             attr = smem;
         }
-        conv_bwd_weight_kernel<<<grid, T * T, smem, stream>>>(src, x, (float*)scratch, B, Cin, Cout);
+        b200::pdl(conv_bwd_weight_kernel, dim3(grid), dim3(T * T), smem, stream, 3)(src, x, (float*)scratch, B, Cin, Cout);
         B200_CHECK_CUDA(cudaGetLastError());
         const int nW = Cout * Cin * 9;
         B200_CHECK_CUDA(b200::launch_reduce_partials((const float*)scratch, (int)(grid.x * grid.y), nW + Cout, nW, dw, db,

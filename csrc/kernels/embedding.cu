@@ -5,6 +5,7 @@
 // PE[pos, 2i+1] = cos(same) on the CPU every forward and copies it to the device; SentenceEmbedding returns
 // dropout(embedding(x) + PE).  Here PE is a device-resident table built once (b200ml_pe_table) and the three ops are
 // one pass.  LSTM use (distributed_lstm.py:115,128): no PE, no dropout, padding_idx row receives zero gradient.
+#include "../common/pdl.cuh"
 #include "../../include/b200ml.h"
 #include "../common/host.h"
 #include "../common/ptx.cuh"
@@ -14,6 +15,8 @@ namespace b200 {
 namespace emb {
 
 __global__ void pe_table_kernel(float* __restrict__ pe, int S, int d) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= S * d) return;
     const int pos = idx / d, c = idx % d;
@@ -30,6 +33,8 @@ __global__ void __launch_bounds__(256)
 embedding_fwd_kernel(const long long* __restrict__ tokens, const __nv_bfloat16* __restrict__ table,
                      const float* __restrict__ pe, OutT* __restrict__ out, int n_tokens, int S, int d, int V, float p,
                      const RngState* __restrict__ rng, uint32_t site) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (warp >= n_tokens) return;
     long long tok = tokens[warp];
@@ -86,6 +91,8 @@ __global__ void __launch_bounds__(256)
 embedding_bwd_kernel(const long long* __restrict__ tokens, const InT* __restrict__ dout, float* __restrict__ dtable,
                      int n_tokens, int d, int V, long long padding_idx, float p, const RngState* __restrict__ rng,
                      uint32_t site) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (warp >= n_tokens) return;
     long long tok = tokens[warp];
@@ -117,7 +124,7 @@ extern "C" {
 int b200ml_pe_table(float* pe, int S, int d, cudaStream_t stream) {
     B200_REQUIRE(pe && S > 0 && d > 0, "pe_table: bad args");
     const int n = S * d;
-    b200::emb::pe_table_kernel<<<(n + 255) / 256, 256, 0, stream>>>(pe, S, d);
+    b200::pdl(b200::emb::pe_table_kernel, dim3((n + 255) / 256), dim3(256), 0, stream)(pe, S, d);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
@@ -131,11 +138,11 @@ int b200ml_embedding_fwd(const long long* tokens, const void* table_bf16, const 
     if (n_tokens <= 0) return 0;
     const int grid = (n_tokens + 7) / 8;
     if (out_fp32)
-        embedding_fwd_kernel<float><<<grid, 256, 0, stream>>>(tokens, (const __nv_bfloat16*)table_bf16, pe, (float*)out,
+        b200::pdl(embedding_fwd_kernel<float>, dim3(grid), dim3(256), 0, stream)(tokens, (const __nv_bfloat16*)table_bf16, pe, (float*)out,
                                                               n_tokens, S, d, V, dropout_p,
                                                               (const b200::RngState*)rng_state, rng_site);
     else
-        embedding_fwd_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(
+        b200::pdl(embedding_fwd_kernel<__nv_bfloat16>, dim3(grid), dim3(256), 0, stream)(
             tokens, (const __nv_bfloat16*)table_bf16, pe, (__nv_bfloat16*)out, n_tokens, S, d, V, dropout_p,
             (const b200::RngState*)rng_state, rng_site);
     B200_CHECK_CUDA(cudaGetLastError());
@@ -150,11 +157,11 @@ int b200ml_embedding_bwd(const long long* tokens, const void* dout, int dout_fp3
     if (n_tokens <= 0) return 0;
     const int grid = (n_tokens + 7) / 8;
     if (dout_fp32)
-        embedding_bwd_kernel<float><<<grid, 256, 0, stream>>>(tokens, (const float*)dout, dtable, n_tokens, d, V,
+        b200::pdl(embedding_bwd_kernel<float>, dim3(grid), dim3(256), 0, stream)(tokens, (const float*)dout, dtable, n_tokens, d, V,
                                                               padding_idx, dropout_p, (const b200::RngState*)rng_state,
                                                               rng_site);
     else
-        embedding_bwd_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(
+        b200::pdl(embedding_bwd_kernel<__nv_bfloat16>, dim3(grid), dim3(256), 0, stream)(
             tokens, (const __nv_bfloat16*)dout, dtable, n_tokens, d, V, padding_idx, dropout_p,
             (const b200::RngState*)rng_state, rng_site);
     B200_CHECK_CUDA(cudaGetLastError());

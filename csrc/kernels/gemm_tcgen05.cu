@@ -20,6 +20,7 @@
 
 #include "../../include/b200ml.h"
 #include "../common/host.h"
+#include "../common/pdl.cuh"
 #include "../common/ptx.cuh"
 #include "../common/rng.cuh"
 
@@ -150,6 +151,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr_smem;
+    pdl_trigger();  // dependents may take SMs as they free up ...
+    pdl_wait();     // ... and everything above overlapped the tail of the kernel before this one
 
     const int m_tiles = (M + kTileM - 1) / kTileM;
     const int n_tiles = (N + BN - 1) / BN;
@@ -465,6 +468,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 __global__ void __launch_bounds__(256)
 splitk_reduce_kernel(const float* __restrict__ ws, int splits, long long mn, int N, void* __restrict__ Cp,
                      long long ldc, int c_fp32, int accumulate, float alpha, const float* __restrict__ alpha_dev) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
     const float a = alpha * (alpha_dev ? *alpha_dev : 1.f);
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < mn; i += stride) {
@@ -488,6 +493,8 @@ splitk_reduce_kernel(const float* __restrict__ ws, int splits, long long mn, int
 __global__ void __launch_bounds__(256)
 gemm_simt_kernel(const __nv_bfloat16* __restrict__ A, long long lda, int a_mn, const __nv_bfloat16* __restrict__ B,
                  long long ldb, int b_mn, int M, int N, int K, int k_per_split, Epilogue ep) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
     __shared__ float sa[16][17];
     __shared__ float sb[16][17];
     const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
@@ -578,29 +585,14 @@ static int launch(const b200ml_gemm_args* g, Epilogue ep, int splits, cudaStream
     const int slots = sm_count() / kCtas;
     const int grid = (tiles < slots ? tiles : slots) * kCtas;
     if (splits > 1) ep.splitk_ws = reinterpret_cast<float*>(g->workspace);
-    if (kCtas == 1) {
-        kern<<<grid, kNumThreads, C::kSmemBytes, stream>>>(ta, tb, tc, g->M, g->N, g->K, splits, ep);
-    } else {
-        cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3(grid);
-        cfg.blockDim = dim3(kNumThreads);
-        cfg.dynamicSmemBytes = C::kSmemBytes;
-        cfg.stream = stream;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeClusterDimension;  // a pair = cluster of two CTAs (same TPC)
-        attr[0].val.clusterDim.x = 2;
-        attr[0].val.clusterDim.y = 1;
-        attr[0].val.clusterDim.z = 1;
-        cfg.attrs = attr;
-        cfg.numAttrs = 1;
-        B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, g->M, g->N, g->K, splits, ep));
-    }
-    B200_CHECK_CUDA(cudaGetLastError());
+    // a pair = cluster of two CTAs (same TPC)
+    B200_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kNumThreads), C::kSmemBytes, stream, kCtas, 1, ta, tb, tc, g->M, g->N,
+                               g->K, splits, ep));
     if (splits > 1) {
         const long long mn = (long long)g->M * g->N;
         long long blocks = (mn + 255) / 256;
         if (blocks > 4LL * sm_count()) blocks = 4LL * sm_count();
-        splitk_reduce_kernel<<<(int)blocks, 256, 0, stream>>>(ep.splitk_ws, splits, mn, g->N, g->C, g->ldc, g->c_fp32,
+        b200::pdl(splitk_reduce_kernel, dim3((int)blocks), dim3(256), 0, stream)(ep.splitk_ws, splits, mn, g->N, g->C, g->ldc, g->c_fp32,
                                                               g->accumulate, g->alpha, g->alpha_dev);
         B200_CHECK_CUDA(cudaGetLastError());
     }
@@ -654,7 +646,7 @@ extern "C" int b200ml_gemm_bf16(const b200ml_gemm_args* g, cudaStream_t stream) 
             grid.z = splits;
             ep.splitk_ws = reinterpret_cast<float*>(g->workspace);
         }
-        gemm_simt_kernel<<<grid, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(g->A), g->lda, g->a_mn_major,
+        b200::pdl(gemm_simt_kernel, dim3(grid), dim3(256), 0, stream)(reinterpret_cast<const __nv_bfloat16*>(g->A), g->lda, g->a_mn_major,
                                                    reinterpret_cast<const __nv_bfloat16*>(g->B), g->ldb,
                                                    g->b_mn_major, g->M, g->N, g->K, k_per, ep);
         B200_CHECK_CUDA(cudaGetLastError());
@@ -662,7 +654,7 @@ extern "C" int b200ml_gemm_bf16(const b200ml_gemm_args* g, cudaStream_t stream) 
             const long long mn = (long long)g->M * g->N;
             long long blocks = (mn + 255) / 256;
             if (blocks > 4LL * sm_count()) blocks = 4LL * sm_count();
-            splitk_reduce_kernel<<<(int)blocks, 256, 0, stream>>>(ep.splitk_ws, splits, mn, g->N, g->C, g->ldc,
+            b200::pdl(splitk_reduce_kernel, dim3((int)blocks), dim3(256), 0, stream)(ep.splitk_ws, splits, mn, g->N, g->C, g->ldc,
                                                                   g->c_fp32, g->accumulate, g->alpha, g->alpha_dev);
             B200_CHECK_CUDA(cudaGetLastError());
         }

@@ -8,6 +8,7 @@
 // elementwise/reduction launches and four fp32 [B,S,d] temporaries per LayerNorm; here it is one pass over bf16 rows
 // with fp32 statistics.  dgamma/dbeta use a deterministic two-stage reduction through a scratch buffer of per-CTA
 // partial sums (no atomics, so every rank computes bit-identical gradients from identical inputs).
+#include "../common/pdl.cuh"
 #include "../../include/b200ml.h"
 #include "../common/host.h"
 #include "../common/ptx.cuh"
@@ -53,6 +54,8 @@ ln_fwd_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restri
               const float* __restrict__ gamma, const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
               __nv_bfloat16* __restrict__ z_out, float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows,
               int d, float eps, float p, const RngState* __restrict__ rng, uint32_t site) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
     constexpr int kMaxChunks = kChunks;  // shadows the namespace-level maximum inside this kernel
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int row = blockIdx.x * kWarpsPerBlock + warp;
@@ -142,6 +145,8 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
               const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ gamma,
               __nv_bfloat16* __restrict__ dz, __nv_bfloat16* __restrict__ da, float* __restrict__ partial, int rows,
               int d, float p, const RngState* __restrict__ rng, uint32_t site) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
     constexpr int kMaxChunks = kChunks;
     __shared__ float red[kWarpsPerBlock][kMaxChunks * 256];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -232,15 +237,15 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
 
 template <typename... Args>
 static void launch_ln_fwd(int d, int grid, cudaStream_t stream, Args... args) {
-    if (d <= 256) ln_fwd_kernel<1><<<grid, kWarpsPerBlock * 32, 0, stream>>>(args...);
-    else if (d <= 512) ln_fwd_kernel<2><<<grid, kWarpsPerBlock * 32, 0, stream>>>(args...);
-    else ln_fwd_kernel<4><<<grid, kWarpsPerBlock * 32, 0, stream>>>(args...);
+    if (d <= 256) b200::pdl(ln_fwd_kernel<1>, dim3(grid), dim3(kWarpsPerBlock * 32), 0, stream)(args...);
+    else if (d <= 512) b200::pdl(ln_fwd_kernel<2>, dim3(grid), dim3(kWarpsPerBlock * 32), 0, stream)(args...);
+    else b200::pdl(ln_fwd_kernel<4>, dim3(grid), dim3(kWarpsPerBlock * 32), 0, stream)(args...);
 }
 template <typename... Args>
 static void launch_ln_bwd(int d, int grid, cudaStream_t stream, Args... args) {
-    if (d <= 256) ln_bwd_kernel<1><<<grid, kWarpsPerBlock * 32, 0, stream>>>(args...);
-    else if (d <= 512) ln_bwd_kernel<2><<<grid, kWarpsPerBlock * 32, 0, stream>>>(args...);
-    else ln_bwd_kernel<4><<<grid, kWarpsPerBlock * 32, 0, stream>>>(args...);
+    if (d <= 256) b200::pdl(ln_bwd_kernel<1>, dim3(grid), dim3(kWarpsPerBlock * 32), 0, stream)(args...);
+    else if (d <= 512) b200::pdl(ln_bwd_kernel<2>, dim3(grid), dim3(kWarpsPerBlock * 32), 0, stream)(args...);
+    else b200::pdl(ln_bwd_kernel<4>, dim3(grid), dim3(kWarpsPerBlock * 32), 0, stream)(args...);
 }
 
 static int bwd_grid(int rows) {

@@ -16,6 +16,7 @@
 // whole 128-byte line (32 consecutive units of one (b, t)) and the next step's operands are prefetched into registers
 // while the current step computes.  fp32 throughout the recurrence, so no rounding error accumulates over time.
 // hidden_size must be 32 (the reference value).
+#include "../common/pdl.cuh"
 #include "../../include/b200ml.h"
 #include "../common/host.h"
 #include "../common/ptx.cuh"
@@ -38,6 +39,8 @@ __global__ void __launch_bounds__(kThreads)
 lstm_rec_fwd_kernel(const float* __restrict__ pre, const float* __restrict__ w_hh, const float* __restrict__ h0,
                     const float* __restrict__ c0, float* __restrict__ h_out, float* __restrict__ gates_out,
                     float* __restrict__ c_out, float* __restrict__ h_n, float* __restrict__ c_n, int B, int T) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
     __shared__ __align__(16) float s_h[kWarps][H];   // h_{t-1} of this warp's batch row
     const int u = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int b = blockIdx.x * kWarps + wid;
@@ -102,6 +105,8 @@ lstm_rec_bwd_kernel(const float* __restrict__ w_hh, const float* __restrict__ c0
                     const float* __restrict__ c_seq, const float* __restrict__ dh_seq, const float* __restrict__ dh_n,
                     const float* __restrict__ dc_n, __nv_bfloat16* __restrict__ dg_out, float* __restrict__ dh0,
                     float* __restrict__ dc0, int B, int T) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
     __shared__ __align__(16) float s_dg[kWarps][G];  // gate gradients of this step for this warp's batch row
     const int u = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int b = blockIdx.x * kWarps + wid;
@@ -168,6 +173,8 @@ lstm_rec_bwd_kernel(const float* __restrict__ w_hh, const float* __restrict__ c0
 // out_bf16[i] = dropout(x[i]) — the (inter-layer) dropout + cast that feeds the hoisted input-projection GEMM
 __global__ void dropout_cast_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, long long n, float p,
                                     const RngState* __restrict__ rng, uint32_t site) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
     const bool drop = p > 0.f && rng != nullptr;
     uint64_t key = 0;
     uint32_t thr = 0;
@@ -188,6 +195,8 @@ __global__ void dropout_cast_kernel(const float* __restrict__ x, __nv_bfloat16* 
 template <typename GT>
 __global__ void dropout_bwd_kernel(const GT* __restrict__ g, float* __restrict__ dx, long long n, float p,
                                    const RngState* __restrict__ rng, uint32_t site) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
     const bool drop = p > 0.f && rng != nullptr;
     uint64_t key = 0;
     uint32_t thr = 0;
@@ -218,7 +227,7 @@ int b200ml_lstm_rec_fwd(const float* pre, const float* w_hh, const float* h0, co
     B200_REQUIRE(hidden == H, "lstm: hidden_size must be %d (got %d)", H, hidden);
     B200_REQUIRE((gates_out == nullptr) == (c_out == nullptr), "lstm_rec_fwd: gates_out and c_out go together");
     if (B <= 0 || T <= 0) return 0;
-    lstm_rec_fwd_kernel<<<(B + kWarps - 1) / kWarps, kThreads, 0, stream>>>(pre, w_hh, h0, c0, h_out, gates_out, c_out, h_n,
+    b200::pdl(lstm_rec_fwd_kernel, dim3((B + kWarps - 1) / kWarps), dim3(kThreads), 0, stream)(pre, w_hh, h0, c0, h_out, gates_out, c_out, h_n,
                                                                     c_n, B, T);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
@@ -231,7 +240,7 @@ int b200ml_lstm_rec_bwd(const float* w_hh, const float* c0, const float* gates, 
     B200_REQUIRE(w_hh && gates && c_seq && dg_out_bf16, "lstm_rec_bwd: null pointer");
     B200_REQUIRE(hidden == H, "lstm: hidden_size must be %d (got %d)", H, hidden);
     if (B <= 0 || T <= 0) return 0;
-    lstm_rec_bwd_kernel<<<(B + kWarps - 1) / kWarps, kThreads, 0, stream>>>(w_hh, c0, gates, c_seq, dh_seq, dh_n, dc_n,
+    b200::pdl(lstm_rec_bwd_kernel, dim3((B + kWarps - 1) / kWarps), dim3(kThreads), 0, stream)(w_hh, c0, gates, c_seq, dh_seq, dh_n, dc_n,
                                                                     (__nv_bfloat16*)dg_out_bf16, dh0, dc0, B, T);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
@@ -243,7 +252,7 @@ int b200ml_dropout_cast(const float* x, void* out_bf16, long long n, float p, co
     if (n <= 0) return 0;
     long long blocks = (n + 255) / 256;
     if (blocks > 8LL * b200::sm_count()) blocks = 8LL * b200::sm_count();
-    b200::lstm::dropout_cast_kernel<<<(int)blocks, 256, 0, stream>>>(x, (__nv_bfloat16*)out_bf16, n, p,
+    b200::pdl(b200::lstm::dropout_cast_kernel, dim3((int)blocks), dim3(256), 0, stream)(x, (__nv_bfloat16*)out_bf16, n, p,
                                                                      (const b200::RngState*)rng_state, rng_site);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
@@ -256,10 +265,10 @@ int b200ml_dropout_bwd(const void* g, int g_fp32, float* dx, long long n, float 
     long long blocks = (n + 255) / 256;
     if (blocks > 8LL * b200::sm_count()) blocks = 8LL * b200::sm_count();
     if (g_fp32)
-        b200::lstm::dropout_bwd_kernel<float><<<(int)blocks, 256, 0, stream>>>((const float*)g, dx, n, p,
+        b200::pdl(b200::lstm::dropout_bwd_kernel<float>, dim3((int)blocks), dim3(256), 0, stream)((const float*)g, dx, n, p,
                                                                                (const b200::RngState*)rng_state, rng_site);
     else
-        b200::lstm::dropout_bwd_kernel<__nv_bfloat16><<<(int)blocks, 256, 0, stream>>>(
+        b200::pdl(b200::lstm::dropout_bwd_kernel<__nv_bfloat16>, dim3((int)blocks), dim3(256), 0, stream)(
             (const __nv_bfloat16*)g, dx, n, p, (const b200::RngState*)rng_state, rng_site);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;

@@ -4,6 +4,7 @@
 // Reference: torch.optim.SGD(lr) / Adam(lr) + optimizer.zero_grad() (distributed_cnn.py:138,179-183;
 // distributed_lstm.py:141,192-194; pytorch_machine_translator.py:129,192-196); accuracy_fn
 // (distributed_cnn.py:144-147).
+#include "../common/pdl.cuh"
 #include "../../include/b200ml.h"
 #include "../common/host.h"
 #include "../common/optim.cuh"
@@ -27,6 +28,8 @@ template <typename GT>
 __global__ void __launch_bounds__(256)
 optim_step_kernel(float* __restrict__ p, const GT* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
                   __nv_bfloat16* __restrict__ p16, long long n, OptimSpec o, float grad_scale) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
     AdamCorr c = {0.f, 0.f};
     if (o.kind == 2) c = adam_corr(o);
     const long long stride = (long long)gridDim.x * blockDim.x;
@@ -47,6 +50,8 @@ optim_step_kernel(float* __restrict__ p, const GT* __restrict__ g, float* __rest
 }
 
 __global__ void cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long n) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
         dst[i] = __float2bfloat16(src[i]);
@@ -57,6 +62,8 @@ __global__ void cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat1
 __global__ void __launch_bounds__(256)
 colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, int rows, int cols, int rows_per_split,
                       int vec2_ok, float* __restrict__ partial) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
     __shared__ float red[8][64];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int col = blockIdx.x * 64 + lane * 2;
@@ -91,6 +98,8 @@ colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, int ro
 }
 
 __global__ void counters_advance_kernel(RngState* rng, int* step) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
     if (threadIdx.x == 0 && blockIdx.x == 0) {
         if (rng) rng->step += 1;
         if (step) *step += 1;
@@ -100,6 +109,8 @@ __global__ void counters_advance_kernel(RngState* rng, int* step) {
 template <typename T>
 __global__ void argmax_accuracy_kernel(const T* __restrict__ logits, long long ld, const long long* __restrict__ targets,
                                        int rows, int C, int* __restrict__ pred, int* __restrict__ correct_count) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
     const int row = blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= rows) return;
     float best = -INFINITY;
@@ -142,10 +153,10 @@ int b200ml_optim_step(float* p, const void* g, int g_bf16, float* m, float* v, v
     const long long cap = 8LL * sm_count();
     if (blocks > cap) blocks = cap;
     if (g_bf16)
-        optim_step_kernel<__nv_bfloat16><<<(int)blocks, 256, 0, stream>>>(p, (const __nv_bfloat16*)g, m, v,
+        b200::pdl(optim_step_kernel<__nv_bfloat16>, dim3((int)blocks), dim3(256), 0, stream)(p, (const __nv_bfloat16*)g, m, v,
                                                                            (__nv_bfloat16*)p16, n, o, grad_scale);
     else
-        optim_step_kernel<float><<<(int)blocks, 256, 0, stream>>>(p, (const float*)g, m, v, (__nv_bfloat16*)p16, n, o,
+        b200::pdl(optim_step_kernel<float>, dim3((int)blocks), dim3(256), 0, stream)(p, (const float*)g, m, v, (__nv_bfloat16*)p16, n, o,
                                                                   grad_scale);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
@@ -157,7 +168,7 @@ int b200ml_cast_f32_bf16(const float* src, void* dst, long long n, cudaStream_t 
     long long blocks = (n + 255) / 256;
     const long long cap = 8LL * b200::sm_count();
     if (blocks > cap) blocks = cap;
-    b200::opt::cast_f32_bf16_kernel<<<(int)blocks, 256, 0, stream>>>(src, (__nv_bfloat16*)dst, n);
+    b200::pdl(b200::opt::cast_f32_bf16_kernel, dim3((int)blocks), dim3(256), 0, stream)(src, (__nv_bfloat16*)dst, n);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
@@ -176,7 +187,7 @@ int b200ml_colsum_bf16(const void* x, long long ldx, int rows, int cols, float* 
     const int rps = (rows + splits - 1) / splits;
     dim3 grid((cols + 63) / 64, splits);
     const int vec2_ok = (ldx % 2 == 0) && ((reinterpret_cast<uintptr_t>(x) & 3) == 0);
-    colsum_partial_kernel<<<grid, 256, 0, stream>>>((const __nv_bfloat16*)x, ldx, rows, cols, rps, vec2_ok,
+    b200::pdl(colsum_partial_kernel, dim3(grid), dim3(256), 0, stream)((const __nv_bfloat16*)x, ldx, rows, cols, rps, vec2_ok,
                                                     (float*)scratch);
     B200_CHECK_CUDA(cudaGetLastError());
     B200_CHECK_CUDA(b200::launch_reduce_partials((const float*)scratch, splits, cols, cols, out, nullptr, accumulate,
@@ -185,7 +196,7 @@ int b200ml_colsum_bf16(const void* x, long long ldx, int rows, int cols, float* 
 }
 
 int b200ml_counters_advance(void* rng_state, int* step_dev, cudaStream_t stream) {
-    b200::opt::counters_advance_kernel<<<1, 32, 0, stream>>>((b200::RngState*)rng_state, step_dev);
+    b200::pdl(b200::opt::counters_advance_kernel, dim3(1), dim3(32), 0, stream)((b200::RngState*)rng_state, step_dev);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
@@ -196,10 +207,10 @@ int b200ml_argmax_accuracy(const void* logits, int logits_fp32, long long ld, co
     B200_REQUIRE(logits, "argmax: null pointer");
     if (rows <= 0) return 0;
     if (logits_fp32)
-        argmax_accuracy_kernel<float><<<(rows + 127) / 128, 128, 0, stream>>>((const float*)logits, ld, targets, rows, C,
+        b200::pdl(argmax_accuracy_kernel<float>, dim3((rows + 127) / 128), dim3(128), 0, stream)((const float*)logits, ld, targets, rows, C,
                                                                               pred, correct_count);
     else
-        argmax_accuracy_kernel<__nv_bfloat16><<<(rows + 127) / 128, 128, 0, stream>>>(
+        b200::pdl(argmax_accuracy_kernel<__nv_bfloat16>, dim3((rows + 127) / 128), dim3(128), 0, stream)(
             (const __nv_bfloat16*)logits, ld, targets, rows, C, pred, correct_count);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;

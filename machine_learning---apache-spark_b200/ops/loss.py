@@ -12,8 +12,16 @@ import os
 
 import torch
 
-from .. import _native
+import ctypes as C
+
+from .. import _native, _native_ext
+from ..utils import workspace
 from .gemm import colsum, deliver_grad, gemm, working_copy
+
+_vp, _i, _ll, _f, _sz = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_size_t
+_native_ext.register("b200ml_xent_rows", [_vp, _ll, _vp, _vp, _vp, _f, _i, _i, _ll, _i, _vp, _vp, _sz, _vp])
+_native_ext.register("b200ml_xent_rows_scratch_bytes", [_i], size_t_return=True)
+XENT_ROWS_MAX_V = 20480  # csrc/kernels/xent.cu kBigMaxV
 
 # Optional row-chunking of the head (B200ML_HEAD_CHUNK_MB > 0) keeps each logits chunk L2-resident between the GEMM, the
 # loss kernel and the input-gradient GEMM.  Measured on B200 at the translator shape it LOSES (2.12 ms vs 1.80 ms per
@@ -101,20 +109,34 @@ class _LinearCrossEntropy(torch.autograd.Function):
             chunk_rows = max(128, (HEAD_CHUNK_BYTES // (ld * 2)) // 128 * 128) if HEAD_CHUNK_BYTES > 0 else rows
             dh = torch.empty(rows, d, dtype=torch.bfloat16, device=dev) if (need_grad and h.requires_grad) else None
             b_ = None if bias is None else bias.detach()
+            # single-chunk large-vocabulary path: one read of the logits, gradient in place, bias gradient for free
+            fused_rows = chunk_rows >= rows and V <= XENT_ROWS_MAX_V
+            db_pre = None
+            if fused_rows and need_grad and bias is not None and bias.requires_grad:
+                db_pre = torch.empty(ld, dtype=torch.float32, device=dev)[:V]  # the kernel writes V rounded up to 8
             for r0 in range(0, rows, chunk_rows):
                 r1 = min(rows, r0 + chunk_rows)
                 lg = logits[r0:r1]
                 gemm(h2[r0:r1], w16, out=lg, bias=b_, n_logical=V)
-                _native.check(lib.b200ml_xent_fwd_bwd(lg.data_ptr(), 0, ld, t[r0:r1].data_ptr(),
-                                                      row_loss[r0:r1].data_ptr(), inv.data_ptr(), 0.0, r1 - r0, V,
-                                                      ignore_index, int(need_grad), st), "xent_fwd_bwd")
+                if fused_rows:
+                    nb = int(lib.b200ml_xent_rows_scratch_bytes(V)) if db_pre is not None else 0
+                    ws = workspace.get(f"xent_rows@{workspace.lane()}", nb, dev) if nb else None
+                    _native.check(lib.b200ml_xent_rows(lg.data_ptr(), ld, t.data_ptr(), row_loss.data_ptr(),
+                                                       inv.data_ptr(), 0.0, rows, V, ignore_index, int(need_grad),
+                                                       _native.ptr(db_pre), _native.ptr(ws), nb, st), "xent_rows")
+                else:
+                    _native.check(lib.b200ml_xent_fwd_bwd(lg.data_ptr(), 0, ld, t[r0:r1].data_ptr(),
+                                                          row_loss[r0:r1].data_ptr(), inv.data_ptr(), 0.0, r1 - r0, V,
+                                                          ignore_index, int(need_grad), st), "xent_fwd_bwd")
                 if dh is not None:
                     gemm(lg[:, :V], w16, b_mn=True, out=dh[r0:r1])  # d(loss)/dh for an upstream gradient of 1
             _native.check(lib.b200ml_loss_reduce(row_loss.data_ptr(), rows, inv.data_ptr(), 0.0, loss.data_ptr(), st),
                           "loss_reduce")
-            ctx.save_for_backward(h2, logits, dh if dh is not None else h2.new_empty(0))
+            ctx.save_for_backward(h2, logits, dh if dh is not None else h2.new_empty(0),
+                                  db_pre if db_pre is not None else h2.new_empty(0))
             ctx.V = V
             ctx.has_dh = dh is not None
+            ctx.has_db = db_pre is not None
             return loss[0]
         zf = h2.float() @ weight.float().t()
         if bias is not None:
@@ -125,14 +147,15 @@ class _LinearCrossEntropy(torch.autograd.Function):
         picked = zf.gather(1, t.clamp(0, V - 1).unsqueeze(1)).squeeze(1)
         loss = ((lse - picked) * valid).sum() / cnt
         g = (torch.softmax(zf, -1) - torch.nn.functional.one_hot(t.clamp(0, V - 1), V)) * valid.unsqueeze(1) / cnt
-        ctx.save_for_backward(h2, g, h2.new_empty(0))
+        ctx.save_for_backward(h2, g, h2.new_empty(0), h2.new_empty(0))
         ctx.V = V
         ctx.has_dh = False
+        ctx.has_db = False
         return loss
 
     @staticmethod
     def backward(ctx, gout):
-        h2, g, dh_pre = ctx.saved_tensors
+        h2, g, dh_pre, db_pre = ctx.saved_tensors
         weight, bias = ctx.params
         V = ctx.V
         d = weight.shape[1]
@@ -152,7 +175,9 @@ class _LinearCrossEntropy(torch.autograd.Function):
                                                                  alpha_dev=gdev), (V, d))
             if bias is not None and bias.requires_grad:
                 def _db(out, acc):
-                    if acc:
+                    if ctx.has_db:   # column sums of the gradient were accumulated by the loss kernel itself
+                        out.add_(db_pre * gdev) if acc else torch.mul(db_pre, gdev, out=out)
+                    elif acc:
                         out.add_(colsum(gv) * gdev)
                     else:
                         colsum(gv, out=out)

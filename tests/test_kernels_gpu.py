@@ -104,10 +104,13 @@ def test_cross_entropy(rows, V, dtype):
     assert _rel(z.grad, zr.grad) < (0.02 if dtype == torch.bfloat16 else 1e-4)
 
 
-def test_linear_cross_entropy_head():
+@pytest.mark.parametrize("rows,V", [(512, 19214), (77, 1000), (300, 20480), (64, 20488)])
+def test_linear_cross_entropy_head(rows, V):
+    """V <= 20480 takes the persistent row-cached loss kernel with the fused bias-gradient column sums (several rows
+    per CTA when rows > SMs, ragged last vector when V % 8 != 0); V = 20488 falls back to the generic kernel."""
     from b200ml.ops.loss import linear_cross_entropy
     torch.manual_seed(0)
-    rows, d, V = 512, 512, 19214
+    d = 512
     h = (torch.randn(rows, d, device="cuda") * 0.5).to(torch.bfloat16).requires_grad_()
     w = (torch.randn(V, d, device="cuda") * 0.05).requires_grad_()
     b = (torch.randn(V, device="cuda") * 0.05).requires_grad_()
