@@ -277,9 +277,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 #pragma unroll
                 for (int j = 0; j < 32; ++j) v[j] += s_bias[ct + j];  // smem broadcast; zero beyond N
             }
-            if (ep.act) {
+            if (ep.act == 1) {  // branch on the (uniform) activation once per chunk, not per element
 #pragma unroll
-                for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], ep.act);
+                for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+            } else if (ep.act == 2) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = 1.f / (1.f + __expf(-v[j]));
             }
             if (do_drop) {
                 // element index row*N + col; N % 4 == 0 and col0 % 4 == 0 make each group of 4 share one hash
