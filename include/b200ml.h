@@ -219,6 +219,22 @@ int b200ml_allreduce_update(const b200ml_comm* cm, long long start, long long n,
                             float beta1, float beta2, float eps, float weight_decay, const int* step_dev, float* m,
                             float* v, float* out, int push_master, int max_blocks, cudaStream_t stream);
 
+/* ------------------------------------------------------------------------------------------------ gradient buckets
+ * Host-side bucket manager of the data-parallel engine (csrc/runtime/reducer.cpp): the role of torch's c10d Reducer
+ * behind DistributedDataParallel (distributed_cnn.py:156).  offsets[n_params + 1] are element offsets into the flat
+ * gradient buffer; group_ends[n_groups] are parameter-index boundaries buckets must not cross. */
+typedef struct b200ml_reducer b200ml_reducer;
+b200ml_reducer* b200ml_reducer_create(int n_params, const long long* offsets, int n_groups, const int* group_ends,
+                                      long long cap_elems);
+void b200ml_reducer_destroy(b200ml_reducer* r);
+int b200ml_reducer_num_buckets(const b200ml_reducer* r);
+int b200ml_reducer_bucket(const b200ml_reducer* r, int b, long long* start, long long* numel, int* first_param,
+                          int* n_params, int* group);
+int b200ml_reducer_bucket_of(const b200ml_reducer* r, int param);
+void b200ml_reducer_begin_step(b200ml_reducer* r);
+int b200ml_reducer_mark_ready(b200ml_reducer* r, int param); /* completed bucket index, or -1 */
+int b200ml_reducer_flush(b200ml_reducer* r, int* out_buckets, int cap);
+
 #ifdef __cplusplus
 }
 #endif

@@ -88,26 +88,12 @@ class DataParallelEngine:
         # buckets: contiguous ranges of the flat buffer; gradients become ready roughly in reverse registration
         # order, so within each group the LAST bucket completes first.  (start, numel, [param indices], bf16_push)
         cap = max(int(bucket_mb * (1 << 20) / 4), 1)
-        self.buckets = []
         n_params = len(self.flat.params)
-        for lo_i, hi_i, bf16_push in ((0, n_w16, True), (n_w16, n_params, False)):
-            if hi_i <= lo_i:
-                continue
-            group_end = self.flat.offsets[hi_i] if hi_i < n_params else self.flat.numel
-            start, idxs = self.flat.offsets[lo_i], []
-            for i in range(lo_i, hi_i):
-                end = self.flat.offsets[i + 1] if i + 1 < hi_i else group_end
-                idxs.append(i)
-                if end - start >= cap:
-                    self.buckets.append((start, end - start, idxs, bf16_push))
-                    start, idxs = end, []
-            if idxs:
-                self.buckets.append((start, group_end - start, idxs, bf16_push))
-        self._bucket_of = {}
-        for b, (_, _, ids, _) in enumerate(self.buckets):
-            for i in ids:
-                self._bucket_of[i] = b
-        self._pending = [0] * len(self.buckets)
+        from .reducer import make_reducer
+
+        # native bucket manager (csrc/runtime/reducer.cpp); group 0 = bf16-push weights, group 1 = everything else
+        self.reducer = make_reducer(list(self.flat.offsets[:n_params]) + [self.flat.numel], [n_w16, n_params], cap)
+        self.buckets = [(start, n, ids, group == 0 and n_w16 > 0) for start, n, ids, group in self.reducer.buckets]
         self._events = [dict() for _ in self.buckets]
         # side stream for the parameter-gradient kernels (ops/gemm.py GradSideStream)
         self.side = None
@@ -146,7 +132,7 @@ class DataParallelEngine:
         def ready():
             if not self._in_step:
                 return
-            b = self._bucket_of[i]
+            b = self.reducer.bucket_of(i)
             if self.comm_stream is not None:
                 # gradients of one bucket may be produced on several streams (backward runs each node on the stream of
                 # its forward; wgrads run on the side stream): remember the latest point of each
@@ -158,8 +144,7 @@ class DataParallelEngine:
                     ev2 = torch.cuda.Event()
                     ev2.record(self.side.stream)
                     self._events[b][self.side.stream.cuda_stream] = ev2
-            self._pending[b] -= 1
-            if self._pending[b] == 0:
+            if self.reducer.mark_ready(i) == b:   # this report completed the bucket
                 self._bucket_ready(b)
         return ready
 
@@ -195,8 +180,8 @@ class DataParallelEngine:
     def begin_step(self) -> None:
         self.counters.advance(rng=True, opt_tensor=self.step_tensor)
         self.flat.zero_accumulating_slots()
-        for b, (_, _, ids, _) in enumerate(self.buckets):
-            self._pending[b] = len(ids)
+        self.reducer.begin_step()
+        for b in range(len(self.buckets)):
             self._events[b].clear()
         self._in_step = True
         if self.side is not None:
@@ -213,10 +198,8 @@ class DataParallelEngine:
                             self.betas, self.eps, self.weight_decay, self.step_tensor)
             return
         # parameters that never reported (unused in this forward) still need their bucket processed
-        for b in range(len(self.buckets)):
-            if self._pending[b] > 0:
-                self._pending[b] = 0
-                self._bucket_ready(b)
+        for b in self.reducer.flush():
+            self._bucket_ready(b)
         if self.comm_stream is not None:
             torch.cuda.current_stream().wait_stream(self.comm_stream)
         if self.side is not None:
@@ -290,6 +273,7 @@ class DataParallelEngine:
             self.sync_master()
             self.comm.close()
             self.comm = None
+        self.reducer.close()
         for p in self.flat.params:
             p._b200_ready = None
             p._b200_side = None
