@@ -162,6 +162,9 @@ int b200ml_attn_bwd(const b200ml_attn_operand* q, const b200ml_attn_operand* k, 
  * ref: FashionMNISTModel (distributed_cnn.py:51-73). */
 int b200ml_conv3x3_relu_fwd(const float* x, const float* w, const float* bias, float* y, unsigned char* pool_idx, int B,
                             int Cin, int Cout, int H, int W, int pool, cudaStream_t stream);
+/* 0 = automatic (tcgen05 implicit GEMM once 9 * C >= 64), 1 = direct CUDA-core kernels, 2 = implicit GEMM; also the
+ * B200ML_CONV_ALGO environment variable.  The weight gradient always uses the direct partial-sum kernel. */
+void b200ml_conv_set_algo(int algo);
 size_t b200ml_conv3x3_bwd_scratch_bytes(int B, int Cin, int Cout, int H, int W);
 int b200ml_conv3x3_relu_bwd(const float* dy, const float* ysaved, const unsigned char* pool_idx, const float* x,
                             const float* w, float* dx, float* dw, float* db, void* scratch, size_t scratch_bytes, int B,

@@ -10,6 +10,7 @@ from ..utils import workspace
 from .gemm import deliver_grad
 
 vp, i, sz = C.c_void_p, C.c_int, C.c_size_t
+_native_ext.register("b200ml_conv_set_algo", [i])
 _native_ext.register("b200ml_conv3x3_relu_fwd", [vp, vp, vp, vp, vp, i, i, i, i, i, i, vp])
 _native_ext.register("b200ml_conv3x3_bwd_scratch_bytes", [i, i, i, i, i], size_t_return=True)
 _native_ext.register("b200ml_conv3x3_relu_bwd", [vp, vp, vp, vp, vp, vp, vp, vp, vp, sz, i, i, i, i, i, i, i, vp])
@@ -72,3 +73,9 @@ class _ConvReluPool(torch.autograd.Function):
 def conv3x3_relu(x, weight, bias, pool: bool):
     assert weight.shape[2:] == (3, 3), "only 3x3 kernels (stride 1, padding 1) are implemented"
     return _ConvReluPool.apply(x, weight, bias, pool)
+
+
+def set_algo(algo: str) -> None:
+    """'auto' (tcgen05 implicit GEMM for forward / data gradient once 9*C >= 64), 'direct' (fp32 CUDA-core kernels) or
+    'igemm' (always the implicit GEMM, bf16 operands).  Also the B200ML_CONV_ALGO environment variable (0/1/2)."""
+    _native.load().b200ml_conv_set_algo({"auto": 0, "direct": 1, "igemm": 2}[algo])

@@ -13,8 +13,20 @@ def _rel(a, b):
 
 @pytest.mark.parametrize("B,Cin,Cout,HW,pool", [(4, 1, 10, 28, False), (4, 10, 10, 28, True), (3, 3, 10, 32, False),
                                                 (2, 10, 10, 14, True), (2, 7, 13, 20, True), (1, 64, 64, 16, False)])
-def test_conv3x3_relu_pool(B, Cin, Cout, HW, pool):
+@pytest.mark.parametrize("algo", ["direct", "igemm"])
+def test_conv3x3_relu_pool(B, Cin, Cout, HW, pool, algo):
+    """direct = fp32 CUDA-core kernels; igemm = tcgen05 implicit GEMM (bf16 operands) for forward and data gradient."""
     from b200ml.ops.conv import conv3x3_relu
+    from b200ml.ops.conv_native import set_algo
+    set_algo(algo)
+    try:
+        _run_conv_case(B, Cin, Cout, HW, pool, conv3x3_relu, 1e-5 if algo == "direct" else 1e-2,
+                       1e-4 if algo == "direct" else 3e-2)
+    finally:
+        set_algo("auto")
+
+
+def _run_conv_case(B, Cin, Cout, HW, pool, conv3x3_relu, tol_y, tol_g):
     torch.manual_seed(0)
     x = torch.randn(B, Cin, HW, HW, device="cuda", requires_grad=True)
     w = (torch.randn(Cout, Cin, 3, 3, device="cuda") * 0.3).requires_grad_()
@@ -23,14 +35,19 @@ def test_conv3x3_relu_pool(B, Cin, Cout, HW, pool):
     g = torch.randn_like(y)
     (y * g).sum().backward()
     xr, wr, br = [t.detach().cpu().requires_grad_() for t in (x, w, b)]
-    yr = F.relu(F.conv2d(xr, wr, br, padding=1))
+    if tol_y > 1e-4:   # implicit GEMM: the oracle sees the same bf16-rounded operands, so ReLU / arg-max decisions agree
+        yr = F.relu(F.conv2d(xr.to(torch.bfloat16).float(), wr.to(torch.bfloat16).float(), br, padding=1))
+    else:
+        yr = F.relu(F.conv2d(xr, wr, br, padding=1))
     if pool:
         yr = F.max_pool2d(yr, 2)
     (yr * g.cpu()).sum().backward()
-    assert _rel(y, yr) < 1e-5
-    assert _rel(x.grad, xr.grad) < 1e-4
-    assert _rel(w.grad, wr.grad) < 1e-4
-    assert _rel(b.grad, br.grad) < 1e-4
+    assert _rel(y, yr) < tol_y
+    assert _rel(x.grad, xr.grad) < tol_g
+    assert _rel(w.grad, wr.grad) < tol_g
+    # bf16 operands flip a few ReLU gates of near-zero pre-activations; the bias gradient (a plain sum of gated values) is
+    # the most sensitive to that
+    assert _rel(b.grad, br.grad) < (tol_g if tol_g < 1e-3 else 8e-2)
 
 
 @pytest.mark.parametrize("B,T,E", [(32, 128, 32), (5, 17, 32), (40, 9, 24)])
