@@ -29,6 +29,16 @@ def main():
         out = torch.empty(6400, 19216, dtype=torch.bfloat16, device="cuda")
         for _ in range(3):
             gemm(a, b, out=out, bias=bias, n_logical=19214)
+    elif what == "head":
+        # the translator's output projection + loss as one autograd node: pair GEMM (fwd), row-buffered loss kernel,
+        # pair GEMM (dgrad), pair GEMM (wgrad)
+        from b200ml.ops.loss import linear_cross_entropy
+        h = (torch.randn(6400, 512, device="cuda") * 0.5).to(torch.bfloat16).requires_grad_()
+        w = (torch.randn(19214, 512, device="cuda") * 0.05).requires_grad_()
+        b = (torch.randn(19214, device="cuda") * 0.05).requires_grad_()
+        t = torch.randint(0, 19214, (6400,), device="cuda")
+        for _ in range(2):
+            linear_cross_entropy(h, w, b, t, ignore_index=0).backward()
     elif what == "gemm_wgrad":
         # weight-gradient shapes (both operands MN-major, K = B*S = 6400) and a long-K NN shape at the narrow tile
         a = torch.randn(6400, 1536, device="cuda").to(torch.bfloat16)

@@ -61,13 +61,17 @@ struct Epilogue {
 template <int BN, int kCtas = 1>
 struct Cfg {
     static constexpr int kBRows = BN / kCtas;  // N extent of B staged by one CTA
-    static constexpr int kStages = kCtas == 2 ? 6 : (BN == 256 ? 4 : (BN == 128 ? 6 : 8));
+    static constexpr int kStages = kCtas == 2 ? 5 : (BN == 256 ? 4 : (BN == 128 ? 6 : 8));
     static constexpr int kABytes = BLOCK_M * BLOCK_K * 2;
     static constexpr int kBBytes = kBRows * BLOCK_K * 2;
     static constexpr int kStageBytes = kABytes + kBBytes;
     static constexpr int kTmemCols = 2 * BN;  // double-buffered accumulator
-    // epilogue staging: one 32-row x 64-col bf16 slab (4 KB, 128B-swizzled) per epilogue warp for the TMA store path
-    static constexpr int kCStageBytes = BN >= 128 ? kEpiWarps * 4096 : 0;
+    // epilogue staging for the TMA store path: 32-row x 64-col bf16 slabs (4 KB, 128B-swizzled) per epilogue warp.  The
+    // pair kernel gives every warp one slab per 64 columns it owns (two), so a tile's stores never wait for each other
+    // (ncu on the head projection: tensor pipe 49 % busy, the epilogue warps sat in cp.async.bulk.wait_group.read);
+    // the single-CTA kernel has no shared memory left for that and reuses one slab.
+    static constexpr int kSlabsPerWarp = (kCtas == 2 && BN == 256) ? 2 : 1;
+    static constexpr int kCStageBytes = BN >= 128 ? kEpiWarps * 4096 * kSlabsPerWarp : 0;
     static constexpr int kBiasBytes = 1024;  // BN floats
     static constexpr int kSmemBytes =
         kStages * kStageBytes + kCStageBytes + kBiasBytes + 1024 /*align slack*/ + 256 /*barriers*/;
@@ -267,7 +271,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                                      : ((ep.ldc & 7) == 0 && (reinterpret_cast<uintptr_t>(ep.C) & 15) == 0);
         const bool vec_aux = ep.aux_mode && (ep.ldaux & 7) == 0 && (reinterpret_cast<uintptr_t>(ep.aux) & 15) == 0;
         const bool use_tma_store = C::kCStageBytes > 0 && ep.tma_store != 0;
-        uint8_t* my_stage = stage_c + (warp - 2) * 4096;
+        uint8_t* my_stage = stage_c + (warp - 2) * 4096 * C::kSlabsPerWarp;
 
         // fused math on 32 consecutive accumulator columns of one row (ct = column offset inside the tile)
         auto epi_math = [&](float (&v)[32], const uint32_t (&r)[32], int row, int col0, int ct) {
@@ -360,7 +364,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     float v0[32], v1[32];
                     epi_math(v0, r0, row, t.n0 + c, c);
                     epi_math(v1, r1, row, t.n0 + c + 32, c + 32);
-                    if (lane == 0) tma_store_wait_read<0>();  // previous slab has left this warp's staging buffer
+                    uint8_t* slab = my_stage + (C::kSlabsPerWarp == 2 ? (g >> 6) * 4096 : 0);
+                    // the staging slab must have been read by the store that used it last (previous slab, or - with one
+                    // slab per 64 columns - the previous tile)
+                    if (lane == 0 && (C::kSlabsPerWarp == 1 || g == 0)) tma_store_wait_read<0>();
                     __syncwarp();
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
@@ -369,17 +376,17 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         o.y = pack_bf16x2(v0[8 * j + 2], v0[8 * j + 3]);
                         o.z = pack_bf16x2(v0[8 * j + 4], v0[8 * j + 5]);
                         o.w = pack_bf16x2(v0[8 * j + 6], v0[8 * j + 7]);
-                        *reinterpret_cast<uint4*>(my_stage + swz128_offset(lane, j)) = o;
+                        *reinterpret_cast<uint4*>(slab + swz128_offset(lane, j)) = o;
                         o.x = pack_bf16x2(v1[8 * j], v1[8 * j + 1]);
                         o.y = pack_bf16x2(v1[8 * j + 2], v1[8 * j + 3]);
                         o.z = pack_bf16x2(v1[8 * j + 4], v1[8 * j + 5]);
                         o.w = pack_bf16x2(v1[8 * j + 6], v1[8 * j + 7]);
-                        *reinterpret_cast<uint4*>(my_stage + swz128_offset(lane, 4 + j)) = o;
+                        *reinterpret_cast<uint4*>(slab + swz128_offset(lane, 4 + j)) = o;
                     }
                     fence_proxy_async_smem();
                     __syncwarp();
                     if (lane == 0) {
-                        tma_store_2d(&tmap_c, my_stage, t.n0 + c, t.m0 + quarter * 32);  // edges clipped by TMA
+                        tma_store_2d(&tmap_c, slab, t.n0 + c, t.m0 + quarter * 32);  // edges clipped by TMA
                         tma_store_commit();
                     }
                 }

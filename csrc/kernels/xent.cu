@@ -397,7 +397,8 @@ size_t b200ml_xent_rows_scratch_bytes(int V) {
 
 int b200ml_xent_rows(void* logits_bf16, long long ld_logits, const long long* targets, float* row_loss,
                      const float* grad_scale_dev, float grad_scale_host, int rows, int V, long long ignore_index,
-                     int write_grad, float* colsum_out, void* scratch, size_t scratch_bytes, cudaStream_t stream) {
+                     int write_grad, float* colsum_out, int colsum_accumulate, void* scratch, size_t scratch_bytes,
+                     cudaStream_t stream) {
     using namespace b200::xent;
     B200_REQUIRE(logits_bf16 && targets && row_loss, "xent_rows: null pointer");
     B200_REQUIRE(V >= 1 && V <= kBigMaxV, "xent_rows: V must be <= %d (got %d)", kBigMaxV, V);
@@ -426,7 +427,8 @@ int b200ml_xent_rows(void* logits_bf16, long long ld_logits, const long long* ta
     B200_CHECK_CUDA(cudaGetLastError());
     if (colsum_out)
         // partial rows are pitched at ldp = V rounded up to 8; colsum_out must have room for ldp floats
-        B200_CHECK_CUDA(b200::launch_reduce_partials(partial, grid, (int)ldp, (int)ldp, colsum_out, nullptr, 0, stream));
+        B200_CHECK_CUDA(b200::launch_reduce_partials(partial, grid, (int)ldp, (int)ldp, colsum_out, nullptr,
+                                                     colsum_accumulate, stream));
     return 0;
 }
 

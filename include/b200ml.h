@@ -111,11 +111,12 @@ int b200ml_xent_fwd_bwd(void* logits, int logits_fp32, long long ld_logits, cons
                         int write_grad, cudaStream_t stream);
 /* Large-vocabulary variant (bf16 logits, rows 16-byte aligned and padded to a multiple of 8 columns, V <= 20480): one
  * HBM read of each row, gradient written in place, and optionally colsum_out[V rounded up to 8] = column sums of that gradient (the
- * bias gradient of the projection; the padding entries are zero) through `scratch` (b200ml_xent_rows_scratch_bytes(V) bytes). */
+ * bias gradient of the projection; the padding entries are zero; colsum_accumulate != 0 adds to colsum_out, for callers that walk the rows in chunks) through `scratch` (b200ml_xent_rows_scratch_bytes(V) bytes). */
 size_t b200ml_xent_rows_scratch_bytes(int V);
 int b200ml_xent_rows(void* logits_bf16, long long ld_logits, const long long* targets, float* row_loss,
                      const float* grad_scale_dev, float grad_scale_host, int rows, int V, long long ignore_index,
-                     int write_grad, float* colsum_out, void* scratch, size_t scratch_bytes, cudaStream_t stream);
+                     int write_grad, float* colsum_out, int colsum_accumulate, void* scratch, size_t scratch_bytes,
+                     cudaStream_t stream);
 
 int b200ml_loss_reduce(const float* row_loss, int rows, const float* inv_count_dev, float inv_host, float* out,
                        cudaStream_t stream);

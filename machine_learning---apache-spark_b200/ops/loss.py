@@ -19,13 +19,14 @@ from ..utils import workspace
 from .gemm import colsum, deliver_grad, gemm, working_copy
 
 _vp, _i, _ll, _f, _sz = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_size_t
-_native_ext.register("b200ml_xent_rows", [_vp, _ll, _vp, _vp, _vp, _f, _i, _i, _ll, _i, _vp, _vp, _sz, _vp])
+_native_ext.register("b200ml_xent_rows", [_vp, _ll, _vp, _vp, _vp, _f, _i, _i, _ll, _i, _vp, _i, _vp, _sz, _vp])
 _native_ext.register("b200ml_xent_rows_scratch_bytes", [_i], size_t_return=True)
 XENT_ROWS_MAX_V = 20480  # csrc/kernels/xent.cu kBigMaxV
 
 # Optional row-chunking of the head (B200ML_HEAD_CHUNK_MB > 0) keeps each logits chunk L2-resident between the GEMM, the
-# loss kernel and the input-gradient GEMM.  Measured on B200 at the translator shape it LOSES (2.12 ms vs 1.80 ms per
-# step at 32 MB chunks): the per-chunk dgrad has too few output tiles to fill 148 SMs.  Default: one chunk.
+# loss kernel and the input-gradient GEMM.  First measurement on B200 at the translator shape: it LOST (2.12 ms vs
+# 1.80 ms per step at 32 MB chunks) because the per-chunk dgrad had too few output tiles to fill 148 SMs; see
+# BASELINE.md for the re-measurement with the CTA-pair GEMM.  Default: one chunk.
 HEAD_CHUNK_BYTES = int(float(os.environ.get("B200ML_HEAD_CHUNK_MB", "0")) * (1 << 20))
 
 
@@ -110,7 +111,7 @@ class _LinearCrossEntropy(torch.autograd.Function):
             dh = torch.empty(rows, d, dtype=torch.bfloat16, device=dev) if (need_grad and h.requires_grad) else None
             b_ = None if bias is None else bias.detach()
             # single-chunk large-vocabulary path: one read of the logits, gradient in place, bias gradient for free
-            fused_rows = chunk_rows >= rows and V <= XENT_ROWS_MAX_V
+            fused_rows = V <= XENT_ROWS_MAX_V
             db_pre = None
             if fused_rows and need_grad and bias is not None and bias.requires_grad:
                 db_pre = torch.empty(ld, dtype=torch.float32, device=dev)[:V]  # the kernel writes V rounded up to 8
@@ -121,9 +122,10 @@ class _LinearCrossEntropy(torch.autograd.Function):
                 if fused_rows:
                     nb = int(lib.b200ml_xent_rows_scratch_bytes(V)) if db_pre is not None else 0
                     ws = workspace.get(f"xent_rows@{workspace.lane()}", nb, dev) if nb else None
-                    _native.check(lib.b200ml_xent_rows(lg.data_ptr(), ld, t.data_ptr(), row_loss.data_ptr(),
-                                                       inv.data_ptr(), 0.0, rows, V, ignore_index, int(need_grad),
-                                                       _native.ptr(db_pre), _native.ptr(ws), nb, st), "xent_rows")
+                    _native.check(lib.b200ml_xent_rows(lg.data_ptr(), ld, t[r0:r1].data_ptr(),
+                                                       row_loss[r0:r1].data_ptr(), inv.data_ptr(), 0.0, r1 - r0, V,
+                                                       ignore_index, int(need_grad), _native.ptr(db_pre), int(r0 > 0),
+                                                       _native.ptr(ws), nb, st), "xent_rows")
                 else:
                     _native.check(lib.b200ml_xent_fwd_bwd(lg.data_ptr(), 0, ld, t[r0:r1].data_ptr(),
                                                           row_loss[r0:r1].data_ptr(), inv.data_ptr(), 0.0, r1 - r0, V,
