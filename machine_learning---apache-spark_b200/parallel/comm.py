@@ -10,6 +10,7 @@ involved.  This is the B200 counterpart of gloo's TCP pairs + c10d's Reducer buc
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 import torch.distributed as dist
@@ -202,7 +203,7 @@ class FusedAllReduce:
                        torch.as_tensor(_RawCuda(self.cs.params[r], flat.numel, "<f4"), device=dev)
                        for r in range(self.world)]
         self.push_master = 1
-        self.max_blocks = 0
+        self.max_blocks = int(os.environ.get("B200ML_AR_BLOCKS", "0"))  # 0 = library default (96 CTAs)
         torch.cuda.synchronize(dev)
         dist.barrier(group=group)  # nobody launches before every mapping exists
 
@@ -244,7 +245,7 @@ class FusedAllReduce:
                        torch.as_tensor(_RawCuda(self.cs.params[r], flat.numel, "<f4"), device=dev)
                        for r in range(self.world)]
         self.push_master = 1
-        self.max_blocks = 0
+        self.max_blocks = int(os.environ.get("B200ML_AR_BLOCKS", "0"))
         torch.cuda.synchronize(dev)
         dist.barrier(group=group)
 
