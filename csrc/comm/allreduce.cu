@@ -13,6 +13,8 @@
 // Cross-GPU barriers are per-CTA flag exchanges through a peer-mapped signal pad with release/acquire at system scope;
 // flag values are a monotonically increasing epoch kept in device memory, so a captured CUDA graph replays correctly.
 // Spins are bounded: a dead peer traps the kernel instead of hanging the GPU.
+#include <cstdlib>
+
 #include "../../include/b200ml.h"
 #include "../common/host.h"
 #include "../common/optim.cuh"
@@ -97,8 +99,12 @@ __device__ __forceinline__ uint2 pack4_bf16(float4 v) {
 }
 
 // kind 0: out[i] = sum/N (no weight update).  `start`, `n` in elements, both multiples of 4.
-template <bool kTwoShot>
-__global__ void __launch_bounds__(kThreads)
+// kSlim: 128-thread CTAs, one float4 per thread per trip, at most 80 registers - small enough to be co-resident with a
+// persistent tcgen05 GEMM CTA (320 threads x 168 registers leave ~11.7 K registers and no shared memory is needed), so
+// the reduction of a finished bucket proceeds WHILE backward's GEMMs own the SMs instead of queueing behind them.  The
+// wide variant (512 threads x 128 registers = a whole register file) is faster only on an otherwise idle GPU.
+template <bool kTwoShot, bool kSlim>
+__global__ void __launch_bounds__(kSlim ? 128 : kThreads, kSlim ? 6 : 1)
 allreduce_update_kernel(Peers c, long long start, long long n, OptimSpec o, float* __restrict__ m,
                         float* __restrict__ v, float* __restrict__ out, int push_master) {
     const uint32_t epoch = c.counter[0] + 1;
@@ -156,6 +162,20 @@ allreduce_update_kernel(Peers c, long long start, long long n, OptimSpec o, floa
     };
     // Two float4 per thread per trip: all 2 x world peer loads are issued before the first add, which doubles the
     // bytes in flight per CTA (NVLink round trips are ~2-3 us; bandwidth needs ~2 MB outstanding per GPU).
+    if (kSlim) {
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+            const long long e0 = start + lo + i * 4;
+            float4 t0[kMaxRanks];
+#pragma unroll
+            for (int r = 0; r < kMaxRanks; ++r)
+                if (r < c.world) t0[r] = ld_peer_f4(c.g[r] + e0);
+            float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int r = 0; r < kMaxRanks; ++r)   // fixed rank order => the same bits on every rank
+                if (r < c.world) { a0.x += t0[r].x; a0.y += t0[r].y; a0.z += t0[r].z; a0.w += t0[r].w; }
+            apply(e0, a0);
+        }
+    } else
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += 2 * stride) {
         const long long e0 = start + lo + i * 4;
         const bool two = i + stride < nvec;
@@ -432,8 +452,11 @@ int b200ml_allreduce_update(const b200ml_comm* cm, long long start, long long n,
     bool two = algo == 2 || (algo == 0 && kind != 0 && n * 4 > (512 << 10));
     if (kind == 0) two = false;
     const long long work = two ? (n / cm->world + 3) / 4 : n / 4;
-    long long blocks = (work + kThreads * 8 - 1) / (kThreads * 8);
-    int cap = max_blocks > 0 ? max_blocks : 96;
+    // B200ML_AR_SLIM (default 1): the co-resident 128-thread variant, two CTAs per SM; 0 = the wide 512-thread variant
+    static const bool slim = [] { const char* e = getenv("B200ML_AR_SLIM"); return !(e && e[0] == '0'); }();
+    const int threads = slim ? 128 : kThreads;
+    long long blocks = (work + threads * 8 - 1) / (threads * 8);
+    int cap = max_blocks > 0 ? max_blocks : (slim ? 2 * sm_count() : 96);
     if (cap > kMaxBlocks) cap = kMaxBlocks;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
@@ -446,10 +469,14 @@ int b200ml_allreduce_update(const b200ml_comm* cm, long long start, long long n,
         allreduce_push_kernel<<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, push_master);
     else if (nvls)
         allreduce_nvls_kernel<<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, out, push_master);
+    else if (two && slim)
+        allreduce_update_kernel<true, true><<<(int)blocks, 128, 0, stream>>>(c, start, n, o, m, v, out, push_master);
     else if (two)
-        allreduce_update_kernel<true><<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, out, push_master);
+        allreduce_update_kernel<true, false><<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, out, push_master);
+    else if (slim)
+        allreduce_update_kernel<false, true><<<(int)blocks, 128, 0, stream>>>(c, start, n, o, m, v, out, push_master);
     else
-        allreduce_update_kernel<false><<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, out, push_master);
+        allreduce_update_kernel<false, false><<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, out, push_master);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
