@@ -101,8 +101,8 @@ __device__ __forceinline__ uint2 pack4_bf16(float4 v) {
 // kind 0: out[i] = sum/N (no weight update).  `start`, `n` in elements, both multiples of 4.
 // kSlim: 128-thread CTAs, one float4 per thread per trip, at most 80 registers - small enough to be co-resident with a
 // persistent tcgen05 GEMM CTA (320 threads x 168 registers leave ~11.7 K registers and no shared memory is needed), so
-// the reduction of a finished bucket proceeds WHILE backward's GEMMs own the SMs instead of queueing behind them.  The
-// wide variant (512 threads x 128 registers = a whole register file) is faster only on an otherwise idle GPU.
+// the reduction of a finished bucket can proceed WHILE backward's GEMMs own the SMs instead of queueing behind them.
+// Opt-in (B200ML_AR_SLIM=1): in the measured training steps the wide variant (512 threads x 128 registers) still wins.
 template <bool kTwoShot, bool kSlim>
 __global__ void __launch_bounds__(kSlim ? 128 : kThreads, kSlim ? 6 : 1)
 allreduce_update_kernel(Peers c, long long start, long long n, OptimSpec o, float* __restrict__ m,
@@ -452,8 +452,9 @@ int b200ml_allreduce_update(const b200ml_comm* cm, long long start, long long n,
     bool two = algo == 2 || (algo == 0 && kind != 0 && n * 4 > (512 << 10));
     if (kind == 0) two = false;
     const long long work = two ? (n / cm->world + 3) / 4 : n / 4;
-    // B200ML_AR_SLIM (default 1): the co-resident 128-thread variant, two CTAs per SM; 0 = the wide 512-thread variant
-    static const bool slim = [] { const char* e = getenv("B200ML_AR_SLIM"); return !(e && e[0] == '0'); }();
+    // B200ML_AR_SLIM=1: the co-resident 128-thread variant, two CTAs per SM.  Default off: measured at 2 GPUs on the
+    // translator step it LOSES (1.84 ms vs 1.67 ms per step) - one float4 per thread keeps too few bytes in flight.
+    static const bool slim = [] { const char* e = getenv("B200ML_AR_SLIM"); return e && e[0] == '1'; }();
     const int threads = slim ? 128 : kThreads;
     long long blocks = (work + threads * 8 - 1) / (threads * 8);
     int cap = max_blocks > 0 ? max_blocks : (slim ? 2 * sm_count() : 96);

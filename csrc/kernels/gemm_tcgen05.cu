@@ -721,6 +721,32 @@ extern "C" int b200ml_gemm_bf16(const b200ml_gemm_args* g, cudaStream_t stream) 
             splits = want;
         }
     }
+    // Tail split (pair tiles, long K): when the last wave of pair tiles would be < 25 % full, e.g. the head's weight
+    // gradient 19214 x 512 x 6400 = 152 tiles on 74 pairs, run the first (waves - 1) full waves as one GEMM and the
+    // remaining rows as a second GEMM whose few tiles are split along K across all pairs - the third wave then costs a
+    // few k-blocks instead of all of them.
+    if (ctas == 2 && splits == 1 && plain && g->workspace && g->split_k != 1 && k_blocks >= 32) {
+        const int slots = sms / 2;
+        const long long n_t = (g->N + 255) / 256, m_t = (g->M + 2 * BLOCK_M - 1) / (2 * BLOCK_M);
+        const long long tiles2 = n_t * m_t, waves = (tiles2 + slots - 1) / slots;
+        const long long rem = tiles2 - (waves - 1) * slots;
+        const long long m_main_tiles = (waves - 1) * slots / n_t;
+        if (waves >= 2 && rem * 4 <= slots && m_main_tiles >= 1 && m_main_tiles < m_t) {
+            const long long m_main = m_main_tiles * 2 * BLOCK_M;
+            b200ml_gemm_args head = *g, tail = *g;
+            head.M = (int)m_main;
+            head.tile_n = 512;
+            head.split_k = 1;
+            tail.M = g->M - (int)m_main;
+            tail.tile_n = 512;
+            tail.split_k = 0;  // automatic: few tiles, long K -> split across the idle pairs
+            const size_t esz = 2;
+            tail.A = reinterpret_cast<const char*>(g->A) + (g->a_mn_major ? m_main : m_main * g->lda) * esz;
+            tail.C = reinterpret_cast<char*>(g->C) + m_main * g->ldc * (g->c_fp32 ? 4 : 2);
+            if (b200ml_gemm_bf16(&head, stream)) return -1;
+            return b200ml_gemm_bf16(&tail, stream);
+        }
+    }
     if (ctas == 2) return dispatch_major<256, 2>(g, ep, splits, stream);
     if (bn == 256) return dispatch_major<256, 1>(g, ep, splits, stream);
     if (bn == 128) return dispatch_major<128, 1>(g, ep, splits, stream);

@@ -90,6 +90,22 @@ def test_gemm_pair_epilogue_and_split_k():
     _check(acc, 1.0 + ref2, K2)
 
 
+def test_gemm_pair_tail_split():
+    """77 pair tiles on 74 pairs: the first 74 run as full tiles, the last 3 (768 rows, the final one ragged) as a
+    split-K GEMM over the idle pairs; the seam must be invisible."""
+    from b200ml.ops.gemm import gemm
+    torch.manual_seed(9)
+    M, N, K = 76 * 256 + 100, 256, 2048
+    a = torch.randn(K, M, device="cuda").to(torch.bfloat16)
+    b = torch.randn(K, N, device="cuda").to(torch.bfloat16)
+    ref = _ref(a, b, True, True)
+    out = gemm(a, b, a_mn=True, b_mn=True, out_dtype=torch.float32, tile_n=512)
+    _check(out, ref, K)
+    a2 = a.t().contiguous()      # K-major A: the tail's row offset goes through lda
+    out2 = gemm(a2, b, b_mn=True, out_dtype=torch.float32, tile_n=512)
+    _check(out2, ref, K)
+
+
 def test_gemm_epilogues():
     from b200ml.ops.gemm import gemm
     torch.manual_seed(2)
