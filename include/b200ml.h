@@ -223,6 +223,14 @@ int b200ml_allreduce_update(const b200ml_comm* cm, long long start, long long n,
                             float beta1, float beta2, float eps, float weight_decay, const int* step_dev, float* m,
                             float* v, float* out, int push_master, int max_blocks, cudaStream_t stream);
 
+/* ------------------------------------------------------------------------------------------------ K20 L-BFGS direction
+ * ref: MultilayerPerceptronClassifier(solver='l-bfgs') (mllib_multilayer_perceptron_classifier.py:35), Breeze LBFGS.
+ * Two-loop recursion over k <= 32 history pairs as one cooperative kernel; float64, rank-reproducible.
+ * S, Y: [k][ld] oldest first.  n <= 148 * 256 * 16 (606 208) on a B200; d must not alias g. */
+size_t b200ml_lbfgs_scratch_bytes(void);
+int b200ml_lbfgs_direction(const double* g, const double* S, const double* Y, int k, long long n, long long ld,
+                           double* d, void* scratch, size_t scratch_bytes, cudaStream_t stream);
+
 /* ------------------------------------------------------------------------------------------------ gradient buckets
  * Host-side bucket manager of the data-parallel engine (csrc/runtime/reducer.cpp): the role of torch's c10d Reducer
  * behind DistributedDataParallel (distributed_cnn.py:156).  offsets[n_params + 1] are element offsets into the flat

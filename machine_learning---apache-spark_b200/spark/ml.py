@@ -99,6 +99,34 @@ def loss_and_grad(weights, layers, X, Y, row_w):
 # ---------------------------------------------------------------------------------------------------------------
 # L-BFGS (two-loop recursion + strong-Wolfe line search), replicated on every rank
 # ---------------------------------------------------------------------------------------------------------------
+def _native_direction(g, S, Yv):
+    """K20 on the GPU: the whole two-loop recursion as one cooperative kernel (csrc/kernels/lbfgs.cu); float64 and
+    bit-identical across ranks (fixed-order reductions).  Returns None when the problem exceeds the kernel's envelope."""
+    import ctypes as C
+
+    from .. import _native, _native_ext
+    from ..utils import workspace
+
+    vp, i, ll, sz = C.c_void_p, C.c_int, C.c_longlong, C.c_size_t
+    _native_ext.register("b200ml_lbfgs_direction", [vp, vp, vp, i, ll, ll, vp, vp, sz, vp])
+    _native_ext.register("b200ml_lbfgs_scratch_bytes", [], size_t_return=True)
+    lib = _native.load()
+    n = g.numel()
+    props = torch.cuda.get_device_properties(g.device)
+    if n > props.multi_processor_count * 256 * 16:
+        return None
+    g = g.contiguous()
+    k = len(S)
+    Sb = torch.stack(S).contiguous() if k else g
+    Yb = torch.stack(Yv).contiguous() if k else g
+    d = torch.empty_like(g)
+    nb = int(lib.b200ml_lbfgs_scratch_bytes())
+    ws = workspace.get(f"lbfgs@{workspace.lane()}", nb, g.device)
+    _native.check(lib.b200ml_lbfgs_direction(g.data_ptr(), Sb.data_ptr(), Yb.data_ptr(), k, n, n, d.data_ptr(),
+                                             ws.data_ptr(), nb, _native.stream_ptr()), "lbfgs_direction")
+    return d
+
+
 class LBFGS:
     def __init__(self, fn, m: int = 10, max_iter: int = 100, tol: float = 1e-6):
         self.fn, self.m, self.max_iter, self.tol = fn, m, max_iter, tol
@@ -110,6 +138,10 @@ class LBFGS:
         return self.fn(w)
 
     def two_loop(self, g, S, Yv):
+        if g.is_cuda and g.dtype == torch.float64 and len(S) <= 32:
+            d = _native_direction(g, S, Yv)
+            if d is not None:
+                return d
         q = g.clone()
         alphas = []
         for s, y in zip(reversed(S), reversed(Yv)):

@@ -149,3 +149,19 @@ def test_flat_optimizer_matches_torch(kind):
     for p, r in zip(ps, rs):
         assert (p - r).abs().max().item() < 1e-5
         assert (p._b200_w16.float() - p.detach()).abs().max().item() < 0.02 * p.abs().max().item()
+
+
+@pytest.mark.parametrize("n,k", [(64, 0), (64, 3), (5000, 10), (535818, 10)])
+def test_lbfgs_direction_kernel_matches_two_loop(n, k):
+    """K20: cooperative two-loop kernel vs the plain torch recursion (float64), and run-to-run bit reproducibility."""
+    from b200ml.spark.ml import LBFGS, _native_direction
+    torch.manual_seed(0)
+    g = torch.randn(n, dtype=torch.float64, device="cuda")
+    S = [torch.randn(n, dtype=torch.float64, device="cuda") * 0.1 for _ in range(k)]
+    Y = [s * (1.0 + 0.5 * torch.rand(n, dtype=torch.float64, device="cuda")) for s in S]   # <s, y> > 0
+    d = _native_direction(g, S, Y)
+    assert d is not None
+    opt = LBFGS(lambda w: None)
+    ref = LBFGS.two_loop(opt, g.cpu(), [s.cpu() for s in S], [y.cpu() for y in Y])   # CPU tensors -> torch path
+    assert ((d.cpu() - ref).norm() / ref.norm()).item() < 1e-11
+    assert torch.equal(d, _native_direction(g, S, Y))
