@@ -43,6 +43,57 @@ __device__ __forceinline__ float bias_of(int mask_mode, int q, int k) {
     return 0.f;
 }
 
+__device__ __forceinline__ float ex2_approx(float x) {  // 2^x, one MUFU; -inf -> 0
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+// Scaled, biased score in the log2 domain for one (query row, key column) pair.
+template <int MODE>
+__device__ __forceinline__ float score2(uint32_t raw, float sc, int qrow, int kc) {
+    float x = __uint_as_float(raw) * sc;
+    if (MODE == 1) x += kc < qrow ? kLog2e : 0.f;
+    if (MODE == 2) x = kc > qrow ? -INFINITY : x;
+    return x;
+}
+// forward pass 1: running maximum over 32 columns; `live` = number of valid columns in the chunk (>= 32: no checks)
+template <int MODE>
+__device__ __forceinline__ float fwd_chunk_max(const uint32_t (&rg)[32], float sc, int qrow, int kc0, int live, float mx) {
+    if (live >= 32) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) mx = fmaxf(mx, score2<MODE>(rg[j], sc, qrow, kc0 + j));
+    } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+            if (j < live) mx = fmaxf(mx, score2<MODE>(rg[j], sc, qrow, kc0 + j));
+    }
+    return mx;
+}
+// forward pass 2: p = 2^(x - mx) rounded to bf16 (what the tensor core will see), packed; returns the row-sum share
+template <int MODE>
+__device__ __forceinline__ float fwd_chunk_exp(const uint32_t (&rg)[32], float sc, int qrow, int kc0, int live, float mx,
+                                               uint32_t (&pk)[16]) {
+    float sum = 0.f;
+#pragma unroll
+    for (int j = 0; j < 32; j += 2) {
+        float e0 = ex2_approx(score2<MODE>(rg[j], sc, qrow, kc0 + j) - mx);
+        float e1 = ex2_approx(score2<MODE>(rg[j + 1], sc, qrow, kc0 + j + 1) - mx);
+        if (live < 32) {
+            e0 = j < live ? e0 : 0.f;
+            e1 = j + 1 < live ? e1 : 0.f;
+        }
+        const __nv_bfloat162 h = __floats2bfloat162_rn(e0, e1);
+        const float2 r = __bfloat1622float2(h);
+        sum += r.x + r.y;
+        pk[j >> 1] = *reinterpret_cast<const uint32_t*>(&h);
+    }
+    return sum;
+}
+
 // Write 32 consecutive bf16 values of one row into 128B-swizzled K-major tiles ([rows][64] per tile, 16 KB apart
 // for 128-row tiles).
 __device__ __forceinline__ void store_row_chunk32(uint8_t* tiles, uint32_t tile_bytes, int row, int col0,
@@ -149,12 +200,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
         uint32_t rg[32];
         tmem_ld_32x32b_x32(trow + c, rg);
         tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            const int kc = c + j;
-            const float x = __uint_as_float(rg[j]) * sc + bias_of(mask_mode, qrow, kc) * kLog2e;
-            if (kc < Skv) mx = fmaxf(mx, x);
-        }
+        const int live = Skv - c;
+        if (mask_mode == 1) mx = fwd_chunk_max<1>(rg, sc, qrow, c, live, mx);
+        else if (mask_mode == 2) mx = fwd_chunk_max<2>(rg, sc, qrow, c, live, mx);
+        else mx = fwd_chunk_max<0>(rg, sc, qrow, c, live, mx);
     }
     x_max[half * TILE + r] = mx;
     __syncthreads();
@@ -164,20 +213,18 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
     // alias it.
     float sum = 0.f;
     for (int c = half * 32; c < skv_pad; c += 64) {
-        uint32_t rg[32];
+        uint32_t rg[32], pk[16];
         tmem_ld_32x32b_x32(trow + c, rg);
         tmem_ld_wait();
-        float p[32];
+        const int live = Skv - c;
+        if (mask_mode == 1) sum += fwd_chunk_exp<1>(rg, sc, qrow, c, live, mx, pk);
+        else if (mask_mode == 2) sum += fwd_chunk_exp<2>(rg, sc, qrow, c, live, mx, pk);
+        else sum += fwd_chunk_exp<0>(rg, sc, qrow, c, live, mx, pk);
+        const uint32_t base = smem_u32(sP) + (c >> 6) * (TILE * 128);
+        const int chunk0 = (c & 63) >> 3;
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            const int kc = c + j;
-            const float x = __uint_as_float(rg[j]) * sc + bias_of(mask_mode, qrow, kc) * kLog2e;
-            float e = kc < Skv ? exp2f(x - mx) : 0.f;
-            e = __bfloat162float(__float2bfloat16(e));  // the value the tensor core will see
-            p[j] = e;
-            sum += e;
-        }
-        store_row_chunk32(sP, TILE * 128, r, c, p);
+        for (int c4 = 0; c4 < 4; ++c4)
+            sts128(base + swz128_offset(r, chunk0 + c4), pk[4 * c4], pk[4 * c4 + 1], pk[4 * c4 + 2], pk[4 * c4 + 3]);
     }
     x_sum[half * TILE + r] = sum;
     tc_fence_before();
@@ -481,14 +528,6 @@ attn_bwd_kv_kernel(const __grid_constant__ CUtensorMap tk, const __grid_constant
 // smem: [Q 32K][dO 32K][K 32K][V 32K][P 32K][dS 32K][lse 1K][D 1K]      TMEM: S 128 | dP 128 | dQ_0 64 | dQ_1 64 | dV 64 | dK 64
 constexpr int kBwdFusedSmem = 6 * 32768 + 2048 + 1024 + 128;
 
-__device__ __forceinline__ float ex2_approx(float x) {  // 2^x, one MUFU; -inf -> 0
-    float y;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-    return y;
-}
-__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
-    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
-}
 // P and dS of 32 consecutive keys of one query row, packed to bf16 pairs.  No range masks: rows / keys outside the
 // sequence are zero in shared memory (TMA zero fill + the tail clear at kernel start), which makes their S, dP and
 // therefore dS exactly harmless, and TMEM columns beyond the live keys only reach gradient rows that are never stored.
