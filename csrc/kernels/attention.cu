@@ -10,11 +10,14 @@
 //            +1.0 where key < query (transformer.py:17-20 as written; the padding mask adds a per-row constant and is a
 //            softmax no-op) | 2 causal: -inf where key > query (what the reference intended).
 //
-// Shapes: head_dim = 64, S_q and S_kv <= 256 (the translator uses 200); one CTA per (128-row tile, head, batch).
-//   fwd    : S = Q·Kᵀ (UMMA 128×S_kv×64) -> softmax in registers (1 thread = 1 row = 1 TMEM lane) -> P (bf16, 128B-swizzled
-//            smem) -> O = P·V (V consumed MN-major from the very bytes TMA wrote) -> O/rowsum, lse
-//   bwd_q  : S, dP = dO·Vᵀ -> dS = P∘(dP − D)·scale -> dQ = dS·K
-//   bwd_kv : Sᵀ = K·Qᵀ, dPᵀ = V·dOᵀ (this CTA owns 128 keys) -> Pᵀ, dSᵀ -> dV = Pᵀ·dO, dK = dSᵀ·Q
+// Shapes: head_dim = 64, S_q and S_kv <= 256 (the translator uses 200).
+//   fwd (one CTA per 128-row query tile, head, batch):
+//            S = Q·Kᵀ (UMMA 128×S_kv×64) -> softmax in registers (a row is split over two threads) -> P (bf16,
+//            128B-swizzled smem) -> O = P·V (V consumed MN-major from the very bytes TMA wrote) -> O/rowsum, lse
+//   bwd (default: attn_bwd_fused_kernel, one CTA per head and batch, all three gradients, see its header comment)
+//   bwd, B200ML_ATTN_BWD=split (the first implementation, kept as a cross-check):
+//     bwd_q  : S, dP = dO·Vᵀ -> dS = P∘(dP − D)·scale -> dQ = dS·K
+//     bwd_kv : Sᵀ = K·Qᵀ, dPᵀ = V·dOᵀ (this CTA owns 128 keys) -> Pᵀ, dSᵀ -> dV = Pᵀ·dO, dK = dSᵀ·Q
 // No atomics, every gradient element is written exactly once => bit-reproducible.
 #include "../common/pdl.cuh"
 #include <cstdlib>

@@ -1,4 +1,5 @@
-// b200ml — K6: softmax cross-entropy, forward and backward in one kernel, one CTA per row.
+// b200ml — K6: softmax cross-entropy, forward and backward in one kernel: a generic one-CTA-per-row kernel and a
+// persistent row-buffered kernel for large vocabularies (xent_rows_kernel below).
 //
 //   loss_i  = logsumexp(z_i) - z_i[y_i]          (0 when y_i == ignore_index)
 //   dz_i    = (softmax(z_i) - onehot(y_i)) * grad_scale * valid_i          written IN PLACE over the logits
