@@ -305,7 +305,7 @@ allreduce_nvls_kernel(Peers c, long long start, long long n, OptimSpec o, float*
 // ---------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads)
 allreduce_push_kernel(Peers c, long long start, long long n, OptimSpec o, float* __restrict__ m,
-                      float* __restrict__ v, int push_master) {
+                      float* __restrict__ v, int push_master, int scattered) {
     const uint32_t epoch = c.counter[0] + 1;
     const float inv_world = 1.f / (float)c.world;
     AdamCorr corr = {0.f, 0.f};
@@ -315,9 +315,11 @@ allreduce_push_kernel(Peers c, long long start, long long n, OptimSpec o, float*
     const long long tid0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const float* g_local = c.g[c.rank];
 
-    // phase 1: scatter my gradient slices to their owners (remote 16-byte stores)
+    // phase 1: scatter my gradient slices to their owners (remote 16-byte stores) - unless the kernels that produced
+    // the gradients already did it while storing them (`scattered`: b200ml_scatter in the weight-gradient GEMMs)
 #pragma unroll 1
     for (int s = 0; s < c.world; ++s) {
+        if (scattered) break;
         if (s == c.rank) continue;
         const long long lo = per * s;
         if (lo >= n) break;
@@ -464,10 +466,11 @@ int b200ml_allreduce_update(const b200ml_comm* cm, long long start, long long n,
     const bool nvls = (algo == 3 || (algo == 0 && two)) && kind != 0 && c.mc_g && c.mc_w16 && (c.mc_p || !push_master) &&
                       start % 8 == 0 && n % 8 == 0;
     B200_REQUIRE(algo != 3 || nvls, "allreduce: NVLS requested but multicast addresses / 8-element alignment missing");
-    const bool push = (algo == 4 || (algo == 0 && two)) && kind != 0 && c.stage[0] != nullptr && cm->world > 1;
-    B200_REQUIRE(algo != 4 || push, "allreduce: push variant requested but no staging buffers were registered");
+    const bool push = (algo == 4 || algo == 5 || (algo == 0 && two)) && kind != 0 && c.stage[0] != nullptr && cm->world > 1;
+    B200_REQUIRE((algo != 4 && algo != 5) || push,
+                 "allreduce: push variant requested but no staging buffers were registered");
     if (push && algo != 3)
-        allreduce_push_kernel<<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, push_master);
+        allreduce_push_kernel<<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, push_master, algo == 5);
     else if (nvls)
         allreduce_nvls_kernel<<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, out, push_master);
     else if (two && slim)

@@ -34,6 +34,26 @@ constexpr int kEpiWarps = 8;
 constexpr int kPairTileCost = 250;  // relative cost of one 256 x 256 pair tile per wave (a 128 x 256 tile: 288)
 constexpr int kNumThreads = 64 + kEpiWarps * 32;  // 10 warps
 
+// device copy of b200ml_scatter (by value in the kernel parameters); world == 0: off
+struct Scatter {
+    int world, rank;
+    long long per, n;
+    const float* bucket_base;
+    float* stage_base[8];
+};
+// Mirror a just-stored fp32 vector of `kElems` consecutive elements at local address `p` into its owner's staging slice.
+// Slice boundaries are multiples of 4 elements and `p` is kElems-aligned, so a vector never straddles two owners.
+template <int kElems, typename V>
+__device__ __forceinline__ void scatter_store(const Scatter& sc, const float* p, V v) {
+    if (sc.world == 0) return;
+    const long long e = p - sc.bucket_base;
+    if (e < 0 || e >= sc.n) return;
+    const int s = (int)(e / sc.per);
+    if (s == sc.rank) return;
+    const int j = sc.rank - (sc.rank > s ? 1 : 0);
+    *reinterpret_cast<V*>(sc.stage_base[s] + (long long)j * sc.per + (e - (long long)s * sc.per)) = v;
+}
+
 struct Epilogue {
     void* C;
     long long ldc;
@@ -53,6 +73,7 @@ struct Epilogue {
     float* splitk_ws;        // != nullptr: write raw fp32 partial tiles to ws[split][M][N] instead of C
     int tma_store;           // bf16 C through smem staging + cp.async.bulk.tensor stores (needs tmap_c)
     int debug;               // B200ML_GEMM_DEBUG (timing experiments only, results are garbage): 1 = no TMA loads, 2 = no MMAs
+    Scatter scatter;         // fp32 direct-store path only
 };
 
 // kCtas == 2: a CTA pair (cluster of two on one TPC) computes a 256 x BN tile with tcgen05.mma.cta_group::2; each CTA
@@ -426,11 +447,16 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                                     o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
                                 }
                                 *reinterpret_cast<float4*>(out + j) = o;
+                                scatter_store<4>(ep.scatter, out + j, o);
                             }
                         } else {
 #pragma unroll
                             for (int j = 0; j < 32; ++j)
-                                if (col0 + j < N) out[j] = ep.accumulate ? out[j] + v[j] : v[j];
+                                if (col0 + j < N) {
+                                    const float o = ep.accumulate ? out[j] + v[j] : v[j];
+                                    out[j] = o;
+                                    scatter_store<1>(ep.scatter, out + j, o);
+                                }
                         }
                     } else {
                         __nv_bfloat16* out =
@@ -475,13 +501,36 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 }
 
 // Second stage of split-K: C = alpha * sum_s ws[s]  (fixed order), fp32 or bf16 store, optional accumulate.
+// vec4 != 0 (N, ldc multiples of 4, fp32 C): one float4 per thread-trip, and the optional scatter to the owner's staging.
 __global__ void __launch_bounds__(256)
 splitk_reduce_kernel(const float* __restrict__ ws, int splits, long long mn, int N, void* __restrict__ Cp,
-                     long long ldc, int c_fp32, int accumulate, float alpha, const float* __restrict__ alpha_dev) {
+                     long long ldc, int c_fp32, int accumulate, float alpha, const float* __restrict__ alpha_dev,
+                     int vec4, Scatter sc) {
     b200::pdl_trigger();
     b200::pdl_wait();
     const float a = alpha * (alpha_dev ? *alpha_dev : 1.f);
     const long long stride = (long long)gridDim.x * blockDim.x;
+    if (vec4) {
+        const long long nv = mn >> 2;
+        for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < nv; q += stride) {
+            const long long i = q << 2;
+            float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int k = 0; k < splits; ++k) {
+                const float4 t = *reinterpret_cast<const float4*>(ws + (long long)k * mn + i);
+                s.x += t.x; s.y += t.y; s.z += t.z; s.w += t.w;
+            }
+            s.x *= a; s.y *= a; s.z *= a; s.w *= a;
+            const long long row = i / N, col = i - row * N;
+            float* o = reinterpret_cast<float*>(Cp) + row * ldc + col;
+            if (accumulate) {
+                const float4 old = *reinterpret_cast<const float4*>(o);
+                s.x += old.x; s.y += old.y; s.z += old.z; s.w += old.w;
+            }
+            *reinterpret_cast<float4*>(o) = s;
+            scatter_store<4>(sc, o, s);
+        }
+        return;
+    }
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < mn; i += stride) {
         float s = 0.f;
         for (int k = 0; k < splits; ++k) s += ws[(long long)k * mn + i];
@@ -489,7 +538,9 @@ splitk_reduce_kernel(const float* __restrict__ ws, int splits, long long mn, int
         const long long row = i / N, col = i - row * N;
         if (c_fp32) {
             float* o = reinterpret_cast<float*>(Cp) + row * ldc + col;
-            *o = accumulate ? *o + s : s;
+            const float r = accumulate ? *o + s : s;
+            *o = r;
+            scatter_store<1>(sc, o, r);
         } else {
             reinterpret_cast<__nv_bfloat16*>(Cp)[row * ldc + col] = __float2bfloat16(s);
         }
@@ -550,7 +601,9 @@ gemm_simt_kernel(const __nv_bfloat16* __restrict__ A, long long lda, int a_mn, c
     }
     if (ep.c_fp32) {
         float* out = reinterpret_cast<float*>(ep.C) + (long long)row * ep.ldc + col;
-        *out = ep.accumulate ? *out + v : v;
+        const float r = ep.accumulate ? *out + v : v;
+        *out = r;
+        scatter_store<1>(ep.scatter, out, r);
     } else {
         reinterpret_cast<__nv_bfloat16*>(ep.C)[(long long)row * ep.ldc + col] = __float2bfloat16(v);
     }
@@ -602,8 +655,9 @@ static int launch(const b200ml_gemm_args* g, Epilogue ep, int splits, cudaStream
         const long long mn = (long long)g->M * g->N;
         long long blocks = (mn + 255) / 256;
         if (blocks > 4LL * sm_count()) blocks = 4LL * sm_count();
+        const int vec4 = g->c_fp32 && g->N % 4 == 0 && g->ldc % 4 == 0 && (reinterpret_cast<uintptr_t>(g->C) & 15) == 0;
         b200::pdl(splitk_reduce_kernel, dim3((int)blocks), dim3(256), 0, stream)(ep.splitk_ws, splits, mn, g->N, g->C, g->ldc, g->c_fp32,
-                                                              g->accumulate, g->alpha, g->alpha_dev);
+                                                              g->accumulate, g->alpha, g->alpha_dev, vec4, ep.scatter);
         B200_CHECK_CUDA(cudaGetLastError());
     }
     return 0;
@@ -634,6 +688,18 @@ extern "C" int b200ml_gemm_bf16(const b200ml_gemm_args* g, cudaStream_t stream) 
     ep.rng = reinterpret_cast<const RngState*>(g->rng_state); ep.rng_site = g->rng_site;
     ep.splitk_ws = nullptr;
     ep.tma_store = 0;
+    ep.scatter.world = 0;
+    if (g->scatter) {
+        B200_REQUIRE(g->c_fp32, "gemm: the scatter option needs an fp32 output");
+        B200_REQUIRE(g->scatter->world >= 2 && g->scatter->world <= 8 && g->scatter->per > 0 && g->scatter->per % 4 == 0,
+                     "gemm: bad scatter descriptor");
+        ep.scatter.world = g->scatter->world;
+        ep.scatter.rank = g->scatter->rank;
+        ep.scatter.per = g->scatter->per;
+        ep.scatter.n = g->scatter->n;
+        ep.scatter.bucket_base = g->scatter->bucket_base;
+        for (int r = 0; r < 8; ++r) ep.scatter.stage_base[r] = g->scatter->stage_base[r];
+    }
     static const int debug_flags = [] { const char* e = getenv("B200ML_GEMM_DEBUG"); return e ? atoi(e) : 0; }();
     ep.debug = debug_flags;
 
@@ -664,8 +730,10 @@ extern "C" int b200ml_gemm_bf16(const b200ml_gemm_args* g, cudaStream_t stream) 
             const long long mn = (long long)g->M * g->N;
             long long blocks = (mn + 255) / 256;
             if (blocks > 4LL * sm_count()) blocks = 4LL * sm_count();
+            const int vec4 = g->c_fp32 && g->N % 4 == 0 && g->ldc % 4 == 0 && (reinterpret_cast<uintptr_t>(g->C) & 15) == 0;
             b200::pdl(splitk_reduce_kernel, dim3((int)blocks), dim3(256), 0, stream)(ep.splitk_ws, splits, mn, g->N, g->C, g->ldc,
-                                                                  g->c_fp32, g->accumulate, g->alpha, g->alpha_dev);
+                                                                  g->c_fp32, g->accumulate, g->alpha, g->alpha_dev, vec4,
+                                                                  ep.scatter);
             B200_CHECK_CUDA(cudaGetLastError());
         }
         return 0;

@@ -36,6 +36,19 @@ int b200ml_device_info(int* sm_count, int* cc_major, int* cc_minor, size_t* smem
  *   fp32 may accumulate into C).
  * ref: every nn.Linear + ReLU/Sigmoid/Dropout neighbour (transformer.py:71-72,107-117,177-179,272;
  *      distributed_multilayer_perceptron.py:47-53). */
+/* Optional "weight gradient -> reduce-scatter" fusion for data-parallel training: while the GEMM (or its split-K
+ * second stage) stores an fp32 output vector into the local gradient buffer, it also stores it - over NVLink - into the
+ * staging buffer of the rank that owns that slice of the bucket, so the all-reduce that follows (algo 5 of
+ * b200ml_allreduce_update) starts with its scatter phase already done.  Layout as in the push all-reduce: the bucket
+ * [bucket_base, bucket_base + n) is cut into `world` slices of `per` elements; source rank r's copy of owner s's slice
+ * lives at stage_base[s] + j * per, j = r - (r > s). */
+typedef struct {
+    int world, rank;
+    long long per, n;
+    const float* bucket_base;   /* local gradient buffer + bucket start */
+    float* stage_base[8];       /* peers' staging buffers + bucket start (entry `rank` unused) */
+} b200ml_scatter;
+
 typedef struct {
     int M, N, K;
     const void* A; long long lda; int a_mn_major;
@@ -53,6 +66,7 @@ typedef struct {
     int split_k;     /* 0 = auto, 1 = never, n > 1 = request n K-splits (plain epilogue only; needs workspace) */
     void* workspace; size_t workspace_bytes; /* fp32 scratch for split-K partial tiles (optional) */
     int epilogue_direct; /* testing: 1 = register->global stores even where the TMA-store epilogue applies */
+    const b200ml_scatter* scatter; /* optional, fp32 C only: see b200ml_scatter */
 } b200ml_gemm_args;
 int b200ml_gemm_bf16(const b200ml_gemm_args* args, cudaStream_t stream);
 
@@ -219,6 +233,8 @@ int b200ml_comm_free(void* ptr);
 int b200ml_ipc_export(const void* ptr, unsigned char* handle64);
 int b200ml_ipc_import(const unsigned char* handle64, void** ptr);
 int b200ml_ipc_close(void* ptr);
+/* algo: 0 auto, 1 one-shot pull, 2 two-shot pull, 3 NVLS, 4 push through staging buffers, 5 = 4 with the scatter phase
+ * already done by the producers of the gradients (b200ml_scatter). */
 int b200ml_allreduce_update(const b200ml_comm* cm, long long start, long long n, int algo, int kind, float lr,
                             float beta1, float beta2, float eps, float weight_decay, const int* step_dev, float* m,
                             float* v, float* out, int push_master, int max_blocks, cudaStream_t stream);

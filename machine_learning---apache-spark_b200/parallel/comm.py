@@ -131,7 +131,15 @@ def use_staging() -> bool:
 
     # opt-in: on the 2-GPU measurements the store-based variant was not faster than the pull two-shot (227 vs 189 us at
     # 116 MiB), and it costs one more flat-sized buffer per rank
-    return os.environ.get("B200ML_AR_PUSH", "0") == "1"
+    return os.environ.get("B200ML_AR_PUSH", "0") == "1" or gemm_scatter()
+
+
+def gemm_scatter() -> bool:
+    """B200ML_GEMM_SCATTER=1: the weight-gradient GEMMs mirror their outputs into the slice owners' staging buffers over
+    NVLink (b200ml_scatter), so the all-reduce of those buckets starts with its reduce-scatter traffic already done."""
+    import os
+
+    return os.environ.get("B200ML_GEMM_SCATTER", "0") == "1"
 
 
 def make_allocator(device, group=None):
@@ -203,6 +211,7 @@ class FusedAllReduce:
                        torch.as_tensor(_RawCuda(self.cs.params[r], flat.numel, "<f4"), device=dev)
                        for r in range(self.world)]
         self.push_master = 1
+        self._scatter_descs = []
         self.max_blocks = int(os.environ.get("B200ML_AR_BLOCKS", "0"))  # 0 = library default (96 CTAs)
         torch.cuda.synchronize(dev)
         dist.barrier(group=group)  # nobody launches before every mapping exists
@@ -245,6 +254,7 @@ class FusedAllReduce:
                        torch.as_tensor(_RawCuda(self.cs.params[r], flat.numel, "<f4"), device=dev)
                        for r in range(self.world)]
         self.push_master = 1
+        self._scatter_descs = []
         self.max_blocks = int(os.environ.get("B200ML_AR_BLOCKS", "0"))
         torch.cuda.synchronize(dev)
         dist.barrier(group=group)
@@ -258,12 +268,29 @@ class FusedAllReduce:
             None if out is None else out.data_ptr(), self.push_master, self.max_blocks, _native.stream_ptr()),
             "allreduce_update")
 
-    def pull_master(self, start: int, n: int) -> None:
+    def scatter_desc(self, start: int, n: int):
+        """b200ml_scatter for the bucket [start, start + n): same slice ownership as the two-shot / push kernels."""
+        if self.cs.stage[0] is None and self.cs.stage[1] is None:
+            return None
+        n4 = (n + 3) // 4 * 4
+        d = _native.ScatterDesc()
+        d.world, d.rank = self.world, self.rank
+        d.per = ((n4 // 4 + self.world - 1) // self.world) * 4
+        d.n = n4
+        d.bucket_base = self.flat.flat_g.data_ptr() + start * 4
+        for r in range(self.world):
+            d.stage_base[r] = (self.cs.stage[r] or 0) + start * 4
+        self._scatter_descs.append(d)  # keep alive: the GEMM reads it through a raw pointer
+        return d
+
+    def pull_master(self, start: int, n: int, sliced: bool | None = None) -> None:
         """Refresh the fp32 master values of [start, start+n) that other ranks own (two-shot buckets updated with
         push_master = 0).  One-sided peer reads; the owners' values are final once our own last all-reduce kernel
         has returned, because that kernel's closing barrier waits for every rank's update."""
         n4 = (n + 3) // 4 * 4
-        if n4 * 4 <= (512 << 10):
+        if sliced is None:
+            sliced = n4 * 4 > (512 << 10)
+        if not sliced:
             return  # such a bucket takes the one-shot path: every rank already updated all of it locally
         gran = 8 if (self.cs.mc_grads and self.cs.mc_w16 and start % 8 == 0 and n4 % 8 == 0) else 4  # NVLS: 8-wide
         per = ((n4 // gran + self.world - 1) // self.world) * gran

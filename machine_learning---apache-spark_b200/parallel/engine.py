@@ -70,8 +70,20 @@ class DataParallelEngine:
             for m in module.modules():
                 if isinstance(m, (nn.Linear, nn.Embedding)):
                     w16_only.add(id(m.weight))
-        order = ([i for i, p in enumerate(params) if id(p) in w16_only] +
+        # B200ML_GEMM_SCATTER=1: nn.Linear weights (their gradients all come out of GEMMs) form a group of their own, and
+        # those GEMMs mirror their outputs into the slice owners' staging buffers (ops/gemm.py, b200ml_scatter)
+        from .comm import gemm_scatter
+
+        self._scatter = mode == "fused" and self._bf16_push and self.world > 1 and gemm_scatter()
+        lin = set()
+        if self._scatter:
+            for m in module.modules():
+                if isinstance(m, nn.Linear):
+                    lin.add(id(m.weight))
+        order = ([i for i, p in enumerate(params) if id(p) in lin] +
+                 [i for i, p in enumerate(params) if id(p) in w16_only and id(p) not in lin] +
                  [i for i, p in enumerate(params) if id(p) not in w16_only])
+        n_lin = sum(1 for p in params if id(p) in lin)
         n_w16 = sum(1 for p in params if id(p) in w16_only)
         self.flat = FlatParams(params, allocator=sym_alloc, order=order)
         self.counters = DeviceCounters.get(self.device)
@@ -92,8 +104,12 @@ class DataParallelEngine:
         from .reducer import make_reducer
 
         # native bucket manager (csrc/runtime/reducer.cpp); group 0 = bf16-push weights, group 1 = everything else
-        self.reducer = make_reducer(list(self.flat.offsets[:n_params]) + [self.flat.numel], [n_w16, n_params], cap)
-        self.buckets = [(start, n, ids, group == 0 and n_w16 > 0) for start, n, ids, group in self.reducer.buckets]
+        # groups: 0 = Linear weights with producer-side scatter (empty unless B200ML_GEMM_SCATTER), 1 = other bf16-push
+        # weights, 2 = everything else
+        self.reducer = make_reducer(list(self.flat.offsets[:n_params]) + [self.flat.numel], [n_lin, n_w16, n_params],
+                                    cap)
+        self.buckets = [(start, n, ids, group <= 1 and n_w16 > 0) for start, n, ids, group in self.reducer.buckets]
+        self._scatter_buckets = {b for b, (_, _, _, group) in enumerate(self.reducer.buckets) if group == 0}
         self._events = [dict() for _ in self.buckets]
         # side stream for the parameter-gradient kernels (ops/gemm.py GradSideStream)
         self.side = None
@@ -115,6 +131,16 @@ class DataParallelEngine:
 
                 self.comm = FusedAllReduce(self.flat, self.m, self.v, self.pg, allocator=sym_alloc)
                 self.allreduce_mode = "fused:" + self.comm.transport + (":bf16push" if self._bf16_push else "")
+                if self._scatter:
+                    descs = {b: self.comm.scatter_desc(self.buckets[b][0], self.buckets[b][1])
+                             for b in self._scatter_buckets}
+                    if all(d is not None for d in descs.values()) and descs:
+                        for b, d in descs.items():
+                            for i in self.buckets[b][2]:
+                                self.flat.params[i]._b200_scatter = d
+                        self.allreduce_mode += ":gemm-scatter"
+                    else:
+                        self._scatter, self._scatter_buckets = False, set()
                 if self._bf16_push:
                     # model.state_dict() on any rank first pulls the fp32 slices it does not own
                     module.register_state_dict_pre_hook(lambda *a, **k: self.sync_master())
@@ -148,7 +174,7 @@ class DataParallelEngine:
                 self._bucket_ready(b)
         return ready
 
-    def _bucket_ready(self, b: int) -> None:
+    def _bucket_ready(self, b: int, complete: bool = True) -> None:
         if (self.world == 1 and not self._local_overlap) or not self.sync_gradients:
             return  # single fused optimizer launch in finish_step
         if self.comm_stream is not None:
@@ -156,16 +182,24 @@ class DataParallelEngine:
             for ev in self._events[b].values():
                 self.comm_stream.wait_event(ev)
             with torch.cuda.stream(self.comm_stream):
-                self._reduce_and_update(b)
+                self._reduce_and_update(b, complete)
         else:
-            self._reduce_and_update(b)
+            self._reduce_and_update(b, complete)
 
-    def _reduce_and_update(self, b: int) -> None:
+    def _reduce_and_update(self, b: int, complete: bool = True) -> None:
         start, n, _, bf16_push = self.buckets[b]
         if self.comm is not None:
             self.comm.push_master = 0 if (bf16_push and self._bf16_push) else 1
+            algo = 0
+            if self._scatter:
+                if b in self._scatter_buckets:
+                    # 5: the GEMMs already scattered this bucket; 4 (full push) when a parameter never reported, because
+                    # its staged copies on the owners would be last step's
+                    algo = 5 if complete else 4
+                else:
+                    algo = 2 if n * 4 > (512 << 10) else 1   # staging exists, but these buckets keep the pull kernels
             self.comm.allreduce_update(start, n, self.kind, self.lr, self.betas, self.eps, self.weight_decay,
-                                       self.step_tensor)
+                                       self.step_tensor, algo=algo)
             return
         if self.world == 1:
             optim_step_flat(self.flat.flat_p, self.flat.flat_g, self.m, self.v, self.flat.flat_w16, self.kind, self.lr,
@@ -199,7 +233,7 @@ class DataParallelEngine:
             return
         # parameters that never reported (unused in this forward) still need their bucket processed
         for b in self.reducer.flush():
-            self._bucket_ready(b)
+            self._bucket_ready(b, complete=False)
         if self.comm_stream is not None:
             torch.cuda.current_stream().wait_stream(self.comm_stream)
         if self.side is not None:
@@ -241,9 +275,10 @@ class DataParallelEngine:
         if not self._master_stale and self._graph is None:
             return
         torch.cuda.current_stream().synchronize()
-        for start, n, _, bf16_push in self.buckets:
+        for b, (start, n, _, bf16_push) in enumerate(self.buckets):
             if bf16_push:
-                self.comm.pull_master(start, n)
+                # scatter buckets always go through the owner-updates-its-slice kernel, whatever their size
+                self.comm.pull_master(start, n, sliced=True if b in self._scatter_buckets else None)
         torch.cuda.current_stream().synchronize()
         self._master_stale = False
 
@@ -275,5 +310,6 @@ class DataParallelEngine:
             self.comm = None
         self.reducer.close()
         for p in self.flat.params:
+            p._b200_scatter = None
             p._b200_ready = None
             p._b200_side = None

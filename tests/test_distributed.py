@@ -28,3 +28,13 @@ def test_dp_engine_gloo_world2():
 def test_fused_allreduce_two_gpus():
     out = _launch(["allreduce_raw", "allreduce_nvls", "fused_matches_nccl", "dp_equals_big_batch"], 2, 29612)
     assert out.count("allreduce_raw ok") == 2 and out.count("fused_matches_nccl ok") == 2
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+def test_gemm_scatter_two_gpus():
+    """Weight-gradient GEMMs mirror their outputs into the slice owners' staging buffers (b200ml_scatter) and the
+    all-reduce skips its scatter phase (algo 5): same weights as NCCL all-reduce + optimizer."""
+    out = _launch(["fused_matches_nccl", "dp_equals_big_batch"], 2, 29613, {"B200ML_GEMM_SCATTER": "1"})
+    assert out.count("fused_matches_nccl ok") == 2 and out.count("dp_equals_big_batch ok") == 2
+    assert "gemm-scatter" in out
