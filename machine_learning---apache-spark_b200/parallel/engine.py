@@ -99,6 +99,7 @@ class DataParallelEngine:
 
         # buckets: contiguous ranges of the flat buffer; gradients become ready roughly in reverse registration
         # order, so within each group the LAST bucket completes first.  (start, numel, [param indices], bf16_push)
+        bucket_mb = float(os.environ.get("B200ML_BUCKET_MB", bucket_mb))   # experiment knob; the argument is the default
         cap = max(int(bucket_mb * (1 << 20) / 4), 1)
         n_params = len(self.flat.params)
         from .reducer import make_reducer
