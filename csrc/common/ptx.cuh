@@ -200,6 +200,36 @@ B200_DEVICE uint32_t mapa_shared(uint32_t smem_addr, uint32_t rank) {
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank));
     return r;
 }
+// mbarrier wait with cluster-scope acquire: pairs with mbar_arrive_cluster (release.cluster) from peer CTAs, making their
+// shared-memory writes visible to this thread's subsequent distributed-shared-memory loads.  Bounded like mbar_wait.
+B200_DEVICE void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+    const long long t0 = clock64();
+    for (;;) {
+        uint32_t ok;
+        asm volatile(
+            "{\n\t.reg .pred P;\n\t"
+            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 P, [%1], %2, 0x989680;\n\t"
+            "selp.u32 %0, 1, 0, P;\n\t}\n"
+            : "=r"(ok)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+        if (ok) return;
+        if (clock64() - t0 > 8000000000LL) {
+            printf("b200ml: cluster mbarrier timeout block=%d thread=%d parity=%u\n", blockIdx.x, threadIdx.x, parity);
+            __trap();
+        }
+    }
+}
+// 16-byte load from the shared memory of CTA `rank` of this cluster (distributed shared memory)
+B200_DEVICE float4 ld_dsmem_f4(uint32_t local_smem_addr, uint32_t rank) {
+    float4 v;
+    const uint32_t a = mapa_shared(local_smem_addr, rank);
+    asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "r"(a)
+                 : "memory");
+    return v;
+}
 B200_DEVICE void mbar_arrive_cluster(uint32_t cluster_addr) {  // arrive on a (possibly remote) CTA's barrier
     asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }

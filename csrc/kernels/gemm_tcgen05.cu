@@ -74,6 +74,7 @@ struct Epilogue {
     int tma_store;           // bf16 C through smem staging + cp.async.bulk.tensor stores (needs tmap_c)
     int debug;               // B200ML_GEMM_DEBUG (timing experiments only, results are garbage): 1 = no TMA loads, 2 = no MMAs
     Scatter scatter;         // fp32 direct-store path only
+    int cluster_splits;      // > 1: split-K over the CTAs of a cluster, partial tiles reduced through DSMEM (one tile per CTA)
 };
 
 // kCtas == 2: a CTA pair (cluster of two on one TPC) computes a 256 x BN tile with tcgen05.mma.cta_group::2; each CTA
@@ -147,6 +148,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     uint64_t* tmem_full = bars + 2 * C::kStages;
     uint64_t* tmem_empty = tmem_full + 2;
     uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+    uint64_t* xbar = tmem_empty + 4;  // cluster split-K: one arrival per CTA of the cluster, two phases
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -165,6 +167,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             mbar_init(&tmem_full[i], 1);
             mbar_init(&tmem_empty[i], kEpiWarps * kCtas);  // one arrive per epilogue warp (of both CTAs of a pair)
         }
+        if (kCtas == 1 && ep.cluster_splits > 1) mbar_init(xbar, ep.cluster_splits);
         fence_barrier_init();
     }
     if (warp == 2) {
@@ -172,7 +175,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         else tmem_alloc<C::kTmemCols>(tmem_ptr_smem);
     }
     tc_fence_before();
-    if (kCtas == 2) cluster_sync_all();  // the peer's barriers must be initialised before anything signals them
+    // the peers' barriers must be initialised before anything signals them (pairs, cluster split-K)
+    if (kCtas == 2 || ep.cluster_splits > 1) cluster_sync_all();
     else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr_smem;
@@ -183,7 +187,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     const int n_tiles = (N + BN - 1) / BN;
     const int num_tiles = m_tiles * n_tiles * splits;
     const int k_blocks = (K + BLOCK_K - 1) / BLOCK_K;
-    const int first_tile = blockIdx.x / kCtas, tile_step = gridDim.x / kCtas;  // both CTAs of a pair walk the same tiles
+    // both CTAs of a pair walk the same tiles; with cluster split-K the cluster index is the output tile and the rank
+    // inside the cluster is the K split (exactly one tile per CTA: the host sizes the grid that way)
+    const int csplit = (kCtas == 1 && ep.cluster_splits > 1) ? ep.cluster_splits : 0;
+    const int mn_tiles = m_tiles * n_tiles;
+    const int first_tile = csplit ? (int)(blockIdx.x / csplit) + (int)cluster_ctarank() * mn_tiles : (int)(blockIdx.x / kCtas);
+    const int tile_step = csplit ? num_tiles : (int)(gridDim.x / kCtas);
 
     if (warp == 0) {
         // ===================== TMA producer =====================
@@ -421,6 +430,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     if (row >= M) continue;
                     const int col0 = t.n0 + c;
                     const bool full = col0 + 32 <= N;
+                    if (csplit) {  // raw partial sums into this CTA's own shared memory (the pipeline stages are idle now)
+                        float* red = reinterpret_cast<float*>(smem) + (quarter * 32 + lane) * (BN + 4) + c;
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4)
+                            *reinterpret_cast<uint4*>(red + j) = make_uint4(r[j], r[j + 1], r[j + 2], r[j + 3]);
+                        continue;
+                    }
                     if (ep.splitk_ws) {  // raw partial sums; the reduce kernel applies alpha and the store mode
                         float* out = ep.splitk_ws + ((long long)t.split * M + row) * N + col0;
                         if (full && (N & 3) == 0) {
@@ -478,6 +494,59 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         }
                     }
                 }
+            }
+            if (csplit) {
+                // every split's partial tile is in its CTA's shared memory: CTA r of the cluster sums rows
+                // [r * rows_per, ...) over the splits in rank order (deterministic) and writes the result
+                named_bar_sync(1, kEpiWarps * 32);   // all eight epilogue warps have written their part
+                if (etid == 0)
+                    for (int sp = 0; sp < csplit; ++sp) mbar_arrive_cluster(mapa_shared(smem_u32(xbar), (uint32_t)sp));
+                mbar_wait_cluster(xbar, 0);          // every CTA of the cluster has published its partial tile
+                const int my = (int)cluster_ctarank();
+                const int rows_per = (BLOCK_M + csplit - 1) / csplit;
+                const int r_lo = my * rows_per, r_hi = r_lo + rows_per < BLOCK_M ? r_lo + rows_per : BLOCK_M;
+                const int vec_per_row = BN / 4;
+                const uint32_t red0 = smem_u32(smem);
+                for (int it = etid; it < (r_hi - r_lo) * vec_per_row; it += kEpiWarps * 32) {
+                    const int rr = r_lo + it / vec_per_row, cc = (it % vec_per_row) * 4;
+                    const int grow = t.m0 + rr, gcol = t.n0 + cc;
+                    if (grow >= M || gcol >= N) continue;
+                    float4 s4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                    for (int sp = 0; sp < csplit; ++sp) {
+                        const float4 v4 = ld_dsmem_f4(red0 + (uint32_t)(rr * (BN + 4) + cc) * 4u, (uint32_t)sp);
+                        s4.x += v4.x; s4.y += v4.y; s4.z += v4.z; s4.w += v4.w;
+                    }
+                    s4.x *= alpha; s4.y *= alpha; s4.z *= alpha; s4.w *= alpha;
+                    const float vals[4] = {s4.x, s4.y, s4.z, s4.w};
+                    if (ep.c_fp32) {
+                        float* out = reinterpret_cast<float*>(ep.C) + (long long)grow * ep.ldc + gcol;
+                        if (gcol + 4 <= N && vec_c) {
+                            float4 o = s4;
+                            if (ep.accumulate) {
+                                const float4 old = *reinterpret_cast<const float4*>(out);
+                                o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
+                            }
+                            *reinterpret_cast<float4*>(out) = o;
+                            scatter_store<4>(ep.scatter, out, o);
+                        } else {
+                            for (int j = 0; j < 4; ++j)
+                                if (gcol + j < N) {
+                                    const float o = ep.accumulate ? out[j] + vals[j] : vals[j];
+                                    out[j] = o;
+                                    scatter_store<1>(ep.scatter, out + j, o);
+                                }
+                        }
+                    } else {
+                        __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(ep.C) + (long long)grow * ep.ldc + gcol;
+                        for (int j = 0; j < 4; ++j)
+                            if (gcol + j < N) out[j] = __float2bfloat16(vals[j]);
+                    }
+                }
+                // peers may still be reading this CTA's partial tile: leave only when all of them are done
+                named_bar_sync(1, kEpiWarps * 32);
+                if (etid == 0)
+                    for (int sp = 0; sp < csplit; ++sp) mbar_arrive_cluster(mapa_shared(smem_u32(xbar), (uint32_t)sp));
+                mbar_wait_cluster(xbar, 1);
             }
             tc_fence_before();
             __syncwarp();
@@ -647,6 +716,13 @@ static int launch(const b200ml_gemm_args* g, Epilogue ep, int splits, cudaStream
     const int tiles = m_tiles * n_tiles * splits;       // per CTA (kCtas == 1) or per CTA pair
     const int slots = sm_count() / kCtas;
     const int grid = (tiles < slots ? tiles : slots) * kCtas;
+    const bool cluster_split = kCtas == 1 && ep.cluster_splits > 1;   // splits == cluster size, one tile per CTA
+    if (cluster_split) {
+        B200_REQUIRE(splits == ep.cluster_splits && tiles <= slots, "gemm: bad cluster split-K configuration");
+        B200_CHECK_CUDA(launch_pdl(kern, dim3(tiles), dim3(kNumThreads), C::kSmemBytes, stream, splits, 1, ta, tb, tc,
+                                   g->M, g->N, g->K, splits, ep));
+        return 0;
+    }
     if (splits > 1) ep.splitk_ws = reinterpret_cast<float*>(g->workspace);
     // a pair = cluster of two CTAs (same TPC)
     B200_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kNumThreads), C::kSmemBytes, stream, kCtas, 1, ta, tb, tc, g->M, g->N,
@@ -664,6 +740,42 @@ static int launch(const b200ml_gemm_args* g, Epilogue ep, int splits, cudaStream
         B200_CHECK_CUDA(cudaGetLastError());
     }
     return 0;
+}
+
+// How many clusters of `cs` CTAs of this kernel can be resident at once (they must fit inside GPCs); cached.
+template <bool A_MN, bool B_MN, int BN>
+static int max_active_clusters(int cs) {
+    static int cache[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    if (cs < 2 || cs > 8) return 0;
+    if (cache[cs]) return cache[cs] < 0 ? 0 : cache[cs];
+    using C = Cfg<BN, 1>;
+    auto kern = gemm_bf16_kernel<A_MN, B_MN, BN, 1>;
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(cs * 64);
+    cfg.blockDim = dim3(kNumThreads);
+    cfg.dynamicSmemBytes = C::kSmemBytes;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = cs;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess) {
+        cudaGetLastError();
+        n = 0;
+    }
+    cache[cs] = n > 0 ? n : -1;
+    return n;
+}
+template <int BN>
+static int max_active_clusters_major(const b200ml_gemm_args* g, int cs) {
+    if (!g->a_mn_major && !g->b_mn_major) return max_active_clusters<false, false, BN>(cs);
+    if (!g->a_mn_major && g->b_mn_major) return max_active_clusters<false, true, BN>(cs);
+    if (g->a_mn_major && !g->b_mn_major) return max_active_clusters<true, false, BN>(cs);
+    return max_active_clusters<true, true, BN>(cs);
 }
 
 template <int BN, int kCtas>
@@ -692,6 +804,7 @@ extern "C" int b200ml_gemm_bf16(const b200ml_gemm_args* g, cudaStream_t stream) 
     ep.splitk_ws = nullptr;
     ep.tma_store = 0;
     ep.scatter.world = 0;
+    ep.cluster_splits = 0;
     if (g->scatter) {
         B200_REQUIRE(g->c_fp32, "gemm: the scatter option needs an fp32 output");
         B200_REQUIRE(g->scatter->world >= 2 && g->scatter->world <= 8 && g->scatter->per > 0 && g->scatter->per % 4 == 0,
@@ -817,6 +930,26 @@ extern "C" int b200ml_gemm_bf16(const b200ml_gemm_args* g, cudaStream_t stream) 
             tail.C = reinterpret_cast<char*>(g->C) + m_main * g->ldc * (g->c_fp32 ? 4 : 2);
             if (b200ml_gemm_bf16(&head, stream)) return -1;
             return b200ml_gemm_bf16(&tail, stream);
+        }
+    }
+    // Split-K inside a thread-block cluster: the <= 8 CTAs that share an output tile are co-scheduled, keep their fp32
+    // partial tiles in their own shared memory and reduce them through distributed shared memory - no workspace round
+    // trip through L2 and no second kernel.  B200ML_SPLITK_CLUSTER=0 keeps the workspace + reduce-kernel path.
+    ep.cluster_splits = 0;
+    static const bool use_cluster = [] { const char* e = getenv("B200ML_SPLITK_CLUSTER"); return !(e && e[0] == '0'); }();
+    if (ctas == 1 && splits > 1 && use_cluster) {
+        // largest cluster size <= the wanted split count whose clusters are ALL resident at once (a cluster needs its
+        // CTAs inside one GPC, so e.g. 16 clusters of 8 full-SM CTAs do not always fit on 148 SMs)
+        for (int cs = splits < 8 ? splits : 8; cs >= 2; --cs) {
+            const int per = (k_blocks + cs - 1) / cs;
+            if ((k_blocks + per - 1) / per != cs) continue;  // would leave an empty split
+            const int fit = bn == 256 ? max_active_clusters_major<256>(g, cs)
+                                      : (bn == 128 ? max_active_clusters_major<128>(g, cs) : max_active_clusters_major<64>(g, cs));
+            if (tiles_mn <= fit) {
+                splits = cs;
+                ep.cluster_splits = cs;
+                break;
+            }
         }
     }
     if (ctas == 2) return dispatch_major<256, 2>(g, ep, splits, stream);
