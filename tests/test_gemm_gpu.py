@@ -90,6 +90,29 @@ def test_gemm_pair_epilogue_and_split_k():
     _check(acc, 1.0 + ref2, K2)
 
 
+@pytest.mark.parametrize("M,N,K,tile_n", [(512, 512, 6400, 128), (512, 512, 6400, 256), (300, 200, 3000, 0),
+                                          (1024, 136, 4096, 64)])
+def test_gemm_cluster_split_k(M, N, K, tile_n):
+    """Long K, few tiles: split-K inside a thread-block cluster (DSMEM reduction), incl. ragged M / N, fp32
+    accumulate with alpha, and a bf16 output."""
+    from b200ml.ops.gemm import gemm
+    torch.manual_seed(13)
+    a = torch.randn(K, M, device="cuda").to(torch.bfloat16)
+    b = torch.randn(K, N, device="cuda").to(torch.bfloat16)
+    ref = _ref(a, b, True, True)
+    out = gemm(a, b, a_mn=True, b_mn=True, out_dtype=torch.float32, tile_n=tile_n)
+    _check(out, ref, K)
+    one = gemm(a, b, a_mn=True, b_mn=True, out_dtype=torch.float32, tile_n=tile_n, split_k=1)
+    _check(one, ref, K)
+    acc = torch.full((M, N), 2.0, device="cuda")
+    gemm(a, b, a_mn=True, b_mn=True, out=acc, accumulate=True, alpha=0.25, tile_n=tile_n)
+    _check(acc, 2.0 + 0.25 * ref, K)
+    ldc = (N + 7) // 8 * 8
+    o16 = torch.empty(M, ldc, dtype=torch.bfloat16, device="cuda")[:, :N]
+    gemm(a, b, a_mn=True, b_mn=True, out=o16, tile_n=tile_n)
+    _check(o16, ref, K, tol_scale=2.0)
+
+
 def test_gemm_pair_tail_split():
     """77 pair tiles on 74 pairs: the first 74 run as full tiles, the last 3 (768 rows, the final one ragged) as a
     split-K GEMM over the idle pairs; the seam must be invisible."""
