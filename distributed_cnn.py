@@ -37,6 +37,15 @@ def train_func():
                                   image_size=size).to(device)
     DDP_model = DataParallelEngine(cnn_model, optimizer="sgd", lr=0.01)
     Epochs = S.env_int("B200ML_EPOCHS", 1 if S.quick() else 3)
+    def one_step(data, target):
+        predictions = cnn_model(data)
+        train_loss = cross_entropy(predictions, target)
+        DDP_model.zero_grad()
+        train_loss.backward()
+        DDP_model.step()
+        return train_loss.detach()
+
+    train_step = DDP_model.graphed(one_step)   # full batches replay as one CUDA graph; a short last batch runs eagerly
     timer = S.DeviceTimer(device).start()
     cnn_model.train()
     n_samples = 0
@@ -45,12 +54,7 @@ def train_func():
         total_train_loss = torch.zeros((), device=device)
         for batch_idx, (data, target) in enumerate(train_dataloader):
             data, target = data.to(device, non_blocking=True), target.to(device, non_blocking=True)
-            predictions = cnn_model(data)
-            train_loss = cross_entropy(predictions, target)
-            DDP_model.zero_grad()
-            train_loss.backward()
-            DDP_model.step()
-            total_train_loss += train_loss.detach()
+            total_train_loss += train_step(data, target)
             n_samples += len(target)
     secs = S.max_over_ranks(timer.elapsed(), device)
     DDP_model.weights_hash()

@@ -44,16 +44,22 @@ def train_func(features_tensor, target_tensor):
     DDP_model = DataParallelEngine(multilayer_model, optimizer="sgd", lr=0.03)
     epochs = S.env_int("B200ML_EPOCHS", 10 if S.quick() else 100)
     multilayer_model.train()
+
+    def one_step(features, labels):
+        predictions = multilayer_model(features)
+        loss = cross_entropy(predictions, labels)
+        DDP_model.zero_grad()
+        loss.backward()
+        DDP_model.step()
+        return loss.detach()
+
+    train_step = DDP_model.graphed(one_step)
     timer = S.DeviceTimer(device).start()
     for epoch in range(epochs):
         sampler.set_epoch(epoch)
         for features, labels in train_loader:
             features, labels = features.to(device), labels.to(device)
-            predictions = multilayer_model(features)
-            loss = cross_entropy(predictions, labels)
-            DDP_model.zero_grad()
-            loss.backward()
-            DDP_model.step()
+            loss = train_step(features, labels)
     secs = S.max_over_ranks(timer.elapsed(), device)
     if rank == 0:
         print(f"PyTorch Training Time: {secs:.2f} seconds")

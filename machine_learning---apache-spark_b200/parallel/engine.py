@@ -267,6 +267,14 @@ class DataParallelEngine:
         self._graph = g
         return g
 
+    def graphed(self, step_fn, warmup: int = 2, max_graphs: int = 4):
+        """Wrap a whole training step ``step_fn(*tensors) -> tensor(s)`` (zero_grad/forward/backward/step included) so
+        that, once a given input signature has run ``warmup`` times eagerly, it is captured into a CUDA graph and
+        replayed: inputs are copied into static buffers, the returned tensors are the graph's static outputs (valid
+        until the next call).  Other signatures (e.g. a short last batch) and CPU runs stay eager.  ``B200ML_GRAPH=0``
+        turns capturing off."""
+        return GraphedStep(self, step_fn, warmup, max_graphs)
+
     # ------------------------------------------------------------------------------------------------ utilities
     def sync_master(self) -> None:
         """Make every fp32 master parameter current on THIS rank (no-op unless the bf16-only push is active).
@@ -314,3 +322,40 @@ class DataParallelEngine:
             p._b200_scatter = None
             p._b200_ready = None
             p._b200_side = None
+
+
+class GraphedStep:
+    """See ``DataParallelEngine.graphed``.  The reference's loops call zero_grad / backward / step eagerly
+    (pytorch_machine_translator.py:172-196); here the same loop body is replayed as one CUDA graph per input shape."""
+
+    def __init__(self, engine: DataParallelEngine, step_fn, warmup: int = 2, max_graphs: int = 4):
+        self.engine, self.fn, self.warmup, self.max_graphs = engine, step_fn, warmup, max_graphs
+        self.enabled = engine.device.type == "cuda" and os.environ.get("B200ML_GRAPH", "1") != "0"
+        self._seen: dict = {}
+        self._graphs: dict = {}
+        self.replays = 0
+
+    def __call__(self, *inputs):
+        if not self.enabled:
+            return self.fn(*inputs)
+        key = tuple((tuple(t.shape), t.dtype) for t in inputs)
+        entry = self._graphs.get(key)
+        if entry is None:
+            n = self._seen.get(key, 0) + 1
+            self._seen[key] = n
+            if n <= self.warmup or len(self._graphs) >= self.max_graphs:
+                return self.fn(*inputs)      # eager: first uses allocate workspaces / build caches
+            static_in = [t.clone() for t in inputs]
+            holder = []
+            graph = self.engine.capture(lambda: holder.append(self.fn(*static_in)))
+            if graph is None:                # e.g. the NCCL baseline path stays eager
+                self.enabled = False
+                return self.fn(*inputs)
+            entry = (graph, static_in, holder[0])
+            self._graphs[key] = entry
+        graph, static_in, out = entry
+        for s, t in zip(static_in, inputs):
+            s.copy_(t, non_blocking=True)
+        graph.replay()
+        self.replays += 1
+        return out

@@ -72,6 +72,23 @@ def main():
     loader = DataLoader(train_dataset, batch_size=batch_size, shuffle=sampler is None, sampler=sampler, drop_last=True)
     max_steps = S.env_int("B200ML_STEPS", 6 if S.quick() else 10 ** 9)
 
+    look_ahead_mask = create_look_ahead_mask(max_sequence_length).to(device)
+    pad_id = en_vocab["<pad>"]
+
+    def train_step(src_tensor, trg_tensor):
+        padding_mask_x = (src_tensor != pad_id).unsqueeze(1).unsqueeze(2)
+        engine.zero_grad()
+        hidden = model(src_tensor, trg_tensor, padding_mask_x, look_ahead_mask, look_ahead_mask, return_hidden=True)
+        # head Linear + CrossEntropy(ignore_index=0) + masked mean as one fused node
+        loss = linear_cross_entropy(hidden, model.linear.weight, model.linear.bias, trg_tensor,
+                                    ignore_index=de_vocab["<pad>"])
+        loss.backward()
+        engine.step()
+        return loss.detach()
+
+    # every batch is exactly [32, 200] (PadTransform), so after two eager steps the whole step replays as a CUDA graph
+    step = engine.graphed(train_step)
+
     total = S.DeviceTimer(device).start()
     for epoch in range(epochs):
         if sampler is not None:
@@ -82,15 +99,7 @@ def main():
                 break
             src_tensor = en_text_transform([en_tokenizer(s) for s in src]).to(device)
             trg_tensor = de_text_transform([de_tokenizer(t) for t in trg]).to(device)
-            padding_mask_x = (src_tensor != en_vocab["<pad>"]).unsqueeze(1).unsqueeze(2)
-            look_ahead_mask = create_look_ahead_mask(trg_tensor.size(1)).to(device)
-            engine.zero_grad()
-            hidden = model(src_tensor, trg_tensor, padding_mask_x, look_ahead_mask, look_ahead_mask, return_hidden=True)
-            # head Linear + CrossEntropy(ignore_index=0) + masked mean as one fused node
-            loss = linear_cross_entropy(hidden, model.linear.weight, model.linear.bias, trg_tensor,
-                                        ignore_index=de_vocab["<pad>"])
-            loss.backward()
-            engine.step()
+            loss = step(src_tensor, trg_tensor)
             if rank == 0 and (batch_idx % 100 == 0 or S.quick()):
                 print(f"Iteration {batch_idx} : {loss.item()}")
             if batch_idx > 1 and batch_idx % 100 == 0:
