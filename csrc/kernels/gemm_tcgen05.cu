@@ -72,7 +72,7 @@ struct Epilogue {
     uint32_t rng_site;
     float* splitk_ws;        // != nullptr: write raw fp32 partial tiles to ws[split][M][N] instead of C
     int tma_store;           // bf16 C through smem staging + cp.async.bulk.tensor stores (needs tmap_c)
-    int debug;               // B200ML_GEMM_DEBUG (timing experiments only, results are garbage): 1 = no TMA loads, 2 = no MMAs
+    int debug;               // B200ML_GEMM_DEBUG (timing experiments only, results are garbage): 1 = no TMA loads, 2 = no MMAs, 4 = no TMA stores
     Scatter scatter;         // fp32 direct-store path only
     int cluster_splits;      // > 1: split-K over the CTAs of a cluster, partial tiles reduced through DSMEM (one tile per CTA)
 };
@@ -94,9 +94,10 @@ struct Cfg {
     // the single-CTA kernel has no shared memory left for that and reuses one slab.
     static constexpr int kSlabsPerWarp = (kCtas == 2 && BN == 256) ? 2 : 1;
     static constexpr int kCStageBytes = BN >= 128 ? kEpiWarps * 4096 * kSlabsPerWarp : 0;
-    static constexpr int kBiasBytes = 1024;  // BN floats
+    static constexpr int kBiasBytes = 2048;  // 2 x BN floats: the bias slice of a tile is double-buffered
     static constexpr int kSmemBytes =
-        kStages * kStageBytes + kCStageBytes + kBiasBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+        kStages * kStageBytes + kCStageBytes + kBiasBytes + 256 /*barriers*/;
+    static_assert(kSmemBytes <= 232448, "more than 227 KB of shared memory");
 };
 
 __device__ __forceinline__ float apply_act(float v, int act) {
@@ -138,10 +139,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     using C = Cfg<BN, kCtas>;
     constexpr int kTileM = BLOCK_M * kCtas;
     const uint32_t cta_rank = kCtas == 2 ? cluster_ctarank() : 0u;  // rank 0 of a pair issues the MMAs
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    // the kernel has no static shared memory, so the dynamic window starts at the 1024-byte alignment the swizzled TMA /
+    // UMMA tiles need (checked once below instead of paying 1 KB of slack)
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = smem_raw;
     uint8_t* stage_c = smem + C::kStages * C::kStageBytes;                       // 1024-aligned
-    float* s_bias = reinterpret_cast<float*>(stage_c + C::kCStageBytes);
+    float* const s_bias_base = reinterpret_cast<float*>(stage_c + C::kCStageBytes);
+    float* s_bias = s_bias_base;
+    int bias_buf = 0;
     uint64_t* bars = reinterpret_cast<uint64_t*>(stage_c + C::kCStageBytes + C::kBiasBytes);
     uint64_t* full_bar = bars;
     uint64_t* empty_bar = bars + C::kStages;
@@ -152,6 +157,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
+    if (threadIdx.x == 0 && (smem_u32(smem) & 1023u) != 0) {
+        printf("b200ml: GEMM shared memory window is not 1024-byte aligned\n");
+        __trap();
+    }
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmap_a);
@@ -371,8 +380,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         for (int tile = first_tile; tile < num_tiles; tile += tile_step) {
             TileCoord t = tile_coord(tile, m_tiles, n_tiles, BN, k_blocks, splits, kTileM);
             t.m0 += cta_rank * BLOCK_M;  // this CTA's rows
-            if (ep.bias) {  // stage this tile's bias slice once (overlaps the MMA of this tile)
-                named_bar_sync(1, kEpiWarps * 32);  // everyone is done with the previous tile's slice
+            if (ep.bias) {
+                // Stage this tile's bias slice once (overlaps the MMA of this tile).  Two buffers, one barrier per tile:
+                // a warp reaches this barrier only after it finished reading the other buffer for the previous tile.
+                s_bias = s_bias_base + (bias_buf ^= 1) * 256;
                 if (etid < BN) s_bias[etid] = t.n0 + etid < N ? __ldg(ep.bias + t.n0 + etid) : 0.f;
                 named_bar_sync(1, kEpiWarps * 32);
             }
@@ -415,7 +426,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     }
                     fence_proxy_async_smem();
                     __syncwarp();
-                    if (lane == 0) {
+                    if (lane == 0 && !(ep.debug & 4)) {   // debug 4: timing experiment without the output stores
                         tma_store_2d(&tmap_c, slab, t.n0 + c, t.m0 + quarter * 32);  // edges clipped by TMA
                         tma_store_commit();
                     }
