@@ -286,7 +286,7 @@ class Transformer(nn.Module):
         self.set_mask_mode(mask_mode)
         # run the decoder's encoder-independent prefix on a second stream (forward, and therefore backward too)
         self.overlap_streams = os.environ.get("B200ML_OVERLAP_STREAMS", "1") != "0"
-        self._dec_stream = None
+        self._dec_stream = None   # lazily created side stream for the decoder prefix (runtime state, never pickled)
 
     def set_mask_mode(self, mode: str) -> None:
         assert mode in ("reference", "causal")
@@ -295,6 +295,13 @@ class Transformer(nn.Module):
             if isinstance(m, (EncoderLayer, DecoderLayer)):
                 m.mask_mode = mode
 
+
+    def __getstate__(self):
+        # a returned / pickled model (TorchDistributor ships rank 0's return value to the driver) must not drag CUDA
+        # stream handles along
+        state = dict(self.__dict__)
+        state["_dec_stream"] = None
+        return state
     def forward(self, x, y, encoder_self_attention_mask=None, decoder_self_attention_mask=None,
                 decoder_cross_attention_mask=None, return_hidden: bool = False):
         if self.overlap_streams and x.is_cuda and len(self.decoder.layers) > 0:

@@ -92,6 +92,8 @@ class DataParallelEngine:
         self.v = torch.zeros_like(self.flat.flat_p) if self.kind == 2 else None
         self.launches_in_capture = 0
         self._graph = None
+        self._graphed_steps: list = []
+        self._sd_hook = None
 
         if self.world > 1:
             dist.broadcast(self.flat.flat_p, src=0, group=self.pg)
@@ -144,7 +146,7 @@ class DataParallelEngine:
                         self._scatter, self._scatter_buckets = False, set()
                 if self._bf16_push:
                     # model.state_dict() on any rank first pulls the fp32 slices it does not own
-                    module.register_state_dict_pre_hook(lambda *a, **k: self.sync_master())
+                    self._sd_hook = module.register_state_dict_pre_hook(lambda *a, **k: self.sync_master())
             if self.device.type == "cuda":
                 self.comm_stream = torch.cuda.Stream(device=self.device, priority=-1)
         # single GPU: the per-bucket optimizer launches also run on a side stream, overlapping the rest of backward
@@ -273,7 +275,9 @@ class DataParallelEngine:
         replayed: inputs are copied into static buffers, the returned tensors are the graph's static outputs (valid
         until the next call).  Other signatures (e.g. a short last batch) and CPU runs stay eager.  ``B200ML_GRAPH=0``
         turns capturing off."""
-        return GraphedStep(self, step_fn, warmup, max_graphs)
+        gs = GraphedStep(self, step_fn, warmup, max_graphs)
+        self._graphed_steps.append(gs)
+        return gs
 
     # ------------------------------------------------------------------------------------------------ utilities
     def sync_master(self) -> None:
@@ -313,10 +317,22 @@ class DataParallelEngine:
             self.v.copy_(sd["v"])
 
     def close(self) -> None:
+        # drop everything that is not picklable / must not outlive the engine: a script may return the module afterwards
+        # (TorchDistributor ships rank 0's return value to the driver); graphs go before the peer mappings they use
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+        for gs in self._graphed_steps:
+            gs._graphs.clear()
+            gs.enabled = False
+        self._graphed_steps = []
+        self._graph = None
         if self.comm is not None:
             self.sync_master()
             self.comm.close()
             self.comm = None
+        if self._sd_hook is not None:
+            self._sd_hook.remove()
+            self._sd_hook = None
         self.reducer.close()
         for p in self.flat.params:
             p._b200_scatter = None
