@@ -64,3 +64,32 @@ def test_engine_uses_native_reducer():
     loss.backward()
     eng.finish_step()
     eng.close()
+
+
+def test_graphed_step_is_plain_call_on_cpu_and_close_is_idempotent():
+    import pickle
+
+    import torch
+    from b200ml.parallel.engine import DataParallelEngine
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(8, 16), torch.nn.Sigmoid(), torch.nn.Linear(16, 3))
+    eng = DataParallelEngine(model, optimizer="sgd", lr=0.1)
+    calls = []
+
+    def one_step(x, y):
+        calls.append(tuple(x.shape))
+        loss = torch.nn.functional.cross_entropy(model(x), y)
+        eng.zero_grad()
+        loss.backward()
+        eng.step()
+        return loss.detach()
+
+    step = eng.graphed(one_step)
+    assert not step.enabled                      # no CUDA device: every call is the eager function
+    l0 = float(step(torch.randn(5, 8), torch.randint(0, 3, (5,))))
+    for _ in range(20):
+        l1 = float(step(torch.randn(5, 8), torch.randint(0, 3, (5,))))
+    assert len(calls) == 21 and step.replays == 0 and l1 == l1 and l0 == l0
+    eng.close()
+    eng.close()                                  # a second close must be harmless
+    pickle.loads(pickle.dumps(model))            # the module carries no engine state afterwards
