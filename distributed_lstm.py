@@ -36,6 +36,21 @@ def train_func():
     loader = DataLoader(train_dataset, batch_size=batch_size, sampler=sampler, drop_last=True)
     n_epochs = S.env_int("B200ML_EPOCHS", 1 if S.quick() else epochs)
     text_classifier.train()
+
+    def one_step(text_tokens, labels):
+        bs = labels.shape[0]
+        hidden = torch.zeros(num_layers, bs, hidden_size, device=device)
+        memory = torch.zeros(num_layers, bs, hidden_size, device=device)
+        pred, hidden, memory = text_classifier(text_tokens, hidden, memory)
+        loss = cross_entropy(pred[:, -1, :], labels)
+        DDP_model.zero_grad()
+        loss.backward()
+        DDP_model.step()
+        return (pred[:, -1, :].argmax(1) == labels).sum()
+
+    # batches are padded to their own longest text (<= 129 tokens); most hit the truncation cap, so a handful of
+    # sequence lengths covers nearly every batch: each gets its own CUDA graph, rare lengths run eagerly
+    train_step = DDP_model.graphed(one_step, max_graphs=16)
     timer = S.DeviceTimer(device).start()
     n_samples = 0
     train_acc = torch.zeros((), device=device)
@@ -45,14 +60,7 @@ def train_func():
             bs = labels.shape[0]
             text_tokens = text_tranform([tokenizer(t) for t in texts]).to(device)
             labels = (labels - 1).to(device)
-            hidden = torch.zeros(num_layers, bs, hidden_size, device=device)
-            memory = torch.zeros(num_layers, bs, hidden_size, device=device)
-            pred, hidden, memory = text_classifier(text_tokens, hidden, memory)
-            loss = cross_entropy(pred[:, -1, :], labels)
-            DDP_model.zero_grad()
-            loss.backward()
-            DDP_model.step()
-            train_acc += (pred[:, -1, :].argmax(1) == labels).sum()
+            train_acc += train_step(text_tokens, labels)
             n_samples += bs
     secs = S.max_over_ranks(timer.elapsed(), device)
     DDP_model.weights_hash()
