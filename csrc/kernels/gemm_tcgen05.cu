@@ -522,11 +522,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     const int rr = r_lo + it / vec_per_row, cc = (it % vec_per_row) * 4;
                     const int grow = t.m0 + rr, gcol = t.n0 + cc;
                     if (grow >= M || gcol >= N) continue;
+                    // all remote loads first (their latencies overlap), then the adds in rank order
+                    float4 part[8];
+#pragma unroll
+                    for (int sp = 0; sp < 8; ++sp)
+                        if (sp < csplit) part[sp] = ld_dsmem_f4(red0 + (uint32_t)(rr * (BN + 4) + cc) * 4u, (uint32_t)sp);
                     float4 s4 = make_float4(0.f, 0.f, 0.f, 0.f);
-                    for (int sp = 0; sp < csplit; ++sp) {
-                        const float4 v4 = ld_dsmem_f4(red0 + (uint32_t)(rr * (BN + 4) + cc) * 4u, (uint32_t)sp);
-                        s4.x += v4.x; s4.y += v4.y; s4.z += v4.z; s4.w += v4.w;
-                    }
+#pragma unroll
+                    for (int sp = 0; sp < 8; ++sp)
+                        if (sp < csplit) { s4.x += part[sp].x; s4.y += part[sp].y; s4.z += part[sp].z; s4.w += part[sp].w; }
                     s4.x *= alpha; s4.y *= alpha; s4.z *= alpha; s4.w *= alpha;
                     const float vals[4] = {s4.x, s4.y, s4.z, s4.w};
                     if (ep.c_fp32) {
