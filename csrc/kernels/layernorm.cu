@@ -313,9 +313,10 @@ int b200ml_layernorm_bwd(const void* dy, const void* z, const float* mean, const
 // from.  For them the per-CTA partial sums of dgamma/dbeta live in a file-scope device array that is part of the
 // library image: every GPU that loads libb200ml.so carries these ~2.3 MiB until the process exits.
 //
-// Limits: d <= 1024 and d % 8 == 0 (as for b200ml_layernorm_bwd); at most kNoAllocMaxCtas CTAs are used, so on a GPU
-// with more than 148 SMs this variant launches a smaller grid than the scratch-taking one (same results up to fp32
-// summation order).  Anything else is refused with an error, nothing is truncated silently.
+// Limits: d <= 1024 and d % 8 == 0 (as for b200ml_layernorm_bwd).  The grid is capped at kNoAllocMaxCtas = 296 CTAs,
+// whereas the scratch-taking entry point uses up to 4 CTAs per SM (592 on a B200): for rows > 2368 this variant
+// therefore already runs with half the CTAs on the B200 itself (the kernel is grid-stride over rows, so results are the
+// same up to fp32 summation order).  Anything else is refused with an error, nothing is truncated silently.
 // ================================================================================================================
 namespace b200 {
 namespace ln {

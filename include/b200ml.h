@@ -91,7 +91,8 @@ int b200ml_layernorm_bwd(const void* dy, const void* z, const float* mean, const
  * must not call cudaMalloc/cudaFree after start-up (the call can fail when the pool holds the rest of HBM, and it
  * synchronises the device), and for C/FFI callers with no allocator to borrow a workspace from.
  *   - limit: d % 8 == 0 and d <= b200ml_layernorm_bwd_noalloc_max_d() (1024); larger d is refused with an error —
- *     use the scratch-taking entry point for it.  rows is unlimited.
+ *     use the scratch-taking entry point for it.  rows is unlimited, but the grid is capped at 296 CTAs (the
+ *     scratch-taking entry point uses up to 4 per SM, 592 on a B200), so large inputs run somewhat slower here.
  *   - the FIRST call on each device looks up the array's device address (cudaGetSymbolAddress, with that device
  *     current); make that first call before any stream capture begins.
  *   - all calls on a device share the one array.  Nothing in it needs clearing between calls (each call overwrites

@@ -73,11 +73,9 @@ class FlatOptimizer:
             if p.grad is not None:
                 p._b200_grad.copy_(p.grad.reshape(-1))
                 p.grad = None
-        if self.flat.device.type == "cuda":
-            _native.check(_native.load().b200ml_counters_advance(None, self.step_tensor.data_ptr(),
-                                                                 _native.stream_ptr()), "counters_advance")
-        else:
-            self.step_tensor += 1
+        # one one-thread kernel bumps this optimizer's step AND the dropout RNG step: backward has consumed this step's
+        # masks by now, and without the bump every training step would draw the identical masks
+        self.counters.advance(rng=True, opt_tensor=self.step_tensor)
         optim_step_flat(self.flat.flat_p, self.flat.flat_g, self.m, self.v, self.flat.flat_w16, self.kind, self.lr,
                         self.betas, self.eps, self.weight_decay, self.step_tensor, grad_scale)
 

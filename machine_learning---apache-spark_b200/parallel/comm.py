@@ -283,6 +283,21 @@ class FusedAllReduce:
         self._scatter_descs.append(d)  # keep alive: the GEMM reads it through a raw pointer
         return d
 
+    def owned_slice(self, start: int, n: int, sliced: bool | None = None, rank: int | None = None):
+        """(lo, hi) relative to ``start``: the part of bucket [start, start+n) whose optimizer state (fp32 master under
+        bf16 push, Adam moments always) rank ``rank`` keeps, or None when the bucket takes the one-shot path and every
+        rank updates all of it.  Mirrors the slice arithmetic of csrc/comm/allreduce.cu."""
+        n4 = (n + 3) // 4 * 4
+        if sliced is None:
+            sliced = n4 * 4 > (512 << 10)
+        if not sliced:
+            return None
+        gran = 8 if (self.cs.mc_grads and self.cs.mc_w16 and start % 8 == 0 and n4 % 8 == 0) else 4  # NVLS: 8-wide
+        per = ((n4 // gran + self.world - 1) // self.world) * gran
+        r = self.rank if rank is None else rank
+        lo = min(per * r, n4)
+        return lo, min(lo + per, n4)
+
     def pull_master(self, start: int, n: int, sliced: bool | None = None) -> None:
         """Refresh the fp32 master values of [start, start+n) that other ranks own (two-shot buckets updated with
         push_master = 0).  One-sided peer reads; the owners' values are final once our own last all-reduce kernel

@@ -3,12 +3,15 @@
 rebuilt around flat buckets and a fused all-reduce + optimizer kernel.
 
 Per step:
-  begin_step()   bump the device RNG / optimizer-step counters, clear the few gradient slots that accumulate
+  begin_step()   bump the optimizer-step counter, clear the few gradient slots that accumulate
   forward/backward   wgrad kernels write straight into the flat fp32 gradient buffer; each parameter reports "ready"
   (as buckets complete)  world > 1: the bucket is reduced across ranks and the optimizer applied in ONE kernel
                          (parallel/comm.py: one-shot / two-shot P2P over NVLink), on a side stream, overlapping the
                          rest of backward;  "nccl" mode (the measured baseline) uses torch.distributed.all_reduce
-  finish_step()  join the side stream (world == 1: one fused optimizer launch over the whole flat buffer)
+  finish_step()  join the side stream (world == 1: one fused optimizer launch over the whole flat buffer), then bump
+                 the device dropout-RNG step: forward and backward of one step always see the same draw, wherever
+                 zero_grad() sits between them (the reference calls it after forward in distributed_lstm.py:192-194
+                 and before forward in pytorch_machine_translator.py:172)
 
 Rank 0's parameters are broadcast at construction (what DDP's constructor does); gradients are
 averaged (sum / world), so N ranks with batch B reproduce one rank with batch N·B.
@@ -215,7 +218,9 @@ class DataParallelEngine:
 
     # ------------------------------------------------------------------------------------------------ step API
     def begin_step(self) -> None:
-        self.counters.advance(rng=True, opt_tensor=self.step_tensor)
+        # only the optimizer step moves here; the dropout RNG step moves at the END of the step (finish_step), after
+        # backward has regenerated its masks - zero_grad() may legally sit between forward and backward
+        self.counters.advance(rng=False, opt_tensor=self.step_tensor)
         self.flat.zero_accumulating_slots()
         self.reducer.begin_step()
         for b in range(len(self.buckets)):
@@ -233,6 +238,7 @@ class DataParallelEngine:
         if (self.world == 1 and not self._local_overlap) or not self.sync_gradients:
             optim_step_flat(self.flat.flat_p, self.flat.flat_g, self.m, self.v, self.flat.flat_w16, self.kind, self.lr,
                             self.betas, self.eps, self.weight_decay, self.step_tensor)
+            self.counters.advance(rng=True)
             return
         # parameters that never reported (unused in this forward) still need their bucket processed
         for b in self.reducer.flush():
@@ -241,6 +247,9 @@ class DataParallelEngine:
             torch.cuda.current_stream().wait_stream(self.comm_stream)
         if self.side is not None:
             self.side.join()
+        # every backward kernel of this step is ordered before this point on the current stream (autograd joined its
+        # streams, the side and comm streams were joined above): the next forward draws fresh dropout masks
+        self.counters.advance(rng=True)
         self._master_stale = self._bf16_push and self.comm is not None
 
     # torch.optim-flavoured aliases so the entry scripts read like the reference loops
@@ -307,8 +316,36 @@ class DataParallelEngine:
                 raise RuntimeError(f"rank divergence: weight checksum differs across ranks ({lo.item()} vs {hi.item()})")
         return float(h.item())
 
+    def gather_moments(self):
+        """Full Adam moments (m, v), identical on every rank.  In the fused two-shot all-reduce only the owner of a
+        slice runs the optimizer for it, so a rank's own ``m`` / ``v`` are current only inside the slices it owns; the
+        other ranges are stale (zero if never loaded).  Collective: every rank must call it.  Each rank contributes
+        its owned slices, the rest comes from a sum over ranks of buffers that are zero outside the owned ranges."""
+        if self.m is None:
+            return None, None
+        if self.comm is None or self.world == 1:
+            return self.m, self.v
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+        out = []
+        for t in (self.m, self.v):
+            full = t.clone()
+            for b, (start, n, _, _) in enumerate(self.buckets):
+                own = self.comm.owned_slice(start, n)
+                if own is None:
+                    continue        # one-shot bucket: every rank ran the identical update
+                lo, hi = own
+                n4 = (n + 3) // 4 * 4
+                full[start:start + lo].zero_()
+                full[start + hi:start + n4].zero_()
+                dist.all_reduce(full[start:start + n4], group=self.pg)
+            out.append(full)
+        return out[0], out[1]
+
     def state_dict(self):
-        return {"step": int(self.step_tensor.item()), "m": self.m, "v": self.v, "kind": self.kind}
+        """Collective when world > 1 (see gather_moments)."""
+        m, v = self.gather_moments()
+        return {"step": int(self.step_tensor.item()), "m": m, "v": v, "kind": self.kind}
 
     def load_state_dict(self, sd) -> None:
         self.step_tensor.fill_(sd["step"])

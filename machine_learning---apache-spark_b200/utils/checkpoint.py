@@ -13,14 +13,21 @@ def _per_param_state(engine_or_opt):
     flat = engine_or_opt.flat
     out = {}
     if getattr(engine_or_opt, "m", None) is not None:
+        # multi-GPU engine: only a slice's owner keeps its Adam moments current -> gather them first (collective)
+        if hasattr(engine_or_opt, "gather_moments"):
+            m, v = engine_or_opt.gather_moments()
+        else:
+            m, v = engine_or_opt.m, engine_or_opt.v
         for i, p in enumerate(flat.params):
             o, n = flat.slot(i)
-            out[i] = {"m": engine_or_opt.m[o:o + n].detach().cpu().clone(), "v": engine_or_opt.v[o:o + n].detach().cpu().clone()}
+            out[i] = {"m": m[o:o + n].detach().cpu().clone(), "v": v[o:o + n].detach().cpu().clone()}
     return out
 
 
 def save_checkpoint(path: str, model, engine_or_opt=None, extra: dict | None = None) -> None:
-    """Call on every rank (the fp32 master pull is one-sided); only rank 0 writes."""
+    """Call on EVERY rank: gathering the Adam moments from the slice owners is a collective (the fp32 master pull is
+    one-sided); only rank 0 writes.  The file holds full per-parameter state, so it can be resumed at another world
+    size or bucket layout: ``load_checkpoint`` gives every rank the full moments, which covers whatever it will own."""
     if engine_or_opt is not None and hasattr(engine_or_opt, "sync_master"):
         engine_or_opt.sync_master()
     rank = int(os.environ.get("RANK", "0"))

@@ -1,13 +1,17 @@
 """Per-device scratch buffers for kernels that need global-memory workspace (two-stage reductions, split-K).
 
-Buffers are cached by name and only ever grow, so their addresses are stable across steps — a requirement for
-CUDA-graph replay — and nothing is allocated in the steady state.
+Buffers are cached by name and nothing is allocated in the steady state.  When a request outgrows a buffer a larger
+one replaces it, but the superseded buffer is RETIRED, never freed: a CUDA graph captured earlier (the engine keeps one
+per input shape, e.g. per LSTM sequence length) has the old address baked in, and replaying it must keep writing into
+memory nobody else owns.  Growth is geometric, so the retired buffers of one name sum to less than twice its final
+size.
 """
 from __future__ import annotations
 
 import torch
 
 _cache: dict = {}
+_retired: list = []   # superseded buffers that captured graphs may still reference
 _lanes: dict = {}   # cuda stream pointer -> small lane id
 
 
@@ -26,10 +30,20 @@ def get(name: str, nbytes: int, device) -> torch.Tensor:
     key = (name, device.type, device.index)
     buf = _cache.get(key)
     if buf is None or buf.numel() < nbytes:
-        buf = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+        size = max(int(nbytes), 256)
+        if buf is not None:
+            _retired.append(buf)
+            size = max(size, buf.numel() * 3 // 2)
+        buf = torch.empty(size, dtype=torch.uint8, device=device)
         _cache[key] = buf
     return buf
 
 
+def retired_bytes() -> int:
+    return sum(b.numel() for b in _retired)
+
+
 def clear() -> None:
+    """Drop every buffer, retired ones included.  Only safe once no captured graph that used them will be replayed."""
     _cache.clear()
+    _retired.clear()

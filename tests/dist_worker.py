@@ -170,7 +170,67 @@ def case_allreduce_nvls(rank, world, dev, mode):
     print(f"[rank {rank}] allreduce_nvls ok")
 
 
-CASES = {"allreduce_nvls": case_allreduce_nvls, "dp_equals_big_batch": case_dp_equals_big_batch, "fused_matches_nccl": case_fused_matches_nccl,
+def case_checkpoint_adam(rank, world, dev, mode):
+    """Adam state of a two-shot (sliced) bucket lives only on the slice owners: a checkpoint written from rank 0 must
+    still hold ALL of it, and resuming from it must continue exactly like the uninterrupted run."""
+    import tempfile
+    from b200ml.models.transformer import Transformer
+    from b200ml.parallel.engine import DataParallelEngine
+    from b200ml.utils.checkpoint import load_checkpoint, save_checkpoint
+
+    def build():
+        torch.manual_seed(11)
+        m = Transformer(128, 256, 2, 0.0, 1, 32, 2000, 80, 2000).to(dev)   # 2000 x 128 fp32 tables/head: 1 MB slots
+        m.eval()
+        return m
+
+    def run(model, eng, steps, seed):
+        from b200ml.ops.loss import linear_cross_entropy
+        g = torch.Generator().manual_seed(seed + rank)
+        la = (torch.tril(torch.ones(32, 32, device=dev)) == 0)[None, None]
+        for _ in range(steps):
+            src = torch.randint(1, 80, (4, 32), generator=g).to(dev)
+            trg = torch.randint(1, 2000, (4, 32), generator=g).to(dev)
+            eng.begin_step()
+            h = model(src, trg, (src != 0)[:, None, None, :], la, la, return_hidden=True)
+            linear_cross_entropy(h, model.linear.weight, model.linear.bias, trg, ignore_index=0).backward()
+            eng.finish_step()
+
+    ref = build()
+    e_ref = DataParallelEngine(ref, optimizer="adam", lr=1e-3, allreduce=mode, bucket_mb=4.0)
+    if e_ref.comm is not None:
+        assert any(e_ref.comm.owned_slice(s, n) is not None for s, n, _, _ in e_ref.buckets), "no sliced bucket in test"
+    run(ref, e_ref, 3, 1)
+    run(ref, e_ref, 2, 2)
+    want = torch.cat([v.detach().reshape(-1).clone() for v in ref.state_dict().values()])
+    e_ref.close()
+
+    a = build()
+    e_a = DataParallelEngine(a, optimizer="adam", lr=1e-3, allreduce=mode, bucket_mb=4.0)
+    run(a, e_a, 3, 1)
+    path = os.path.join(tempfile.gettempdir(), f"b200ml_ck_{os.environ.get('MASTER_PORT', '0')}.pt")
+    save_checkpoint(path, a, e_a)
+    dist.barrier()
+    blob = torch.load(path, weights_only=False)
+    nz = sum(int((st["v"] != 0).sum()) for st in blob["optimizer"]["state"].values())
+    tot = sum(st["v"].numel() for st in blob["optimizer"]["state"].values())
+    e_a.close()
+
+    b = build()
+    with torch.no_grad():
+        for p in b.parameters():
+            p.add_(1.0)    # the checkpoint must overwrite this
+    e_b = DataParallelEngine(b, optimizer="adam", lr=1e-3, allreduce=mode, bucket_mb=4.0)
+    load_checkpoint(path, b, e_b, map_location="cpu")
+    run(b, e_b, 2, 2)
+    got = torch.cat([v.detach().reshape(-1).clone() for v in b.state_dict().values()])
+    e_b.close()
+    err = (got - want).abs().max().item()
+    assert err < 1e-5, f"resume differs from the uninterrupted run by {err}"
+    print(f"[rank {rank}] checkpoint_adam ok err={err:.3e} nonzero_v={nz}/{tot}")
+
+
+CASES = {"checkpoint_adam": case_checkpoint_adam,"allreduce_nvls": case_allreduce_nvls, "dp_equals_big_batch": case_dp_equals_big_batch, "fused_matches_nccl": case_fused_matches_nccl,
          "allreduce_raw": case_allreduce_raw}
 
 if __name__ == "__main__":

@@ -23,6 +23,11 @@ def test_dp_engine_gloo_world2():
     assert out.count("dp_equals_big_batch ok") == 2
 
 
+def test_checkpoint_adam_gloo_world2():
+    out = _launch(["checkpoint_adam"], 2, 29614, {"B200ML_TEST_CPU": "1", "OMP_NUM_THREADS": "2"})
+    assert out.count("checkpoint_adam ok") == 2
+
+
 @pytest.mark.gpu
 @pytest.mark.multigpu
 def test_fused_allreduce_two_gpus():
