@@ -67,7 +67,7 @@ def compile_one(src: str, force: bool) -> tuple[str, str]:
     log = ""
     if force or not os.path.exists(obj):
         for old in os.listdir(BUILD):
-            if old.startswith(base + ".") and old.endswith(".o"):
+            if old.startswith(base + ".") and (old.endswith(".o") or old.endswith(".o.log")):
                 os.remove(os.path.join(BUILD, old))
         cmd = [nvcc(), *ARCH, *NVCC_FLAGS, "-x", "cu", "-c", src, "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)

@@ -2,17 +2,31 @@
 // the SGD / Adam update and the bf16 re-cast of the weights.  Replaces c10d Reducer + gloo all-reduce +
 // optimizer.step() of the reference's intended DDP path (distributed_cnn.py:152-183 etc.).
 //
-// Every rank maps every peer's flat gradient / weight buffers (CUDA IPC) and the kernels dereference those peer
-// pointers directly (ld.global / st.global over NVLink):
+// Every rank maps every peer's flat gradient / weight buffers (CUDA IPC) and the kernels reach them directly:
 //   one-shot  (latency path, small buckets): barrier -> every rank sums the whole bucket from all N ranks in rank
 //             order 0..N-1 (=> bit-identical sums everywhere) -> applies the update to its own weights -> barrier.
-//   two-shot  (bandwidth path): rank r owns slice r of the bucket: pulls slice r from the N-1 peers, reduces, runs the
-//             optimizer ONCE for those elements (Adam math is not repeated N times), then pushes the updated fp32
-//             master + bf16 working weights into every rank's buffers -> barrier.  Gradients are never all-gathered:
-//             the second phase moves weights (2 or 6 bytes/param) instead of fp32 gradients.
+//   two-shot  (bandwidth path): rank r owns slice r of the bucket: it brings slice r of the N-1 peers' gradients in,
+//             reduces, runs the optimizer ONCE for those elements (Adam math is not repeated N times), then writes
+//             the updated bf16 working weights (and, on request, the fp32 masters) into every rank's buffers ->
+//             barrier.  Gradients are never all-gathered: the second phase moves weights (2 or 6 bytes/param).
+//             Three transports for the same ownership:
+//               bulk  (default) - warp-specialised: one producer thread streams 4 KB chunks of the peers' gradient
+//                       slices AND of the local g / p / m / v straight into a shared-memory ring with
+//                       cp.async.bulk (TMA, completion on mbarriers); eight consumer warps reduce from shared
+//                       memory, run the optimizer and hand the bf16 weights back to TMA, which stores them into
+//                       every peer.  Bytes in flight are set by the ring (up to 176 KB per CTA), not by registers,
+//                       so a few dozen CTAs keep NVLink busy.  The TMA loads are plain (non-multicast) copies.
+//               pull  - SM-issued ld.global.cg from the peers, two vectors per thread in flight (round-1 kernel).
+//               nvls  - multimem.ld_reduce / multimem.st on NVSwitch multicast addresses (in-switch sum).
 // Cross-GPU barriers are per-CTA flag exchanges through a peer-mapped signal pad with release/acquire at system scope;
 // flag values are a monotonically increasing epoch kept in device memory, so a captured CUDA graph replays correctly.
 // Spins are bounded: a dead peer traps the kernel instead of hanging the GPU.
+//
+// CONSTRAINT (documented in include/b200ml.h): CTA i of rank a waits for CTA i of every other rank, and nothing
+// co-schedules them.  That is safe as long as (1) every CTA of a launch is resident at once - the launcher clamps the
+// grid to what cudaOccupancyMaxActiveBlocksPerMultiprocessor reports - and (2) one communicator has at most ONE of
+// these kernels in flight at a time, issued in the same order on every rank (the engine uses a single comm stream);
+// two communicators may run concurrently only if their combined grids still fit the device.
 #include <cstdlib>
 
 #include "../../include/b200ml.h"
@@ -34,7 +48,6 @@ struct Peers {
     __nv_bfloat16* w16[kMaxRanks];
     uint32_t* sig[kMaxRanks];  // [2][kMaxBlocks][kMaxRanks] per rank
     uint32_t* counter;         // local: [0] epoch, [1] CTA ticket
-    float* stage[kMaxRanks];   // per-rank staging buffers for the push variant (same size/layout as g; may be null)
     float* mc_g;               // NVLS multicast addresses of the same buffers (null when not available)
     float* mc_p;
     __nv_bfloat16* mc_w16;
@@ -98,15 +111,37 @@ __device__ __forceinline__ uint2 pack4_bf16(float4 v) {
     return u;
 }
 
+// Slice of [0, n) that `rank` owns in the two-shot variants: `gran`-element granularity (8 whenever start and n allow
+// it, so that bf16 slices are 16-byte aligned for TMA and multimem; the Python side mirrors this in owned_slice()).
+__device__ __forceinline__ void owned_range(long long n, int gran, int world, int rank, long long& lo, long long& hi) {
+    const long long per = (n / gran + world - 1) / world * gran;
+    lo = per * rank;
+    if (lo > n) lo = n;
+    hi = lo + per < n ? lo + per : n;
+}
+
+// one float4 of reduced (already averaged) gradient -> new weights; m / v are updated in place (Adam)
+__device__ __forceinline__ float4 update4(float4 p, float4 g, float4& mm, float4& vv, const OptimSpec& o,
+                                          const AdamCorr& corr) {
+    if (o.kind == 2) {
+        p.x = adam_update(p.x, g.x, mm.x, vv.x, o, corr);
+        p.y = adam_update(p.y, g.y, mm.y, vv.y, o, corr);
+        p.z = adam_update(p.z, g.z, mm.z, vv.z, o, corr);
+        p.w = adam_update(p.w, g.w, mm.w, vv.w, o, corr);
+    } else {
+        p.x = sgd_update(p.x, g.x, o);
+        p.y = sgd_update(p.y, g.y, o);
+        p.z = sgd_update(p.z, g.z, o);
+        p.w = sgd_update(p.w, g.w, o);
+    }
+    return p;
+}
+
 // kind 0: out[i] = sum/N (no weight update).  `start`, `n` in elements, both multiples of 4.
-// kSlim: 128-thread CTAs, one float4 per thread per trip, at most 80 registers - small enough to be co-resident with a
-// persistent tcgen05 GEMM CTA (320 threads x 168 registers leave ~11.7 K registers and no shared memory is needed), so
-// the reduction of a finished bucket can proceed WHILE backward's GEMMs own the SMs instead of queueing behind them.
-// Opt-in (B200ML_AR_SLIM=1): in the measured training steps the wide variant (512 threads x 128 registers) still wins.
-template <bool kTwoShot, bool kSlim>
-__global__ void __launch_bounds__(kSlim ? 128 : kThreads, kSlim ? 6 : 1)
+template <bool kTwoShot>
+__global__ void __launch_bounds__(kThreads, 1)
 allreduce_update_kernel(Peers c, long long start, long long n, OptimSpec o, float* __restrict__ m,
-                        float* __restrict__ v, float* __restrict__ out, int push_master) {
+                        float* __restrict__ v, float* __restrict__ out, int push_master, int gran) {
     const uint32_t epoch = c.counter[0] + 1;
     cross_barrier(c, 0, epoch);  // every rank's gradients for this bucket are complete and visible
 
@@ -115,12 +150,7 @@ allreduce_update_kernel(Peers c, long long start, long long n, OptimSpec o, floa
     if (o.kind == 2) corr = adam_corr(o);
 
     long long lo = 0, hi = n;  // range (relative to start) this rank reduces
-    if (kTwoShot) {
-        long long per = (n / 4 + c.world - 1) / c.world * 4;
-        lo = per * c.rank;
-        hi = lo + per < n ? lo + per : n;
-        if (lo > n) lo = n;
-    }
+    if (kTwoShot) owned_range(n, gran, c.world, c.rank, lo, hi);
     const long long nvec = (hi - lo) / 4;
     const long long stride = (long long)gridDim.x * blockDim.x;
     // the update for one float4 of reduced gradient
@@ -131,20 +161,15 @@ allreduce_update_kernel(Peers c, long long start, long long n, OptimSpec o, floa
             return;
         }
         float4 p = *reinterpret_cast<const float4*>(c.p[c.rank] + e);
+        float4 mm = make_float4(0.f, 0.f, 0.f, 0.f), vv = mm;
         if (o.kind == 2) {
-            float4 mm = *reinterpret_cast<const float4*>(m + e);
-            float4 vv = *reinterpret_cast<const float4*>(v + e);
-            p.x = adam_update(p.x, acc.x, mm.x, vv.x, o, corr);
-            p.y = adam_update(p.y, acc.y, mm.y, vv.y, o, corr);
-            p.z = adam_update(p.z, acc.z, mm.z, vv.z, o, corr);
-            p.w = adam_update(p.w, acc.w, mm.w, vv.w, o, corr);
+            mm = *reinterpret_cast<const float4*>(m + e);
+            vv = *reinterpret_cast<const float4*>(v + e);
+        }
+        p = update4(p, acc, mm, vv, o, corr);
+        if (o.kind == 2) {
             *reinterpret_cast<float4*>(m + e) = mm;
             *reinterpret_cast<float4*>(v + e) = vv;
-        } else {
-            p.x = sgd_update(p.x, acc.x, o);
-            p.y = sgd_update(p.y, acc.y, o);
-            p.z = sgd_update(p.z, acc.z, o);
-            p.w = sgd_update(p.w, acc.w, o);
         }
         const uint2 pb = pack4_bf16(p);
         if (kTwoShot) {
@@ -162,20 +187,6 @@ allreduce_update_kernel(Peers c, long long start, long long n, OptimSpec o, floa
     };
     // Two float4 per thread per trip: all 2 x world peer loads are issued before the first add, which doubles the
     // bytes in flight per CTA (NVLink round trips are ~2-3 us; bandwidth needs ~2 MB outstanding per GPU).
-    if (kSlim) {
-        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
-            const long long e0 = start + lo + i * 4;
-            float4 t0[kMaxRanks];
-#pragma unroll
-            for (int r = 0; r < kMaxRanks; ++r)
-                if (r < c.world) t0[r] = ld_peer_f4(c.g[r] + e0);
-            float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-            for (int r = 0; r < kMaxRanks; ++r)   // fixed rank order => the same bits on every rank
-                if (r < c.world) { a0.x += t0[r].x; a0.y += t0[r].y; a0.z += t0[r].z; a0.w += t0[r].w; }
-            apply(e0, a0);
-        }
-    } else
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += 2 * stride) {
         const long long e0 = start + lo + i * 4;
         const bool two = i + stride < nvec;
@@ -206,10 +217,152 @@ allreduce_update_kernel(Peers c, long long start, long long n, OptimSpec o, floa
 }
 
 // ---------------------------------------------------------------------------------------------------------------
+// Bulk-async two-shot (the default bandwidth path).  Chunk = 1024 elements: 4 KB per gradient source.
+//   producer (warp 8, one thread): per chunk, (world-1) cp.async.bulk loads of the peers' gradient slices plus the
+//       local g, p (and m, v for Adam) into ring stage s; completion bytes on full[s]; waits on empty[s] to reuse it.
+//   consumers (warps 0-7, one float4 each): wait full[s]; sum the sources from shared memory in rank order; optimizer;
+//       p / m / v back to local global memory with ordinary stores; bf16 weights into a small triple-buffered
+//       shared-memory tile that thread 0 hands to TMA - one cp.async.bulk store of 2 KB per rank (kBulkStore), or
+//       8-byte stores from every thread (kBulkStore = false).  Masters of non-owned slices only on `push_master`.
+// Nothing here holds loaded data in registers while it is in flight, so the pipeline depth is the ring depth.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int kBulkChunk = 1024;                 // elements per chunk
+constexpr int kBulkChunkBytes = kBulkChunk * 4;
+constexpr int kBulkConsumers = 256;              // one float4 of the chunk per consumer thread
+constexpr int kBulkThreads = kBulkConsumers + 32;
+constexpr int kBulkOutBufs = 3;
+constexpr int kBulkOutBytes = kBulkChunk * 2;    // bf16 tile
+constexpr int kBulkMaxStages = 8;
+constexpr int kBulkSmemBudget = 200 * 1024;
+
+template <bool kAdam, bool kBulkStore>
+__global__ void __launch_bounds__(kBulkThreads, 1)
+allreduce_bulk_kernel(Peers c, long long start, long long n, OptimSpec o, float* __restrict__ m, float* __restrict__ v,
+                      int push_master, int stages) {
+    extern __shared__ __align__(128) uint8_t bsm[];
+    const int tid = threadIdx.x;
+    const int nrem = c.world - 1;
+    const int nslots = nrem + (kAdam ? 4 : 2);
+    const uint32_t stage_bytes = (uint32_t)nslots * kBulkChunkBytes;
+    uint8_t* outbuf = bsm + (size_t)stages * stage_bytes;
+    uint64_t* full = reinterpret_cast<uint64_t*>(outbuf + kBulkOutBufs * kBulkOutBytes);
+    uint64_t* empty = full + kBulkMaxStages;
+    if (tid == 0) {
+        for (int s = 0; s < stages; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], kBulkConsumers / 32);
+        }
+        fence_barrier_init();
+    }
+    const uint32_t epoch = c.counter[0] + 1;
+    cross_barrier(c, 0, epoch);  // (starts with __syncthreads: barrier init is visible) every rank's gradients are final
+
+    long long lo, hi;
+    owned_range(n, 8, c.world, c.rank, lo, hi);
+    const long long len_total = hi - lo;
+    const long long nchunks = (len_total + kBulkChunk - 1) / kBulkChunk;
+    const long long base = start + lo;
+
+    if (tid >= kBulkConsumers) {
+        if (tid == kBulkConsumers) {  // ---------------- producer ----------------
+            fence_proxy_async_all();  // the acquire above ordered the peers' writes; make that hold for the TMA reads too
+            int k = 0;
+            for (long long ch = blockIdx.x; ch < nchunks; ch += gridDim.x, ++k) {
+                const int s = k % stages;
+                if (k >= stages) mbar_wait(&empty[s], ((k / stages) - 1) & 1);
+                const long long e = base + ch * kBulkChunk;
+                const long long left = len_total - ch * kBulkChunk;
+                const uint32_t bytes = (uint32_t)(left < kBulkChunk ? left : kBulkChunk) * 4u;
+                mbar_arrive_expect_tx(&full[s], bytes * (uint32_t)nslots);
+                uint8_t* st = bsm + (size_t)s * stage_bytes;
+                int slot = 0;
+                for (int r = 0; r < c.world; ++r) {
+                    if (r == c.rank) continue;
+                    bulk_load_1d(st + slot * kBulkChunkBytes, c.g[r] + e, bytes, &full[s]);
+                    ++slot;
+                }
+                bulk_load_1d(st + (slot++) * kBulkChunkBytes, c.g[c.rank] + e, bytes, &full[s]);
+                bulk_load_1d(st + (slot++) * kBulkChunkBytes, c.p[c.rank] + e, bytes, &full[s]);
+                if (kAdam) {
+                    bulk_load_1d(st + (slot++) * kBulkChunkBytes, m + e, bytes, &full[s]);
+                    bulk_load_1d(st + (slot++) * kBulkChunkBytes, v + e, bytes, &full[s]);
+                }
+            }
+        }
+    } else {  // ---------------- consumers ----------------
+        const float inv_world = 1.f / (float)c.world;
+        AdamCorr corr = {0.f, 0.f};
+        if (kAdam) corr = adam_corr(o);
+        int k = 0;
+        for (long long ch = blockIdx.x; ch < nchunks; ch += gridDim.x, ++k) {
+            const int s = k % stages;
+            mbar_wait(&full[s], (k / stages) & 1);
+            const long long e = base + ch * kBulkChunk;
+            const long long left = len_total - ch * kBulkChunk;
+            const int len = (int)(left < kBulkChunk ? left : kBulkChunk);
+            const float4* st4 = reinterpret_cast<const float4*>(bsm + (size_t)s * stage_bytes);
+            uint2* ob = reinterpret_cast<uint2*>(outbuf + (k % kBulkOutBufs) * kBulkOutBytes);
+            if (tid * 4 < len) {
+                float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int r = 0; r < c.world; ++r) {  // rank order, the local copy in its own position
+                    const int slot = r < c.rank ? r : (r == c.rank ? nrem : r - 1);
+                    const float4 t = st4[slot * (kBulkChunk / 4) + tid];
+                    acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+                }
+                acc.x *= inv_world; acc.y *= inv_world; acc.z *= inv_world; acc.w *= inv_world;
+                float4 p = st4[(nrem + 1) * (kBulkChunk / 4) + tid];
+                float4 mm = make_float4(0.f, 0.f, 0.f, 0.f), vv = mm;
+                if (kAdam) {
+                    mm = st4[(nrem + 2) * (kBulkChunk / 4) + tid];
+                    vv = st4[(nrem + 3) * (kBulkChunk / 4) + tid];
+                }
+                p = update4(p, acc, mm, vv, o, corr);
+                const long long ee = e + tid * 4;
+                *reinterpret_cast<float4*>(c.p[c.rank] + ee) = p;
+                if (kAdam) {
+                    *reinterpret_cast<float4*>(m + ee) = mm;
+                    *reinterpret_cast<float4*>(v + ee) = vv;
+                }
+                const uint2 pb = pack4_bf16(p);
+                if (kBulkStore) {
+                    ob[tid] = pb;
+                } else {
+                    for (int r = 0; r < c.world; ++r) *reinterpret_cast<uint2*>(c.w16[r] + ee) = pb;
+                }
+                if (push_master) {
+                    for (int r = 0; r < c.world; ++r)
+                        if (r != c.rank) *reinterpret_cast<float4*>(c.p[r] + ee) = p;
+                }
+            }
+            __syncwarp();
+            if ((tid & 31) == 0) mbar_arrive(&empty[s]);  // this warp is done reading stage s
+            if (kBulkStore) {
+                fence_proxy_async_smem();                 // my tile writes -> visible to the TMA engine
+                named_bar_sync(1, kBulkConsumers);
+                if (tid == 0) {
+                    for (int r = 0; r < c.world; ++r) bulk_store_1d(c.w16[r] + e, ob, (uint32_t)len * 2u);
+                    tma_store_commit();
+                    // the tile written two chunks from now was last read by the group before this one
+                    tma_store_wait_read<1>();
+                }
+            }
+        }
+        if (kBulkStore && tid == 0) {
+            tma_store_wait_all<0>();   // every weight store has been performed ...
+            fence_proxy_async_all();   // ... and is ordered before the release of the closing barrier
+        }
+    }
+    cross_barrier(c, 1, epoch);  // peers are done reading my gradients; my weights have landed everywhere
+    finish_epoch(c, epoch);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
 // NVLS variant (NVSwitch multicast objects): the reduce-scatter half is ONE multimem.ld_reduce per 16 bytes — the
 // switch adds the N copies and returns the sum, so a GPU receives n/N instead of (N-1)n/N bytes — and the all-gather
 // half is ONE multimem.st per 16 bytes that the switch fans out to every GPU.  Same two-shot ownership as above, so
-// the optimizer still runs once per element and every rank ends up with the same bits.
+// the optimizer still runs once per element and every rank ends up with the same bits.  Eight ld_reduce (4 x 32 bytes)
+// are in flight per thread before the first result is consumed: an in-switch reduction has a longer round trip than
+// a peer load, and with two in flight (round 1) the kernel was latency-bound.
 // ---------------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ float4 mc_ld_reduce_f4(const float* mc) {
     float4 v;
@@ -225,168 +378,97 @@ __device__ __forceinline__ void mc_st_f4(void* mc, float4 v) {
                  : "memory");
 }
 
+constexpr int kNvlsUnroll = 4;
+
 // `start`, `n` multiples of 8 elements (32 bytes of fp32 / 16 bytes of bf16 per thread-trip).
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 1)
 allreduce_nvls_kernel(Peers c, long long start, long long n, OptimSpec o, float* __restrict__ m,
-                      float* __restrict__ v, float* __restrict__ out, int push_master) {
+                      float* __restrict__ v, int push_master) {
     const uint32_t epoch = c.counter[0] + 1;
     cross_barrier(c, 0, epoch);
     const float inv_world = 1.f / (float)c.world;
     AdamCorr corr = {0.f, 0.f};
     if (o.kind == 2) corr = adam_corr(o);
-    const long long per = (n / 8 + c.world - 1) / c.world * 8;
-    long long lo = per * c.rank;
-    if (lo > n) lo = n;
-    const long long hi = lo + per < n ? lo + per : n;
+    long long lo, hi;
+    owned_range(n, 8, c.world, c.rank, lo, hi);
     const long long nvec = (hi - lo) / 8;
     const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
-        const long long e = start + lo + i * 8;
-        float4 a[2];
-        a[0] = mc_ld_reduce_f4(c.mc_g + e);
-        a[1] = mc_ld_reduce_f4(c.mc_g + e + 4);
-        float4 pw[2];
+    for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < nvec; i0 += kNvlsUnroll * stride) {
+        float4 a[kNvlsUnroll][2];
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            float4 acc = a[h];
-            acc.x *= inv_world; acc.y *= inv_world; acc.z *= inv_world; acc.w *= inv_world;
-            const long long eh = e + 4 * h;
-            if (o.kind == 0) {
-                pw[h] = acc;
-                continue;
+        for (int u = 0; u < kNvlsUnroll; ++u) {
+            const long long i = i0 + u * stride;
+            if (i < nvec) {
+                const long long e = start + lo + i * 8;
+                a[u][0] = mc_ld_reduce_f4(c.mc_g + e);
+                a[u][1] = mc_ld_reduce_f4(c.mc_g + e + 4);
             }
-            float4 p = *reinterpret_cast<const float4*>(c.p[c.rank] + eh);
-            if (o.kind == 2) {
-                float4 mm = *reinterpret_cast<const float4*>(m + eh);
-                float4 vv = *reinterpret_cast<const float4*>(v + eh);
-                p.x = adam_update(p.x, acc.x, mm.x, vv.x, o, corr);
-                p.y = adam_update(p.y, acc.y, mm.y, vv.y, o, corr);
-                p.z = adam_update(p.z, acc.z, mm.z, vv.z, o, corr);
-                p.w = adam_update(p.w, acc.w, mm.w, vv.w, o, corr);
-                *reinterpret_cast<float4*>(m + eh) = mm;
-                *reinterpret_cast<float4*>(v + eh) = vv;
+        }
+#pragma unroll
+        for (int u = 0; u < kNvlsUnroll; ++u) {
+            const long long i = i0 + u * stride;
+            if (i >= nvec) continue;
+            const long long e = start + lo + i * 8;
+            float4 pw[2];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                float4 acc = a[u][h];
+                acc.x *= inv_world; acc.y *= inv_world; acc.z *= inv_world; acc.w *= inv_world;
+                const long long eh = e + 4 * h;
+                float4 p = *reinterpret_cast<const float4*>(c.p[c.rank] + eh);
+                float4 mm = make_float4(0.f, 0.f, 0.f, 0.f), vv = mm;
+                if (o.kind == 2) {
+                    mm = *reinterpret_cast<const float4*>(m + eh);
+                    vv = *reinterpret_cast<const float4*>(v + eh);
+                }
+                p = update4(p, acc, mm, vv, o, corr);
+                if (o.kind == 2) {
+                    *reinterpret_cast<float4*>(m + eh) = mm;
+                    *reinterpret_cast<float4*>(v + eh) = vv;
+                }
+                pw[h] = p;
+            }
+            if (push_master) {
+                mc_st_f4(c.mc_p + e, pw[0]);
+                mc_st_f4(c.mc_p + e + 4, pw[1]);
             } else {
-                p.x = sgd_update(p.x, acc.x, o);
-                p.y = sgd_update(p.y, acc.y, o);
-                p.z = sgd_update(p.z, acc.z, o);
-                p.w = sgd_update(p.w, acc.w, o);
+                *reinterpret_cast<float4*>(c.p[c.rank] + e) = pw[0];
+                *reinterpret_cast<float4*>(c.p[c.rank] + e + 4) = pw[1];
             }
-            pw[h] = p;
+            const uint2 b0 = pack4_bf16(pw[0]), b1 = pack4_bf16(pw[1]);
+            mc_st_f4(c.mc_w16 + e, make_float4(__uint_as_float(b0.x), __uint_as_float(b0.y), __uint_as_float(b1.x),
+                                               __uint_as_float(b1.y)));
         }
-        if (o.kind == 0) {  // plain all-reduce: every rank needs the mean -> multicast it into everyone's `out`?  `out`
-            // is a private buffer, so the owner writes its slice locally and the caller all-gathers; not used by the
-            // engine (kind 0 goes through the one-shot P2P kernel).
-            *reinterpret_cast<float4*>(out + e) = pw[0];
-            *reinterpret_cast<float4*>(out + e + 4) = pw[1];
-            continue;
-        }
-        if (push_master) {
-            mc_st_f4(c.mc_p + e, pw[0]);
-            mc_st_f4(c.mc_p + e + 4, pw[1]);
-        } else {
-            *reinterpret_cast<float4*>(c.p[c.rank] + e) = pw[0];
-            *reinterpret_cast<float4*>(c.p[c.rank] + e + 4) = pw[1];
-        }
-        const uint2 b0 = pack4_bf16(pw[0]), b1 = pack4_bf16(pw[1]);
-        mc_st_f4(c.mc_w16 + e, make_float4(__uint_as_float(b0.x), __uint_as_float(b0.y), __uint_as_float(b1.x),
-                                           __uint_as_float(b1.y)));
     }
     cross_barrier(c, 1, epoch);
     finish_epoch(c, epoch);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// Push variant of the two-shot update.  Measured on B200: peer STORES run at NVLink line rate (~770 GB/s) while the
-// load-based pull above tops out near 320 GB/s, so here the reduce-scatter half is done with stores: every rank writes
-// the slices it does not own into their owners' staging buffers, one barrier, then each owner sums its own slice and
-// the N-1 staged copies from LOCAL memory in rank order (same bits everywhere), runs the optimizer and pushes the new
-// weights.  No opening barrier is needed: a staging region is only rewritten after the closing barrier of the previous
-// call that used it.  Staging region of source r in owner s for bucket [start, start+n): start + j*per, j = r - (r>s).
+// float64 sum over ranks (one-shot): out[i] = sum_r buf[r][i] in rank order, identical bits on every rank.  Used by the
+// MLlib-style L-BFGS trainer, whose loss / gradient vector must keep float64 accuracy (spark/ml.py).  n is even.
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads)
-allreduce_push_kernel(Peers c, long long start, long long n, OptimSpec o, float* __restrict__ m,
-                      float* __restrict__ v, int push_master, int scattered) {
+struct F64Peers {
+    const double* buf[kMaxRanks];
+};
+
+__global__ void __launch_bounds__(256)
+allreduce_sum_f64_kernel(Peers c, F64Peers b, long long n, double* __restrict__ out) {
     const uint32_t epoch = c.counter[0] + 1;
-    const float inv_world = 1.f / (float)c.world;
-    AdamCorr corr = {0.f, 0.f};
-    if (o.kind == 2) corr = adam_corr(o);
-    const long long per = (n / 4 + c.world - 1) / c.world * 4;   // slice length (elements, multiple of 4)
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    const long long tid0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    const float* g_local = c.g[c.rank];
-
-    // phase 1: scatter my gradient slices to their owners (remote 16-byte stores) - unless the kernels that produced
-    // the gradients already did it while storing them (`scattered`: b200ml_scatter in the weight-gradient GEMMs)
-#pragma unroll 1
-    for (int s = 0; s < c.world; ++s) {
-        if (scattered) break;
-        if (s == c.rank) continue;
-        const long long lo = per * s;
-        if (lo >= n) break;
-        const long long len = (lo + per < n ? per : n - lo) / 4;
-        const int j = c.rank - (c.rank > s ? 1 : 0);
-        float* dst = c.stage[s] + start + (long long)j * per;
-        const float* src = g_local + start + lo;
-        for (long long i = tid0; i < len; i += 2 * stride) {
-            const float4 a = *reinterpret_cast<const float4*>(src + i * 4);
-            const bool two = i + stride < len;
-            float4 b = a;
-            if (two) b = *reinterpret_cast<const float4*>(src + (i + stride) * 4);
-            *reinterpret_cast<float4*>(dst + i * 4) = a;
-            if (two) *reinterpret_cast<float4*>(dst + (i + stride) * 4) = b;
-        }
-    }
-    cross_barrier(c, 0, epoch);  // every slice destined to me has landed
-
-    // phase 2: reduce my slice from local memory, update, push the new weights
-    long long lo = per * c.rank;
-    if (lo > n) lo = n;
-    const long long hi = lo + per < n ? lo + per : n;
-    const long long nvec = (hi - lo) / 4;
-    const float* st = c.stage[c.rank] + start;
-    for (long long i = tid0; i < nvec; i += stride) {
-        const long long e = start + lo + i * 4;
-        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    cross_barrier(c, 0, epoch);
+    const long long nvec = n / 2;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long long)gridDim.x * blockDim.x) {
+        double2 t[kMaxRanks];
 #pragma unroll
-        for (int r = 0; r < kMaxRanks; ++r) {
-            if (r < c.world) {
-                float4 t;
-                if (r == c.rank) {
-                    t = *reinterpret_cast<const float4*>(g_local + e);
-                } else {
-                    const int j = r - (r > c.rank ? 1 : 0);
-                    t = __ldcg(reinterpret_cast<const float4*>(st + (long long)j * per + i * 4));  // written by a peer
-                }
-                acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
-            }
-        }
-        acc.x *= inv_world; acc.y *= inv_world; acc.z *= inv_world; acc.w *= inv_world;
-        float4 p = *reinterpret_cast<const float4*>(c.p[c.rank] + e);
-        if (o.kind == 2) {
-            float4 mm = *reinterpret_cast<const float4*>(m + e);
-            float4 vv = *reinterpret_cast<const float4*>(v + e);
-            p.x = adam_update(p.x, acc.x, mm.x, vv.x, o, corr);
-            p.y = adam_update(p.y, acc.y, mm.y, vv.y, o, corr);
-            p.z = adam_update(p.z, acc.z, mm.z, vv.z, o, corr);
-            p.w = adam_update(p.w, acc.w, mm.w, vv.w, o, corr);
-            *reinterpret_cast<float4*>(m + e) = mm;
-            *reinterpret_cast<float4*>(v + e) = vv;
-        } else {
-            p.x = sgd_update(p.x, acc.x, o);
-            p.y = sgd_update(p.y, acc.y, o);
-            p.z = sgd_update(p.z, acc.z, o);
-            p.w = sgd_update(p.w, acc.w, o);
-        }
-        const uint2 pb = pack4_bf16(p);
+        for (int r = 0; r < kMaxRanks; ++r)
+            if (r < c.world) t[r] = __ldcg(reinterpret_cast<const double2*>(b.buf[r]) + i);
+        double2 a = make_double2(0.0, 0.0);
 #pragma unroll
-        for (int r = 0; r < kMaxRanks; ++r) {
-            if (r < c.world) {
-                if (push_master || r == c.rank) *reinterpret_cast<float4*>(c.p[r] + e) = p;
-                *reinterpret_cast<uint2*>(c.w16[r] + e) = pb;
-            }
-        }
+        for (int r = 0; r < kMaxRanks; ++r)
+            if (r < c.world) { a.x += t[r].x; a.y += t[r].y; }
+        reinterpret_cast<double2*>(out)[i] = a;
     }
-    cross_barrier(c, 1, epoch);  // weights have landed everywhere; staging regions are free again
+    cross_barrier(c, 1, epoch);
     finish_epoch(c, epoch);
 }
 
@@ -425,17 +507,16 @@ int b200ml_ipc_close(void* ptr) {
     return 0;
 }
 
-int b200ml_allreduce_update(const b200ml_comm* cm, long long start, long long n, int algo, int kind, float lr,
-                            float beta1, float beta2, float eps, float weight_decay, const int* step_dev, float* m,
-                            float* v, float* out, int push_master, int max_blocks, cudaStream_t stream) {
-    using namespace b200;
-    using namespace b200::comm;
+}  // extern "C"
+
+namespace {
+
+using namespace b200;
+using namespace b200::comm;
+
+int fill_peers(const b200ml_comm* cm, Peers& c) {
     B200_REQUIRE(cm && cm->world >= 1 && cm->world <= kMaxRanks && cm->rank >= 0 && cm->rank < cm->world,
                  "allreduce: bad communicator");
-    B200_REQUIRE(start % 4 == 0 && n % 4 == 0 && n > 0, "allreduce: start/n must be positive multiples of 4");
-    B200_REQUIRE(kind == 0 ? out != nullptr : true, "allreduce: kind 0 needs an output buffer");
-    B200_REQUIRE(kind != 2 || (m && v), "allreduce: Adam needs m and v");
-    Peers c;
     c.world = cm->world;
     c.rank = cm->rank;
     for (int r = 0; r < kMaxRanks; ++r) {
@@ -445,42 +526,121 @@ int b200ml_allreduce_update(const b200ml_comm* cm, long long start, long long n,
         c.sig[r] = r < cm->world ? cm->signals[r] : nullptr;
     }
     c.counter = cm->counter;
-    for (int r = 0; r < kMaxRanks; ++r) c.stage[r] = r < cm->world ? cm->stage[r] : nullptr;
     c.mc_g = cm->mc_grads;
     c.mc_p = cm->mc_params;
     c.mc_w16 = reinterpret_cast<__nv_bfloat16*>(cm->mc_w16);
-    OptimSpec o{kind, lr, beta1, beta2, eps, weight_decay, step_dev};
-    // two-shot pays two NVLink round trips but moves (N-1)/N of the bytes once; one-shot moves (N-1)x the bytes.
-    bool two = algo == 2 || (algo == 0 && kind != 0 && n * 4 > (512 << 10));
-    if (kind == 0) two = false;
-    const long long work = two ? (n / cm->world + 3) / 4 : n / 4;
-    // B200ML_AR_SLIM=1: the co-resident 128-thread variant, two CTAs per SM.  Default off: measured at 2 GPUs on the
-    // translator step it LOSES (1.84 ms vs 1.67 ms per step) - one float4 per thread keeps too few bytes in flight.
-    static const bool slim = [] { const char* e = getenv("B200ML_AR_SLIM"); return e && e[0] == '1'; }();
-    const int threads = slim ? 128 : kThreads;
-    long long blocks = (work + threads * 8 - 1) / (threads * 8);
-    int cap = max_blocks > 0 ? max_blocks : (slim ? 2 * sm_count() : 96);
-    if (cap > kMaxBlocks) cap = kMaxBlocks;
+    return 0;
+}
+
+// Every CTA of a launch must be resident at once (CTA i spins on CTA i of the peers): clamp to what fits.
+template <typename K>
+int resident_cap(K kernel, int threads, size_t smem) {
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem) != cudaSuccess || per_sm < 1)
+        per_sm = 1;
+    long long cap = (long long)per_sm * sm_count();
+    return (int)(cap > kMaxBlocks ? kMaxBlocks : cap);
+}
+
+template <bool kAdam, bool kBulkStore>
+int launch_bulk(const Peers& c, long long start, long long n, const OptimSpec& o, float* m, float* v, int push_master,
+                int max_blocks, cudaStream_t stream) {
+    const int nslots = c.world - 1 + (kAdam ? 4 : 2);
+    const size_t stage_bytes = (size_t)nslots * kBulkChunkBytes;
+    const size_t fixed = (size_t)kBulkOutBufs * kBulkOutBytes + 2 * kBulkMaxStages * sizeof(uint64_t);
+    int stages = (int)((kBulkSmemBudget - fixed) / stage_bytes);
+    if (stages > kBulkMaxStages) stages = kBulkMaxStages;
+    B200_REQUIRE(stages >= 2, "allreduce: bulk ring does not fit (world %d)", c.world);
+    const size_t smem = stages * stage_bytes + fixed;
+    auto kernel = allreduce_bulk_kernel<kAdam, kBulkStore>;
+    static bool attr = false;   // one flag per template instance
+    if (!attr) {
+        B200_CHECK_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBulkSmemBudget));
+        attr = true;
+    }
+    const long long per = (n / 8 + c.world - 1) / c.world * 8;
+    long long blocks = (per + kBulkChunk - 1) / kBulkChunk;  // one chunk per CTA at least
+    // default CTA count: at 2 ranks the kernel is bound by its LOCAL optimizer traffic (30 B/element over half the
+    // bucket) and wants most of the chip; from 4 ranks on it is NVLink-bound and a few dozen rings saturate the links
+    int cap = max_blocks > 0 ? max_blocks : (c.world <= 2 ? 128 : (c.world <= 4 ? 64 : 40));
+    const int res = resident_cap(kernel, kBulkThreads, smem);
+    if (cap > res) cap = res;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-    const bool nvls = (algo == 3 || (algo == 0 && two)) && kind != 0 && c.mc_g && c.mc_w16 && (c.mc_p || !push_master) &&
-                      start % 8 == 0 && n % 8 == 0;
-    B200_REQUIRE(algo != 3 || nvls, "allreduce: NVLS requested but multicast addresses / 8-element alignment missing");
-    const bool push = (algo == 4 || algo == 5 || (algo == 0 && two)) && kind != 0 && c.stage[0] != nullptr && cm->world > 1;
-    B200_REQUIRE((algo != 4 && algo != 5) || push,
-                 "allreduce: push variant requested but no staging buffers were registered");
-    if (push && algo != 3)
-        allreduce_push_kernel<<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, push_master, algo == 5);
-    else if (nvls)
-        allreduce_nvls_kernel<<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, out, push_master);
-    else if (two && slim)
-        allreduce_update_kernel<true, true><<<(int)blocks, 128, 0, stream>>>(c, start, n, o, m, v, out, push_master);
-    else if (two)
-        allreduce_update_kernel<true, false><<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, out, push_master);
-    else if (slim)
-        allreduce_update_kernel<false, true><<<(int)blocks, 128, 0, stream>>>(c, start, n, o, m, v, out, push_master);
+    kernel<<<(int)blocks, kBulkThreads, smem, stream>>>(c, start, n, o, m, v, push_master, stages);
+    B200_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200ml_allreduce_update(const b200ml_comm* cm, long long start, long long n, int algo, int kind, float lr,
+                            float beta1, float beta2, float eps, float weight_decay, const int* step_dev, float* m,
+                            float* v, float* out, int push_master, int max_blocks, cudaStream_t stream) {
+    Peers c;
+    if (fill_peers(cm, c)) return -1;
+    B200_REQUIRE(start % 4 == 0 && n % 4 == 0 && n > 0, "allreduce: start/n must be positive multiples of 4");
+    B200_REQUIRE(kind == 0 ? out != nullptr : true, "allreduce: kind 0 needs an output buffer");
+    B200_REQUIRE(kind != 2 || (m && v), "allreduce: Adam needs m and v");
+    B200_REQUIRE(algo >= 0 && algo <= 5, "allreduce: unknown algo %d", algo);
+    OptimSpec o{kind, lr, beta1, beta2, eps, weight_decay, step_dev};
+    const bool al8 = start % 8 == 0 && n % 8 == 0;
+    // two-shot pays two NVLink round trips but moves (N-1)/N of the bytes once; one-shot moves (N-1)x the bytes.
+    bool two = algo >= 2 || (algo == 0 && n * 4 > (512 << 10));
+    if (kind == 0 || cm->world == 1) two = false;
+    const bool have_mc = c.mc_g && c.mc_w16 && (c.mc_p || !push_master);
+    B200_REQUIRE(algo != 3 || (have_mc && al8 && kind != 0),
+                 "allreduce: NVLS requested but multicast addresses / 8-element alignment missing");
+    B200_REQUIRE((algo != 4 && algo != 5) || (al8 && kind != 0),
+                 "allreduce: the bulk variant needs start and n to be multiples of 8 and an optimizer kind");
+    if (two && (algo == 3 || (algo == 0 && have_mc && al8))) {
+        const long long work = (n / cm->world + 7) / 8;
+        long long blocks = (work + kThreads * kNvlsUnroll - 1) / (kThreads * kNvlsUnroll);
+        int cap = max_blocks > 0 ? max_blocks : 64;
+        const int res = resident_cap(allreduce_nvls_kernel, kThreads, 0);
+        if (cap > res) cap = res;
+        if (blocks > cap) blocks = cap;
+        if (blocks < 1) blocks = 1;
+        allreduce_nvls_kernel<<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, push_master);
+        B200_CHECK_CUDA(cudaGetLastError());
+        return 0;
+    }
+    if (two && al8 && algo != 2) {  // bulk-async (algo 0 / 4; 5 = the same with per-thread weight stores)
+        if (kind == 2)
+            return algo == 5 ? launch_bulk<true, false>(c, start, n, o, m, v, push_master, max_blocks, stream)
+                             : launch_bulk<true, true>(c, start, n, o, m, v, push_master, max_blocks, stream);
+        return algo == 5 ? launch_bulk<false, false>(c, start, n, o, m, v, push_master, max_blocks, stream)
+                         : launch_bulk<false, true>(c, start, n, o, m, v, push_master, max_blocks, stream);
+    }
+    const int gran = al8 ? 8 : 4;
+    const long long work = two ? (n / cm->world + 3) / 4 : n / 4;
+    long long blocks = (work + kThreads * 8 - 1) / (kThreads * 8);
+    int cap = max_blocks > 0 ? max_blocks : 96;
+    const int res = two ? resident_cap(allreduce_update_kernel<true>, kThreads, 0)
+                        : resident_cap(allreduce_update_kernel<false>, kThreads, 0);
+    if (cap > res) cap = res;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    if (two)
+        allreduce_update_kernel<true><<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, out, push_master, gran);
     else
-        allreduce_update_kernel<false, false><<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, out, push_master);
+        allreduce_update_kernel<false><<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, out, push_master, gran);
+    B200_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int b200ml_allreduce_sum_f64(const b200ml_comm* cm, const double* const* bufs, long long n, double* out,
+                             cudaStream_t stream) {
+    Peers c;
+    if (fill_peers(cm, c)) return -1;
+    B200_REQUIRE(bufs && out && n > 0 && n % 2 == 0, "allreduce_sum_f64: n must be a positive even count");
+    F64Peers b;
+    for (int r = 0; r < kMaxRanks; ++r) b.buf[r] = r < cm->world ? bufs[r] : nullptr;
+    long long blocks = (n / 2 + 255) / 256;
+    if (blocks > 64) blocks = 64;
+    allreduce_sum_f64_kernel<<<(int)blocks, 256, 0, stream>>>(c, b, n, out);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
 }

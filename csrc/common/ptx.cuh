@@ -89,6 +89,14 @@ B200_DEVICE void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, 
                  "l"(reinterpret_cast<uint64_t>(gsrc)), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
+// 1-D bulk copy shared -> global (16-byte aligned, size a multiple of 16), completion through the bulk async group
+B200_DEVICE void bulk_store_1d(void* gdst, const void* smem_src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(reinterpret_cast<uint64_t>(gdst)),
+                 "r"(smem_u32(smem_src)), "r"(bytes)
+                 : "memory");
+}
+// orders this thread's earlier generic-proxy accesses (any state space) with its later async-proxy (TMA) operations
+B200_DEVICE void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
 // smem -> global tile store (bulk async group completion); OOB parts of the box are clipped by the hardware
 B200_DEVICE void tma_store_2d(const CUtensorMap* map, const void* smem_src, int32_t c0, int32_t c1) {
     asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(

@@ -34,26 +34,6 @@ constexpr int kEpiWarps = 8;
 constexpr int kPairTileCost = 250;  // relative cost of one 256 x 256 pair tile per wave (a 128 x 256 tile: 288)
 constexpr int kNumThreads = 64 + kEpiWarps * 32;  // 10 warps
 
-// device copy of b200ml_scatter (by value in the kernel parameters); world == 0: off
-struct Scatter {
-    int world, rank;
-    long long per, n;
-    const float* bucket_base;
-    float* stage_base[8];
-};
-// Mirror a just-stored fp32 vector of `kElems` consecutive elements at local address `p` into its owner's staging slice.
-// Slice boundaries are multiples of 4 elements and `p` is kElems-aligned, so a vector never straddles two owners.
-template <int kElems, typename V>
-__device__ __forceinline__ void scatter_store(const Scatter& sc, const float* p, V v) {
-    if (sc.world == 0) return;
-    const long long e = p - sc.bucket_base;
-    if (e < 0 || e >= sc.n) return;
-    const int s = (int)(e / sc.per);
-    if (s == sc.rank) return;
-    const int j = sc.rank - (sc.rank > s ? 1 : 0);
-    *reinterpret_cast<V*>(sc.stage_base[s] + (long long)j * sc.per + (e - (long long)s * sc.per)) = v;
-}
-
 struct Epilogue {
     void* C;
     long long ldc;
@@ -73,7 +53,6 @@ struct Epilogue {
     float* splitk_ws;        // != nullptr: write raw fp32 partial tiles to ws[split][M][N] instead of C
     int tma_store;           // bf16 C through smem staging + cp.async.bulk.tensor stores (needs tmap_c)
     int debug;               // B200ML_GEMM_DEBUG (timing experiments only, results are garbage): 1 = no TMA loads, 2 = no MMAs, 4 = no TMA stores
-    Scatter scatter;         // fp32 direct-store path only
     int cluster_splits;      // > 1: split-K over the CTAs of a cluster, partial tiles reduced through DSMEM (one tile per CTA)
 };
 
@@ -474,7 +453,6 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                                     o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
                                 }
                                 *reinterpret_cast<float4*>(out + j) = o;
-                                scatter_store<4>(ep.scatter, out + j, o);
                             }
                         } else {
 #pragma unroll
@@ -482,7 +460,6 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                                 if (col0 + j < N) {
                                     const float o = ep.accumulate ? out[j] + v[j] : v[j];
                                     out[j] = o;
-                                    scatter_store<1>(ep.scatter, out + j, o);
                                 }
                         }
                     } else {
@@ -542,13 +519,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                                 o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
                             }
                             *reinterpret_cast<float4*>(out) = o;
-                            scatter_store<4>(ep.scatter, out, o);
                         } else {
                             for (int j = 0; j < 4; ++j)
                                 if (gcol + j < N) {
                                     const float o = ep.accumulate ? out[j] + vals[j] : vals[j];
                                     out[j] = o;
-                                    scatter_store<1>(ep.scatter, out + j, o);
                                 }
                         }
                     } else {
@@ -585,11 +560,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 }
 
 // Second stage of split-K: C = alpha * sum_s ws[s]  (fixed order), fp32 or bf16 store, optional accumulate.
-// vec4 != 0 (N, ldc multiples of 4, fp32 C): one float4 per thread-trip, and the optional scatter to the owner's staging.
+// vec4 != 0 (N, ldc multiples of 4, fp32 C): one float4 per thread-trip.
 __global__ void __launch_bounds__(256)
 splitk_reduce_kernel(const float* __restrict__ ws, int splits, long long mn, int N, void* __restrict__ Cp,
                      long long ldc, int c_fp32, int accumulate, float alpha, const float* __restrict__ alpha_dev,
-                     int vec4, Scatter sc) {
+                     int vec4) {
     b200::pdl_trigger();
     b200::pdl_wait();
     const float a = alpha * (alpha_dev ? *alpha_dev : 1.f);
@@ -611,7 +586,6 @@ splitk_reduce_kernel(const float* __restrict__ ws, int splits, long long mn, int
                 s.x += old.x; s.y += old.y; s.z += old.z; s.w += old.w;
             }
             *reinterpret_cast<float4*>(o) = s;
-            scatter_store<4>(sc, o, s);
         }
         return;
     }
@@ -624,7 +598,6 @@ splitk_reduce_kernel(const float* __restrict__ ws, int splits, long long mn, int
             float* o = reinterpret_cast<float*>(Cp) + row * ldc + col;
             const float r = accumulate ? *o + s : s;
             *o = r;
-            scatter_store<1>(sc, o, r);
         } else {
             reinterpret_cast<__nv_bfloat16*>(Cp)[row * ldc + col] = __float2bfloat16(s);
         }
@@ -687,7 +660,6 @@ gemm_simt_kernel(const __nv_bfloat16* __restrict__ A, long long lda, int a_mn, c
         float* out = reinterpret_cast<float*>(ep.C) + (long long)row * ep.ldc + col;
         const float r = ep.accumulate ? *out + v : v;
         *out = r;
-        scatter_store<1>(ep.scatter, out, r);
     } else {
         reinterpret_cast<__nv_bfloat16*>(ep.C)[(long long)row * ep.ldc + col] = __float2bfloat16(v);
     }
@@ -746,12 +718,12 @@ static int launch(const b200ml_gemm_args* g, Epilogue ep, int splits, cudaStream
         const long long mn = (long long)g->M * g->N;
         long long blocks = (mn + 255) / 256;
         if (blocks > 4LL * sm_count()) blocks = 4LL * sm_count();
-        // float4 trips only where they pay: with the scatter option (16-byte remote stores) or for big outputs; a small
+        // float4 trips only where they pay, for big outputs; a small
         // output is latency-bound and wants one element per thread (measured 512x512, 9 splits: 19 us scalar, 23 us vec4)
         const int vec4 = g->c_fp32 && g->N % 4 == 0 && g->ldc % 4 == 0 && (reinterpret_cast<uintptr_t>(g->C) & 15) == 0 &&
-                         (ep.scatter.world != 0 || mn >= (1LL << 21));
+                         mn >= (1LL << 21);
         b200::pdl(splitk_reduce_kernel, dim3((int)blocks), dim3(256), 0, stream)(ep.splitk_ws, splits, mn, g->N, g->C, g->ldc, g->c_fp32,
-                                                              g->accumulate, g->alpha, g->alpha_dev, vec4, ep.scatter);
+                                                              g->accumulate, g->alpha, g->alpha_dev, vec4);
         B200_CHECK_CUDA(cudaGetLastError());
     }
     return 0;
@@ -818,19 +790,7 @@ extern "C" int b200ml_gemm_bf16(const b200ml_gemm_args* g, cudaStream_t stream) 
     ep.rng = reinterpret_cast<const RngState*>(g->rng_state); ep.rng_site = g->rng_site;
     ep.splitk_ws = nullptr;
     ep.tma_store = 0;
-    ep.scatter.world = 0;
     ep.cluster_splits = 0;
-    if (g->scatter) {
-        B200_REQUIRE(g->c_fp32, "gemm: the scatter option needs an fp32 output");
-        B200_REQUIRE(g->scatter->world >= 2 && g->scatter->world <= 8 && g->scatter->per > 0 && g->scatter->per % 4 == 0,
-                     "gemm: bad scatter descriptor");
-        ep.scatter.world = g->scatter->world;
-        ep.scatter.rank = g->scatter->rank;
-        ep.scatter.per = g->scatter->per;
-        ep.scatter.n = g->scatter->n;
-        ep.scatter.bucket_base = g->scatter->bucket_base;
-        for (int r = 0; r < 8; ++r) ep.scatter.stage_base[r] = g->scatter->stage_base[r];
-    }
     static const int debug_flags = [] { const char* e = getenv("B200ML_GEMM_DEBUG"); return e ? atoi(e) : 0; }();
     ep.debug = debug_flags;
 
@@ -862,10 +822,9 @@ extern "C" int b200ml_gemm_bf16(const b200ml_gemm_args* g, cudaStream_t stream) 
             long long blocks = (mn + 255) / 256;
             if (blocks > 4LL * sm_count()) blocks = 4LL * sm_count();
             const int vec4 = g->c_fp32 && g->N % 4 == 0 && g->ldc % 4 == 0 && (reinterpret_cast<uintptr_t>(g->C) & 15) == 0 &&
-                             (ep.scatter.world != 0 || mn >= (1LL << 21));
+                             mn >= (1LL << 21);
             b200::pdl(splitk_reduce_kernel, dim3((int)blocks), dim3(256), 0, stream)(ep.splitk_ws, splits, mn, g->N, g->C, g->ldc,
-                                                                  g->c_fp32, g->accumulate, g->alpha, g->alpha_dev, vec4,
-                                                                  ep.scatter);
+                                                                  g->c_fp32, g->accumulate, g->alpha, g->alpha_dev, vec4);
             B200_CHECK_CUDA(cudaGetLastError());
         }
         return 0;

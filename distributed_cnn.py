@@ -18,6 +18,7 @@ from torch.utils.data import DataLoader, DistributedSampler  # noqa: E402
 
 from b200ml.models import FashionMNISTModel  # noqa: E402
 from b200ml.ops.loss import cross_entropy  # noqa: E402
+from b200ml.ops.metrics import argmax_accuracy  # noqa: E402
 from b200ml.parallel.engine import DataParallelEngine  # noqa: E402
 from b200ml.spark import SparkConf, SparkSession, TorchDistributor  # noqa: E402
 from b200ml.utils import script as S  # noqa: E402
@@ -70,18 +71,17 @@ def train_func():
 
 def eval_func(model, test_dataloader, device):
     model.eval()
-    total_test_loss, correct, count = 0.0, 0, 0
+    total_test_loss, correct, count = 0.0, None, 0
     with torch.no_grad():
         for data, target in test_dataloader:
             data, target = data.to(device), target.to(device)
             predictions = model(data)
-            predicted_classes = torch.argmax(torch.softmax(predictions, dim=1), dim=1)
+            predicted_classes, correct = argmax_accuracy(predictions, target, correct)   # device-side arg-max + count
             total_test_loss += nn.functional.cross_entropy(predictions.float(), target).item()
-            correct += int((predicted_classes == target).sum())
             count += len(target)
     print(f"total_test_loss is:{total_test_loss}")
     print(f"accuracy is :{accuracy_fn(predicted_classes, target)}")
-    print(f"full test-set accuracy is :{100.0 * correct / max(count, 1)}")
+    print(f"full test-set accuracy is :{100.0 * int(correct) / max(count, 1)}")
 
 
 if __name__ == "__main__":

@@ -17,6 +17,7 @@ from torch.utils.data import DataLoader, DistributedSampler  # noqa: E402
 
 from b200ml.models import LSTM  # noqa: E402
 from b200ml.ops.loss import cross_entropy  # noqa: E402
+from b200ml.ops.metrics import argmax_accuracy  # noqa: E402
 from b200ml.parallel.engine import DataParallelEngine  # noqa: E402
 from b200ml.spark import SparkConf, SparkSession, TorchDistributor  # noqa: E402
 from b200ml.utils import script as S  # noqa: E402
@@ -46,14 +47,14 @@ def train_func():
         DDP_model.zero_grad()
         loss.backward()
         DDP_model.step()
-        return (pred[:, -1, :].argmax(1) == labels).sum()
+        return argmax_accuracy(pred[:, -1, :], labels)[1]   # device-side arg-max + number of correct rows
 
     # batches are padded to their own longest text (<= 129 tokens); most hit the truncation cap, so a handful of
     # sequence lengths covers nearly every batch: each gets its own CUDA graph, rare lengths run eagerly
     train_step = DDP_model.graphed(one_step, max_graphs=16)
     timer = S.DeviceTimer(device).start()
     n_samples = 0
-    train_acc = torch.zeros((), device=device)
+    train_acc = torch.zeros(1, dtype=torch.int32, device=device)
     for epoch in range(n_epochs):
         sampler.set_epoch(epoch)
         for batch_idx, (labels, texts) in enumerate(loader):

@@ -20,6 +20,7 @@ from torch.utils.data import DataLoader, DistributedSampler, TensorDataset, rand
 from b200ml.data.libsvm import sample_multiclass_path  # noqa: E402
 from b200ml.models import Multilayer_perceptor  # noqa: E402
 from b200ml.ops.loss import cross_entropy  # noqa: E402
+from b200ml.ops.metrics import argmax_accuracy  # noqa: E402
 from b200ml.parallel.engine import DataParallelEngine  # noqa: E402
 from b200ml.spark import SparkConf, SparkSession, TorchDistributor  # noqa: E402
 from b200ml.utils import script as S  # noqa: E402
@@ -68,12 +69,12 @@ def train_func(features_tensor, target_tensor):
     S.finish_worker()
 
     multilayer_model.eval()
-    total_test_loss = 0
+    total_test_loss, correct = 0, None
     with torch.no_grad():
         for features, labels in test_loader:
             features, labels = features.to(device), labels.to(device)
             predictions = multilayer_model(features)
-            predicted_classes = torch.argmax(torch.softmax(predictions, dim=1), dim=1)
+            predicted_classes, correct = argmax_accuracy(predictions, labels, correct)   # device-side arg-max + count
             test_loss = nn.functional.cross_entropy(predictions.float(), labels)
             total_test_loss += test_loss.item()
     print("Test loss on last batch:", test_loss.item())

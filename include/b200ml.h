@@ -36,19 +36,6 @@ int b200ml_device_info(int* sm_count, int* cc_major, int* cc_minor, size_t* smem
  *   fp32 may accumulate into C).
  * ref: every nn.Linear + ReLU/Sigmoid/Dropout neighbour (transformer.py:71-72,107-117,177-179,272;
  *      distributed_multilayer_perceptron.py:47-53). */
-/* Optional "weight gradient -> reduce-scatter" fusion for data-parallel training: while the GEMM (or its split-K
- * second stage) stores an fp32 output vector into the local gradient buffer, it also stores it - over NVLink - into the
- * staging buffer of the rank that owns that slice of the bucket, so the all-reduce that follows (algo 5 of
- * b200ml_allreduce_update) starts with its scatter phase already done.  Layout as in the push all-reduce: the bucket
- * [bucket_base, bucket_base + n) is cut into `world` slices of `per` elements; source rank r's copy of owner s's slice
- * lives at stage_base[s] + j * per, j = r - (r > s). */
-typedef struct {
-    int world, rank;
-    long long per, n;
-    const float* bucket_base;   /* local gradient buffer + bucket start */
-    float* stage_base[8];       /* peers' staging buffers + bucket start (entry `rank` unused) */
-} b200ml_scatter;
-
 typedef struct {
     int M, N, K;
     const void* A; long long lda; int a_mn_major;
@@ -66,7 +53,6 @@ typedef struct {
     int split_k;     /* 0 = auto, 1 = never, n > 1 = request n K-splits (plain epilogue only; needs workspace) */
     void* workspace; size_t workspace_bytes; /* fp32 scratch for split-K partial tiles (optional) */
     int epilogue_direct; /* testing: 1 = register->global stores even where the TMA-store epilogue applies */
-    const b200ml_scatter* scatter; /* optional, fp32 C only: see b200ml_scatter */
 } b200ml_gemm_args;
 int b200ml_gemm_bf16(const b200ml_gemm_args* args, cudaStream_t stream);
 
@@ -213,9 +199,14 @@ int b200ml_dropout_bwd(const void* g, int g_fp32, float* dx, long long n, float 
  * weight (fp32), working weight (bf16) and signal-pad (2*320*8 uint32, zero-initialised) buffers as mapped in THIS
  * process; counter is a local zero-initialised uint32[2].  Elements [start, start+n) are summed over ranks in rank
  * order, divided by world, and (kind 1 SGD / 2 Adam) applied to the weights; kind 0 writes the mean to `out`.
- * algo: 0 auto, 1 one-shot, 2 two-shot (pull), 4 two-shot (push through the staging buffers; auto prefers it for large
- * buckets when staging is registered), 3 NVLS (multimem.ld_reduce / multimem.st; auto picks it for large buckets when
- * the multicast addresses are set).  Every rank must issue the same sequence of calls.
+ * algo: 0 auto, 1 one-shot, 2 two-shot with SM-issued peer loads, 3 two-shot over NVLS (multimem.ld_reduce /
+ * multimem.st; auto picks it for large buckets when the multicast addresses are set), 4 two-shot with the bulk-async
+ * (TMA) ring - what auto uses for buckets above 512 KB whose start / n are multiples of 8 -, 5 = 4 with per-thread
+ * weight stores instead of TMA stores.  In the two-shot variants rank r owns slice r of the bucket (8-element
+ * granularity when start and n are multiples of 8, else 4) and is the only rank that updates m / v for it.
+ * Every rank must issue the same sequence of calls, and CTA i of a launch waits for CTA i on every peer: a
+ * communicator may have only ONE of these kernels in flight at a time (use one stream); the launcher clamps the grid
+ * to the number of CTAs that are resident at once, so a launch can never wait for a CTA that is not scheduled.
  * ref: DDP bucket all-reduce + optimizer.step (distributed_cnn.py:156,181-183). */
 typedef struct {
     int world, rank;
@@ -224,7 +215,6 @@ typedef struct {
     void* w16[8];
     unsigned* signals[8];
     unsigned* counter;
-    float* stage[8];   /* optional staging buffers (one per rank, same size as grads) for the store-based "push" two-shot */
     float* mc_grads;   /* NVLS multicast addresses of the gradient / master / bf16 buffers, or NULL */
     float* mc_params;
     void* mc_w16;
@@ -234,11 +224,15 @@ int b200ml_comm_free(void* ptr);
 int b200ml_ipc_export(const void* ptr, unsigned char* handle64);
 int b200ml_ipc_import(const unsigned char* handle64, void** ptr);
 int b200ml_ipc_close(void* ptr);
-/* algo: 0 auto, 1 one-shot pull, 2 two-shot pull, 3 NVLS, 4 push through staging buffers, 5 = 4 with the scatter phase
- * already done by the producers of the gradients (b200ml_scatter). */
 int b200ml_allreduce_update(const b200ml_comm* cm, long long start, long long n, int algo, int kind, float lr,
                             float beta1, float beta2, float eps, float weight_decay, const int* step_dev, float* m,
                             float* v, float* out, int push_master, int max_blocks, cudaStream_t stream);
+
+/* out[i] = sum over ranks of bufs[r][i] (float64, rank order: identical bits on every rank); bufs[r] is rank r's
+ * buffer as mapped in this process, n even.  Same barrier protocol and constraints as b200ml_allreduce_update.
+ * ref: the treeAggregate of MLlib's distributed L-BFGS cost function (mllib_multilayer_perceptron_classifier.py:35-39). */
+int b200ml_allreduce_sum_f64(const b200ml_comm* cm, const double* const* bufs, long long n, double* out,
+                             cudaStream_t stream);
 
 /* ------------------------------------------------------------------------------------------------ K20 L-BFGS direction
  * ref: MultilayerPerceptronClassifier(solver='l-bfgs') (mllib_multilayer_perceptron_classifier.py:35), Breeze LBFGS.

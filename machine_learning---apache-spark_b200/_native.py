@@ -24,12 +24,6 @@ class NativeError(RuntimeError):
     pass
 
 
-class ScatterDesc(C.Structure):
-    """b200ml_scatter (include/b200ml.h): where the fp32 outputs of a weight-gradient GEMM are mirrored over NVLink."""
-    _fields_ = [("world", C.c_int), ("rank", C.c_int), ("per", C.c_longlong), ("n", C.c_longlong),
-                ("bucket_base", C.c_void_p), ("stage_base", C.c_void_p * 8)]
-
-
 class GemmArgs(C.Structure):
     _fields_ = [
         ("M", C.c_int), ("N", C.c_int), ("K", C.c_int),
@@ -48,7 +42,6 @@ class GemmArgs(C.Structure):
         ("split_k", C.c_int),
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
         ("epilogue_direct", C.c_int),
-        ("scatter", C.c_void_p),
     ]
 
 

@@ -105,8 +105,6 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     g.force_simt = int(force_simt)
     g.split_k = split_k
     g.epilogue_direct = int(epilogue_direct)
-    if _scatter_ctx[0] is not None and out.dtype == torch.float32:
-        g.scatter = C.addressof(_scatter_ctx[0])  # weight gradient of a scatter bucket: mirror it to the slice owners
     if split_k != 1 and bias is None and not act and not (aux is not None and aux_mode) and dropout_p <= 0:
         ws = workspace.get(f"gemm_splitk@{workspace.lane()}", SPLITK_WORKSPACE_BYTES, a.device)  # one per stream lane
         g.workspace, g.workspace_bytes = ws.data_ptr(), ws.numel()
@@ -182,10 +180,6 @@ class GradSideStream:
         self.keep.clear()
 
 
-# b200ml_scatter descriptor of the parameter whose gradient is being produced (set by deliver_grad around `compute`)
-_scatter_ctx: list = [None]
-
-
 def deliver_grad(param: torch.Tensor, compute, shape) -> torch.Tensor | None:
     """Produce a parameter gradient.  With a DP engine the gradient is written straight into the parameter's slot of
     the flat bucket (``param._b200_grad``) and the engine is told the slot is ready — autograd sees ``None``.
@@ -194,14 +188,10 @@ def deliver_grad(param: torch.Tensor, compute, shape) -> torch.Tensor | None:
     if slot is not None and slot.device == param.device:
         acc = bool(getattr(param, "_b200_grad_accumulate", False))
         side = getattr(param, "_b200_side", None)
-        _scatter_ctx[0] = getattr(param, "_b200_scatter", None)
-        try:
-            if side is not None and side.active and slot.is_cuda:
-                side.run(compute, slot.view(shape), acc)
-            else:
-                compute(slot.view(shape), acc)
-        finally:
-            _scatter_ctx[0] = None
+        if side is not None and side.active and slot.is_cuda:
+            side.run(compute, slot.view(shape), acc)
+        else:
+            compute(slot.view(shape), acc)
         ready = getattr(param, "_b200_ready", None)
         if ready is not None:
             ready()

@@ -24,7 +24,6 @@ SIGNAL_WORDS = 2 * 320 * 8
 class CommStruct(C.Structure):
     _fields_ = [("world", C.c_int), ("rank", C.c_int), ("grads", C.c_void_p * 8), ("params", C.c_void_p * 8),
                 ("w16", C.c_void_p * 8), ("signals", C.c_void_p * 8), ("counter", C.c_void_p),
-                ("stage", C.c_void_p * 8),
                 ("mc_grads", C.c_void_p), ("mc_params", C.c_void_p), ("mc_w16", C.c_void_p)]
 
 
@@ -126,27 +125,11 @@ class SymmMemAllocator:
             self.handles[name] = self._sm.rendezvous(t, group if group is not None else dist.group.WORLD)
 
 
-def use_staging() -> bool:
-    import os
-
-    # opt-in: on the 2-GPU measurements the store-based variant was not faster than the pull two-shot (227 vs 189 us at
-    # 116 MiB), and it costs one more flat-sized buffer per rank
-    return os.environ.get("B200ML_AR_PUSH", "0") == "1" or gemm_scatter()
-
-
-def gemm_scatter() -> bool:
-    """B200ML_GEMM_SCATTER=1: the weight-gradient GEMMs mirror their outputs into the slice owners' staging buffers over
-    NVLink (b200ml_scatter), so the all-reduce of those buckets starts with its reduce-scatter traffic already done."""
-    import os
-
-    return os.environ.get("B200ML_GEMM_SCATTER", "0") == "1"
-
-
 def make_allocator(device, group=None):
     """NVLS-capable symmetric memory when B200ML_NVLS != 0 and torch can provide it, else cudaMalloc + CUDA IPC."""
     import os
 
-    if os.environ.get("B200ML_NVLS", "0") == "1":  # opt-in: the P2P two-shot kernel measured faster at 2 and 8 GPUs
+    if os.environ.get("B200ML_NVLS", "0") == "1":  # opt-in (see profiles/allreduce_microbench.md for the comparison)
         try:
             alloc = SymmMemAllocator(device)
             probe = alloc("_probe", 1024, torch.float32)
@@ -180,12 +163,8 @@ class FusedAllReduce:
         self.alloc = allocator
         self.signals = SymmetricBuffer(SIGNAL_WORDS, torch.int32, dev)
         self.counter = torch.zeros(2, dtype=torch.int32, device=dev)
-        # staging for the store-based reduce-scatter (peer stores run at NVLink line rate, peer loads do not)
-        self.stage = SymmetricBuffer(flat.numel, torch.float32, dev) if use_staging() else None
         mine = {k: b.export() for k, b in allocator.buffers.items()}
         mine["signals"] = self.signals.export()
-        if self.stage is not None:
-            mine["stage"] = self.stage.export()
         gathered = [None] * self.world
         dist.all_gather_object(gathered, mine, group=group)
         self._imported = []
@@ -194,9 +173,6 @@ class FusedAllReduce:
         table = {"flat_g": self.cs.grads, "flat_p": self.cs.params, "flat_w16": self.cs.w16, "signals": self.cs.signals}
         local = {"flat_g": allocator.buffers["flat_g"].ptr, "flat_p": allocator.buffers["flat_p"].ptr,
                  "flat_w16": allocator.buffers["flat_w16"].ptr, "signals": self.signals.ptr}
-        if self.stage is not None:
-            table["stage"] = self.cs.stage
-            local["stage"] = self.stage.ptr
         for r in range(self.world):
             for key, arr in table.items():
                 if r == self.rank:
@@ -211,8 +187,8 @@ class FusedAllReduce:
                        torch.as_tensor(_RawCuda(self.cs.params[r], flat.numel, "<f4"), device=dev)
                        for r in range(self.world)]
         self.push_master = 1
-        self._scatter_descs = []
-        self.max_blocks = int(os.environ.get("B200ML_AR_BLOCKS", "0"))  # 0 = library default (96 CTAs)
+        self.max_blocks = int(os.environ.get("B200ML_AR_BLOCKS", "0"))  # 0 = library default (depends on world / algo)
+        self.default_algo = int(os.environ.get("B200ML_AR_ALGO", "0"))  # 0 auto; 2 / 4 / 5 force a two-shot transport
         torch.cuda.synchronize(dev)
         dist.barrier(group=group)  # nobody launches before every mapping exists
 
@@ -225,8 +201,6 @@ class FusedAllReduce:
         dev = flat.device
         self.alloc = allocator
         self.signals_t = allocator("signals", SIGNAL_WORDS, torch.int32)
-        if use_staging():
-            self.stage_t = allocator("stage", flat.numel, torch.float32)
         self.counter = torch.zeros(2, dtype=torch.int32, device=dev)
         allocator.rendezvous(group)
         h = allocator.handles
@@ -234,8 +208,6 @@ class FusedAllReduce:
         self.cs = CommStruct()
         self.cs.world, self.cs.rank = self.world, self.rank
         table = {"flat_g": self.cs.grads, "flat_p": self.cs.params, "flat_w16": self.cs.w16, "signals": self.cs.signals}
-        if "stage" in h:
-            table["stage"] = self.cs.stage
         for key, arr in table.items():
             ptrs = list(h[key].buffer_ptrs)
             off = int(getattr(h[key], "offset", 0) or 0)
@@ -254,34 +226,21 @@ class FusedAllReduce:
                        torch.as_tensor(_RawCuda(self.cs.params[r], flat.numel, "<f4"), device=dev)
                        for r in range(self.world)]
         self.push_master = 1
-        self._scatter_descs = []
         self.max_blocks = int(os.environ.get("B200ML_AR_BLOCKS", "0"))
+        self.default_algo = int(os.environ.get("B200ML_AR_ALGO", "0"))
         torch.cuda.synchronize(dev)
         dist.barrier(group=group)
 
     def allreduce_update(self, start, n, kind, lr, betas, eps, weight_decay, step_tensor, out=None, algo: int = 0):
         lib = _native.load()
         n4 = (n + 3) // 4 * 4  # slots are 64-element aligned, so rounding up stays inside the bucket
+        if algo == 0 and kind != 0 and n4 * 4 > (512 << 10):
+            algo = self.default_algo
         _native.check(lib.b200ml_allreduce_update(
             C.byref(self.cs), start, n4, algo, kind, lr, betas[0], betas[1], eps, weight_decay, step_tensor.data_ptr(),
             None if self.m is None else self.m.data_ptr(), None if self.v is None else self.v.data_ptr(),
             None if out is None else out.data_ptr(), self.push_master, self.max_blocks, _native.stream_ptr()),
             "allreduce_update")
-
-    def scatter_desc(self, start: int, n: int):
-        """b200ml_scatter for the bucket [start, start + n): same slice ownership as the two-shot / push kernels."""
-        if self.cs.stage[0] is None and self.cs.stage[1] is None:
-            return None
-        n4 = (n + 3) // 4 * 4
-        d = _native.ScatterDesc()
-        d.world, d.rank = self.world, self.rank
-        d.per = ((n4 // 4 + self.world - 1) // self.world) * 4
-        d.n = n4
-        d.bucket_base = self.flat.flat_g.data_ptr() + start * 4
-        for r in range(self.world):
-            d.stage_base[r] = (self.cs.stage[r] or 0) + start * 4
-        self._scatter_descs.append(d)  # keep alive: the GEMM reads it through a raw pointer
-        return d
 
     def owned_slice(self, start: int, n: int, sliced: bool | None = None, rank: int | None = None):
         """(lo, hi) relative to ``start``: the part of bucket [start, start+n) whose optimizer state (fp32 master under
@@ -292,7 +251,7 @@ class FusedAllReduce:
             sliced = n4 * 4 > (512 << 10)
         if not sliced:
             return None
-        gran = 8 if (self.cs.mc_grads and self.cs.mc_w16 and start % 8 == 0 and n4 % 8 == 0) else 4  # NVLS: 8-wide
+        gran = 8 if (start % 8 == 0 and n4 % 8 == 0) else 4   # as owned_range() in csrc/comm/allreduce.cu
         per = ((n4 // gran + self.world - 1) // self.world) * gran
         r = self.rank if rank is None else rank
         lo = min(per * r, n4)
@@ -302,17 +261,13 @@ class FusedAllReduce:
         """Refresh the fp32 master values of [start, start+n) that other ranks own (two-shot buckets updated with
         push_master = 0).  One-sided peer reads; the owners' values are final once our own last all-reduce kernel
         has returned, because that kernel's closing barrier waits for every rank's update."""
-        n4 = (n + 3) // 4 * 4
-        if sliced is None:
-            sliced = n4 * 4 > (512 << 10)
-        if not sliced:
-            return  # such a bucket takes the one-shot path: every rank already updated all of it locally
-        gran = 8 if (self.cs.mc_grads and self.cs.mc_w16 and start % 8 == 0 and n4 % 8 == 0) else 4  # NVLS: 8-wide
-        per = ((n4 // gran + self.world - 1) // self.world) * gran
         for r in range(self.world):
             if r == self.rank:
                 continue
-            lo, hi = per * r, min(per * r + per, n4)
+            own = self.owned_slice(start, n, sliced, rank=r)
+            if own is None:
+                return  # such a bucket takes the one-shot path: every rank already updated all of it locally
+            lo, hi = own
             if hi > lo:
                 self.flat.flat_p[start + lo:start + hi].copy_(self.peer_p[r][start + lo:start + hi])
 

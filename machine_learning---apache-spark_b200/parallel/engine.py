@@ -73,20 +73,8 @@ class DataParallelEngine:
             for m in module.modules():
                 if isinstance(m, (nn.Linear, nn.Embedding)):
                     w16_only.add(id(m.weight))
-        # B200ML_GEMM_SCATTER=1: nn.Linear weights (their gradients all come out of GEMMs) form a group of their own, and
-        # those GEMMs mirror their outputs into the slice owners' staging buffers (ops/gemm.py, b200ml_scatter)
-        from .comm import gemm_scatter
-
-        self._scatter = mode == "fused" and self._bf16_push and self.world > 1 and gemm_scatter()
-        lin = set()
-        if self._scatter:
-            for m in module.modules():
-                if isinstance(m, nn.Linear):
-                    lin.add(id(m.weight))
-        order = ([i for i, p in enumerate(params) if id(p) in lin] +
-                 [i for i, p in enumerate(params) if id(p) in w16_only and id(p) not in lin] +
+        order = ([i for i, p in enumerate(params) if id(p) in w16_only] +
                  [i for i, p in enumerate(params) if id(p) not in w16_only])
-        n_lin = sum(1 for p in params if id(p) in lin)
         n_w16 = sum(1 for p in params if id(p) in w16_only)
         self.flat = FlatParams(params, allocator=sym_alloc, order=order)
         self.counters = DeviceCounters.get(self.device)
@@ -99,6 +87,7 @@ class DataParallelEngine:
         self._sd_hook = None
 
         if self.world > 1:
+            self._verify_layout()
             dist.broadcast(self.flat.flat_p, src=0, group=self.pg)
             self.flat.refresh_working_copy()
 
@@ -110,12 +99,8 @@ class DataParallelEngine:
         from .reducer import make_reducer
 
         # native bucket manager (csrc/runtime/reducer.cpp); group 0 = bf16-push weights, group 1 = everything else
-        # groups: 0 = Linear weights with producer-side scatter (empty unless B200ML_GEMM_SCATTER), 1 = other bf16-push
-        # weights, 2 = everything else
-        self.reducer = make_reducer(list(self.flat.offsets[:n_params]) + [self.flat.numel], [n_lin, n_w16, n_params],
-                                    cap)
-        self.buckets = [(start, n, ids, group <= 1 and n_w16 > 0) for start, n, ids, group in self.reducer.buckets]
-        self._scatter_buckets = {b for b, (_, _, _, group) in enumerate(self.reducer.buckets) if group == 0}
+        self.reducer = make_reducer(list(self.flat.offsets[:n_params]) + [self.flat.numel], [n_w16, n_params], cap)
+        self.buckets = [(start, n, ids, group == 0 and n_w16 > 0) for start, n, ids, group in self.reducer.buckets]
         self._events = [dict() for _ in self.buckets]
         # side stream for the parameter-gradient kernels (ops/gemm.py GradSideStream)
         self.side = None
@@ -137,16 +122,6 @@ class DataParallelEngine:
 
                 self.comm = FusedAllReduce(self.flat, self.m, self.v, self.pg, allocator=sym_alloc)
                 self.allreduce_mode = "fused:" + self.comm.transport + (":bf16push" if self._bf16_push else "")
-                if self._scatter:
-                    descs = {b: self.comm.scatter_desc(self.buckets[b][0], self.buckets[b][1])
-                             for b in self._scatter_buckets}
-                    if all(d is not None for d in descs.values()) and descs:
-                        for b, d in descs.items():
-                            for i in self.buckets[b][2]:
-                                self.flat.params[i]._b200_scatter = d
-                        self.allreduce_mode += ":gemm-scatter"
-                    else:
-                        self._scatter, self._scatter_buckets = False, set()
                 if self._bf16_push:
                     # model.state_dict() on any rank first pulls the fp32 slices it does not own
                     self._sd_hook = module.register_state_dict_pre_hook(lambda *a, **k: self.sync_master())
@@ -158,6 +133,23 @@ class DataParallelEngine:
         if self._local_overlap:
             self.comm_stream = torch.cuda.Stream(device=self.device)
         self._in_step = False
+
+    def _verify_layout(self) -> None:
+        """Every rank must have built the same flat layout (what DDP's constructor verifies across ranks before it
+        broadcasts, distributed_cnn.py:156 / SURVEY 2.4 C2).  The fused all-reduce dereferences peer pointers at
+        identical offsets, so e.g. a vocabulary of another size on one rank would corrupt its peers' memory instead
+        of failing: compare a digest of (offsets, shapes, dtypes, optimizer) first and raise on every rank."""
+        import hashlib
+
+        desc = repr((self.flat.numel, list(self.flat.offsets), [tuple(p.shape) for p in self.flat.params],
+                     [str(p.dtype) for p in self.flat.params], self.kind))
+        mine = hashlib.sha256(desc.encode()).hexdigest()
+        seen = [None] * self.world
+        dist.all_gather_object(seen, (mine, len(self.flat.params), self.flat.numel), group=self.pg)
+        if any(s[0] != seen[0][0] for s in seen):
+            detail = ", ".join(f"rank {r}: {s[1]} params / {s[2]} elements" for r, s in enumerate(seen))
+            raise RuntimeError("DataParallelEngine: the ranks built different parameter layouts (" + detail +
+                               "); every rank must construct the identical model")
 
     # ------------------------------------------------------------------------------------------------ bucket events
     def _make_ready(self, i):
@@ -196,16 +188,8 @@ class DataParallelEngine:
         start, n, _, bf16_push = self.buckets[b]
         if self.comm is not None:
             self.comm.push_master = 0 if (bf16_push and self._bf16_push) else 1
-            algo = 0
-            if self._scatter:
-                if b in self._scatter_buckets:
-                    # 5: the GEMMs already scattered this bucket; 4 (full push) when a parameter never reported, because
-                    # its staged copies on the owners would be last step's
-                    algo = 5 if complete else 4
-                else:
-                    algo = 2 if n * 4 > (512 << 10) else 1   # staging exists, but these buckets keep the pull kernels
             self.comm.allreduce_update(start, n, self.kind, self.lr, self.betas, self.eps, self.weight_decay,
-                                       self.step_tensor, algo=algo)
+                                       self.step_tensor)
             return
         if self.world == 1:
             optim_step_flat(self.flat.flat_p, self.flat.flat_g, self.m, self.v, self.flat.flat_w16, self.kind, self.lr,
@@ -299,8 +283,7 @@ class DataParallelEngine:
         torch.cuda.current_stream().synchronize()
         for b, (start, n, _, bf16_push) in enumerate(self.buckets):
             if bf16_push:
-                # scatter buckets always go through the owner-updates-its-slice kernel, whatever their size
-                self.comm.pull_master(start, n, sliced=True if b in self._scatter_buckets else None)
+                self.comm.pull_master(start, n)
         torch.cuda.current_stream().synchronize()
         self._master_stale = False
 
@@ -372,7 +355,6 @@ class DataParallelEngine:
             self._sd_hook = None
         self.reducer.close()
         for p in self.flat.params:
-            p._b200_scatter = None
             p._b200_ready = None
             p._b200_side = None
 

@@ -16,6 +16,7 @@ from torch.utils.data import DataLoader  # noqa: E402
 from b200ml.data.synthetic import SyntheticImages  # noqa: E402
 from b200ml.models import FashionMNISTModel  # noqa: E402
 from b200ml.ops.loss import cross_entropy  # noqa: E402
+from b200ml.ops.metrics import argmax_accuracy  # noqa: E402
 from b200ml.ops.optim import FlatOptimizer  # noqa: E402
 from b200ml.utils import script as S  # noqa: E402
 
@@ -76,18 +77,17 @@ def main():
 
     def eval_func():
         cnn_model.eval()
-        total_test_loss, correct, count = 0.0, 0, 0
+        total_test_loss, correct, count = 0.0, None, 0
         with torch.no_grad():
             for data, target in test_dataloader:
                 data, target = data.to(device), target.to(device)
                 predictions = cnn_model(data)
-                predicted_classes = torch.argmax(torch.softmax(predictions, dim=1), dim=1)
+                predicted_classes, correct = argmax_accuracy(predictions, target, correct)   # device-side arg-max + count
                 total_test_loss += nn.functional.cross_entropy(predictions.float(), target).item()
-                correct += int((predicted_classes == target).sum())
                 count += len(target)
         print(f"total_test_loss is:{total_test_loss}")
         print(f"accuracy is :{accuracy_fn(predicted_classes, target)}")   # last batch, as the reference computes it
-        print(f"full test-set accuracy is :{100.0 * correct / max(count, 1)}")
+        print(f"full test-set accuracy is :{100.0 * int(correct) / max(count, 1)}")
 
     train_func()
     eval_func()

@@ -17,6 +17,7 @@ from b200ml.data import text as T  # noqa: E402
 from b200ml.data.synthetic import SyntheticNews  # noqa: E402
 from b200ml.models import LSTM  # noqa: E402
 from b200ml.ops.loss import cross_entropy  # noqa: E402
+from b200ml.ops.metrics import argmax_accuracy  # noqa: E402
 from b200ml.ops.optim import FlatOptimizer  # noqa: E402
 from b200ml.utils import script as S  # noqa: E402
 
@@ -70,7 +71,7 @@ def main():
             loss.backward()
             optimizer.step()
             if batch_idx % 100 == 0:
-                acc = accuracy_fn(pred[:, -1, :].argmax(1), labels)
+                acc = accuracy_fn(argmax_accuracy(pred[:, -1, :])[0], labels)
                 print(f"epoch {epoch} batch {batch_idx} loss {loss.item():.4f} accuracy {acc:.1f}")
     print(f"Training time is : {timer.elapsed()}")
     return text_classifier

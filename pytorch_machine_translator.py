@@ -2,7 +2,8 @@
 
 Same pipeline: tokenise → vocab (4 specials first, min_freq 1) → VocabTransform/AddToken/Truncate(199)/AddToken/
 ToTensor/PadTransform(200) → Transformer(d 512, ffn 1024, 8 heads, 1+1 layers, S 200) → CrossEntropy(ignore_index=0,
-'none') + masked mean → Adam(1e-3); loss every step, time every 100 batches.  Multi30k and the spacy models need a
+'none') + masked mean → Adam(1e-3); the loss is printed every step (``B200ML_PRINT_EVERY_STEP=0`` turns that off) and
+loss + time every 100 batches, with the reference's wording.  Multi30k and the spacy models need a
 network, so the corpus is the synthetic Multi30k-shaped one (b200ml.data.synthetic) unless ``B200ML_MULTI30K`` points
 at a TSV of ``english<TAB>german`` lines.
 
@@ -36,6 +37,16 @@ def load_corpus():
     return SyntheticParallelCorpus(n=320 if S.quick() else 2900, vocab_words=400 if S.quick() else 3000)
 
 
+def _batch_tokenizer(tokenizer):
+    """Batch tokenizer with the reference's input check (pytorch_machine_translator.py:25-39: en_text_tokenizer /
+    de_text_tokenizer raise TypeError unless handed a list or tuple of sentences)."""
+    def tokenize(batch):
+        if not isinstance(batch, (list, tuple)):
+            raise TypeError("Input must be a list or tuple.")
+        return [list(tokenizer(text)) for text in batch]
+    return tokenize
+
+
 def create_look_ahead_mask(size):
     mask = torch.tril(torch.ones(size, size)) == 0
     return mask.unsqueeze(0).unsqueeze(0)
@@ -47,6 +58,7 @@ def main():
     de_tokenizer = T.get_tokenizer("spacy", language="de_core_news_sm")
     en_tokenizer = T.get_tokenizer("spacy", language="en_core_web_sm")
     specials = ["<pad>", "<sos>", "<eos>", "<unk>"]
+    en_text_tokenizer, de_text_tokenizer = _batch_tokenizer(en_tokenizer), _batch_tokenizer(de_tokenizer)
     en_vocab = T.build_vocab_from_iterator((en_tokenizer(s) for s, _ in train_dataset), min_freq=1, specials=specials)
     en_vocab.set_default_index(en_vocab["<unk>"])
     de_vocab = T.build_vocab_from_iterator((de_tokenizer(t) for _, t in train_dataset), min_freq=1, specials=specials)
@@ -89,6 +101,9 @@ def main():
     # every batch is exactly [32, 200] (PadTransform), so after two eager steps the whole step replays as a CUDA graph
     step = engine.graphed(train_step)
 
+    # The reference prints the loss tensor after EVERY step, which costs a device->host sync per step; that is the
+    # default here too (same output), B200ML_PRINT_EVERY_STEP=0 keeps only the 100-batch reports.
+    print_every_step = os.environ.get("B200ML_PRINT_EVERY_STEP", "1") != "0"
     total = S.DeviceTimer(device).start()
     for epoch in range(epochs):
         if sampler is not None:
@@ -97,10 +112,13 @@ def main():
         for batch_idx, (src, trg) in enumerate(loader):
             if batch_idx >= max_steps:
                 break
-            src_tensor = en_text_transform([en_tokenizer(s) for s in src]).to(device)
-            trg_tensor = de_text_transform([de_tokenizer(t) for t in trg]).to(device)
+            src_tensor = en_text_transform(en_text_tokenizer(list(src))).to(device)
+            trg_tensor = de_text_transform(de_text_tokenizer(list(trg))).to(device)
             loss = step(src_tensor, trg_tensor)
-            if rank == 0 and (batch_idx % 100 == 0 or S.quick()):
+            if rank == 0 and print_every_step:
+                print(loss)                      # pytorch_machine_translator.py:189 prints the loss tensor every step
+            if rank == 0 and batch_idx > 1 and batch_idx % 100 == 0:
+                print("accuracy - loss is : ", loss)
                 print(f"Iteration {batch_idx} : {loss.item()}")
             if batch_idx > 1 and batch_idx % 100 == 0:
                 secs = S.max_over_ranks(window.elapsed(), device)

@@ -16,6 +16,7 @@ from torch.utils.data import DataLoader, TensorDataset, random_split  # noqa: E4
 from b200ml.data.libsvm import sample_multiclass_path  # noqa: E402
 from b200ml.models import Multilayer_perceptor, mnist_mlp  # noqa: E402
 from b200ml.ops.loss import cross_entropy  # noqa: E402
+from b200ml.ops.metrics import argmax_accuracy  # noqa: E402
 from b200ml.ops.optim import FlatOptimizer  # noqa: E402
 from b200ml.spark import SparkSession  # noqa: E402
 from b200ml.utils import script as S  # noqa: E402
@@ -74,19 +75,18 @@ def main():
     print(f"PyTorch Training Time: {timer.elapsed():.2f} seconds")
 
     multilayer_model.eval()
-    total_test_loss, correct, count = 0.0, 0, 0
+    total_test_loss, correct, count = 0.0, None, 0
     with torch.no_grad():
         for features, labels in test_loader:
             features, labels = features.to(device), labels.to(device)
             predictions = multilayer_model(features)
-            predicted_classes = torch.argmax(torch.softmax(predictions, dim=1), dim=1)
+            predicted_classes, correct = argmax_accuracy(predictions, labels, correct)   # device-side arg-max + count
             test_loss = nn.functional.cross_entropy(predictions.float(), labels)
             total_test_loss += test_loss.item()
-            correct += int((predicted_classes == labels).sum())
             count += len(labels)
     print("Test loss on last batch:", test_loss.item())
     print("accuracy is:", accuracy_fn(labels, predicted_classes))       # last batch, as the reference prints
-    print("full test-set accuracy:", 100.0 * correct / max(count, 1))
+    print("full test-set accuracy:", 100.0 * int(correct) / max(count, 1))
     return multilayer_model
 
 

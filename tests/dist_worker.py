@@ -5,8 +5,6 @@
 import os
 import sys
 
-os.environ.setdefault("B200ML_AR_PUSH", "1")  # exercise the staging (push) variant too
-
 import torch
 import torch.distributed as dist
 
@@ -29,7 +27,9 @@ def setup():
 def small_model(dev):
     from b200ml.models.transformer import Transformer
     torch.manual_seed(7)
-    m = Transformer(128, 256, 2, 0.0, 1, 32, 96, 80, 96).to(dev)
+    # target vocabulary 2000: the decoder table and the head are 1 MB each, so with 1 MB buckets the engine takes the
+    # two-shot (sliced) path for them and the one-shot path for the small buckets
+    m = Transformer(128, 256, 2, 0.0, 1, 32, 2000, 80, 2000).to(dev)
     m.eval()  # SentenceEmbedding keeps the reference's hard-coded Dropout(0.1); eval() makes runs comparable
     return m
 
@@ -65,6 +65,8 @@ def case_dp_equals_big_batch(rank, world, dev, mode):
     # steps are sign-like and amplify it)
     eng = DataParallelEngine(model, optimizer="sgd", lr=0.1, allreduce=mode, bucket_mb=0.05)
     assert len(eng.buckets) > 2
+    if eng.comm is not None:
+        assert any(eng.comm.owned_slice(s, n) is not None for s, n, _, _ in eng.buckets), "no two-shot bucket"
     train(model, eng, rank, world, dev, steps=4, global_batch=8, shard=True)
     eng.weights_hash()
     dp = torch.cat([v.detach().reshape(-1).clone() for v in model.state_dict().values()])
@@ -102,7 +104,9 @@ def case_fused_matches_nccl(rank, world, dev, mode):
 
 
 def case_allreduce_raw(rank, world, dev, mode):
-    """kind-0 reduce of random buffers vs torch.distributed.all_reduce, one-shot and two-shot sizes, SGD variant."""
+    """kind-0 reduce of random buffers vs torch.distributed.all_reduce; SGD and Adam updates through every transport
+    (1 one-shot, 2 SM-issued pull, 4 bulk-async TMA ring, 5 the same with per-thread weight stores), on whole buffers
+    and on sub-ranges so small that some ranks own an EMPTY slice (the `lo > n` clamp) or only a 4-element granule."""
     from b200ml.parallel.comm import FusedAllReduce, SymmetricAllocator
     from b200ml.parallel.flat import FlatParams
     torch.manual_seed(rank)
@@ -111,23 +115,52 @@ def case_allreduce_raw(rank, world, dev, mode):
     flat = FlatParams(ps, allocator=alloc)
     dist.broadcast(flat.flat_p, src=0)
     flat.refresh_working_copy()
-    comm = FusedAllReduce(flat, None, None, None, allocator=alloc)
+    m = torch.zeros_like(flat.flat_p)
+    v = torch.zeros_like(flat.flat_p)
+    comm = FusedAllReduce(flat, m, v, None, allocator=alloc)
     step = torch.ones(1, dtype=torch.int32, device=dev)
-    for algo in (1, 2, 4):
-        flat.flat_g.copy_(torch.randn(flat.numel, device=dev))
-        expect = flat.flat_g.clone()
-        dist.all_reduce(expect)
-        expect /= world
-        out = torch.zeros_like(flat.flat_g)
-        comm.allreduce_update(0, flat.numel, 0, 0.0, (0.9, 0.999), 1e-8, 0.0, step, out=out, algo=1)
-        torch.cuda.synchronize()
-        assert (out - expect).abs().max().item() < 1e-5
-        p0 = flat.flat_p.clone()
-        comm.allreduce_update(0, flat.numel, 1, 0.5, (0.9, 0.999), 1e-8, 0.0, step, algo=algo)
-        torch.cuda.synchronize()
-        dist.barrier()
-        assert (flat.flat_p - (p0 - 0.5 * expect)).abs().max().item() < 1e-5, f"algo {algo}"
-        assert (flat.flat_w16.float() - flat.flat_p).abs().max().item() < 0.05
+    N = flat.numel
+    ranges = [(0, N), (64, 24), (128, 8), (0, 4100), (64, 4096 + 8), (1024, 1024 * world + 8)]
+    for algo in (1, 2, 4, 5):
+        for start, n in ranges:
+            if algo in (4, 5) and (start % 8 or n % 8):
+                continue                      # the bulk ring needs 8-element granularity (auto falls back to 2)
+            flat.flat_g.copy_(torch.randn(N, device=dev))
+            expect = flat.flat_g.clone()
+            dist.all_reduce(expect)
+            expect /= world
+            out = torch.zeros_like(flat.flat_g)
+            comm.allreduce_update(start, n, 0, 0.0, (0.9, 0.999), 1e-8, 0.0, step, out=out, algo=1)
+            torch.cuda.synchronize()
+            assert (out[start:start + n] - expect[start:start + n]).abs().max().item() < 1e-5
+            assert out[:start].abs().max().item() == 0 if start else True
+            # SGD
+            p0 = flat.flat_p.clone()
+            comm.allreduce_update(start, n, 1, 0.5, (0.9, 0.999), 1e-8, 0.0, step, algo=algo)
+            torch.cuda.synchronize()
+            dist.barrier()
+            want = p0.clone()
+            want[start:start + n] -= 0.5 * expect[start:start + n]
+            assert (flat.flat_p - want).abs().max().item() < 1e-5, f"sgd algo {algo} range {(start, n)}"
+            sl = slice(start, start + n)
+            assert (flat.flat_w16[sl].float() - want[sl]).abs().max().item() < 0.05, f"w16 algo {algo} range {(start, n)}"
+            # Adam (first step from zero moments): p -= lr * g / (|g| + eps); m / v live on the slice owners only
+            p0 = flat.flat_p.clone()
+            m.zero_()
+            v.zero_()
+            comm.allreduce_update(start, n, 2, 1e-2, (0.9, 0.999), 1e-8, 0.0, step, algo=algo)
+            torch.cuda.synchronize()
+            dist.barrier()
+            g = expect[sl]
+            want = p0.clone()
+            want[sl] -= 1e-2 * g / (g.abs() + 1e-8)
+            assert (flat.flat_p - want).abs().max().item() < 1e-4, f"adam algo {algo} range {(start, n)}"
+            own = comm.owned_slice(start, n, sliced=algo != 1)
+            lo, hi = (0, n) if own is None else own
+            assert (m[start + lo:start + hi] - 0.1 * g[lo:hi]).abs().max().item() < 1e-6 if hi > lo else True
+            outside = torch.cat([m[:start + lo], m[start + hi:]])
+            assert outside.abs().max().item() == 0, f"m written outside the owned slice, algo {algo} range {(start, n)}"
+            dist.barrier()
     comm.close()
     print(f"[rank {rank}] allreduce_raw ok")
 
@@ -230,7 +263,22 @@ def case_checkpoint_adam(rank, world, dev, mode):
     print(f"[rank {rank}] checkpoint_adam ok err={err:.3e} nonzero_v={nz}/{tot}")
 
 
-CASES = {"checkpoint_adam": case_checkpoint_adam,"allreduce_nvls": case_allreduce_nvls, "dp_equals_big_batch": case_dp_equals_big_batch, "fused_matches_nccl": case_fused_matches_nccl,
+def case_layout_mismatch(rank, world, dev, mode):
+    """A rank that built another model must be caught by the constructor, on every rank, before any peer access."""
+    from b200ml.models.transformer import Transformer
+    from b200ml.parallel.engine import DataParallelEngine
+    vocab = 96 if rank == 0 else 104
+    m = Transformer(128, 256, 2, 0.0, 1, 32, vocab, 80, vocab).to(dev)
+    try:
+        DataParallelEngine(m, optimizer="sgd", lr=0.1, allreduce=mode)
+    except RuntimeError as e:
+        assert "different parameter layouts" in str(e), str(e)
+        print(f"[rank {rank}] layout_mismatch ok")
+        return
+    raise AssertionError("mismatched layouts were accepted")
+
+
+CASES = {"layout_mismatch": case_layout_mismatch, "checkpoint_adam": case_checkpoint_adam,"allreduce_nvls": case_allreduce_nvls, "dp_equals_big_batch": case_dp_equals_big_batch, "fused_matches_nccl": case_fused_matches_nccl,
          "allreduce_raw": case_allreduce_raw}
 
 if __name__ == "__main__":

@@ -23,23 +23,40 @@ def test_dp_engine_gloo_world2():
     assert out.count("dp_equals_big_batch ok") == 2
 
 
+def test_layout_mismatch_is_caught_gloo_world2():
+    out = _launch(["layout_mismatch"], 2, 29615, {"B200ML_TEST_CPU": "1", "OMP_NUM_THREADS": "2"})
+    assert out.count("layout_mismatch ok") == 2
+
+
 def test_checkpoint_adam_gloo_world2():
     out = _launch(["checkpoint_adam"], 2, 29614, {"B200ML_TEST_CPU": "1", "OMP_NUM_THREADS": "2"})
     assert out.count("checkpoint_adam ok") == 2
 
 
-@pytest.mark.gpu
-@pytest.mark.multigpu
-def test_fused_allreduce_two_gpus():
-    out = _launch(["allreduce_raw", "allreduce_nvls", "fused_matches_nccl", "dp_equals_big_batch"], 2, 29612)
-    assert out.count("allreduce_raw ok") == 2 and out.count("fused_matches_nccl ok") == 2
+def _ngpu():
+    import torch
+    return torch.cuda.device_count() if torch.cuda.is_available() else 0
 
 
 @pytest.mark.gpu
 @pytest.mark.multigpu
-def test_gemm_scatter_two_gpus():
-    """Weight-gradient GEMMs mirror their outputs into the slice owners' staging buffers (b200ml_scatter) and the
-    all-reduce skips its scatter phase (algo 5): same weights as NCCL all-reduce + optimizer."""
-    out = _launch(["fused_matches_nccl", "dp_equals_big_batch"], 2, 29613, {"B200ML_GEMM_SCATTER": "1"})
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_fused_allreduce_multi_gpu(world):
+    """Every all-reduce transport, the fused engine against NCCL, DP == big batch, and Adam checkpoint/resume, at 2, 4
+    and 8 ranks (whatever the box has)."""
+    if _ngpu() < world:
+        pytest.skip(f"needs {world} GPUs")
+    out = _launch(["allreduce_raw", "allreduce_nvls", "fused_matches_nccl", "dp_equals_big_batch", "checkpoint_adam",
+                   "layout_mismatch"], world, 29612 + world, timeout=900)
+    for case in ("allreduce_raw", "fused_matches_nccl", "dp_equals_big_batch", "checkpoint_adam", "layout_mismatch"):
+        assert out.count(f"{case} ok") == world, case
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+@pytest.mark.parametrize("algo", [2, 5])
+def test_engine_on_other_transports_two_gpus(algo):
+    """The engine's default two-shot transport is the bulk-async ring; the SM-issued pull (2) and the ring with
+    per-thread stores (5) must give the same training result."""
+    out = _launch(["fused_matches_nccl", "dp_equals_big_batch"], 2, 29640 + algo, {"B200ML_AR_ALGO": str(algo)})
     assert out.count("fused_matches_nccl ok") == 2 and out.count("dp_equals_big_batch ok") == 2
-    assert "gemm-scatter" in out

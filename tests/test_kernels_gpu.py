@@ -40,21 +40,87 @@ def test_layernorm_fwd_bwd(rows, d, with_res):
 
 
 def test_layernorm_dropout_consistent():
+    """Backward regenerates the forward's dropout mask: da is exactly zero where the forward dropped the element and
+    equals dz / (1 - p) where it kept it."""
     from b200ml.ops.norm import layernorm_residual
     from b200ml.utils.rng import DeviceCounters
     DeviceCounters.get("cuda").seed(5)
-    rows, d = 256, 512
+    rows, d, p = 256, 512, 0.5
+    # a = 1 everywhere and no residual: the pre-norm value is 0 (dropped) or 1/(1-p) (kept), which exposes the mask
     a = torch.ones(rows, d, device="cuda", dtype=torch.bfloat16).requires_grad_()
-    x = torch.randn(rows, d, device="cuda").to(torch.bfloat16).requires_grad_()
-    g = torch.ones(d, device="cuda", requires_grad=True)
+    g = (torch.rand(d, device="cuda") + 0.5).requires_grad_()
     b = torch.zeros(d, device="cuda", requires_grad=True)
-    y = layernorm_residual(a, x, g, b, dropout_p=0.5, site=3)
-    y.float().sum().backward()
-    # da must be zero exactly where the mask dropped, and equal dx/(1-p) elsewhere
-    ratio = a.grad.float() / x.grad.float().clamp(min=1e-30).where(x.grad.float().abs() > 1e-6, torch.ones_like(x.grad.float()))
-    dropped = a.grad == 0
-    frac = dropped.float().mean().item()
+    y = layernorm_residual(a, None, g, b, dropout_p=p, site=3)
+    kept_fwd = y.detach().float() > 0        # kept elements sit above the row mean, dropped ones below (gamma > 0)
+    frac = 1.0 - kept_fwd.float().mean().item()
     assert 0.45 < frac < 0.55
+    w = torch.randn(rows, d, device="cuda")
+    (y.float() * w).sum().backward()
+    assert torch.equal(a.grad != 0, kept_fwd) or ((a.grad != 0) ^ kept_fwd).float().mean().item() < 1e-3
+    # with a residual input the same dz reaches both inputs: da == dx / (1 - p) where kept, 0 where dropped
+    a2 = torch.ones(rows, d, device="cuda", dtype=torch.bfloat16).requires_grad_()
+    x2 = torch.zeros(rows, d, device="cuda", dtype=torch.bfloat16).requires_grad_()
+    y2 = layernorm_residual(a2, x2, g, b, dropout_p=p, site=3)
+    assert torch.equal(y2, y)                # same (seed, step, site): same draw
+    (y2.float() * w).sum().backward()
+    da, dx = a2.grad.float(), x2.grad.float()
+    assert torch.equal(da[~kept_fwd], torch.zeros_like(da[~kept_fwd]))
+    want = dx[kept_fwd] / (1 - p)
+    assert (da[kept_fwd] - want).abs().max().item() <= 1e-2 * want.abs().max().item() + 1e-6
+
+
+def test_dropout_masks_survive_counter_bumps_between_forward_and_backward():
+    """The reference's LSTM loop calls zero_grad() between forward and backward (distributed_lstm.py:192-194).  The
+    engine's begin_step() must not move the dropout draw: gradients are the same wherever zero_grad() sits."""
+    from b200ml.models import LSTM
+    from b200ml.ops.loss import cross_entropy
+    from b200ml.parallel.engine import DataParallelEngine
+    from b200ml.utils.rng import manual_seed
+    tok = torch.randint(1, 400, (8, 24), device="cuda")
+    lab = torch.randint(0, 4, (8,), device="cuda")
+    z = torch.zeros(2, 8, 32, device="cuda")
+    grads = []
+    for order in ("before", "between"):
+        manual_seed(3, "cuda")
+        model = LSTM(400, 32, 32, 4).cuda().train()
+        eng = DataParallelEngine(model, optimizer="adam", lr=1e-3)
+        for _ in range(2):                   # second step: fresh masks, still consistent
+            if order == "before":
+                eng.zero_grad()
+            pred, _, _ = model(tok, z, z)
+            loss = cross_entropy(pred[:, -1, :], lab)
+            if order == "between":
+                eng.zero_grad()
+            loss.backward()
+            torch.cuda.synchronize()
+            grads.append(eng.flat.flat_g.clone())
+            eng.step()
+        eng.close()
+    for a, b in ((grads[0], grads[2]), (grads[1], grads[3])):
+        assert (a - b).abs().max().item() <= 1e-4 * a.abs().max().item() + 1e-7
+    assert not torch.allclose(grads[0], grads[1])
+
+
+def test_flat_optimizer_advances_dropout_step():
+    """Two consecutive FlatOptimizer steps must draw different dropout masks (pytorch_lstm.py trains without an engine)."""
+    from b200ml.ops.embedding import embedding
+    from b200ml.ops.optim import FlatOptimizer
+    from b200ml.utils.rng import manual_seed
+    manual_seed(9, "cuda")
+    w = torch.nn.Parameter(torch.ones(64, 128, device="cuda"))
+    w._b200_zero_grad = True                 # scatter-add slot: cleared by zero_grad()
+    opt = FlatOptimizer([w], kind="sgd", lr=0.0)
+    tok = torch.arange(64, device="cuda")[None]
+    masks = []
+    for _ in range(2):
+        opt.zero_grad()
+        out = embedding(tok, w, dropout_p=0.5, site=77, out_dtype=torch.float32)
+        out.sum().backward()
+        masks.append(out.detach() != 0)
+        # backward saw the forward's draw: the gradient rows are non-zero exactly where the output was kept
+        assert torch.equal(w._b200_grad.view(64, 128) != 0, masks[-1][0])
+        opt.step()
+    assert not torch.equal(masks[0], masks[1])
 
 
 def test_embedding_pe_matches_reference_formula():
