@@ -5,7 +5,8 @@
 // collective per bucket as soon as the bucket's last gradient exists.  Here the parameters already live in ONE flat
 // buffer (parallel/flat.py), so a bucket is a contiguous range of it; the gradient kernels write straight into their
 // slots and report "parameter i is ready"; the first report that completes a bucket returns its index and the engine
-// launches the fused all-reduce + optimizer kernel on that range.  Parameters are partitioned into groups (e.g.
+// launches the fused all-reduce + optimizer kernel on that range.  Buckets are cut at `cap` elements, and parameters
+// of cap/4 or more stand alone (see below).  Parameters are partitioned into groups (e.g.
 // "weights whose fp32 master may stay stale on non-owner ranks" vs the rest) and buckets never straddle a group.
 // Reports arrive from the autograd worker thread and the main thread, hence the mutex.
 #include <mutex>
@@ -49,7 +50,18 @@ b200ml_reducer* b200ml_reducer_create(int n_params, const long long* offsets, in
         int first = lo;
         for (int i = lo; i < hi; ++i) {
             const long long end = offsets[i + 1];  // offsets has n_params + 1 entries; the last is the total size
-            if (end - start >= cap_elems || i + 1 == hi) {
+            // A parameter of a quarter of the cap or more gets a bucket of its own.  Its gradient is produced by one
+            // kernel at one point of backward (an embedding table at the very end, the output projection at the very
+            // start); sharing a bucket with neighbours that become ready at another time would hold its all-reduce /
+            // optimizer launch back until then and leave that work exposed after backward has finished.
+            const bool big = (end - offsets[i]) * 4 >= cap_elems;
+            if (big && i > first) {
+                r->buckets.push_back({start, offsets[i] - start, first, i - first, g});
+                for (int p = first; p < i; ++p) r->bucket_of[p] = (int)r->buckets.size() - 1;
+                start = offsets[i];
+                first = i;
+            }
+            if (big || end - start >= cap_elems || i + 1 == hi) {
                 r->buckets.push_back({start, end - start, first, i + 1 - first, g});
                 for (int p = first; p <= i; ++p) r->bucket_of[p] = (int)r->buckets.size() - 1;
                 start = end;

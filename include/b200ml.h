@@ -96,10 +96,29 @@ int b200ml_pe_table(float* pe, int S, int d, cudaStream_t stream);
 int b200ml_embedding_fwd(const long long* tokens, const void* table_bf16, const float* pe, void* out, int out_fp32,
                          int n_tokens, int S, int d, int V, float dropout_p, const void* rng_state, unsigned rng_site,
                          cudaStream_t stream);
-/* dtable (fp32, [V,d]) += scatter of dout; the caller zeroes dtable once per step.  padding_idx < 0 disables it. */
+/* dtable (fp32, [V,d]) += scatter of dout (fp32 atomicAdd: the order of the additions, and so the last bits, vary from
+ * run to run); the caller zeroes dtable once per step.  padding_idx < 0 disables it.  Kept for token counts above
+ * b200ml_embedding_index_max_tokens(); the framework's own path is the sorted pair below. */
 int b200ml_embedding_bwd(const long long* tokens, const void* dout, int dout_fp32, float* dtable, int n_tokens, int d,
                          int V, long long padding_idx, float dropout_p, const void* rng_state, unsigned rng_site,
                          cudaStream_t stream);
+/* Deterministic backward in two steps.  b200ml_embedding_index sorts the keys (token id << 32 | position) of one batch
+ * (single-CTA bitonic sort, n_tokens <= b200ml_embedding_index_max_tokens() = 16384; it depends on the token ids only
+ * and can run at forward time).  b200ml_embedding_bwd_sorted gives each table row to one warp, which sums the dout rows
+ * of its tokens in position order and WRITES the row (accumulate = 0: rows without tokens and the padding row become
+ * zero, so the table needs no clearing; accumulate = 1 adds to what is there).  Rows with more than 64 tokens of the
+ * batch (a padding id, <sos>) are summed by a second kernel in 32 interleaved ways through `scratch`
+ * (b200ml_embedding_bwd_sorted_scratch_bytes; its first bytes are counters that must be ZERO before the first call
+ * and are left zero by every call; calls that share a scratch buffer must not overlap).  Any sorted key array of that
+ * form is accepted, whoever sorted it.  ref: nn.Embedding backward (transformer.py:52-61; distributed_lstm.py:115,128). */
+int b200ml_embedding_index_max_tokens(void);
+int b200ml_embedding_index(const long long* tokens, int n_tokens, int V, unsigned long long* keys_out,
+                           cudaStream_t stream);
+size_t b200ml_embedding_bwd_sorted_scratch_bytes(int n_tokens, int d);
+int b200ml_embedding_bwd_sorted(const unsigned long long* keys_sorted, const void* dout, int dout_fp32, float* dtable,
+                                int n_tokens, int d, int V, long long padding_idx, float dropout_p,
+                                const void* rng_state, unsigned rng_site, int accumulate, void* scratch,
+                                size_t scratch_bytes, cudaStream_t stream);
 
 /* ------------------------------------------------------------------------------------------------ K6 cross-entropy
  * ref: nn.CrossEntropyLoss (distributed_cnn.py:141) and ignore_index=0 + masked mean

@@ -1,14 +1,60 @@
-"""Embedding gather (+ sinusoidal positional encoding + dropout) and its dense scatter-add backward
-(csrc/kernels/embedding.cu).  Reference: transformer.py:27-62; distributed_lstm.py:115,128."""
+"""Embedding gather (+ sinusoidal positional encoding + dropout) and its backward (csrc/kernels/embedding.cu).
+Reference: transformer.py:27-62; distributed_lstm.py:115,128.
+
+Backward is deterministic: the batch's (token, position) keys are sorted once - at forward time, on an auxiliary stream,
+because only the token ids are needed - and each row of the table gradient is then written exactly once by the warp
+that owns it (sum over its tokens in position order, zero for rows the batch does not touch).  No clearing of the
+table gradient, no atomics, the same bits on every run."""
 from __future__ import annotations
+
+import ctypes as C
 
 import torch
 
-from .. import _native
+from .. import _native, _native_ext
+from ..utils import workspace
 from ..utils.rng import DeviceCounters
 from .gemm import working_copy
 
+_vp, _i, _ll, _f, _u = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_uint
+_native_ext.register("b200ml_embedding_index", [_vp, _i, _i, _vp, _vp])
+_native_ext.register("b200ml_embedding_bwd_sorted", [_vp, _vp, _i, _vp, _i, _i, _i, _ll, _f, _vp, _u, _i, _vp,
+                                                     C.c_size_t, _vp])
+_native_ext.register("b200ml_embedding_bwd_sorted_scratch_bytes", [_i, _i], size_t_return=True)
+INDEX_MAX_TOKENS = 16384   # csrc/kernels/embedding.cu kIndexMaxTokens
+
 _pe_cache: dict = {}
+_aux_streams: dict = {}
+
+
+def _aux_stream(device) -> torch.cuda.Stream:
+    key = (device.type, device.index)
+    st = _aux_streams.get(key)
+    if st is None:
+        st = _aux_streams[key] = torch.cuda.Stream(device=device)
+    return st
+
+
+def sorted_token_keys(tok: torch.Tensor, V: int):
+    """(keys, event): uint64 keys ``token << 32 | position`` of the flat token tensor, sorted, produced on the auxiliary
+    stream; ``event`` marks their completion.  Batches above INDEX_MAX_TOKENS are sorted by torch instead."""
+    n = tok.numel()
+    cur = torch.cuda.current_stream()
+    aux = _aux_stream(tok.device)
+    # `keys` is allocated on the CURRENT stream (it is read there, in backward, after waiting for `event`) and only
+    # written on the auxiliary one; `tok` is saved for backward, so both outlive the auxiliary kernel
+    keys = torch.empty(n, dtype=torch.int64, device=tok.device)
+    aux.wait_stream(cur)
+    with torch.cuda.stream(aux):
+        if n <= INDEX_MAX_TOKENS:
+            _native.check(_native.load().b200ml_embedding_index(tok.data_ptr(), n, V, keys.data_ptr(),
+                                                                _native.stream_ptr()), "embedding_index")
+        else:
+            t = torch.where((tok < 0) | (tok >= V), torch.zeros_like(tok), tok)
+            keys.copy_(((t << 32) | torch.arange(n, device=tok.device)).sort().values)
+        ev = torch.cuda.Event()
+        ev.record(aux)
+    return keys, ev
 
 
 def positional_encoding_table(S: int, d: int, device) -> torch.Tensor:
@@ -47,7 +93,11 @@ class _Embedding(torch.autograd.Function):
             _native.check(_native.load().b200ml_embedding_fwd(
                 tok.data_ptr(), w16.data_ptr(), _native.ptr(pe), out.data_ptr(), int(out_dtype == torch.float32), n, S,
                 d, V, p, rng, site, _native.stream_ptr()), "embedding_fwd")
-            ctx.save_for_backward(tok)
+            keys = tok
+            ctx.keys_event = None
+            if weight.requires_grad:
+                keys, ctx.keys_event = sorted_token_keys(tok, V)
+            ctx.save_for_backward(tok, keys)
             ctx.mask = None
             return out.reshape(*lead, d)
         out = weight.float()[tok]
@@ -57,13 +107,13 @@ class _Embedding(torch.autograd.Function):
         if p > 0:
             mask = (torch.rand_like(out) >= p).float() / (1.0 - p)
             out = out * mask
-        ctx.save_for_backward(tok)
+        ctx.save_for_backward(tok, tok)
         ctx.mask = mask
         return out.to(out_dtype).reshape(*lead, d)
 
     @staticmethod
     def backward(ctx, dout):
-        (tok,) = ctx.saved_tensors
+        tok, keys = ctx.saved_tensors
         V, d, p, site, padding_idx, lead = ctx.meta
         weight = ctx.weight
         n = tok.numel()
@@ -74,14 +124,24 @@ class _Embedding(torch.autograd.Function):
             g = dout.reshape(n, d).contiguous()
             if g.dtype not in (torch.float32, torch.bfloat16):
                 g = g.float()
+            # every row is written exactly once (zeros where the batch has no token), so nothing is cleared beforehand
+            acc = 0
             if slot is not None:
-                dt = slot.view(V, d)  # zeroed by the engine at the start of the step
+                dt = slot.view(V, d)
+                acc = int(bool(getattr(weight, "_b200_grad_accumulate", False)))
             else:
-                dt = torch.zeros(V, d, dtype=torch.float32, device=weight.device)
+                dt = torch.empty(V, d, dtype=torch.float32, device=weight.device)
             rng = DeviceCounters.get(weight.device).rng.data_ptr() if p > 0 else None
-            _native.check(_native.load().b200ml_embedding_bwd(
-                tok.data_ptr(), g.data_ptr(), int(g.dtype == torch.float32), dt.data_ptr(), n, d, V,
-                -1 if padding_idx is None else padding_idx, p, rng, site, _native.stream_ptr()), "embedding_bwd")
+            if ctx.keys_event is not None:
+                torch.cuda.current_stream().wait_event(ctx.keys_event)
+            lib = _native.load()
+            nb = int(lib.b200ml_embedding_bwd_sorted_scratch_bytes(n, d))
+            # one scratch per table: the backward passes of two tables (encoder / decoder) may run concurrently
+            ws = workspace.get_zeroed(f"emb_bwd@{id(weight)}", nb, weight.device)
+            _native.check(lib.b200ml_embedding_bwd_sorted(
+                keys.data_ptr(), g.data_ptr(), int(g.dtype == torch.float32), dt.data_ptr(), n, d, V,
+                -1 if padding_idx is None else padding_idx, p, rng, site, acc, ws.data_ptr(), ws.numel(),
+                _native.stream_ptr()), "embedding_bwd_sorted")
             if slot is not None:
                 ready = getattr(weight, "_b200_ready", None)
                 if ready is not None:
@@ -93,7 +153,12 @@ class _Embedding(torch.autograd.Function):
             g = g * ctx.mask
         if padding_idx is not None:
             g = g * (tok != padding_idx).unsqueeze(1)
-        dt = slot.view(V, d) if slot is not None else torch.zeros(V, d, dtype=torch.float32, device=weight.device)
+        if slot is not None:
+            dt = slot.view(V, d)
+            if not getattr(weight, "_b200_grad_accumulate", False):
+                dt.zero_()
+        else:
+            dt = torch.zeros(V, d, dtype=torch.float32, device=weight.device)
         dt.index_add_(0, tok, g)
         if slot is not None:
             ready = getattr(weight, "_b200_ready", None)

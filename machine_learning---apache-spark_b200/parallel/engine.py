@@ -130,8 +130,15 @@ class DataParallelEngine:
         # single GPU: the per-bucket optimizer launches also run on a side stream, overlapping the rest of backward
         self._local_overlap = (self.world == 1 and self.device.type == "cuda" and self.sync_gradients and
                                os.environ.get("B200ML_OPT_OVERLAP", "1") != "0")
+        # Single GPU: no cross-rank ordering to respect, so the per-bucket optimizer launches rotate over a few streams
+        # and each waits only for ITS bucket's gradients (one stream would make a bucket that has been ready for
+        # 100 us queue behind one whose last weight gradient is still being computed).  Multi-GPU: the fused kernels of
+        # one communicator must run one at a time and in the same order on every rank -> one stream.
+        self._opt_streams = []
         if self._local_overlap:
-            self.comm_stream = torch.cuda.Stream(device=self.device)
+            n_opt = max(1, int(os.environ.get("B200ML_OPT_STREAMS", "3")))
+            self._opt_streams = [torch.cuda.Stream(device=self.device) for _ in range(n_opt)]
+            self.comm_stream = self._opt_streams[0]
         self._in_step = False
 
     def _verify_layout(self) -> None:
@@ -165,9 +172,10 @@ class DataParallelEngine:
                 ev.record(cur)
                 self._events[b][cur.cuda_stream] = ev
                 if self.side is not None and self.side.active and self.side.used:
+                    # deliver_grad queued this parameter's kernels on side.last just before reporting it ready
                     ev2 = torch.cuda.Event()
-                    ev2.record(self.side.stream)
-                    self._events[b][self.side.stream.cuda_stream] = ev2
+                    ev2.record(self.side.last)
+                    self._events[b][self.side.last.cuda_stream] = ev2
             if self.reducer.mark_ready(i) == b:   # this report completed the bucket
                 self._bucket_ready(b)
         return ready
@@ -176,10 +184,11 @@ class DataParallelEngine:
         if (self.world == 1 and not self._local_overlap) or not self.sync_gradients:
             return  # single fused optimizer launch in finish_step
         if self.comm_stream is not None:
-            self.comm_stream.wait_stream(torch.cuda.current_stream())
+            st = self._opt_streams[b % len(self._opt_streams)] if self._opt_streams else self.comm_stream
+            st.wait_stream(torch.cuda.current_stream())
             for ev in self._events[b].values():
-                self.comm_stream.wait_event(ev)
-            with torch.cuda.stream(self.comm_stream):
+                st.wait_event(ev)
+            with torch.cuda.stream(st):
                 self._reduce_and_update(b, complete)
         else:
             self._reduce_and_update(b, complete)
@@ -228,7 +237,8 @@ class DataParallelEngine:
         for b in self.reducer.flush():
             self._bucket_ready(b, complete=False)
         if self.comm_stream is not None:
-            torch.cuda.current_stream().wait_stream(self.comm_stream)
+            for st in (self._opt_streams or [self.comm_stream]):
+                torch.cuda.current_stream().wait_stream(st)
         if self.side is not None:
             self.side.join()
         # every backward kernel of this step is ordered before this point on the current stream (autograd joined its

@@ -2,7 +2,8 @@
 fp32 gradient buffer and a flat bf16 working-copy buffer.
 
 This is the memory layout the whole training path is built on:
-  * wgrad kernels write gradients straight into their slot (``param._b200_grad``) — no copy-in, no ``zero_grad``;
+  * gradient kernels (wgrad GEMMs, the embedding segment reduction, LayerNorm) write straight into their slot
+    (``param._b200_grad``) and overwrite it — no copy-in, no ``zero_grad``;
   * the optimizer (and the fused all-reduce epilogue, parallel/engine.py) walks contiguous ranges — one launch updates
     fp32 masters, Adam moments and the bf16 working copies the GEMMs read (``param._b200_w16``);
   * ``state_dict()`` of the model is untouched: parameters keep their names, shapes and fp32 dtype.
@@ -41,7 +42,7 @@ class FlatParams:
         self.flat_p = allocator("flat_p", off, torch.float32)
         self.flat_g = allocator("flat_g", off, torch.float32)
         self.flat_w16 = allocator("flat_w16", off, torch.bfloat16) if bf16_copy else None
-        self.zero_ranges = []  # slots whose backward accumulates (embedding scatter-add) and need clearing per step
+        self.zero_ranges = []  # slots of parameters flagged `_b200_zero_grad` (a backward that accumulates): cleared per step
         for p, o in zip(params, self.offsets):
             n = p.numel()
             self.flat_p[o:o + n].copy_(p.data.reshape(-1))

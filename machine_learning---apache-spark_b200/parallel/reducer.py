@@ -76,7 +76,13 @@ class PyReducer:
             start, first = (offsets[lo] if lo < hi else 0), lo
             for i in range(lo, hi):
                 end = offsets[i + 1]
-                if end - start >= cap_elems or i + 1 == hi:
+                big = (end - offsets[i]) * 4 >= cap_elems     # stands alone, as in reducer.cpp
+                if big and i > first:
+                    for p in range(first, i):
+                        self._of[p] = len(self.buckets)
+                    self.buckets.append((start, offsets[i] - start, list(range(first, i)), g))
+                    start, first = offsets[i], i
+                if big or end - start >= cap_elems or i + 1 == hi:
                     for p in range(first, i + 1):
                         self._of[p] = len(self.buckets)
                     self.buckets.append((start, end - start, list(range(first, i + 1)), g))

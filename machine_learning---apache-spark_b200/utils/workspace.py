@@ -39,6 +39,18 @@ def get(name: str, nbytes: int, device) -> torch.Tensor:
     return buf
 
 
+def get_zeroed(name: str, nbytes: int, device) -> torch.Tensor:
+    """Like ``get``, but the buffer is zero-filled when it is (re)allocated - for kernels that keep counters in their
+    scratch and leave them at zero after every call (e.g. the hot-row list of the embedding backward)."""
+    device = torch.device(device)
+    key = (name, device.type, device.index)
+    before = _cache.get(key)
+    buf = get(name, nbytes, device)
+    if buf is not before:
+        buf.zero_()
+    return buf
+
+
 def retired_bytes() -> int:
     return sum(b.numel() for b in _retired)
 

@@ -85,22 +85,32 @@ def case_dp_equals_big_batch(rank, world, dev, mode):
 
 
 def case_fused_matches_nccl(rank, world, dev, mode):
-    """Fused P2P all-reduce+Adam gives the same weights as NCCL all-reduce + the flat optimizer kernel."""
+    """The fused all-reduce + optimizer gives the same weights as NCCL all-reduce + the flat optimizer kernel.
+    The two paths round differently in the last bit (NCCL adds in another order than our rank-order sum, and the
+    scale / update arithmetic is fused differently); SGD keeps that at rounding level, while Adam turns the noise of
+    gradients that are mathematically zero (the key bias of every attention block) into +-lr steps - there only the
+    bulk of the elements is held to the tight tolerance.  (The exact Adam arithmetic of every transport is checked in
+    allreduce_raw.)"""
     from b200ml.parallel.engine import DataParallelEngine
-    outs = []
-    for m in ("fused", "nccl"):
-        model = small_model(dev)
-        eng = DataParallelEngine(model, optimizer="adam", lr=1e-3, allreduce=m, bucket_mb=0.05)
-        train(model, eng, rank, world, dev, steps=3, global_batch=8, shard=True)
-        eng.weights_hash()
-        # state_dict() pulls the fp32 slices this rank does not own (bf16-only push), and is layout independent
-        outs.append(torch.cat([v.detach().reshape(-1).clone() for v in model.state_dict().values()]))
-        w16 = eng.flat.flat_w16.float()
-        assert (w16 - eng.flat.flat_p).abs().max().item() <= 0.01 * eng.flat.flat_p.abs().max().item()
-        eng.close()
-    err = (outs[0] - outs[1]).abs().max().item()
-    assert err < 1e-5, f"fused vs nccl differ by {err}"
-    print(f"[rank {rank}] fused_matches_nccl ok err={err:.3e}")
+    for optimizer, lr in (("sgd", 0.1), ("adam", 1e-3)):
+        outs = []
+        for m in ("fused", "nccl"):
+            model = small_model(dev)
+            eng = DataParallelEngine(model, optimizer=optimizer, lr=lr, allreduce=m, bucket_mb=0.05)
+            train(model, eng, rank, world, dev, steps=3, global_batch=8, shard=True)
+            eng.weights_hash()
+            # state_dict() pulls the fp32 slices this rank does not own (bf16-only push), and is layout independent
+            outs.append(torch.cat([v.detach().reshape(-1).clone() for v in model.state_dict().values()]))
+            w16 = eng.flat.flat_w16.float()
+            assert (w16 - eng.flat.flat_p).abs().max().item() <= 0.01 * eng.flat.flat_p.abs().max().item()
+            eng.close()
+        err = (outs[0] - outs[1]).abs()
+        if optimizer == "sgd":
+            assert err.max().item() < 1e-5, f"sgd: fused vs nccl differ by {err.max().item()}"
+        else:
+            assert (err > 1e-5).float().mean().item() < 0.01 and err.max().item() <= 3.5 * 3 * lr, \
+                f"adam: fused vs nccl differ by {err.max().item()}, {(err > 1e-5).float().mean().item():.4f} of the elements"
+    print(f"[rank {rank}] fused_matches_nccl ok err={err.max().item():.3e}")
 
 
 def case_allreduce_raw(rank, world, dev, mode):
@@ -133,7 +143,7 @@ def case_allreduce_raw(rank, world, dev, mode):
             comm.allreduce_update(start, n, 0, 0.0, (0.9, 0.999), 1e-8, 0.0, step, out=out, algo=1)
             torch.cuda.synchronize()
             assert (out[start:start + n] - expect[start:start + n]).abs().max().item() < 1e-5
-            assert out[:start].abs().max().item() == 0 if start else True
+            assert start == 0 or out[:start].abs().max().item() == 0
             # SGD
             p0 = flat.flat_p.clone()
             comm.allreduce_update(start, n, 1, 0.5, (0.9, 0.999), 1e-8, 0.0, step, algo=algo)
@@ -157,8 +167,8 @@ def case_allreduce_raw(rank, world, dev, mode):
             assert (flat.flat_p - want).abs().max().item() < 1e-4, f"adam algo {algo} range {(start, n)}"
             own = comm.owned_slice(start, n, sliced=algo != 1)
             lo, hi = (0, n) if own is None else own
-            assert (m[start + lo:start + hi] - 0.1 * g[lo:hi]).abs().max().item() < 1e-6 if hi > lo else True
-            outside = torch.cat([m[:start + lo], m[start + hi:]])
+            assert hi <= lo or (m[start + lo:start + hi] - 0.1 * g[lo:hi]).abs().max().item() < 1e-6
+            outside = torch.cat([m[:start + lo], m[start + hi:], m.new_zeros(1)])
             assert outside.abs().max().item() == 0, f"m written outside the owned slice, algo {algo} range {(start, n)}"
             dist.barrier()
     comm.close()

@@ -93,3 +93,19 @@ def test_graphed_step_is_plain_call_on_cpu_and_close_is_idempotent():
     eng.close()
     eng.close()                                  # a second close must be harmless
     pickle.loads(pickle.dumps(model))            # the module carries no engine state afterwards
+
+
+def test_big_parameters_get_their_own_bucket():
+    """A parameter of cap/4 or more never shares a bucket: the translator's embedding tables (ready at the very end of
+    backward) and output projection (ready at the very start) must not wait for their neighbours."""
+    from b200ml.parallel.reducer import NativeReducer, PyReducer
+    M = 1 << 20
+    sizes = [5 * M, M // 2, M // 4, 9 * M, M // 2, 9 * M, 64]      # emb, small, small, emb, small, head, bias
+    offsets = [0]
+    for s in sizes:
+        offsets.append(offsets[-1] + s)
+    cap = 6 * M + M // 2
+    for R in (NativeReducer, PyReducer):
+        r = R(offsets, [len(sizes)], cap)
+        assert [ids for _, _, ids, _ in r.buckets] == [[0], [1, 2], [3], [4], [5], [6]], R.__name__
+        r.close()
