@@ -118,23 +118,69 @@ embedding_bwd_kernel(const long long* __restrict__ tokens, const InT* __restrict
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// Deterministic backward.  Step 1 (embedding_index_kernel, ONE CTA): keys (token id << 32 | position) are sorted with
-// a bitonic network in shared memory; it only needs the token ids, so the op launches it at FORWARD time on an
-// auxiliary stream and it is off every critical path.  Step 2 (embedding_bwd_rows_kernel): one warp per TABLE ROW finds
-// its segment of the sorted keys by binary search, sums the gradient rows of its tokens in position order (dropout
-// mask regenerated per element), and writes the row once - zeros when no token of the batch maps to it.  No memset of
-// the 22 / 39 MB tables, no atomics, bit-identical results from run to run.
+// Deterministic backward in two launches.
+//
+// embedding_index_kernel (ONE CTA, launched at FORWARD time on an auxiliary stream - it needs the token ids only, so it
+// is off every critical path): sorts the keys (token id << 32 | position) with a bitonic network in shared memory, then
+// derives everything backward needs to run without searching: the start of every segment of equal tokens (`heads`,
+// by a block-wide scan of the boundary flags), the list of "hot" segments with more than kHotTokens tokens (the padding
+// id of the translator's batches collects ~3000 of the 6400, <sos> one per sentence), and a byte per table row that
+// says whether the batch touches it.
+//
+// embedding_bwd_sorted_kernel (one launch, three kinds of CTA by block index):
+//   fill     - one warp per table row: rows the batch does not touch (and the padding row) are written as zeros;
+//   segment  - one warp per segment of at most kHotTokens tokens: sums the gradient rows of its tokens in position
+//              order (positions fetched by the lanes at once and handed around by shuffle, four loads in flight,
+//              dropout mask regenerated per element) and writes the table row;
+//   hot      - a hot segment is summed in kHotWays interleaved ways (way w takes tokens w, w + kHotWays, ...), eight
+//              ways per CTA; the last CTA of a (row, column chunk) to finish adds the ways 0..kHotWays-1 in order.
+// Every table row is written exactly once per call; no memset of the 22 / 39 MB tables, no floating-point atomics, and
+// the order of every sum is fixed by the batch alone - bit-identical results from run to run.
 // ---------------------------------------------------------------------------------------------------------------
 constexpr int kIndexThreads = 1024;
 constexpr int kIndexMaxTokens = 16384;   // 128 KB of 64-bit keys
+constexpr int kHotTokens = 64;
+constexpr int kHotWays = 32;
+
+// Index buffer produced by embedding_index_kernel (all offsets in bytes from its start, 16-byte aligned pieces):
+//   keys   uint64[n]      sorted keys
+//   meta   int[4]         [0] number of segments, [1] number of hot segments
+//   heads  int[n + 1]     heads[k] = first sorted position of segment k; heads[nseg] = n
+//   hot    int[n / kHotTokens + 1]   segment numbers of the hot segments
+//   touched uint8[V]      1 when some token of the batch maps to the row
+struct IndexLayout {
+    size_t keys, meta, heads, hot, touched, total;
+    int hot_cap;
+};
+__host__ __device__ inline IndexLayout index_layout(int n, int V) {
+    IndexLayout L;
+    auto up = [](size_t x) { return (x + 15) / 16 * 16; };
+    L.hot_cap = n / kHotTokens + 1;
+    L.keys = 0;
+    L.meta = up((size_t)n * 8);
+    L.heads = L.meta + 16;
+    L.hot = up(L.heads + ((size_t)n + 1) * 4);
+    L.touched = up(L.hot + (size_t)L.hot_cap * 4);
+    L.total = up(L.touched + (size_t)V);
+    return L;
+}
 
 __global__ void __launch_bounds__(kIndexThreads, 1)
 embedding_index_kernel(const long long* __restrict__ tokens, int n_tokens, int n_pad, int V,
-                       unsigned long long* __restrict__ keys_out) {
+                       unsigned char* __restrict__ index) {
     extern __shared__ __align__(16) unsigned long long skeys[];
+    __shared__ int warp_sums[kIndexThreads / 32];
+    __shared__ int s_nhot;
     b200::pdl_trigger();
     b200::pdl_wait();
-    for (int i = threadIdx.x; i < n_pad; i += kIndexThreads) {
+    const IndexLayout L = index_layout(n_tokens, V);
+    unsigned long long* keys_out = reinterpret_cast<unsigned long long*>(index + L.keys);
+    int* meta = reinterpret_cast<int*>(index + L.meta);
+    int* heads = reinterpret_cast<int*>(index + L.heads);
+    int* hot = reinterpret_cast<int*>(index + L.hot);
+    unsigned char* touched = index + L.touched;
+    const int tid = threadIdx.x;
+    for (int i = tid; i < n_pad; i += kIndexThreads) {
         unsigned long long k = ~0ull;
         if (i < n_tokens) {
             long long t = tokens[i];
@@ -143,10 +189,12 @@ embedding_index_kernel(const long long* __restrict__ tokens, int n_tokens, int n
         }
         skeys[i] = k;
     }
+    for (int i = tid; i < V; i += kIndexThreads) touched[i] = 0;
+    if (tid == 0) s_nhot = 0;
     __syncthreads();
     for (int size = 2; size <= n_pad; size <<= 1) {
         for (int stride = size >> 1; stride > 0; stride >>= 1) {
-            for (int t = threadIdx.x; t < (n_pad >> 1); t += kIndexThreads) {
+            for (int t = tid; t < (n_pad >> 1); t += kIndexThreads) {
                 const int lo = 2 * t - (t & (stride - 1));      // index of the lower element of pair t
                 const int hi = lo + stride;
                 const bool up = (lo & size) == 0;
@@ -159,16 +207,55 @@ embedding_index_kernel(const long long* __restrict__ tokens, int n_tokens, int n
             __syncthreads();
         }
     }
-    for (int i = threadIdx.x; i < n_tokens; i += kIndexThreads) keys_out[i] = skeys[i];
-}
-
-__device__ __forceinline__ int lower_bound_key(const unsigned long long* __restrict__ keys, int n, unsigned long long k) {
-    int lo = 0, hi = n;
-    while (lo < hi) {
-        const int mid = (lo + hi) >> 1;
-        if (keys[mid] < k) lo = mid + 1; else hi = mid;
+    // sorted keys out; row flags; segment heads by a block-wide exclusive scan of the boundary flags.  Thread t owns
+    // the contiguous positions [t * per, (t + 1) * per).
+    const int per = n_pad / kIndexThreads > 0 ? n_pad / kIndexThreads : 1;
+    const int i0 = tid * per;
+    int local = 0;
+    for (int i = i0; i < i0 + per && i < n_tokens; ++i) {
+        const unsigned long long k = skeys[i];
+        keys_out[i] = k;
+        const unsigned row = (unsigned)(k >> 32);
+        const bool head = i == 0 || (unsigned)(skeys[i - 1] >> 32) != row;
+        if (head) {
+            touched[row] = 1;
+            ++local;
+        }
     }
-    return lo;
+    int incl = local;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((tid & 31) >= o) incl += v;
+    }
+    if ((tid & 31) == 31) warp_sums[tid >> 5] = incl;
+    __syncthreads();
+    if (tid < 32) {
+        int w = warp_sums[tid];
+        int wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, wi, o);
+            if (tid >= o) wi += v;
+        }
+        warp_sums[tid] = wi - w;   // exclusive prefix of the warp totals
+        if (tid == 31) {
+            meta[0] = wi;          // number of segments
+            heads[wi] = n_tokens;
+        }
+    }
+    __syncthreads();
+    int at = warp_sums[tid >> 5] + incl - local;
+    for (int i = i0; i < i0 + per && i < n_tokens; ++i) {
+        const bool head = i == 0 || (unsigned)(skeys[i - 1] >> 32) != (unsigned)(skeys[i] >> 32);
+        if (head) heads[at++] = i;
+    }
+    __syncthreads();               // heads[] written by this CTA are visible to it after the barrier
+    const int nseg = meta[0];
+    for (int k = tid; k < nseg; k += kIndexThreads)
+        if (heads[k + 1] - heads[k] > kHotTokens) hot[atomicAdd(&s_nhot, 1)] = k;   // at most n / kHotTokens of them
+    __syncthreads();
+    if (tid == 0) meta[1] = s_nhot;
 }
 
 // gradient of one token row: four consecutive columns starting at `col`, dropout mask regenerated
@@ -194,39 +281,41 @@ __device__ __forceinline__ float4 load_grad4(const InT* __restrict__ dout, long 
     return make_float4(g[0], g[1], g[2], g[3]);
 }
 
-// Rows with more than kHotTokens tokens of the batch (the padding id of the translator's batches collects ~3000 of
-// the 6400, <sos> one per sentence) would serialise thousands of dependent loads in one warp.  The row kernel hands
-// them to embedding_bwd_hot_kernel through a list in `state`; at most n_tokens / kHotTokens rows can qualify, which
-// bounds the list and the scratch.  Which rows are hot depends only on the batch, and each hot row is summed in a fixed
-// order (way w takes tokens w, w + kHotWays, ... of the segment; ways are added 0..kHotWays-1), so the result is
-// still the same on every run.
-constexpr int kHotTokens = 64;
-constexpr int kHotWays = 32;
-// state (ints, zero before first use): [0] number of hot rows, [1] CTA ticket of the hot kernel, [2 + 4*h ..] per hot
-// row: row, segment begin, segment end, unused; then per (hot row, column chunk) tickets
-__host__ __device__ __forceinline__ int hot_capacity(int n_tokens) { return n_tokens / kHotTokens + 1; }
+__device__ __forceinline__ void store_row4(float* __restrict__ o, float4 acc, int accumulate) {
+    if (accumulate) {
+        const float4 old = *reinterpret_cast<const float4*>(o);
+        acc.x += old.x; acc.y += old.y; acc.z += old.z; acc.w += old.w;
+    }
+    *reinterpret_cast<float4*>(o) = acc;
+}
 
+// tickets: int[hot_cap * n_chunks], zero before the first call and left zero by every call; partial: [hot][way][d]
 template <typename InT>
 __global__ void __launch_bounds__(256)
-embedding_bwd_rows_kernel(const unsigned long long* __restrict__ keys, const InT* __restrict__ dout,
-                          float* __restrict__ dtable, int n_tokens, int d, int V, long long padding_idx, float p,
-                          const RngState* __restrict__ rng, uint32_t site, int accumulate, int* __restrict__ state) {
+embedding_bwd_sorted_kernel(const unsigned char* __restrict__ index, const InT* __restrict__ dout,
+                            float* __restrict__ dtable, int n_tokens, int d, int V, long long padding_idx, float p,
+                            const RngState* __restrict__ rng, uint32_t site, int accumulate, int fill_blocks,
+                            int seg_blocks, int n_chunks, int hot_slots, int* __restrict__ tickets,
+                            float* __restrict__ partial) {
     b200::pdl_trigger();
     b200::pdl_wait();
-    const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    if (row >= V) return;
-    int seg_lo = 0, seg_hi = 0;
-    if (row != padding_idx) {
-        seg_lo = lower_bound_key(keys, n_tokens, (unsigned long long)row << 32);
-        seg_hi = lower_bound_key(keys, n_tokens, (unsigned long long)(row + 1) << 32);
-    }
-    if (seg_hi - seg_lo > kHotTokens) {
-        if (lane == 0) {
-            const int h = atomicAdd(&state[0], 1);   // < hot_capacity(n_tokens) by counting
-            state[2 + 4 * h] = row;
-            state[3 + 4 * h] = seg_lo;
-            state[4 + 4 * h] = seg_hi;
-        }
+    __shared__ int sh_last;
+    const IndexLayout L = index_layout(n_tokens, V);
+    const unsigned long long* keys = reinterpret_cast<const unsigned long long*>(index + L.keys);
+    const int* meta = reinterpret_cast<const int*>(index + L.meta);
+    const int* heads = reinterpret_cast<const int*>(index + L.heads);
+    const int* hot = reinterpret_cast<const int*>(index + L.hot);
+    const unsigned char* touched = index + L.touched;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // block order = scheduling order: the few long-running hot CTAs go first, the cheap fill CTAs last
+    const int hot_blocks = n_chunks * (kHotWays / 8) * hot_slots;
+    int blk = (int)blockIdx.x - hot_blocks;
+    if (blk >= seg_blocks) {  // ------------------------------------------------ rows without tokens
+        const int row = (blk - seg_blocks) * 8 + warp;
+        if (row >= V || accumulate) return;
+        if (touched[row] && row != padding_idx) return;
+        float4* o = reinterpret_cast<float4*>(dtable + (long long)row * d);
+        for (int c = lane; c < d / 4; c += 32) o[c] = make_float4(0.f, 0.f, 0.f, 0.f);
         return;
     }
     const bool drop = p > 0.f && rng != nullptr;
@@ -238,97 +327,85 @@ embedding_bwd_rows_kernel(const unsigned long long* __restrict__ keys, const InT
         thr = rng_thr16(p);
         ks = 1.f / (1.f - p);
     }
-    float* out = dtable + (long long)row * d;
-    for (int col = lane * 4; col < d; col += 128) {
-        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int s = seg_lo; s < seg_hi; ++s) {           // position order: deterministic sum
-            const float4 g = load_grad4(dout, (long long)(keys[s] & 0xFFFFFFFFull), d, col, drop, key, thr, ks);
-            acc.x += g.x; acc.y += g.y; acc.z += g.z; acc.w += g.w;
-        }
-        float4* o = reinterpret_cast<float4*>(out + col);
-        if (accumulate) {
-            const float4 old = *o;
-            acc.x += old.x; acc.y += old.y; acc.z += old.z; acc.w += old.w;
-        }
-        *o = acc;
-    }
-}
-
-// grid (column chunks of 128, kHotWays / 8, slots); 8 warps = 8 ways per CTA.  partial: [hot row][way][d] fp32.
-template <typename InT>
-__global__ void __launch_bounds__(256)
-embedding_bwd_hot_kernel(const unsigned long long* __restrict__ keys, const InT* __restrict__ dout,
-                         float* __restrict__ dtable, int n_tokens, int d, float p, const RngState* __restrict__ rng,
-                         uint32_t site, int accumulate, int* __restrict__ state, float* __restrict__ partial) {
-    b200::pdl_trigger();
-    b200::pdl_wait();
-    __shared__ int sh_last;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n_hot = state[0];
-    const int cap = hot_capacity(n_tokens);
-    int* tickets = state + 2 + 4 * cap;               // [hot row][column chunk]
-    const int chunk = blockIdx.x, n_chunks = gridDim.x;
-    const int way = blockIdx.y * 8 + warp;
-    const int col = chunk * 128 + lane * 4;
-    const bool drop = p > 0.f && rng != nullptr;
-    uint64_t key = 0;
-    uint32_t thr = 0;
-    float ks = 1.f;
-    if (drop) {
-        key = rng_key(rng->seed, rng->step, site);
-        thr = rng_thr16(p);
-        ks = 1.f / (1.f - p);
-    }
-    for (int h = blockIdx.z; h < n_hot; h += gridDim.z) {
-        const int row = state[2 + 4 * h], lo = state[3 + 4 * h], hi = state[4 + 4 * h];
-        if (col < d) {
+    if (blk >= 0) {  // ---------------------------------------------------------- ordinary segments
+        const int k = blk * 8 + warp;
+        if (k >= meta[0]) return;
+        const int lo = heads[k], len = heads[k + 1] - lo;
+        if (len > kHotTokens) return;
+        const int row = (int)(keys[lo] >> 32);
+        if (row == padding_idx) return;
+        int pos0 = 0, pos1 = 0;        // lane l holds the positions of tokens l and l + 32 of the segment
+        if (lane < len) pos0 = (int)(keys[lo + lane] & 0xFFFFFFFFull);
+        if (lane + 32 < len) pos1 = (int)(keys[lo + lane + 32] & 0xFFFFFFFFull);
+        float* out = dtable + (long long)row * d;
+        const int col_end = (d + 127) / 128 * 128;                  // uniform trip count for the shuffles
+        for (int col = lane * 4; col < col_end; col += 128) {
+            const bool on = col < d;
             float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-            int s = lo + way;
-            for (; s + 3 * kHotWays < hi; s += 4 * kHotWays) {   // four independent loads in flight, added in order
+            for (int t0 = 0; t0 < len; t0 += 4) {
                 float4 g[4];
 #pragma unroll
-                for (int u = 0; u < 4; ++u)
-                    g[u] = load_grad4(dout, (long long)(keys[s + u * kHotWays] & 0xFFFFFFFFull), d, col, drop, key, thr, ks);
+                for (int u = 0; u < 4; ++u) {
+                    const int t = t0 + u;
+                    const int pos = __shfl_sync(0xffffffffu, t < 32 ? pos0 : pos1, t & 31);
+                    g[u] = (t < len && on) ? load_grad4(dout, (long long)pos, d, col, drop, key, thr, ks)
+                                           : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
 #pragma unroll
                 for (int u = 0; u < 4; ++u) { acc.x += g[u].x; acc.y += g[u].y; acc.z += g[u].z; acc.w += g[u].w; }
             }
-            for (; s < hi; s += kHotWays) {
-                const float4 g = load_grad4(dout, (long long)(keys[s] & 0xFFFFFFFFull), d, col, drop, key, thr, ks);
-                acc.x += g.x; acc.y += g.y; acc.z += g.z; acc.w += g.w;
-            }
-            *reinterpret_cast<float4*>(partial + ((long long)h * kHotWays + way) * d + col) = acc;
+            if (on) store_row4(out + col, acc, accumulate);
         }
+        return;
+    }
+    blk = blockIdx.x;
+    // ------------------------------------------------------------------------- hot segments
+    const int n_hot = meta[1];
+    const int chunk = blk % n_chunks, wgrp = (blk / n_chunks) % (kHotWays / 8), slot = blk / (n_chunks * (kHotWays / 8));
+    const int way = wgrp * 8 + warp;
+    const int col = chunk * 128 + lane * 4;
+    const bool on = col < d;
+    for (int h = slot; h < n_hot; h += hot_slots) {
+        const int k = hot[h];
+        const int lo = heads[k], hi = heads[k + 1];
+        const int row = (int)(keys[lo] >> 32);
+        if (row == padding_idx) continue;                              // uniform over the CTA
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int cnt = hi - lo > way ? (hi - lo - way + kHotWays - 1) / kHotWays : 0;
+        for (int j0 = 0; j0 < cnt; j0 += 32) {   // the lanes fetch 32 positions at once, then walk them by shuffle
+            int mypos = 0;
+            if (j0 + lane < cnt) mypos = (int)(keys[lo + way + (j0 + lane) * kHotWays] & 0xFFFFFFFFull);
+            const int m = cnt - j0 < 32 ? cnt - j0 : 32;
+            for (int t0 = 0; t0 < m; t0 += 8) {
+                float4 g[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const int pos = __shfl_sync(0xffffffffu, mypos, (t0 + u) & 31);
+                    g[u] = (t0 + u < m && on) ? load_grad4(dout, (long long)pos, d, col, drop, key, thr, ks)
+                                              : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+#pragma unroll
+                for (int u = 0; u < 8; ++u) { acc.x += g[u].x; acc.y += g[u].y; acc.z += g[u].z; acc.w += g[u].w; }
+            }
+        }
+        if (on) *reinterpret_cast<float4*>(partial + ((long long)h * kHotWays + way) * d + col) = acc;
         __threadfence();
         __syncthreads();
-        if (threadIdx.x == 0) sh_last = atomicAdd(&tickets[h * n_chunks + chunk], 1) == (int)gridDim.y - 1;
+        if (threadIdx.x == 0) sh_last = atomicAdd(&tickets[h * n_chunks + chunk], 1) == kHotWays / 8 - 1;
         __syncthreads();
         if (sh_last) {                                   // the last CTA of this (row, chunk) adds the ways in order
             __threadfence();
-            if (warp == 0 && col < d) {
-                float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (warp == 0 && on) {
+                float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
                 for (int w = 0; w < kHotWays; ++w) {
                     const float4 t = __ldcg(reinterpret_cast<const float4*>(partial + ((long long)h * kHotWays + w) * d + col));
-                    acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+                    sum.x += t.x; sum.y += t.y; sum.z += t.z; sum.w += t.w;
                 }
-                float4* o = reinterpret_cast<float4*>(dtable + (long long)row * d + col);
-                if (accumulate) {
-                    const float4 old = *o;
-                    acc.x += old.x; acc.y += old.y; acc.z += old.z; acc.w += old.w;
-                }
-                *o = acc;
+                store_row4(dtable + (long long)row * d + col, sum, accumulate);
             }
             if (threadIdx.x == 0) tickets[h * n_chunks + chunk] = 0;   // ready for the next step / graph replay
         }
         __syncthreads();
-    }
-    // the very last CTA of the launch clears the hot-row count for the next step (every CTA has read it by then)
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        const int total = gridDim.x * gridDim.y * gridDim.z;
-        if (atomicAdd(&state[1], 1) == total - 1) {
-            state[1] = 0;
-            state[0] = 0;
-        }
     }
 }
 
@@ -386,13 +463,15 @@ int b200ml_embedding_bwd(const long long* tokens, const void* dout, int dout_fp3
 
 int b200ml_embedding_index_max_tokens(void) { return b200::emb::kIndexMaxTokens; }
 
-int b200ml_embedding_index(const long long* tokens, int n_tokens, int V, unsigned long long* keys_out,
-                           cudaStream_t stream) {
+size_t b200ml_embedding_index_bytes(int n_tokens, int V) { return b200::emb::index_layout(n_tokens, V).total; }
+
+int b200ml_embedding_index(const long long* tokens, int n_tokens, int V, void* index_out, cudaStream_t stream) {
     using namespace b200::emb;
-    B200_REQUIRE(tokens && keys_out, "embedding_index: null pointer");
+    B200_REQUIRE(tokens && index_out, "embedding_index: null pointer");
+    B200_REQUIRE((reinterpret_cast<uintptr_t>(index_out) & 15) == 0, "embedding_index: the index buffer must be 16-byte aligned");
     B200_REQUIRE(n_tokens > 0 && n_tokens <= kIndexMaxTokens, "embedding_index: n_tokens=%d outside (0, %d]", n_tokens,
                  kIndexMaxTokens);
-    int n_pad = 2;
+    int n_pad = kIndexThreads;              // at least one position per thread keeps the scan simple
     while (n_pad < n_tokens) n_pad <<= 1;
     const size_t smem = (size_t)n_pad * sizeof(unsigned long long);
     static bool attr = false;
@@ -401,49 +480,47 @@ int b200ml_embedding_index(const long long* tokens, int n_tokens, int V, unsigne
                                              kIndexMaxTokens * (int)sizeof(unsigned long long)));
         attr = true;
     }
-    b200::pdl(embedding_index_kernel, dim3(1), dim3(kIndexThreads), smem, stream)(tokens, n_tokens, n_pad, V, keys_out);
+    b200::pdl(embedding_index_kernel, dim3(1), dim3(kIndexThreads), smem, stream)(tokens, n_tokens, n_pad, V,
+                                                                                   (unsigned char*)index_out);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
 
 size_t b200ml_embedding_bwd_sorted_scratch_bytes(int n_tokens, int d) {
     using namespace b200::emb;
-    const size_t cap = (size_t)hot_capacity(n_tokens);
+    const size_t cap = (size_t)(n_tokens / kHotTokens + 1);
     const size_t chunks = ((size_t)d + 127) / 128;
-    const size_t state = (2 + 4 * cap + cap * chunks) * sizeof(int);
-    return (state + 255) / 256 * 256 + cap * kHotWays * (size_t)d * sizeof(float);
+    return (cap * chunks * sizeof(int) + 255) / 256 * 256 + cap * kHotWays * (size_t)d * sizeof(float);
 }
 
-int b200ml_embedding_bwd_sorted(const unsigned long long* keys_sorted, const void* dout, int dout_fp32, float* dtable,
-                                int n_tokens, int d, int V, long long padding_idx, float dropout_p,
-                                const void* rng_state, unsigned rng_site, int accumulate, void* scratch,
-                                size_t scratch_bytes, cudaStream_t stream) {
+int b200ml_embedding_bwd_sorted(const void* index, const void* dout, int dout_fp32, float* dtable, int n_tokens, int d,
+                                int V, long long padding_idx, float dropout_p, const void* rng_state,
+                                unsigned rng_site, int accumulate, void* scratch, size_t scratch_bytes,
+                                cudaStream_t stream) {
     using namespace b200::emb;
-    B200_REQUIRE(keys_sorted && dout && dtable && scratch, "embedding_bwd_sorted: null pointer");
-    B200_REQUIRE(d % 4 == 0 && V > 0 && n_tokens >= 0, "embedding_bwd_sorted: d=%d must be a multiple of 4", d);
+    B200_REQUIRE(index && dout && dtable && scratch, "embedding_bwd_sorted: null pointer");
+    B200_REQUIRE(d % 4 == 0 && V > 0 && n_tokens > 0 && n_tokens <= kIndexMaxTokens,
+                 "embedding_bwd_sorted: d=%d must be a multiple of 4 and n_tokens=%d in (0, %d]", d, n_tokens,
+                 kIndexMaxTokens);
     B200_REQUIRE(scratch_bytes >= b200ml_embedding_bwd_sorted_scratch_bytes(n_tokens, d),
                  "embedding_bwd_sorted: scratch too small (%zu bytes)", scratch_bytes);
-    const size_t cap = (size_t)hot_capacity(n_tokens);
+    const int cap = n_tokens / kHotTokens + 1;
     const int chunks = (d + 127) / 128;
-    int* state = (int*)scratch;
-    float* partial = (float*)((char*)scratch + ((2 + 4 * cap + cap * chunks) * sizeof(int) + 255) / 256 * 256);
-    const int grid = (V + 7) / 8;
-    int slots = (int)cap < 8 ? (int)cap : 8;
-    const dim3 hot_grid(chunks, kHotWays / 8, slots);
+    int* tickets = (int*)scratch;
+    float* partial = (float*)((char*)scratch + ((size_t)cap * chunks * sizeof(int) + 255) / 256 * 256);
+    const int fill_blocks = (V + 7) / 8;
+    const int seg_blocks = (n_tokens + 7) / 8;
+    const int slots = cap < 8 ? cap : 8;
+    const int grid = fill_blocks + seg_blocks + chunks * (kHotWays / 8) * slots;
     const b200::RngState* rng = (const b200::RngState*)rng_state;
-    if (dout_fp32) {
-        b200::pdl(embedding_bwd_rows_kernel<float>, dim3(grid), dim3(256), 0, stream)(
-            keys_sorted, (const float*)dout, dtable, n_tokens, d, V, padding_idx, dropout_p, rng, rng_site, accumulate, state);
-        b200::pdl(embedding_bwd_hot_kernel<float>, hot_grid, dim3(256), 0, stream)(
-            keys_sorted, (const float*)dout, dtable, n_tokens, d, dropout_p, rng, rng_site, accumulate, state, partial);
-    } else {
-        b200::pdl(embedding_bwd_rows_kernel<__nv_bfloat16>, dim3(grid), dim3(256), 0, stream)(
-            keys_sorted, (const __nv_bfloat16*)dout, dtable, n_tokens, d, V, padding_idx, dropout_p, rng, rng_site,
-            accumulate, state);
-        b200::pdl(embedding_bwd_hot_kernel<__nv_bfloat16>, hot_grid, dim3(256), 0, stream)(
-            keys_sorted, (const __nv_bfloat16*)dout, dtable, n_tokens, d, dropout_p, rng, rng_site, accumulate, state,
-            partial);
-    }
+    if (dout_fp32)
+        b200::pdl(embedding_bwd_sorted_kernel<float>, dim3(grid), dim3(256), 0, stream)(
+            (const unsigned char*)index, (const float*)dout, dtable, n_tokens, d, V, padding_idx, dropout_p, rng, rng_site,
+            accumulate, fill_blocks, seg_blocks, chunks, slots, tickets, partial);
+    else
+        b200::pdl(embedding_bwd_sorted_kernel<__nv_bfloat16>, dim3(grid), dim3(256), 0, stream)(
+            (const unsigned char*)index, (const __nv_bfloat16*)dout, dtable, n_tokens, d, V, padding_idx, dropout_p, rng,
+            rng_site, accumulate, fill_blocks, seg_blocks, chunks, slots, tickets, partial);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
 }

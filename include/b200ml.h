@@ -102,23 +102,24 @@ int b200ml_embedding_fwd(const long long* tokens, const void* table_bf16, const 
 int b200ml_embedding_bwd(const long long* tokens, const void* dout, int dout_fp32, float* dtable, int n_tokens, int d,
                          int V, long long padding_idx, float dropout_p, const void* rng_state, unsigned rng_site,
                          cudaStream_t stream);
-/* Deterministic backward in two steps.  b200ml_embedding_index sorts the keys (token id << 32 | position) of one batch
- * (single-CTA bitonic sort, n_tokens <= b200ml_embedding_index_max_tokens() = 16384; it depends on the token ids only
- * and can run at forward time).  b200ml_embedding_bwd_sorted gives each table row to one warp, which sums the dout rows
- * of its tokens in position order and WRITES the row (accumulate = 0: rows without tokens and the padding row become
- * zero, so the table needs no clearing; accumulate = 1 adds to what is there).  Rows with more than 64 tokens of the
- * batch (a padding id, <sos>) are summed by a second kernel in 32 interleaved ways through `scratch`
- * (b200ml_embedding_bwd_sorted_scratch_bytes; its first bytes are counters that must be ZERO before the first call
- * and are left zero by every call; calls that share a scratch buffer must not overlap).  Any sorted key array of that
- * form is accepted, whoever sorted it.  ref: nn.Embedding backward (transformer.py:52-61; distributed_lstm.py:115,128). */
+/* Deterministic backward in two launches.  b200ml_embedding_index (one CTA; n_tokens <=
+ * b200ml_embedding_index_max_tokens() = 16384; depends on the token ids only, so it can run at forward time) sorts the
+ * keys (token id << 32 | position) of one batch and writes, into a caller buffer of b200ml_embedding_index_bytes()
+ * bytes, the sorted keys, the start of every segment of equal tokens, the list of segments with more than 64 tokens
+ * and one byte per table row telling whether the batch touches it.  b200ml_embedding_bwd_sorted then WRITES every row
+ * of dtable exactly once: the sum over the row's tokens in position order, zeros for untouched rows and the padding
+ * row (accumulate = 0; the table needs no clearing), or adds to what is there (accumulate = 1).  Long segments are
+ * summed in 32 interleaved ways through `scratch` (b200ml_embedding_bwd_sorted_scratch_bytes; it starts with counters
+ * that must be ZERO before the first call and are left zero by every call; calls sharing a scratch must not overlap).
+ * ref: nn.Embedding backward (transformer.py:52-61; distributed_lstm.py:115,128). */
 int b200ml_embedding_index_max_tokens(void);
-int b200ml_embedding_index(const long long* tokens, int n_tokens, int V, unsigned long long* keys_out,
-                           cudaStream_t stream);
+size_t b200ml_embedding_index_bytes(int n_tokens, int V);
+int b200ml_embedding_index(const long long* tokens, int n_tokens, int V, void* index_out, cudaStream_t stream);
 size_t b200ml_embedding_bwd_sorted_scratch_bytes(int n_tokens, int d);
-int b200ml_embedding_bwd_sorted(const unsigned long long* keys_sorted, const void* dout, int dout_fp32, float* dtable,
-                                int n_tokens, int d, int V, long long padding_idx, float dropout_p,
-                                const void* rng_state, unsigned rng_site, int accumulate, void* scratch,
-                                size_t scratch_bytes, cudaStream_t stream);
+int b200ml_embedding_bwd_sorted(const void* index, const void* dout, int dout_fp32, float* dtable, int n_tokens, int d,
+                                int V, long long padding_idx, float dropout_p, const void* rng_state,
+                                unsigned rng_site, int accumulate, void* scratch, size_t scratch_bytes,
+                                cudaStream_t stream);
 
 /* ------------------------------------------------------------------------------------------------ K6 cross-entropy
  * ref: nn.CrossEntropyLoss (distributed_cnn.py:141) and ignore_index=0 + masked mean

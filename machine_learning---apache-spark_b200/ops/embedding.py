@@ -18,6 +18,7 @@ from .gemm import working_copy
 
 _vp, _i, _ll, _f, _u = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_uint
 _native_ext.register("b200ml_embedding_index", [_vp, _i, _i, _vp, _vp])
+_native_ext.register("b200ml_embedding_index_bytes", [_i, _i], size_t_return=True)
 _native_ext.register("b200ml_embedding_bwd_sorted", [_vp, _vp, _i, _vp, _i, _i, _i, _ll, _f, _vp, _u, _i, _vp,
                                                      C.c_size_t, _vp])
 _native_ext.register("b200ml_embedding_bwd_sorted_scratch_bytes", [_i, _i], size_t_return=True)
@@ -35,26 +36,24 @@ def _aux_stream(device) -> torch.cuda.Stream:
     return st
 
 
-def sorted_token_keys(tok: torch.Tensor, V: int):
-    """(keys, event): uint64 keys ``token << 32 | position`` of the flat token tensor, sorted, produced on the auxiliary
-    stream; ``event`` marks their completion.  Batches above INDEX_MAX_TOKENS are sorted by torch instead."""
+def build_token_index(tok: torch.Tensor, V: int):
+    """(index, event): the backward index of one batch (sorted ``token << 32 | position`` keys, segment starts, hot
+    segments, touched-row flags - csrc/kernels/embedding.cu IndexLayout), built by ONE CTA on the auxiliary stream;
+    ``event`` marks its completion.  Only called for batches of at most INDEX_MAX_TOKENS tokens."""
     n = tok.numel()
+    lib = _native.load()
     cur = torch.cuda.current_stream()
     aux = _aux_stream(tok.device)
-    # `keys` is allocated on the CURRENT stream (it is read there, in backward, after waiting for `event`) and only
+    # the buffer is allocated on the CURRENT stream (it is read there, in backward, after waiting for `event`) and only
     # written on the auxiliary one; `tok` is saved for backward, so both outlive the auxiliary kernel
-    keys = torch.empty(n, dtype=torch.int64, device=tok.device)
+    index = torch.empty(int(lib.b200ml_embedding_index_bytes(n, V)) // 8 + 1, dtype=torch.int64, device=tok.device)
     aux.wait_stream(cur)
     with torch.cuda.stream(aux):
-        if n <= INDEX_MAX_TOKENS:
-            _native.check(_native.load().b200ml_embedding_index(tok.data_ptr(), n, V, keys.data_ptr(),
-                                                                _native.stream_ptr()), "embedding_index")
-        else:
-            t = torch.where((tok < 0) | (tok >= V), torch.zeros_like(tok), tok)
-            keys.copy_(((t << 32) | torch.arange(n, device=tok.device)).sort().values)
+        _native.check(lib.b200ml_embedding_index(tok.data_ptr(), n, V, index.data_ptr(), _native.stream_ptr()),
+                      "embedding_index")
         ev = torch.cuda.Event()
         ev.record(aux)
-    return keys, ev
+    return index, ev
 
 
 def positional_encoding_table(S: int, d: int, device) -> torch.Tensor:
@@ -95,8 +94,8 @@ class _Embedding(torch.autograd.Function):
                 d, V, p, rng, site, _native.stream_ptr()), "embedding_fwd")
             keys = tok
             ctx.keys_event = None
-            if weight.requires_grad:
-                keys, ctx.keys_event = sorted_token_keys(tok, V)
+            if weight.requires_grad and n <= INDEX_MAX_TOKENS:
+                keys, ctx.keys_event = build_token_index(tok, V)
             ctx.save_for_backward(tok, keys)
             ctx.mask = None
             return out.reshape(*lead, d)
@@ -124,7 +123,6 @@ class _Embedding(torch.autograd.Function):
             g = dout.reshape(n, d).contiguous()
             if g.dtype not in (torch.float32, torch.bfloat16):
                 g = g.float()
-            # every row is written exactly once (zeros where the batch has no token), so nothing is cleared beforehand
             acc = 0
             if slot is not None:
                 dt = slot.view(V, d)
@@ -132,16 +130,25 @@ class _Embedding(torch.autograd.Function):
             else:
                 dt = torch.empty(V, d, dtype=torch.float32, device=weight.device)
             rng = DeviceCounters.get(weight.device).rng.data_ptr() if p > 0 else None
-            if ctx.keys_event is not None:
-                torch.cuda.current_stream().wait_event(ctx.keys_event)
             lib = _native.load()
-            nb = int(lib.b200ml_embedding_bwd_sorted_scratch_bytes(n, d))
-            # one scratch per table: the backward passes of two tables (encoder / decoder) may run concurrently
-            ws = workspace.get_zeroed(f"emb_bwd@{id(weight)}", nb, weight.device)
-            _native.check(lib.b200ml_embedding_bwd_sorted(
-                keys.data_ptr(), g.data_ptr(), int(g.dtype == torch.float32), dt.data_ptr(), n, d, V,
-                -1 if padding_idx is None else padding_idx, p, rng, site, acc, ws.data_ptr(), ws.numel(),
-                _native.stream_ptr()), "embedding_bwd_sorted")
+            pad = -1 if padding_idx is None else padding_idx
+            if ctx.keys_event is not None:
+                # sorted path: every row is written exactly once (zeros where the batch has no token): nothing is
+                # cleared beforehand, nothing is added atomically
+                torch.cuda.current_stream().wait_event(ctx.keys_event)
+                nb = int(lib.b200ml_embedding_bwd_sorted_scratch_bytes(n, d))
+                # one scratch per table: the backward passes of two tables (encoder / decoder) may run concurrently
+                ws = workspace.get_zeroed(f"emb_bwd@{id(weight)}", nb, weight.device)
+                _native.check(lib.b200ml_embedding_bwd_sorted(
+                    keys.data_ptr(), g.data_ptr(), int(g.dtype == torch.float32), dt.data_ptr(), n, d, V, pad, p, rng,
+                    site, acc, ws.data_ptr(), ws.numel(), _native.stream_ptr()), "embedding_bwd_sorted")
+            else:
+                # more tokens than the single-CTA sort takes: clear + fp32 atomicAdd scatter (sum order not fixed)
+                if not acc:
+                    dt.zero_()
+                _native.check(lib.b200ml_embedding_bwd(
+                    tok.data_ptr(), g.data_ptr(), int(g.dtype == torch.float32), dt.data_ptr(), n, d, V, pad, p, rng,
+                    site, _native.stream_ptr()), "embedding_bwd")
             if slot is not None:
                 ready = getattr(weight, "_b200_ready", None)
                 if ready is not None:

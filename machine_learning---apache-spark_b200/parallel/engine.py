@@ -140,6 +140,7 @@ class DataParallelEngine:
             self._opt_streams = [torch.cuda.Stream(device=self.device) for _ in range(n_opt)]
             self.comm_stream = self._opt_streams[0]
         self._in_step = False
+        self._streams_used: set = set()
 
     def _verify_layout(self) -> None:
         """Every rank must have built the same flat layout (what DDP's constructor verifies across ranks before it
@@ -185,6 +186,7 @@ class DataParallelEngine:
             return  # single fused optimizer launch in finish_step
         if self.comm_stream is not None:
             st = self._opt_streams[b % len(self._opt_streams)] if self._opt_streams else self.comm_stream
+            self._streams_used.add(st)
             st.wait_stream(torch.cuda.current_stream())
             for ev in self._events[b].values():
                 st.wait_event(ev)
@@ -237,8 +239,11 @@ class DataParallelEngine:
         for b in self.reducer.flush():
             self._bucket_ready(b, complete=False)
         if self.comm_stream is not None:
-            for st in (self._opt_streams or [self.comm_stream]):
+            # only the streams this step actually used: inside a graph capture, waiting on a stream that is not part
+            # of the capture is an error
+            for st in self._streams_used:
                 torch.cuda.current_stream().wait_stream(st)
+            self._streams_used.clear()
         if self.side is not None:
             self.side.join()
         # every backward kernel of this step is ordered before this point on the current stream (autograd joined its

@@ -154,11 +154,13 @@ def test_embedding_padding_idx():
     assert w.grad[3].sum().item() == pytest.approx(d)
 
 
-@pytest.mark.parametrize("n_tokens,V,d", [(6400, 19214, 512), (4128, 95815, 32), (37, 11, 64), (20000, 300, 64)])
+@pytest.mark.parametrize("n_tokens,V,d", [(6400, 19214, 512), (4128, 95815, 32), (37, 11, 64), (16384, 300, 64),
+                                          (20000, 300, 64)])
 def test_embedding_backward_is_deterministic_and_exact(n_tokens, V, d):
     """Sort + segment reduction: every table row written once, fp32 sums in position order -> identical bits on every
     run, equal to the fp32 index_add_ oracle up to summation order; untouched rows and the padding row are exactly 0
-    even when the gradient buffer held garbage.  20000 tokens exceed the single-CTA sort and take the torch.sort path."""
+    even when the gradient buffer held garbage.  20000 tokens exceed the single-CTA sort and take the atomicAdd path
+    (same values up to summation order, not bit-reproducible)."""
     from b200ml.ops.embedding import embedding
     torch.manual_seed(1)
     tok = torch.randint(0, V, (1, n_tokens), device="cuda")
@@ -171,7 +173,8 @@ def test_embedding_backward_is_deterministic_and_exact(n_tokens, V, d):
         out = embedding(tok, w, padding_idx=0, out_dtype=torch.float32)
         (out * gout).sum().backward()
         grads.append(w.grad.clone())
-    assert torch.equal(grads[0], grads[1]) and torch.equal(grads[0], grads[2])
+    if n_tokens <= 16384:
+        assert torch.equal(grads[0], grads[1]) and torch.equal(grads[0], grads[2])
     g = gout.reshape(-1, d).clone()
     g[tok.reshape(-1) == 0] = 0
     ref = torch.zeros(V, d, device="cuda", dtype=torch.float64).index_add_(0, tok.reshape(-1), g.double())
@@ -187,7 +190,10 @@ def test_embedding_backward_is_deterministic_and_exact(n_tokens, V, d):
     w._b200_grad.fill_(123.0)
     out = embedding(tok, w, padding_idx=0, out_dtype=torch.float32)
     (out * gout).sum().backward()
-    assert torch.equal(w._b200_grad.view(V, d), grads[0])
+    if n_tokens <= 16384:
+        assert torch.equal(w._b200_grad.view(V, d), grads[0])
+    else:
+        assert (w._b200_grad.view(V, d) - grads[0]).abs().max().item() <= 1e-5 * grads[0].abs().max().item()
 
 
 @pytest.mark.parametrize("rows,V,dtype", [(32, 10, torch.float32), (30, 3, torch.float32), (640, 19214, torch.bfloat16)])
