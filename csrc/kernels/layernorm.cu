@@ -1,7 +1,8 @@
 // b200ml — K11/K12: residual + dropout + LayerNorm, forward and backward, one warp per row.
 //
 //   forward : z = x + dropout(a) ;  y = gamma * (z - mean(z)) / sqrt(var(z) + eps) + beta     (biased variance)
-//   backward: dz, d_a (= dz with the regenerated dropout mask), dgamma, dbeta
+//   backward: dz, d_a (= dz with the regenerated dropout mask), dgamma, dbeta - and, on request, the column sums of
+//             d_a, which are the bias gradient of the Linear that produced `a` (saves that layer's own column-sum pass)
 //
 // Reference semantics: transformer.py:86-101 (LayerNormalization: params gamma/beta, eps inside the sqrt, biased
 // variance) used as norm(dropout(sublayer(x)) + x) at transformer.py:130-139,209-224.  The reference spends ~8
@@ -138,8 +139,9 @@ ln_fwd_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restri
     }
 }
 
-// Stage 1: each CTA walks rows (grid-stride), writes dz / d_a, and leaves per-CTA partial dgamma/dbeta in scratch.
-template <int kChunks>
+// Stage 1: each CTA walks rows (grid-stride), writes dz / d_a, and leaves per-CTA partial dgamma/dbeta in scratch
+// ([grid][2 * d]; kBias adds a third vector, the column sums of d_a: [grid][3 * d]).
+template <int kChunks, bool kBias = false>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ z,
               const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ gamma,
@@ -160,11 +162,14 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
         ks = 1.f / (1.f - p);
     }
     const int chunks = d / 256 + ((d % 256) ? 1 : 0);
-    float dg[kMaxChunks][8], db[kMaxChunks][8];
+    float dg[kMaxChunks][8], db[kMaxChunks][8], dbi[kBias ? kMaxChunks : 1][8];
 #pragma unroll
     for (int c = 0; c < kMaxChunks; ++c)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) dg[c][j] = db[c][j] = 0.f;
+        for (int j = 0; j < 8; ++j) {
+            dg[c][j] = db[c][j] = 0.f;
+            if (kBias) dbi[c][j] = 0.f;
+        }
 
     for (int row = blockIdx.x * kWarpsPerBlock + warp; row < rows; row += gridDim.x * kWarpsPerBlock) {
         const float mu = mean[row], rs = rstd[row];
@@ -214,22 +219,28 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
                     }
                     *reinterpret_cast<uint4*>(da + off) = pack8(o);
                 }
+                if (kBias) {   // o[] is d_a here (dz itself when there is no dropout)
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) dbi[c][j] += o[j];
+                }
             }
         }
     }
-    // block reduction of dgamma then dbeta across the 8 warps, through smem
+    // block reduction of dgamma, dbeta (and the bias column sums) across the 8 warps, through smem
+    constexpr int kVecs = kBias ? 3 : 2;
 #pragma unroll
-    for (int pass = 0; pass < 2; ++pass) {
+    for (int pass = 0; pass < kVecs; ++pass) {
 #pragma unroll
         for (int c = 0; c < kMaxChunks; ++c)
 #pragma unroll
-            for (int j = 0; j < 8; ++j) red[warp][c * 256 + lane * 8 + j] = pass == 0 ? dg[c][j] : db[c][j];
+            for (int j = 0; j < 8; ++j)
+                red[warp][c * 256 + lane * 8 + j] = pass == 0 ? dg[c][j] : (pass == 1 ? db[c][j] : dbi[kBias ? c : 0][j]);
         __syncthreads();
         for (int col = threadIdx.x; col < d; col += blockDim.x) {
             float t = 0.f;
 #pragma unroll
             for (int w = 0; w < kWarpsPerBlock; ++w) t += red[w][col];
-            partial[((long long)blockIdx.x * 2 + pass) * d + col] = t;
+            partial[((long long)blockIdx.x * kVecs + pass) * d + col] = t;
         }
         __syncthreads();
     }
@@ -246,6 +257,12 @@ static void launch_ln_bwd(int d, int grid, cudaStream_t stream, Args... args) {
     if (d <= 256) b200::pdl(ln_bwd_kernel<1>, dim3(grid), dim3(kWarpsPerBlock * 32), 0, stream)(args...);
     else if (d <= 512) b200::pdl(ln_bwd_kernel<2>, dim3(grid), dim3(kWarpsPerBlock * 32), 0, stream)(args...);
     else b200::pdl(ln_bwd_kernel<4>, dim3(grid), dim3(kWarpsPerBlock * 32), 0, stream)(args...);
+}
+template <typename... Args>
+static void launch_ln_bwd_bias(int d, int grid, cudaStream_t stream, Args... args) {
+    if (d <= 256) b200::pdl(ln_bwd_kernel<1, true>, dim3(grid), dim3(kWarpsPerBlock * 32), 0, stream)(args...);
+    else if (d <= 512) b200::pdl(ln_bwd_kernel<2, true>, dim3(grid), dim3(kWarpsPerBlock * 32), 0, stream)(args...);
+    else b200::pdl(ln_bwd_kernel<4, true>, dim3(grid), dim3(kWarpsPerBlock * 32), 0, stream)(args...);
 }
 
 static int bwd_grid(int rows) {
@@ -276,7 +293,29 @@ int b200ml_layernorm_fwd(const void* a, const void* x, const float* gamma, const
 }
 
 size_t b200ml_layernorm_bwd_scratch_bytes(int rows, int d) {
-    return (size_t)b200::ln::bwd_grid(rows) * 2 * (size_t)d * sizeof(float);
+    return (size_t)b200::ln::bwd_grid(rows) * 3 * (size_t)d * sizeof(float);   // room for the optional third vector
+}
+
+int b200ml_layernorm_bwd_bias(const void* dy, const void* z, const float* mean, const float* rstd, const float* gamma,
+                              void* dz, void* da, float* dgamma, float* dbeta, float* dbias_a, void* scratch,
+                              size_t scratch_bytes, int rows, int d, float dropout_p, const void* rng_state,
+                              unsigned rng_site, int accumulate, int accumulate_bias, cudaStream_t stream) {
+    using namespace b200::ln;
+    B200_REQUIRE(dy && z && mean && rstd && gamma && dz && dgamma && dbeta && dbias_a && scratch,
+                 "layernorm_bwd_bias: null pointer");
+    B200_REQUIRE(d % 8 == 0 && d <= kMaxChunks * 256, "layernorm_bwd_bias: d=%d must be a multiple of 8 and <= %d", d,
+                 kMaxChunks * 256);
+    if (rows <= 0) return 0;
+    const int grid = bwd_grid(rows);
+    B200_REQUIRE(scratch_bytes >= (size_t)grid * 3 * d * sizeof(float), "layernorm_bwd_bias: scratch too small (%zu < %zu)",
+                 scratch_bytes, (size_t)grid * 3 * d * sizeof(float));
+    launch_ln_bwd_bias(d, grid, stream,
+        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)z, mean, rstd, gamma, (__nv_bfloat16*)dz, (__nv_bfloat16*)da,
+        (float*)scratch, rows, d, dropout_p, (const b200::RngState*)rng_state, rng_site);
+    B200_CHECK_CUDA(cudaGetLastError());
+    B200_CHECK_CUDA(b200::launch_reduce_partials((const float*)scratch, grid, 3 * d, d, dgamma, dbeta, accumulate, stream,
+                                                 dbias_a, accumulate_bias));
+    return 0;
 }
 
 int b200ml_layernorm_bwd(const void* dy, const void* z, const float* mean, const float* rstd, const float* gamma,

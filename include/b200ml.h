@@ -70,6 +70,15 @@ int b200ml_layernorm_bwd(const void* dy, const void* z, const float* mean, const
                          int d, float dropout_p, const void* rng_state, unsigned rng_site, int accumulate,
                          cudaStream_t stream);
 
+/* The same, plus dbias_a[d] = column sums of d_a (of dz when there is no dropout): the bias gradient of the Linear whose
+ * output `a` was, produced from the registers that hold d_a anyway instead of by a separate pass over it.  scratch:
+ * b200ml_layernorm_bwd_scratch_bytes.  ref: the bias of every Linear that feeds a residual LayerNorm
+ * (transformer.py:108,130-139; 177-179,209-224). */
+int b200ml_layernorm_bwd_bias(const void* dy, const void* z, const float* mean, const float* rstd, const float* gamma,
+                              void* dz, void* da, float* dgamma, float* dbeta, float* dbias_a, void* scratch,
+                              size_t scratch_bytes, int rows, int d, float dropout_p, const void* rng_state,
+                              unsigned rng_site, int accumulate, int accumulate_bias, cudaStream_t stream);
+
 /* LayerNorm backward WITHOUT caller scratch and without any allocation (no counterpart in the reference; added for
  * hosts that may not allocate).  Same arguments and results as b200ml_layernorm_bwd minus (scratch, scratch_bytes): the
  * per-CTA partial sums of dgamma/dbeta go to a ~2.3 MiB array that is compiled into the library and lives on every GPU

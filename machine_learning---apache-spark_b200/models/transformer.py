@@ -103,14 +103,24 @@ class MultiHeadAttention(nn.Module):
         self.qkv_layer = nn.Linear(d_model, 3 * d_model)
         self.linear_layer = nn.Linear(d_model, d_model)
 
-    def forward(self, x, mask=None, mask_mode: str = "reference", decoder: bool = False):
+    def forward(self, x, mask=None, mask_mode: str = "reference", decoder: bool = False, fork: bool = False,
+                skip_out_bias_grad: bool = False):
+        """``fork`` / ``skip_out_bias_grad`` are used by the encoder / decoder layers: with ``fork`` the result is
+        ``(out, x_skip)`` where ``x_skip`` is ``x`` routed through the qkv projection's autograd node (its backward adds
+        the residual branch's gradient in the dgrad GEMM epilogue); ``skip_out_bias_grad`` leaves the output
+        projection's bias gradient to the LayerNorm that consumes ``out`` (ops/norm.py ``a_bias``)."""
         kind = _mask_kind(mask, mask_mode, decoder)
-        qkv = _linear(x, self.qkv_layer.weight, self.qkv_layer.bias)
+        x_skip = None
+        if fork:
+            qkv, x_skip = _linear(x, self.qkv_layer.weight, self.qkv_layer.bias, fork=True)
+        else:
+            qkv = _linear(x, self.qkv_layer.weight, self.qkv_layer.bias)
         if isinstance(kind, torch.Tensor):
             values = _generic_attention(qkv, None, self.num_heads, kind)
         else:
             values = _att.attention(qkv, num_heads=self.num_heads, mask_mode=kind)
-        return _linear(values, self.linear_layer.weight, self.linear_layer.bias)
+        out = _linear(values, self.linear_layer.weight, self.linear_layer.bias, skip_bias_grad=skip_out_bias_grad)
+        return (out, x_skip) if fork else out
 
 
 def _generic_attention(qsrc, kvsrc, H, mask):
@@ -130,15 +140,22 @@ class LayerNormalization(nn.Module):
         self.gamma = nn.Parameter(torch.ones(parameters_shape))
         self.beta = nn.Parameter(torch.zeros(parameters_shape))
 
-    def forward(self, inputs, residual=None, dropout_p: float = 0.0, site: int = 0):
+    @property
+    def fusable(self) -> bool:
+        """True when the fused kernel path is taken (1-D parameters): only then may a producer leave its bias
+        gradient to this LayerNorm (``a_bias``)."""
+        return len(self.parameters_shape) == 1
+
+    def forward(self, inputs, residual=None, dropout_p: float = 0.0, site: int = 0, a_bias=None):
         """LN(dropout(inputs) + residual); with the defaults this is the reference's plain LayerNormalization."""
         if len(self.parameters_shape) != 1:
+            assert a_bias is None
             dims = [-(i + 1) for i in range(len(self.parameters_shape))]
             z = inputs if residual is None else inputs + residual
             mean = z.mean(dim=dims, keepdim=True)
             var = ((z - mean) ** 2).mean(dim=dims, keepdim=True)
             return self.gamma * ((z - mean) / (var + self.eps).sqrt()) + self.beta
-        return _ln_res(inputs, residual, self.gamma, self.beta, self.eps, dropout_p, site, self.training)
+        return _ln_res(inputs, residual, self.gamma, self.beta, self.eps, dropout_p, site, self.training, a_bias)
 
 
 class PositionwiseFeedForward(nn.Module):
@@ -150,9 +167,11 @@ class PositionwiseFeedForward(nn.Module):
         self.dropout = nn.Dropout(p=drop_prob)
         self._site = new_site()
 
-    def forward(self, x):
+    def forward(self, x, fork: bool = False, skip_out_bias_grad: bool = False):
+        """With ``fork`` the result is ``(out, x_skip)``; see MultiHeadAttention.forward."""
         return _mlp_chain(x, [self.linear1.weight, self.linear2.weight], [self.linear1.bias, self.linear2.bias],
-                          ["relu", None], [self.dropout.p, 0.0], [self._site, 0], self.training)
+                          ["relu", None], [self.dropout.p, 0.0], [self._site, 0], self.training, fork=fork,
+                          skip_last_bias_grad=skip_out_bias_grad)
 
 
 class EncoderLayer(nn.Module):
@@ -168,10 +187,16 @@ class EncoderLayer(nn.Module):
         self.mask_mode = "reference"
 
     def forward(self, x, self_attention_mask=None):
-        a = self.attention(x, mask=self_attention_mask, mask_mode=self.mask_mode, decoder=False)
-        x = self.norm1(a, x, self.dropout1.p, self._sites[0])
-        f = self.ffn(x)
-        return self.norm2(f, x, self.dropout2.p, self._sites[1])
+        # Each sub-layer is LN(dropout(sub(x)) + x).  `x` reaches the LayerNorm through the sub-layer's first GEMM node
+        # (fork), so backward adds the two gradients of `x` in that GEMM's epilogue instead of in an elementwise
+        # kernel, and the bias gradient of the sub-layer's last Linear comes out of the LayerNorm backward kernel.
+        f1, f2 = self.norm1.fusable, self.norm2.fusable
+        a, x_skip = self.attention(x, mask=self_attention_mask, mask_mode=self.mask_mode, decoder=False, fork=True,
+                                   skip_out_bias_grad=f1)
+        x = self.norm1(a, x_skip, self.dropout1.p, self._sites[0],
+                       a_bias=self.attention.linear_layer.bias if f1 else None)
+        f, x_skip = self.ffn(x, fork=True, skip_out_bias_grad=f2)
+        return self.norm2(f, x_skip, self.dropout2.p, self._sites[1], a_bias=self.ffn.linear2.bias if f2 else None)
 
 
 class SequentialEncoder(nn.Sequential):
@@ -204,16 +229,23 @@ class MultiHeadCrossAttention(nn.Module):
         self.q_layer = nn.Linear(d_model, d_model)
         self.linear_layer = nn.Linear(d_model, d_model)
 
-    def forward(self, x, y, mask=None, mask_mode: str = "reference"):
-        """x: encoder output (keys/values), y: decoder stream (queries)."""
+    def forward(self, x, y, mask=None, mask_mode: str = "reference", fork: bool = False,
+                skip_out_bias_grad: bool = False):
+        """x: encoder output (keys/values), y: decoder stream (queries).  ``fork``: returns ``(out, y_skip)`` with
+        ``y`` routed through the query projection's autograd node; see MultiHeadAttention.forward."""
         kind = _mask_kind(mask, mask_mode, False)
         kv = _linear(x, self.kv_layer.weight, self.kv_layer.bias)
-        q = _linear(y, self.q_layer.weight, self.q_layer.bias)
+        y_skip = None
+        if fork:
+            q, y_skip = _linear(y, self.q_layer.weight, self.q_layer.bias, fork=True)
+        else:
+            q = _linear(y, self.q_layer.weight, self.q_layer.bias)
         if isinstance(kind, torch.Tensor):
             values = _generic_attention(q, kv, self.num_heads, kind)
         else:
             values = _att.attention(q, kv, num_heads=self.num_heads, mask_mode=kind)
-        return _linear(values, self.linear_layer.weight, self.linear_layer.bias)
+        out = _linear(values, self.linear_layer.weight, self.linear_layer.bias, skip_bias_grad=skip_out_bias_grad)
+        return (out, y_skip) if fork else out
 
 
 class DecoderLayer(nn.Module):
@@ -233,16 +265,23 @@ class DecoderLayer(nn.Module):
 
     def forward_self(self, y, self_attention_mask=None):
         """Self-attention sub-layer: the part of the decoder layer that does not depend on the encoder output."""
-        a = self.self_attention(y, mask=self_attention_mask, mask_mode=self.mask_mode, decoder=True)
-        return self.layer_norm1(a, y, self.dropout1.p, self._sites[0])
+        f1 = self.layer_norm1.fusable
+        a, y_skip = self.self_attention(y, mask=self_attention_mask, mask_mode=self.mask_mode, decoder=True, fork=True,
+                                        skip_out_bias_grad=f1)
+        return self.layer_norm1(a, y_skip, self.dropout1.p, self._sites[0],
+                                a_bias=self.self_attention.linear_layer.bias if f1 else None)
 
     def forward(self, x, y, self_attention_mask=None, cross_attention_mask=None, self_done: bool = False):
         if not self_done:
             y = self.forward_self(y, self_attention_mask)
-        c = self.encoder_decoder_attention(x, y, mask=cross_attention_mask, mask_mode=self.mask_mode)
-        y = self.layer_norm2(c, y, self.dropout2.p, self._sites[1])
-        f = self.ffn(y)
-        return self.layer_norm3(f, y, self.dropout3.p, self._sites[2])
+        f2, f3 = self.layer_norm2.fusable, self.layer_norm3.fusable
+        c, y_skip = self.encoder_decoder_attention(x, y, mask=cross_attention_mask, mask_mode=self.mask_mode, fork=True,
+                                                   skip_out_bias_grad=f2)
+        y = self.layer_norm2(c, y_skip, self.dropout2.p, self._sites[1],
+                             a_bias=self.encoder_decoder_attention.linear_layer.bias if f2 else None)
+        f, y_skip = self.ffn(y, fork=True, skip_out_bias_grad=f3)
+        return self.layer_norm3(f, y_skip, self.dropout3.p, self._sites[2],
+                                a_bias=self.ffn.linear2.bias if f3 else None)
 
 
 class SequentialDecoder(nn.Sequential):

@@ -229,10 +229,15 @@ class _MLPChain(torch.autograd.Function):
 
     Saves only the layer inputs (bf16).  Backward per layer: dW = dZᵀ·X, db = colsum(dZ), dX = dZ·W with the previous
     layer's activation derivative applied in the dgrad epilogue (aux_mode 1 / 3), so no elementwise pass exists.
-    """
+
+    ``fork``: the op also returns its input as a second output, to be used as the residual branch of the LayerNorm
+    that closes the sub-layer (y = LN(chain(x) + x)).  Autograd then hands backward the residual branch's gradient
+    separately instead of summing it with an elementwise kernel, and the first layer's dgrad GEMM adds it in its
+    epilogue (aux_mode 2): dX = dZ·W + d_skip.  ``skip_last_bias``: the last layer's bias gradient is produced elsewhere
+    (by the LayerNorm backward that consumes this op's output, ops/norm.py)."""
 
     @staticmethod
-    def forward(ctx, x, n_layers, acts, drops, sites, *params):
+    def forward(ctx, x, n_layers, acts, drops, sites, fork, skip_last_bias, *params):
         weights = params[:n_layers]
         biases = params[n_layers:]
         lead = x.shape[:-1]
@@ -250,17 +255,21 @@ class _MLPChain(torch.autograd.Function):
             h = gemm(h, w16, bias=None if b is None else b.detach(), act=acts[i], dropout_p=drops[i], site=sites[i],
                      out_dtype=torch.bfloat16 if native else h.dtype)
         ctx.n_layers, ctx.acts, ctx.drops = n_layers, acts, drops
+        ctx.fork, ctx.skip_last_bias = fork, skip_last_bias
         ctx.params = params
         ctx.x_dtype = x.dtype
         ctx.save_for_backward(*inputs, h)
-        return h.reshape(*lead, h.shape[-1])
+        out = h.reshape(*lead, h.shape[-1])
+        return (out, x) if fork else out
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, dskip=None):
         n = ctx.n_layers
         weights, biases = ctx.params[:n], ctx.params[n:]
         saved = ctx.saved_tensors
         inputs, y = saved[:n], saved[n]
+        if dy is None:   # only the skip output was used
+            return (dskip, None, None, None, None, None, None, *([None] * (2 * n)))
         dz = dy.reshape(-1, dy.shape[-1])
         native = _native.use_native(dz)
         cdt = torch.bfloat16 if native else y.dtype
@@ -295,6 +304,13 @@ class _MLPChain(torch.autograd.Function):
                 elif i > 0 and ctx.acts[i - 1] == ACT_SIGMOID:
                     assert ctx.drops[i - 1] == 0, "sigmoid followed by dropout is not fused"
                     dz = gemm(dz, w16, b_mn=True, aux=xin, aux_mode=3, out_dtype=cdt)
+                elif i == 0 and dskip is not None:
+                    sk = dskip.reshape(-1, K)
+                    if sk.dtype != cdt:
+                        sk = sk.to(cdt)
+                    if not sk.is_contiguous():
+                        sk = sk.contiguous()
+                    dz = gemm(dz, w16, b_mn=True, aux=sk, aux_mode=2, out_dtype=cdt)   # dX = dZ·W + d_skip
                 else:
                     dz = gemm(dz, w16, b_mn=True, out_dtype=cdt)
                 if i == 0:
@@ -303,22 +319,27 @@ class _MLPChain(torch.autograd.Function):
                 gw[i] = deliver_grad(w, lambda out, acc, g=dz_this, xin=xin: gemm(g, xin, a_mn=True, b_mn=True, out=out,
                                                                                  accumulate=acc), (N, K))
             b = biases[i]
-            if b is not None and b.requires_grad:
+            if b is not None and b.requires_grad and not (ctx.skip_last_bias and i == n - 1):
                 gb[i] = deliver_grad(b, lambda out, acc, g=dz_this: colsum(g, out=out, accumulate=acc), (N,))
         if dx is not None:
             dx = dx.reshape(*dy.shape[:-1], dx.shape[-1]).to(ctx.x_dtype)
-        return (dx, None, None, None, None, *gw, *gb)
+        elif dskip is not None and ctx.needs_input_grad[0]:
+            dx = dskip
+        return (dx, None, None, None, None, None, None, *gw, *gb)
 
 
-def mlp_chain(x, weights, biases, acts, drops=None, sites=None, training: bool = True):
-    """Fused chain of Linear layers; ``acts[i]`` follows layer i ('relu' | 'sigmoid' | None), ``drops[i]`` follows it."""
+def mlp_chain(x, weights, biases, acts, drops=None, sites=None, training: bool = True, fork: bool = False,
+              skip_last_bias_grad: bool = False):
+    """Fused chain of Linear layers; ``acts[i]`` follows layer i ('relu' | 'sigmoid' | None), ``drops[i]`` follows it.
+    ``fork=True`` returns ``(y, x_skip)``; see _MLPChain."""
     n = len(weights)
     acts = tuple(_ACT[a] for a in acts)
     drops = tuple((d if training else 0.0) for d in (drops or [0.0] * n))
     sites = tuple(sites or [0] * n)
-    return _MLPChain.apply(x, n, acts, drops, sites, *weights, *biases)
+    return _MLPChain.apply(x, n, acts, drops, sites, bool(fork), bool(skip_last_bias_grad), *weights, *biases)
 
 
-def linear(x, weight, bias=None, act=None, dropout_p: float = 0.0, site: int = 0, training: bool = True):
+def linear(x, weight, bias=None, act=None, dropout_p: float = 0.0, site: int = 0, training: bool = True,
+           fork: bool = False, skip_bias_grad: bool = False):
     """y = dropout(act(x·Wᵀ + b)) — nn.Linear with its activation/dropout fused into the GEMM epilogue."""
-    return mlp_chain(x, [weight], [bias], [act], [dropout_p], [site], training)
+    return mlp_chain(x, [weight], [bias], [act], [dropout_p], [site], training, fork, skip_bias_grad)

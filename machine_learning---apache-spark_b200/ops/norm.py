@@ -7,15 +7,25 @@ from __future__ import annotations
 
 import torch
 
-from .. import _native
+import ctypes as C
+
+from .. import _native, _native_ext
 from ..utils import workspace
 from ..utils.rng import DeviceCounters
 from .gemm import deliver_grad
 
 
+_vp, _i, _f, _u = C.c_void_p, C.c_int, C.c_float, C.c_uint
+_native_ext.register("b200ml_layernorm_bwd_bias", [_vp] * 11 + [C.c_size_t, _i, _i, _f, _vp, _u, _i, _i, _vp])
+
+
 class _LayerNormResidual(torch.autograd.Function):
+    """``a_bias`` (optional) is the bias of the Linear that produced ``a``: its gradient is the column sum of d_a, which
+    the backward kernel has in registers anyway; the producing op is then told to skip its own bias-gradient pass
+    (``skip_last_bias_grad`` of ops.gemm.mlp_chain / linear)."""
+
     @staticmethod
-    def forward(ctx, a, x, gamma, beta, eps, p, site):
+    def forward(ctx, a, x, gamma, beta, eps, p, site, a_bias=None):
         d = gamma.numel()
         lead = a.shape
         a2 = a.reshape(-1, d)
@@ -23,6 +33,7 @@ class _LayerNormResidual(torch.autograd.Function):
         rows = a2.shape[0]
         ctx.p, ctx.site, ctx.has_x = p, site, x is not None
         ctx.params = (gamma, beta)
+        ctx.a_bias = a_bias
         ctx.in_dtype = a.dtype
         if _native.use_native(a2):
             a2 = a2.to(torch.bfloat16).contiguous()
@@ -80,10 +91,29 @@ class _LayerNormResidual(torch.autograd.Function):
                 dg = torch.empty(d, dtype=torch.float32, device=z.device)
                 db = torch.empty(d, dtype=torch.float32, device=z.device)
                 acc = 0
-            _native.check(lib.b200ml_layernorm_bwd(dy2.data_ptr(), z.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
-                                                   gamma.data_ptr(), dz.data_ptr(), _native.ptr(da), dg.data_ptr(),
-                                                   db.data_ptr(), ws.data_ptr(), ws.numel(), rows, d, ctx.p, rng,
-                                                   ctx.site, acc, _native.stream_ptr()), "layernorm_bwd")
+            ab = ctx.a_bias
+            dab = None
+            if ab is not None and ab.requires_grad:
+                slot_ab = getattr(ab, "_b200_grad", None)
+                if slot_ab is not None:
+                    dab_t, acc_ab = slot_ab, int(bool(getattr(ab, "_b200_grad_accumulate", False)))
+                else:
+                    dab_t, acc_ab = torch.empty(d, dtype=torch.float32, device=z.device), 0
+                _native.check(lib.b200ml_layernorm_bwd_bias(
+                    dy2.data_ptr(), z.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gamma.data_ptr(), dz.data_ptr(),
+                    _native.ptr(da), dg.data_ptr(), db.data_ptr(), dab_t.data_ptr(), ws.data_ptr(), ws.numel(), rows, d,
+                    ctx.p, rng, ctx.site, acc, acc_ab, _native.stream_ptr()), "layernorm_bwd_bias")
+                if slot_ab is not None:
+                    ready = getattr(ab, "_b200_ready", None)
+                    if ready is not None:
+                        ready()
+                else:
+                    dab = dab_t
+            else:
+                _native.check(lib.b200ml_layernorm_bwd(dy2.data_ptr(), z.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
+                                                       gamma.data_ptr(), dz.data_ptr(), _native.ptr(da), dg.data_ptr(),
+                                                       db.data_ptr(), ws.data_ptr(), ws.numel(), rows, d, ctx.p, rng,
+                                                       ctx.site, acc, _native.stream_ptr()), "layernorm_bwd")
             if direct:
                 for prm in (gamma, beta):
                     ready = getattr(prm, "_b200_ready", None)
@@ -92,7 +122,7 @@ class _LayerNormResidual(torch.autograd.Function):
                 dg = db = None
             dz_r = dz.reshape(dy.shape)
             da_r = dz_r if da is None else da.reshape(dy.shape)
-            return da_r, (dz_r if ctx.has_x else None), dg, db, None, None, None
+            return da_r, (dz_r if ctx.has_x else None), dg, db, None, None, None, dab
         dyf = dy2.float()
         xh = (z - mean[:, None]) * rstd[:, None]
         dg = (dyf * xh).sum(0)
@@ -104,11 +134,16 @@ class _LayerNormResidual(torch.autograd.Function):
         da = dz if ctx.mask is None else dz * ctx.mask
         dgo = deliver_grad(gamma, lambda out, acc: out.add_(dg) if acc else out.copy_(dg), (d,))
         dbo = deliver_grad(beta, lambda out, acc: out.add_(db) if acc else out.copy_(db), (d,))
+        dab = None
+        if ctx.a_bias is not None and ctx.a_bias.requires_grad:
+            s_a = da.sum(0)
+            dab = deliver_grad(ctx.a_bias, lambda out, acc: out.add_(s_a) if acc else out.copy_(s_a), (d,))
         return (da.to(ctx.in_dtype).reshape(dy.shape), dz.to(ctx.in_dtype).reshape(dy.shape) if ctx.has_x else None,
-                dgo, dbo, None, None, None)
+                dgo, dbo, None, None, None, dab)
 
 
 def layernorm_residual(a, residual, gamma, beta, eps: float = 1e-5, dropout_p: float = 0.0, site: int = 0,
-                       training: bool = True):
-    """LayerNorm(dropout(a) + residual) over the last dimension (``residual`` may be None)."""
-    return _LayerNormResidual.apply(a, residual, gamma, beta, eps, dropout_p if training else 0.0, site)
+                       training: bool = True, a_bias=None):
+    """LayerNorm(dropout(a) + residual) over the last dimension (``residual`` may be None).  ``a_bias``: the bias of the
+    Linear that produced ``a`` when that op was told to leave its bias gradient to this one."""
+    return _LayerNormResidual.apply(a, residual, gamma, beta, eps, dropout_p if training else 0.0, site, a_bias)

@@ -1,0 +1,156 @@
+"""Full Transformer against the reference class (transformer.py:255-284 with the loss / optimizer of
+pytorch_machine_translator.py:125-129,182-196): logits, loss, EVERY parameter gradient, and a 20-step Adam loss curve,
+with weights loaded from the reference state_dict and dropout off.  The CPU variant runs through the PyTorch
+restatements of every op (fp32: tight tolerances); the GPU variant runs the CUDA kernels (bf16 activations / working
+weights: bf16 tolerances) against the fp32 CPU reference."""
+import importlib.util
+import os
+
+import pytest
+import torch
+
+
+class _V:
+    def __init__(self, n):
+        self.n = n
+
+    def __len__(self):
+        return self.n
+
+
+@pytest.fixture(scope="module")
+def ref_transformer(reference_dir):
+    spec = importlib.util.spec_from_file_location("ref_transformer_p", os.path.join(reference_dir, "transformer.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def _batch(B, S, Ve, Vd, seed):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randint(4, Ve, (B, S), generator=g)
+    y = torch.randint(4, Vd, (B, S), generator=g)
+    lx = torch.randint(S // 2, S + 1, (B,), generator=g)
+    ly = torch.randint(S // 2, S + 1, (B,), generator=g)
+    ar = torch.arange(S)[None]
+    x = torch.where(ar < lx[:, None], x, torch.zeros_like(x))
+    y = torch.where(ar < ly[:, None], y, torch.zeros_like(y))
+    x[:, 0] = 1
+    y[:, 0] = 1
+    return x, y
+
+
+def _ref_loss(rm, x, y, S):
+    dev = next(rm.parameters()).device
+    x, y = x.to(dev), y.to(dev)
+    pad = (x != 0).unsqueeze(1).unsqueeze(2)
+    la = (torch.tril(torch.ones(S, S, device=dev)) == 0).unsqueeze(0).unsqueeze(0)
+    pred = rm(x, y, pad, la, la)
+    loss = torch.nn.CrossEntropyLoss(ignore_index=0, reduction="none")(pred.view(-1, pred.size(-1)), y.view(-1))
+    valid = y.view(-1) != 0
+    return pred, loss[valid].sum() / valid.sum()
+
+
+def _own_loss(m, x, y, S, dev):
+    from b200ml.ops.loss import linear_cross_entropy
+    x, y = x.to(dev), y.to(dev)
+    pad = (x != 0).unsqueeze(1).unsqueeze(2)
+    la = (torch.tril(torch.ones(S, S, device=dev)) == 0).unsqueeze(0).unsqueeze(0)
+    h = m(x, y, pad, la, la, return_hidden=True)
+    return linear_cross_entropy(h, m.linear.weight, m.linear.bias, y, ignore_index=0)
+
+
+def _build(ref_transformer, cfg, dev):
+    from b200ml.models.transformer import Transformer
+    d, ffn, H, L, S, Ve, Vd = cfg
+    torch.manual_seed(0)
+    rm = ref_transformer.Transformer(d, ffn, H, 0.0, L, S, Vd, _V(Ve), _V(Vd)).to(dev)
+    rm.eval()                                   # SentenceEmbedding hard-codes Dropout(0.1): eval() switches it off
+    m = Transformer(d, ffn, H, 0.0, L, S, Vd, _V(Ve), _V(Vd)).to(dev)
+    m.load_state_dict(rm.state_dict(), strict=True)
+    m.eval()
+    return rm, m
+
+
+def _rel(a, b):
+    return (a.detach().float().cpu() - b.detach().float().cpu()).norm().item() / max(b.detach().float().norm().item(), 1e-12)
+
+
+def _check_grads(ref_transformer, cfg, dev, tol_logits, tol_loss, tol_grad):
+    d, ffn, H, L, S, Ve, Vd = cfg
+    rm, m = _build(ref_transformer, cfg, dev)
+    x, y = _batch(4, S, Ve, Vd, seed=3)
+    pred_ref, loss_ref = _ref_loss(rm, x, y, S)
+    loss_ref.backward()
+    pad = (x != 0).unsqueeze(1).unsqueeze(2).to(dev)
+    la = (torch.tril(torch.ones(S, S, device=dev)) == 0).unsqueeze(0).unsqueeze(0)
+    with torch.no_grad():
+        logits = m(x.to(dev), y.to(dev), pad, la, la)
+    assert _rel(logits, pred_ref) < tol_logits
+    loss = _own_loss(m, x, y, S, dev)
+    loss.backward()
+    assert abs(loss.item() - loss_ref.item()) < tol_loss * max(1.0, abs(loss_ref.item()))
+    ref_grads = dict(rm.named_parameters())
+    worst = ("", 0.0)
+    for name, p in m.named_parameters():
+        gr = ref_grads[name].grad
+        assert p.grad is not None, name
+        # the key bias of an attention block has a mathematically zero gradient (softmax is shift-invariant): compare
+        # gradients against the scale of the whole parameter group instead of their own (noise-level) norm
+        scale = max(gr.norm().item(), 1e-3 * max(g.grad.norm().item() for g in ref_grads.values()))
+        err = (p.grad.detach().float().cpu() - gr.cpu()).norm().item() / scale
+        if err > worst[1]:
+            worst = (name, err)
+    assert worst[1] < tol_grad, f"gradient of {worst[0]} is off by {worst[1]:.3e} (relative)"
+
+
+def _check_curve(ref_transformer, cfg, dev, tol):
+    from b200ml.parallel.engine import DataParallelEngine
+    d, ffn, H, L, S, Ve, Vd = cfg
+    rm, m = _build(ref_transformer, cfg, dev)
+    opt_ref = torch.optim.Adam(rm.parameters(), lr=1e-3)
+    eng = DataParallelEngine(m, optimizer="adam", lr=1e-3)
+    ref_curve, own_curve = [], []
+    for step in range(20):
+        x, y = _batch(8, S, Ve, Vd, seed=100 + step)
+        _, l = _ref_loss(rm, x, y, S)
+        opt_ref.zero_grad()
+        l.backward()
+        opt_ref.step()
+        ref_curve.append(l.item())
+        eng.zero_grad()
+        lo = _own_loss(m, x, y, S, dev)
+        lo.backward()
+        eng.step()
+        own_curve.append(lo.item())
+    eng.close()
+    assert ref_curve[-1] < ref_curve[0] - 0.3, "the reference did not train"
+    worst = max(abs(a - b) for a, b in zip(own_curve, ref_curve))
+    assert worst < tol, f"loss curves diverge by {worst:.4f}: own {own_curve[::4]} ref {ref_curve[::4]}"
+    return own_curve, ref_curve
+
+
+CFG_SMALL = (64, 128, 2, 2, 24, 50, 60)
+
+
+def test_transformer_gradients_match_reference_cpu(ref_transformer):
+    _check_grads(ref_transformer, CFG_SMALL, torch.device("cpu"), 1e-5, 1e-5, 1e-4)
+
+
+def test_transformer_adam_curve_matches_reference_cpu(ref_transformer):
+    _check_curve(ref_transformer, CFG_SMALL, torch.device("cpu"), 2e-3)
+
+
+# head_dim 64, S <= 256: the shapes the attention kernel covers; vocabulary sizes not multiples of 8
+CFG_GPU = (128, 256, 2, 1, 64, 301, 517)
+
+
+@pytest.mark.gpu
+def test_transformer_gradients_match_reference_gpu(ref_transformer):
+    _check_grads(ref_transformer, CFG_GPU, torch.device("cuda"), 2e-2, 5e-3, 4e-2)
+
+
+@pytest.mark.gpu
+def test_transformer_adam_curve_matches_reference_gpu(ref_transformer):
+    own, ref = _check_curve(ref_transformer, CFG_GPU, torch.device("cuda"), 0.05)
+    print("loss curve own", [round(v, 3) for v in own[::4]], "ref", [round(v, 3) for v in ref[::4]])
