@@ -701,7 +701,9 @@ static int launch(const b200ml_gemm_args* g, Epilogue ep, int splits, cudaStream
     }
     const int m_tiles = (g->M + BLOCK_M * kCtas - 1) / (BLOCK_M * kCtas), n_tiles = (g->N + BN - 1) / BN;
     const int tiles = m_tiles * n_tiles * splits;       // per CTA (kCtas == 1) or per CTA pair
-    const int slots = sm_count() / kCtas;
+    int slots = sm_count() / kCtas;
+    if (g->max_ctas > 0 && g->max_ctas / kCtas >= 1 && g->max_ctas / kCtas < slots && !(kCtas == 1 && ep.cluster_splits > 1))
+        slots = g->max_ctas / kCtas;
     const int grid = (tiles < slots ? tiles : slots) * kCtas;
     const bool cluster_split = kCtas == 1 && ep.cluster_splits > 1;   // splits == cluster size, one tile per CTA
     if (cluster_split) {

@@ -53,6 +53,8 @@ typedef struct {
     int split_k;     /* 0 = auto, 1 = never, n > 1 = request n K-splits (plain epilogue only; needs workspace) */
     void* workspace; size_t workspace_bytes; /* fp32 scratch for split-K partial tiles (optional) */
     int epilogue_direct; /* testing: 1 = register->global stores even where the TMA-store epilogue applies */
+    int max_ctas;    /* > 0: use at most this many CTAs of the persistent tcgen05 kernel (a leaf GEMM that should leave
+                        SMs to kernels on the critical path of other streams); 0 = one per SM */
 } b200ml_gemm_args;
 int b200ml_gemm_bf16(const b200ml_gemm_args* args, cudaStream_t stream);
 

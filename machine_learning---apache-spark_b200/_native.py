@@ -42,6 +42,7 @@ class GemmArgs(C.Structure):
         ("split_k", C.c_int),
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
         ("epilogue_direct", C.c_int),
+        ("max_ctas", C.c_int),
     ]
 
 

@@ -28,6 +28,9 @@ XENT_ROWS_MAX_V = 20480  # csrc/kernels/xent.cu kBigMaxV
 # 1.80 ms per step at 32 MB chunks) because the per-chunk dgrad had too few output tiles to fill 148 SMs; see
 # BASELINE.md for the re-measurement with the CTA-pair GEMM.  Default: one chunk.
 HEAD_CHUNK_BYTES = int(float(os.environ.get("B200ML_HEAD_CHUNK_MB", "0")) * (1 << 20))
+# The head's weight gradient is a leaf of backward but, as a persistent GEMM on every SM, it keeps the kernels of the
+# critical path (LayerNorm backward, the decoder's dgrads) waiting for an SM.  > 0: run it on at most this many CTAs.
+HEAD_WGRAD_CTAS = int(os.environ.get("B200ML_HEAD_WGRAD_CTAS", "0"))
 
 
 def _xent_native(logits, ld, targets, V, ignore_index, write_grad=True):
@@ -108,7 +111,10 @@ class _LinearCrossEntropy(torch.autograd.Function):
             # twice and overwrites it with the gradient, and the input-gradient GEMM consumes that gradient — all before
             # the chunk is evicted, so the [rows, V] matrix makes one trip to HBM instead of four.
             chunk_rows = max(128, (HEAD_CHUNK_BYTES // (ld * 2)) // 128 * 128) if HEAD_CHUNK_BYTES > 0 else rows
-            dh = torch.empty(rows, d, dtype=torch.bfloat16, device=dev) if (need_grad and h.requires_grad) else None
+            # the input gradient is computed here only in chunked mode (while the gradient chunk is L2-resident);
+            # otherwise backward computes it with the upstream gradient folded into the GEMM epilogue
+            dh = (torch.empty(rows, d, dtype=torch.bfloat16, device=dev)
+                  if (need_grad and h.requires_grad and HEAD_CHUNK_BYTES > 0) else None)
             b_ = None if bias is None else bias.detach()
             # single-chunk large-vocabulary path: one read of the logits, gradient in place, bias gradient for free
             fused_rows = V <= XENT_ROWS_MAX_V
@@ -174,7 +180,7 @@ class _LinearCrossEntropy(torch.autograd.Function):
             dw = db = None
             if weight.requires_grad:
                 dw = deliver_grad(weight, lambda out, acc: gemm(gv, h2, a_mn=True, b_mn=True, out=out, accumulate=acc,
-                                                                 alpha_dev=gdev), (V, d))
+                                                                 alpha_dev=gdev, max_ctas=HEAD_WGRAD_CTAS), (V, d))
             if bias is not None and bias.requires_grad:
                 def _db(out, acc):
                     if ctx.has_db:   # column sums of the gradient were accumulated by the loss kernel itself
