@@ -562,7 +562,8 @@ int launch_bulk(const Peers& c, long long start, long long n, const OptimSpec& o
     long long blocks = (per + kBulkChunk - 1) / kBulkChunk;  // one chunk per CTA at least
     // default CTA count: at 2 ranks the kernel is bound by its LOCAL optimizer traffic (30 B/element over half the
     // bucket) and wants most of the chip; from 4 ranks on it is NVLink-bound and a few dozen rings saturate the links
-    int cap = max_blocks > 0 ? max_blocks : (c.world <= 2 ? 128 : (c.world <= 4 ? 64 : 40));
+    // (measured, 116 MiB: 2 ranks 16 CTAs 1022 us ... 128 CTAs 174 us; 8 ranks 16 CTAs 277 us = 148 CTAs 280 us)
+    int cap = max_blocks > 0 ? max_blocks : (c.world <= 2 ? 128 : (c.world <= 4 ? 48 : 24));
     const int res = resident_cap(kernel, kBulkThreads, smem);
     if (cap > res) cap = res;
     if (blocks > cap) blocks = cap;

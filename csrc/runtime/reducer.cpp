@@ -5,8 +5,8 @@
 // collective per bucket as soon as the bucket's last gradient exists.  Here the parameters already live in ONE flat
 // buffer (parallel/flat.py), so a bucket is a contiguous range of it; the gradient kernels write straight into their
 // slots and report "parameter i is ready"; the first report that completes a bucket returns its index and the engine
-// launches the fused all-reduce + optimizer kernel on that range.  Buckets are cut at `cap` elements, and parameters
-// of cap/4 or more stand alone (see below).  Parameters are partitioned into groups (e.g.
+// launches the fused all-reduce + optimizer kernel on that range.  Buckets are cut at `cap` elements; parameters of
+// cap/4 or more start a bucket of their own (see below).  Parameters are partitioned into groups (e.g.
 // "weights whose fp32 master may stay stale on non-owner ranks" vs the rest) and buckets never straddle a group.
 // Reports arrive from the autograd worker thread and the main thread, hence the mutex.
 #include <mutex>
@@ -46,26 +46,32 @@ b200ml_reducer* b200ml_reducer_create(int n_params, const long long* offsets, in
             delete r;
             return nullptr;
         }
+        // Bucket boundaries.  Ordinary parameters are packed until the bucket reaches `cap`.  A parameter of a quarter
+        // of the cap or more ("big": an embedding table, the output projection) never joins the parameters registered
+        // BEFORE it - their gradients appear at another time of backward, and a shared bucket would hold the big one's
+        // all-reduce / optimizer launch back - but it takes the small parameters registered right AFTER it along, up
+        // to cap/2 of them: for an embedding table those are the weights of the layer it feeds, whose gradients become
+        // ready just before the table's, at the end of backward, so one launch (one pair of cross-GPU barriers)
+        // serves both instead of two launches queued behind each other.
         long long start = lo < hi ? offsets[lo] : 0;
         int first = lo;
+        long long big_end = -1;                       // end offset of the big parameter of the open bucket, if any
+        auto is_big = [&](int i) { return (offsets[i + 1] - offsets[i]) * 4 >= cap_elems; };
         for (int i = lo; i < hi; ++i) {
-            const long long end = offsets[i + 1];  // offsets has n_params + 1 entries; the last is the total size
-            // A parameter of a quarter of the cap or more gets a bucket of its own.  Its gradient is produced by one
-            // kernel at one point of backward (an embedding table at the very end, the output projection at the very
-            // start); sharing a bucket with neighbours that become ready at another time would hold its all-reduce /
-            // optimizer launch back until then and leave that work exposed after backward has finished.
-            const bool big = (end - offsets[i]) * 4 >= cap_elems;
-            if (big && i > first) {
-                r->buckets.push_back({start, offsets[i] - start, first, i - first, g});
-                for (int p = first; p < i; ++p) r->bucket_of[p] = (int)r->buckets.size() - 1;
-                start = offsets[i];
-                first = i;
+            if (is_big(i)) big_end = offsets[i + 1];
+            const long long end = offsets[i + 1];
+            bool close = i + 1 == hi;
+            if (!close) {
+                if (is_big(i + 1)) close = true;
+                else if (big_end >= 0) close = offsets[i + 2] - big_end > cap_elems / 2;
+                else close = end - start >= cap_elems;
             }
-            if (big || end - start >= cap_elems || i + 1 == hi) {
+            if (close) {
                 r->buckets.push_back({start, end - start, first, i + 1 - first, g});
                 for (int p = first; p <= i; ++p) r->bucket_of[p] = (int)r->buckets.size() - 1;
                 start = end;
                 first = i + 1;
+                big_end = -1;
             }
         }
         lo = hi;

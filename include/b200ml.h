@@ -265,6 +265,18 @@ int b200ml_allreduce_update(const b200ml_comm* cm, long long start, long long n,
 int b200ml_allreduce_sum_f64(const b200ml_comm* cm, const double* const* bufs, long long n, double* out,
                              cudaStream_t stream);
 
+/* ------------------------------------------------------------------------------------------------ K19 MLPC loss + gradient
+ * float64 forward / softmax cross-entropy / backward of the MLlib feed-forward topology (Affine -> Sigmoid -> ... ->
+ * Affine -> Softmax) over one rank's rows.  `weights` is MLlib's flat vector (per layer [W (in x out, row-major) ‖ b]);
+ * layers[n_layers] are the widths; X is [rows, layers[0]] with row pitch ldx; row_w[i] = 1 / size of row i's block
+ * (MLlib averages per block of blockSize rows).  out_grad_loss receives the gradient in the same flat layout followed by
+ * the weighted loss: num_weights + 1 doubles.  Deterministic (no atomics).  scratch: b200ml_mlpc_scratch_bytes.
+ * ref: MultilayerPerceptronClassifier(...).fit (mllib_multilayer_perceptron_classifier.py:35-39). */
+size_t b200ml_mlpc_scratch_bytes(const int* layers, int n_layers, int rows);
+int b200ml_mlpc_loss_grad(const double* weights, const int* layers, int n_layers, const double* X, long long ldx,
+                          const long long* y, const double* row_w, int rows, double* out_grad_loss, void* scratch,
+                          size_t scratch_bytes, cudaStream_t stream);
+
 /* ------------------------------------------------------------------------------------------------ K20 L-BFGS direction
  * ref: MultilayerPerceptronClassifier(solver='l-bfgs') (mllib_multilayer_perceptron_classifier.py:35), Breeze LBFGS.
  * Two-loop recursion over k <= 32 history pairs as one cooperative kernel; float64, rank-reproducible.

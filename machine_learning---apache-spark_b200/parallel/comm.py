@@ -47,7 +47,7 @@ class _RawCuda:
 class SymmetricBuffer:
     """Device buffer allocated by libb200ml and exportable over CUDA IPC; ``.tensor`` is a torch view of it."""
 
-    _DT = {torch.float32: ("<f4", 4), torch.uint8: ("|u1", 1), torch.int32: ("<i4", 4)}
+    _DT = {torch.float32: ("<f4", 4), torch.uint8: ("|u1", 1), torch.int32: ("<i4", 4), torch.float64: ("<f8", 8)}
 
     def __init__(self, numel: int, dtype, device):
         lib = _native.load()
@@ -142,6 +142,64 @@ def make_allocator(device, group=None):
             if os.environ.get("B200ML_DEBUG"):
                 print(f"[b200ml] symmetric-memory/NVLS unavailable: {e}")
     return SymmetricAllocator(device)
+
+
+_native_ext.register("b200ml_allreduce_sum_f64", [C.POINTER(CommStruct), C.POINTER(C.c_void_p * 8), ll, vp, vp])
+
+
+class F64AllReduce:
+    """Sum of one float64 vector over the ranks of a node with the one-shot peer-memory kernel
+    (b200ml_allreduce_sum_f64): every rank owns a symmetric buffer ``self.buf`` that producers write straight into,
+    ``reduce()`` returns the rank-order sum (identical bits on every rank) in ``self.out``.  Used by the MLlib-style
+    L-BFGS trainer (spark/ml.py) in place of Spark's treeAggregate (mllib_multilayer_perceptron_classifier.py:35-39)."""
+
+    def __init__(self, n: int, device, group=None):
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        assert self.world <= MAX_RANKS
+        self.group = group
+        self.n = (n + 1) // 2 * 2
+        self._buf = SymmetricBuffer(self.n, torch.float64, device)
+        self.buf = self._buf.tensor
+        self.buf.zero_()
+        self.out = torch.zeros(self.n, dtype=torch.float64, device=device)
+        self._signals = SymmetricBuffer(SIGNAL_WORDS, torch.int32, device)
+        self._counter = torch.zeros(2, dtype=torch.int32, device=device)
+        mine = {"buf": self._buf.export(), "signals": self._signals.export()}
+        gathered = [None] * self.world
+        dist.all_gather_object(gathered, mine, group=group)
+        self._imported = []
+        self.cs = CommStruct()
+        self.cs.world, self.cs.rank = self.world, self.rank
+        self._bufs = (C.c_void_p * 8)()
+        for r in range(self.world):
+            if r == self.rank:
+                self._bufs[r], self.cs.signals[r] = self._buf.ptr, self._signals.ptr
+            else:
+                self._bufs[r] = _import(gathered[r]["buf"])
+                self.cs.signals[r] = _import(gathered[r]["signals"])
+                self._imported += [self._bufs[r], self.cs.signals[r]]
+        self.cs.counter = self._counter.data_ptr()
+        torch.cuda.synchronize(device)
+        dist.barrier(group=group)
+
+    def reduce(self) -> torch.Tensor:
+        _native.check(_native.load().b200ml_allreduce_sum_f64(C.byref(self.cs), C.byref(self._bufs), self.n,
+                                                              self.out.data_ptr(), _native.stream_ptr()),
+                      "allreduce_sum_f64")
+        return self.out
+
+    def close(self) -> None:
+        try:
+            torch.cuda.synchronize(self.buf.device)
+            if dist.is_initialized():
+                dist.barrier(group=self.group)
+        except Exception:  # noqa: BLE001
+            pass
+        lib = _native.load()
+        for p in self._imported:
+            lib.b200ml_ipc_close(p)
+        self._imported = []
 
 
 class FusedAllReduce:

@@ -73,20 +73,28 @@ class PyReducer:
         self.buckets, self._of = [], {}
         lo = 0
         for g, hi in enumerate(group_ends):
-            start, first = (offsets[lo] if lo < hi else 0), lo
-            for i in range(lo, hi):
+            start, first, big_end = (offsets[lo] if lo < hi else 0), lo, -1
+
+            def is_big(i):
+                return (offsets[i + 1] - offsets[i]) * 4 >= cap_elems
+
+            for i in range(lo, hi):          # same rules as reducer.cpp
+                if is_big(i):
+                    big_end = offsets[i + 1]
                 end = offsets[i + 1]
-                big = (end - offsets[i]) * 4 >= cap_elems     # stands alone, as in reducer.cpp
-                if big and i > first:
-                    for p in range(first, i):
-                        self._of[p] = len(self.buckets)
-                    self.buckets.append((start, offsets[i] - start, list(range(first, i)), g))
-                    start, first = offsets[i], i
-                if big or end - start >= cap_elems or i + 1 == hi:
+                close = i + 1 == hi
+                if not close:
+                    if is_big(i + 1):
+                        close = True
+                    elif big_end >= 0:
+                        close = offsets[i + 2] - big_end > cap_elems // 2
+                    else:
+                        close = end - start >= cap_elems
+                if close:
                     for p in range(first, i + 1):
                         self._of[p] = len(self.buckets)
                     self.buckets.append((start, end - start, list(range(first, i + 1)), g))
-                    start, first = end, i + 1
+                    start, first, big_end = end, i + 1, -1
             lo = hi
         self._pending = [0] * len(self.buckets)
         self._reported: set = set()

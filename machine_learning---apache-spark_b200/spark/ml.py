@@ -247,45 +247,54 @@ class LBFGS:
 # ---------------------------------------------------------------------------------------------------------------
 # distributed cost function
 # ---------------------------------------------------------------------------------------------------------------
+def _native_loss_grad(weights, layers, X, Y, row_w, out_vec):
+    """K19 on the GPU (csrc/kernels/mlpc.cu): writes [gradient ‖ weighted loss] (num_weights + 1 float64) into
+    ``out_vec`` with the float64 GEMM / softmax kernels of this library - no torch / cuBLAS op in the evaluation."""
+    import ctypes as C
+
+    from .. import _native, _native_ext
+    from ..utils import workspace
+
+    vp, i, ll, sz = C.c_void_p, C.c_int, C.c_longlong, C.c_size_t
+    _native_ext.register("b200ml_mlpc_loss_grad", [vp, vp, i, vp, ll, vp, vp, i, vp, vp, sz, vp])
+    _native_ext.register("b200ml_mlpc_scratch_bytes", [vp, i, i], size_t_return=True)
+    lib = _native.load()
+    la = (C.c_int * len(layers))(*[int(v) for v in layers])
+    rows = X.shape[0]
+    nb = int(lib.b200ml_mlpc_scratch_bytes(la, len(layers), rows))
+    ws = workspace.get(f"mlpc@{workspace.lane()}", nb, X.device)
+    _native.check(lib.b200ml_mlpc_loss_grad(weights.data_ptr(), la, len(layers), X.data_ptr(), X.stride(0),
+                                            Y.data_ptr(), row_w.data_ptr(), rows, out_vec.data_ptr(), ws.data_ptr(),
+                                            ws.numel(), _native.stream_ptr()), "mlpc_loss_grad")
+
+
 class _Reducer:
-    """All-reduce of the [grad ‖ loss ‖ blocks] vector: fused one-shot NVLink kernel on GPUs, gloo/NCCL otherwise."""
+    """Owner of the [grad ‖ loss ‖ blocks] vector and its sum over ranks.  GPUs of one node: the vector lives in a
+    symmetric (peer-mapped) float64 buffer that the loss / gradient kernels write directly, and ONE one-shot kernel
+    adds it over the ranks in rank order (parallel/comm.py F64AllReduce) - native float64, no hi/lo split, no staging
+    copies.  CPU ranks (gloo) or ``B200ML_ALLREDUCE=nccl``: torch.distributed.all_reduce."""
 
     def __init__(self, n: int, device, dtype):
         self.world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
         self.fused = None
         self.n = n
         if self.world > 1 and device.type == "cuda" and os.environ.get("B200ML_ALLREDUCE", "fused") == "fused":
-            try:
-                from ..parallel.comm import FusedAllReduce, SymmetricAllocator
-                from ..parallel.flat import FlatParams
+            from ..parallel.comm import F64AllReduce
 
-                n4 = (n + 3) // 4 * 4
-                self._p = torch.zeros(n4, dtype=torch.float32, device=device, requires_grad=True)
-                alloc = SymmetricAllocator(device)
-                self._flat = FlatParams([self._p], allocator=alloc)
-                self.fused = FusedAllReduce(self._flat, None, None, None, allocator=alloc)
-                self._out = torch.zeros(self._flat.numel, dtype=torch.float32, device=device)
-                self._step = torch.ones(1, dtype=torch.int32, device=device)
-            except Exception as e:  # noqa: BLE001
-                print(f"[b200ml] fused all-reduce unavailable for MLPC ({e}); using torch.distributed")
-                self.fused = None
+            self.fused = F64AllReduce(n, device)
+            self.vec = self.fused.buf[:n]
+        else:
+            self.vec = torch.zeros(n, dtype=dtype, device=device)
 
-    def __call__(self, vec: torch.Tensor) -> torch.Tensor:
+    def __call__(self) -> torch.Tensor:
+        """Sum of ``self.vec`` over the ranks (``self.vec`` itself when there is one rank)."""
         if self.world == 1:
-            return vec
+            return self.vec
         if self.fused is not None:
-            # hi/lo split keeps ~float64 accuracy through the fp32 kernel: v = hi + lo, both reduced
-            hi = vec.float()
-            lo = (vec - hi.double()).float()
-            out = torch.zeros_like(vec)
-            for part in (hi, lo):
-                self._flat.flat_g[:self.n].copy_(part)
-                self.fused.allreduce_update(0, self._flat.numel, 0, 0.0, (0.9, 0.999), 1e-8, 0.0, self._step,
-                                            out=self._out, algo=1)
-                out += self._out[:self.n].double() * self.world
-            return out
-        dist.all_reduce(vec)
-        return vec
+            return self.fused.reduce()[:self.n]
+        out = self.vec.clone()
+        dist.all_reduce(out)
+        return out
 
     def close(self):
         if self.fused is not None:
@@ -309,20 +318,34 @@ def _fit_local(X, y, layers, block_size, max_iter, tol, solver, step_size, seed,
     nw = num_weights(layers)
     reducer = _Reducer(nw + 2, dev, torch.float64)
 
+    vec = reducer.vec                       # [gradient (nw) ‖ loss ‖ #blocks]; the kernels write into it directly
+    vec.zero_()
+    vec[nw + 1] = local_blocks
+    native = dev.type == "cuda" and os.environ.get("B200ML_MLPC_NATIVE", "1") != "0"
+
     def fn(w):
-        if n:
+        if n and native:
+            _native_loss_grad(w.contiguous(), layers, Xd, Yd, row_w, vec)
+        elif n:
             loss, grad = loss_and_grad(w, layers, Xd, Yd, row_w)
-        else:
-            loss, grad = torch.zeros((), dtype=torch.float64, device=dev), torch.zeros(nw, dtype=torch.float64, device=dev)
-        vec = torch.cat([grad, loss.reshape(1), torch.tensor([local_blocks], dtype=torch.float64, device=dev)])
-        vec = reducer(vec)
-        blocks = vec[-1].clamp_min(1.0)
-        return vec[-2] / blocks, vec[:-2] / blocks
+            vec[:nw].copy_(grad)
+            vec[nw] = loss
+        total = reducer()
+        blocks = total[nw + 1].clamp_min(1.0)
+        return total[nw] / blocks, total[:nw] / blocks
 
     w0 = (torch.as_tensor(np.asarray(initial_weights), dtype=torch.float64) if initial_weights is not None
           else init_weights(layers, seed)).to(dev)
     if world > 1:
         dist.broadcast(w0, src=0)
+    if dev.type == "cuda":
+        # untimed: the first launches load the kernels (loss / gradient, the two-loop kernel, torch's dot products)
+        # and size the scratch buffers - a launcher worker is a fresh process every time
+        if solver == "l-bfgs":
+            LBFGS(fn, m=10, max_iter=2, tol=0.0).minimize(w0)
+        else:
+            fn(w0)
+        torch.cuda.synchronize(dev)
     t0 = time.time()
     if solver == "l-bfgs":
         opt = LBFGS(fn, m=10, max_iter=max_iter, tol=tol)
@@ -340,9 +363,12 @@ def _fit_local(X, y, layers, block_size, max_iter, tol, solver, step_size, seed,
         iters = len(history)
     else:
         raise ValueError(f"solver must be 'l-bfgs' or 'gd', got {solver!r}")
+    if dev.type == "cuda":
+        torch.cuda.synchronize(dev)
+    fit_s = time.time() - t0
     reducer.close()
     return {"weights": w.detach().cpu().numpy(), "objectiveHistory": history, "totalIterations": iters,
-            "functionEvaluations": evals, "fitSeconds": time.time() - t0, "world": world}
+            "functionEvaluations": evals, "fitSeconds": fit_s, "world": world}
 
 
 def _fit_worker(shards, kwargs):

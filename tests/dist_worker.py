@@ -161,7 +161,9 @@ def case_allreduce_raw(rank, world, dev, mode):
             comm.allreduce_update(start, n, 2, 1e-2, (0.9, 0.999), 1e-8, 0.0, step, algo=algo)
             torch.cuda.synchronize()
             dist.barrier()
-            g = expect[sl]
+            # Adam divides by |g| + eps, so where the mean gradient is nearly zero the last-bit difference between NCCL's
+            # summation order and ours would be amplified: use our own (rank-order) mean, checked against NCCL above
+            g = out[sl]
             want = p0.clone()
             want[sl] -= 1e-2 * g / (g.abs() + 1e-8)
             assert (flat.flat_p - want).abs().max().item() < 1e-4, f"adam algo {algo} range {(start, n)}"
@@ -288,7 +290,34 @@ def case_layout_mismatch(rank, world, dev, mode):
     raise AssertionError("mismatched layouts were accepted")
 
 
-CASES = {"layout_mismatch": case_layout_mismatch, "checkpoint_adam": case_checkpoint_adam,"allreduce_nvls": case_allreduce_nvls, "dp_equals_big_batch": case_dp_equals_big_batch, "fused_matches_nccl": case_fused_matches_nccl,
+def case_mlpc(rank, world, dev, mode):
+    """MLlib-style MLPC over row shards: native loss / gradient kernels writing into the symmetric float64 vector, one
+    one-shot float64 all-reduce; equals the full-data float64 restatement, and every rank ends with the same bits."""
+    from b200ml.spark import ml
+    layers = [20, 33, 7]
+    torch.manual_seed(5)
+    rows = 128 * world * 3                       # whole blocks per rank: the block weights of shards and full data agree
+    X = torch.randn(rows, layers[0], dtype=torch.float64)
+    Y = torch.randint(0, layers[-1], (rows,))
+    per = rows // world
+    Xs, Ys = X[rank * per:(rank + 1) * per].numpy(), Y[rank * per:(rank + 1) * per].numpy()
+    out = ml._fit_local(Xs, Ys, layers, 128, 12, 1e-9, "l-bfgs", 0.03, 9, None, str(dev))
+    w = torch.as_tensor(out["weights"])
+    gathered = [torch.zeros_like(w) for _ in range(world)]
+    wd = w.to(dev)
+    gl = [torch.zeros_like(wd) for _ in range(world)]
+    dist.all_gather(gl, wd)
+    assert all(torch.equal(g, gl[0]) for g in gl), "ranks ended with different weights"
+    # the objective the distributed run reports == the full-data objective at the returned weights
+    row_w = torch.full((rows,), 1.0 / 128, dtype=torch.float64)
+    loss, _ = ml.loss_and_grad(w, layers, X, Y, row_w)
+    full = loss.item() / (rows / 128)
+    assert abs(full - out["objectiveHistory"][-1]) <= 1e-10 * max(1.0, abs(full)), (full, out["objectiveHistory"][-1])
+    assert out["objectiveHistory"][-1] < out["objectiveHistory"][0]
+    print(f"[rank {rank}] mlpc ok evals={out['functionEvaluations']} obj={full:.6f}")
+
+
+CASES = {"mlpc": case_mlpc, "layout_mismatch": case_layout_mismatch, "checkpoint_adam": case_checkpoint_adam,"allreduce_nvls": case_allreduce_nvls, "dp_equals_big_batch": case_dp_equals_big_batch, "fused_matches_nccl": case_fused_matches_nccl,
          "allreduce_raw": case_allreduce_raw}
 
 if __name__ == "__main__":

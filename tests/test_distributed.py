@@ -28,6 +28,11 @@ def test_layout_mismatch_is_caught_gloo_world2():
     assert out.count("layout_mismatch ok") == 2
 
 
+def test_mlpc_gloo_world2():
+    out = _launch(["mlpc"], 2, 29616, {"B200ML_TEST_CPU": "1", "OMP_NUM_THREADS": "2"})
+    assert out.count("mlpc ok") == 2
+
+
 def test_checkpoint_adam_gloo_world2():
     out = _launch(["checkpoint_adam"], 2, 29614, {"B200ML_TEST_CPU": "1", "OMP_NUM_THREADS": "2"})
     assert out.count("checkpoint_adam ok") == 2
@@ -47,8 +52,9 @@ def test_fused_allreduce_multi_gpu(world):
     if _ngpu() < world:
         pytest.skip(f"needs {world} GPUs")
     out = _launch(["allreduce_raw", "allreduce_nvls", "fused_matches_nccl", "dp_equals_big_batch", "checkpoint_adam",
-                   "layout_mismatch"], world, 29612 + world, timeout=900)
-    for case in ("allreduce_raw", "fused_matches_nccl", "dp_equals_big_batch", "checkpoint_adam", "layout_mismatch"):
+                   "layout_mismatch", "mlpc"], world, 29612 + world, timeout=900)
+    for case in ("allreduce_raw", "fused_matches_nccl", "dp_equals_big_batch", "checkpoint_adam", "layout_mismatch",
+                 "mlpc"):
         assert out.count(f"{case} ok") == world, case
 
 

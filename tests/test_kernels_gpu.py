@@ -275,3 +275,46 @@ def test_lbfgs_direction_kernel_matches_two_loop(n, k):
     ref = LBFGS.two_loop(opt, g.cpu(), [s.cpu() for s in S], [y.cpu() for y in Y])   # CPU tensors -> torch path
     assert ((d.cpu() - ref).norm() / ref.norm()).item() < 1e-11
     assert torch.equal(d, _native_direction(g, S, Y))
+
+
+@pytest.mark.parametrize("layers,rows,block", [([4, 5, 4, 3], 150, 128), ([784, 64, 10], 333, 128), ([20, 130, 70, 65, 7], 1000, 30)])
+def test_mlpc_native_loss_grad_matches_float64_restatement(layers, rows, block):
+    """K19: the float64 GEMM / softmax kernels working on MLlib's flat weight layout against the torch float64
+    restatement of the same math (spark/ml.py loss_and_grad), including the per-block row weights."""
+    from b200ml.spark import ml
+    torch.manual_seed(0)
+    dev = torch.device("cuda")
+    X = torch.randn(rows, layers[0], dtype=torch.float64, device=dev)
+    Y = torch.randint(0, layers[-1], (rows,), device=dev)
+    sizes = torch.full((rows,), float(block), dtype=torch.float64, device=dev)
+    if rows % block:
+        sizes[rows - rows % block:] = float(rows % block)
+    row_w = 1.0 / sizes
+    w = ml.init_weights(layers, 7).to(dev)
+    nw = ml.num_weights(layers)
+    loss_ref, grad_ref = ml.loss_and_grad(w, layers, X, Y, row_w)
+    outs = []
+    for _ in range(2):
+        vec = torch.full((nw + 2,), 123.0, dtype=torch.float64, device=dev)
+        ml._native_loss_grad(w, layers, X, Y, row_w, vec)
+        outs.append(vec.clone())
+    assert torch.equal(outs[0], outs[1])                    # deterministic
+    vec = outs[0]
+    assert vec[nw + 1].item() == 123.0                      # the block count slot is the caller's
+    assert abs(vec[nw].item() - loss_ref.item()) <= 1e-12 * max(1.0, abs(loss_ref.item()))
+    assert (vec[:nw] - grad_ref).abs().max().item() <= 1e-12 * max(1.0, grad_ref.abs().max().item())
+
+
+def test_mlpc_fit_on_gpu_uses_native_kernels_and_matches_cpu(monkeypatch):
+    from b200ml import _native
+    from b200ml.spark import ml
+    rng = torch.Generator().manual_seed(3)
+    X = torch.randn(300, 4, generator=rng, dtype=torch.float64).numpy()
+    y = (torch.randn(300, generator=rng) > 0).long().numpy() + (X[:, 0] > 0.5)
+    kw = dict(layers=[4, 5, 4, 3], block_size=128, max_iter=15, tol=1e-9, solver="l-bfgs", step_size=0.03, seed=11,
+              initial_weights=None)
+    n0 = _native.launches()
+    g = ml._fit_local(X, y, device="cuda", **kw)
+    assert _native.launches() - n0 >= 15                     # every evaluation goes through this library's kernels
+    c = ml._fit_local(X, y, device="cpu", **kw)
+    assert abs(g["objectiveHistory"][-1] - c["objectiveHistory"][-1]) < 1e-6

@@ -95,9 +95,10 @@ def test_graphed_step_is_plain_call_on_cpu_and_close_is_idempotent():
     pickle.loads(pickle.dumps(model))            # the module carries no engine state afterwards
 
 
-def test_big_parameters_get_their_own_bucket():
-    """A parameter of cap/4 or more never shares a bucket: the translator's embedding tables (ready at the very end of
-    backward) and output projection (ready at the very start) must not wait for their neighbours."""
+def test_big_parameters_start_their_own_bucket():
+    """A parameter of cap/4 or more never joins the parameters registered before it (the translator's output projection,
+    ready at the very start of backward, must not wait for the decoder layer) but takes up to cap/2 of small followers
+    along (an embedding table and the weights of the layer it feeds become ready together, at the end)."""
     from b200ml.parallel.reducer import NativeReducer, PyReducer
     M = 1 << 20
     sizes = [5 * M, M // 2, M // 4, 9 * M, M // 2, 9 * M, 64]      # emb, small, small, emb, small, head, bias
@@ -107,5 +108,9 @@ def test_big_parameters_get_their_own_bucket():
     cap = 6 * M + M // 2
     for R in (NativeReducer, PyReducer):
         r = R(offsets, [len(sizes)], cap)
-        assert [ids for _, _, ids, _ in r.buckets] == [[0], [1, 2], [3], [4], [5], [6]], R.__name__
+        assert [ids for _, _, ids, _ in r.buckets] == [[0, 1, 2], [3, 4], [5, 6]], R.__name__
+        r.close()
+        # followers beyond cap/2 are not absorbed: they pack among themselves
+        r = R([0, 9 * M, 10 * M, 11 * M, 12 * M, 13 * M, 22 * M], [6], cap)
+        assert [ids for _, _, ids, _ in r.buckets] == [[0, 1, 2, 3], [4], [5]], R.__name__
         r.close()
