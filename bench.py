@@ -327,6 +327,88 @@ def run_reference(args, rank, world, local):
     }
 
 
+def allreduce_sweep(impl, rank, world, local):
+    """BASELINE row B6 for this arm: device-timed gradient all-reduce + Adam at the four gradient sizes of the
+    reference models (31 KB CNN, 12.3 MB LSTM, a 25 MiB DDP bucket, 116 MiB Transformer-MT).  Own arm: the fused
+    all-reduce + Adam + bf16 re-cast kernel (one launch).  Reference arm: NCCL all_reduce + torch.optim.Adam on one flat
+    parameter (stock torch).  us per call, max over ranks; busbw = 2(N-1)/N * bytes / t."""
+    import torch
+    import torch.distributed as dist
+
+    if world < 2:
+        return {"skipped": "needs >= 2 GPUs"}
+    dev = torch.device("cuda", local)
+    out = {}
+    for name, n in (("cnn_31KB", 7740), ("lstm_12.3MB", 3083108), ("bucket_25MiB", 25 * (1 << 20) // 4),
+                    ("transformer_116MiB", 30500110)):
+        p = torch.randn(n, device=dev).requires_grad_()
+        if impl == "reference":
+            p.grad = torch.randn_like(p)
+            opt = torch.optim.Adam([p], lr=1e-3)
+
+            def fn():
+                dist.all_reduce(p.grad)
+                p.grad.div_(world)
+                opt.step()
+            close = None
+        else:
+            from b200ml.parallel.comm import FusedAllReduce, SymmetricAllocator
+            from b200ml.parallel.flat import FlatParams
+
+            alloc = SymmetricAllocator(dev)
+            flat = FlatParams([p], allocator=alloc)
+            m, v = torch.zeros_like(flat.flat_p), torch.zeros_like(flat.flat_p)
+            comm = FusedAllReduce(flat, m, v, None, allocator=alloc)
+            comm.push_master = 0
+            step = torch.ones(1, dtype=torch.int32, device=dev)
+            flat.flat_g.normal_()
+            numel = flat.numel
+
+            def fn():
+                comm.allreduce_update(0, numel, 2, 1e-3, (0.9, 0.999), 1e-8, 0.0, step)
+            close = comm.close
+        iters = 100 if n < (1 << 18) else 20
+        for _ in range(3):
+            fn()
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / iters], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        us = float(t.item()) * 1e3
+        out[name] = {"us": us, "bus_GBs": 2 * (world - 1) / world * n * 4 / (us * 1e-6) / 1e9}
+        if close is not None:
+            close()
+    return out
+
+
+def other_configs(args, rank, world, local):
+    """BASELINE.json configs 1-3 and the all-reduce row for the selected arm, device-timed, so that the driver-run
+    record carries them next to the headline: CNN (1x28x28 and 3x32x32), LSTM classifier (V 95 815, T 129), MLP (784-dim
+    preset), batch 32 per GPU, samples/s over all GPUs."""
+    sys.path.insert(0, os.path.join(ROOT, "bench"))
+    import bench_models
+
+    out = {}
+    for name in ("cnn", "cnn_cifar", "lstm", "mlp"):
+        try:
+            r = bench_models.bench_small_model(name, args.impl, rank, world, local, steps=30, warmup=5)
+            out[name] = ({"unavailable": r["unavailable"]} if "unavailable" in r else
+                         {"samples_per_s": r["samples_per_s"], "ms_per_step": r["ms_per_step"]})
+        except Exception as e:  # noqa: BLE001
+            out[name] = {"error": f"{type(e).__name__}: {e}"[:200]}
+    try:
+        out["allreduce_adam"] = allreduce_sweep(args.impl, rank, world, local)
+    except Exception as e:  # noqa: BLE001
+        out["allreduce_adam"] = {"error": f"{type(e).__name__}: {e}"[:200]}
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -336,6 +418,7 @@ def main():
     ap.add_argument("--allreduce", default="auto", choices=["auto", "fused", "nccl"])
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--ref-dtype", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--no-extras", action="store_true", help="skip the CNN / LSTM / MLP / all-reduce regions")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 
@@ -349,6 +432,8 @@ def main():
         res = run_reference(args, rank, world, local) if args.impl == "reference" else run_own(args, rank, world, local)
     finally:
         pass
+    if "unavailable" not in res and not args.no_extras:
+        res.setdefault("extra", {})["other_configs"] = other_configs(args, rank, world, local)
     if rank == 0:
         if "unavailable" in res:
             print(json.dumps({"impl": "reference", "unavailable": res["unavailable"]}))

@@ -29,20 +29,14 @@ def extract(path, cls, extra=None):
     return ns[cls]
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--model", default="cnn", choices=["cnn", "cnn_cifar", "lstm", "mlp"])
-    ap.add_argument("--impl", default="b200ml", choices=["b200ml", "reference"])
-    ap.add_argument("--steps", type=int, default=50)
-    ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--no-graph", action="store_true")
-    a = ap.parse_args()
-    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
-    local = int(os.environ.get("LOCAL_RANK", 0))
-    torch.cuda.set_device(local)
+def bench_small_model(name, impl, rank, world, local, steps=50, warmup=5, no_graph=False):
+    """One device-timed region of ``steps`` training steps of a small reference model; the process group (world > 1)
+    must exist.  Returns the result dict (every rank; the time is the max over ranks)."""
+    class A:
+        pass
+    a = A()
+    a.model, a.impl, a.steps, a.warmup, a.no_graph = name, impl, steps, warmup, no_graph
     dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
     torch.manual_seed(0)
     B = 32
     g = torch.Generator().manual_seed(rank)
@@ -62,11 +56,8 @@ def main():
         from torch import nn
         if a.model.startswith("cnn"):
             if a.model == "cnn_cifar":
-                res = {"impl": "reference", "model": a.model,
-                       "unavailable": "the reference FashionMNISTModel hard-codes hidden*7*7 and fails on 3x32x32 inputs"}
-                if rank == 0:
-                    print(json.dumps(res))
-                return
+                return {"impl": "reference", "model": a.model,
+                        "unavailable": "the reference FashionMNISTModel hard-codes hidden*7*7 and fails on 3x32x32 inputs"}
             model = extract("pytorch_cnn.py", "FashionMNISTModel")(1, 10, 10).to(dev)
             opt = torch.optim.SGD(model.parameters(), lr=0.01)
         elif a.model == "lstm":
@@ -156,9 +147,28 @@ def main():
         t = torch.tensor([ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
+    if a.impl != "reference":
+        eng.close()
+    return {"impl": a.impl, "model": a.model, "n_gpus": world, "batch_per_gpu": B, "steps": a.steps,
+            "ms_per_step": ms / a.steps, "samples_per_s": B * world * a.steps / (ms / 1e3)}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--model", default="cnn", choices=["cnn", "cnn_cifar", "lstm", "mlp"])
+    ap.add_argument("--impl", default="b200ml", choices=["b200ml", "reference"])
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--no-graph", action="store_true")
+    a = ap.parse_args()
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    res = bench_small_model(a.model, a.impl, rank, world, local, a.steps, a.warmup, a.no_graph)
     if rank == 0:
-        print(json.dumps({"impl": a.impl, "model": a.model, "n_gpus": world, "batch_per_gpu": B, "steps": a.steps,
-                          "ms_per_step": ms / a.steps, "samples_per_s": B * world * a.steps / (ms / 1e3)}))
+        print(json.dumps(res))
     if world > 1:
         dist.destroy_process_group()
 
