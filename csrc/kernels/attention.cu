@@ -14,10 +14,7 @@
 //   fwd (one CTA per 128-row query tile, head, batch):
 //            S = Q·Kᵀ (UMMA 128×S_kv×64) -> softmax in registers (a row is split over two threads) -> P (bf16,
 //            128B-swizzled smem) -> O = P·V (V consumed MN-major from the very bytes TMA wrote) -> O/rowsum, lse
-//   bwd (default: attn_bwd_fused_kernel, one CTA per head and batch, all three gradients, see its header comment)
-//   bwd, B200ML_ATTN_BWD=split (the first implementation, kept as a cross-check):
-//     bwd_q  : S, dP = dO·Vᵀ -> dS = P∘(dP − D)·scale -> dQ = dS·K
-//     bwd_kv : Sᵀ = K·Qᵀ, dPᵀ = V·dOᵀ (this CTA owns 128 keys) -> Pᵀ, dSᵀ -> dV = Pᵀ·dO, dK = dSᵀ·Q
+//   bwd (attn_bwd_fused_kernel, one CTA per head and batch, all three gradients, see its header comment)
 // No atomics, every gradient element is written exactly once => bit-reproducible.
 #include "../common/pdl.cuh"
 #include <cstdlib>
@@ -270,9 +267,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
     }
 }
 
-// ------------------------------------------------------------------------------------------------ backward, dQ
-// smem: [Q 16K][dO 16K][V 32K][K 32K] ; dS (4 x 16 KB tiles) aliases Q+dO+V after S and dP are in TMEM.
-constexpr int kBwdQSmem = 16384 + 16384 + 32768 + 32768 + 1024 + 128;
+// ------------------------------------------------------------------------------------------------ backward helpers
 
 __device__ __forceinline__ float row_dot64(const __nv_bfloat16* a, const __nv_bfloat16* b) {
     const uint4* pa = reinterpret_cast<const uint4*>(a);
@@ -301,223 +296,6 @@ __device__ __forceinline__ void store_row32_bf16(__nv_bfloat16* out, const uint3
         u.z = pack_bf16x2(__uint_as_float(r[j + 4]), __uint_as_float(r[j + 5]));
         u.w = pack_bf16x2(__uint_as_float(r[j + 6]), __uint_as_float(r[j + 7]));
         *reinterpret_cast<uint4*>(out + j) = u;
-    }
-}
-
-__global__ void __launch_bounds__(kThreads, 1)
-attn_bwd_q_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tdo,
-                  const __grid_constant__ CUtensorMap tk, const __grid_constant__ CUtensorMap tv, Operand q, Operand k,
-                  Operand v, Operand o, Operand dout, Operand dq, const float* __restrict__ lse, int H, int Sq, int Skv,
-                  int skv_pad, float scale, int mask_mode) {
-    b200::pdl_trigger();
-    b200::pdl_wait();
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint8_t* sQ = smem;
-    uint8_t* sdO = smem + 16384;
-    uint8_t* sV = smem + 32768;
-    uint8_t* sK = smem + 65536;
-    uint8_t* sdS = smem;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 98304);
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
-
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int quarter = warp & 3, half = warp >> 2;
-    const int r = quarter * 32 + lane;
-    const int q0 = blockIdx.x * TILE, h = blockIdx.y, b = blockIdx.z;
-    if (tid == 0) {
-        mbar_init(&bars[0], 1);
-        mbar_init(&bars[1], 1);
-        mbar_init(&bars[2], 1);
-        fence_barrier_init();
-    }
-    if (warp == 0) tmem_alloc<512>(tmem_slot);
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem = *tmem_slot;
-
-    if (tid == 0) {
-        mbar_arrive_expect_tx(&bars[0], 2 * TILE * 128 + 2 * skv_pad * 128);
-        tma_load_3d(sQ, &tq, &bars[0], q.col0 + h * q.head_stride, q0, b);
-        tma_load_3d(sdO, &tdo, &bars[0], dout.col0 + h * dout.head_stride, q0, b);
-        tma_load_3d(sK, &tk, &bars[0], k.col0 + h * k.head_stride, 0, b);
-        tma_load_3d(sV, &tv, &bars[0], v.col0 + h * v.head_stride, 0, b);
-        mbar_wait(&bars[0], 0);
-        tc_fence_after();
-        mma_k64(tmem, smem_u32(sQ), smem_u32(sK), skv_pad);          // S   -> cols [0, 256)
-        mma_k64(tmem + 256, smem_u32(sdO), smem_u32(sV), skv_pad);   // dP  -> cols [256, 512)
-        umma_commit(&bars[1]);
-    }
-    // D = rowsum(dO ∘ O) for this thread's query row, from global (two 128-byte rows); both halves compute it
-    const int qrow = q0 + r;
-    float D = 0.f, l2 = 0.f;
-    if (qrow < Sq) {
-        D = row_dot64(o.ptr + ((long long)b * Sq + qrow) * o.ld + o.col0 + h * o.head_stride,
-                      dout.ptr + ((long long)b * Sq + qrow) * dout.ld + dout.col0 + h * dout.head_stride);
-        l2 = lse[((long long)b * H + h) * Sq + qrow] * kLog2e;
-    }
-    mbar_wait(&bars[1], 0);
-    tc_fence_after();
-    const uint32_t trow = tmem + (static_cast<uint32_t>(quarter * 32) << 16);
-    const float sc = scale * kLog2e;
-    for (int c = half * 32; c < skv_pad; c += 64) {
-        uint32_t rs[32], rp[32];
-        tmem_ld_32x32b_x32(trow + c, rs);
-        tmem_ld_32x32b_x32(trow + 256 + c, rp);
-        tmem_ld_wait();
-        float ds[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            const int kc = c + j;
-            const float x = __uint_as_float(rs[j]) * sc + bias_of(mask_mode, qrow, kc) * kLog2e;
-            const bool ok = kc < Skv && qrow < Sq;
-            const float p = ok ? exp2f(x - l2) : 0.f;
-            ds[j] = ok ? p * (__uint_as_float(rp[j]) - D) * scale : 0.f;
-        }
-        store_row_chunk32(sdS, TILE * 128, r, c, ds);
-    }
-    tc_fence_before();
-    fence_proxy_async_smem();
-    __syncthreads();
-    if (tid == 0) {
-        tc_fence_after();
-        mma_tiles_x_mn(tmem, smem_u32(sdS), smem_u32(sK), skv_pad);  // dQ -> cols [0, 64)
-        umma_commit(&bars[2]);
-    }
-    mbar_wait(&bars[2], 0);
-    tc_fence_after();
-    {
-        __nv_bfloat16* out = dq.ptr + ((long long)b * Sq + qrow) * dq.ld + dq.col0 + h * dq.head_stride;
-        const int c = half * 32;
-        uint32_t rg[32];
-        tmem_ld_32x32b_x32(trow + c, rg);
-        tmem_ld_wait();
-        if (qrow < Sq) store_row32_bf16(out + c, rg);
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (warp == 0) {
-        tc_fence_after();
-        tmem_dealloc<512>(tmem);
-    }
-}
-
-// ------------------------------------------------------------------------------------------------ backward, dK / dV
-// smem: [Pᵀ 64K][dSᵀ 64K][Q 32K][dO 32K][lse 1K][D 1K]; the K and V tiles (16 KB each) sit in the first 32 KB and are
-// dead by the time Pᵀ is written.
-constexpr int kBwdKVSmem = 65536 + 65536 + 32768 + 32768 + 2048 + 1024 + 128;
-
-__global__ void __launch_bounds__(kThreads, 1)
-attn_bwd_kv_kernel(const __grid_constant__ CUtensorMap tk, const __grid_constant__ CUtensorMap tv,
-                   const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tdo, Operand q, Operand k,
-                   Operand v, Operand o, Operand dout, Operand dk, Operand dv, const float* __restrict__ lse, int H,
-                   int Sq, int Skv, int sq_pad, float scale, int mask_mode) {
-    b200::pdl_trigger();
-    b200::pdl_wait();
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint8_t* sK = smem;
-    uint8_t* sV = smem + 16384;
-    uint8_t* sPt = smem;
-    uint8_t* sdSt = smem + 65536;
-    uint8_t* sQ = smem + 131072;
-    uint8_t* sdO = smem + 131072 + 32768;
-    float* s_lse = reinterpret_cast<float*>(smem + 196608);
-    float* s_D = s_lse + MAXS;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 196608 + 2048);
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
-
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int quarter = warp & 3, half = warp >> 2;
-    const int r = quarter * 32 + lane;
-    const int k0 = blockIdx.x * TILE, h = blockIdx.y, b = blockIdx.z;
-    if (tid == 0) {
-        mbar_init(&bars[0], 1);
-        mbar_init(&bars[1], 1);
-        mbar_init(&bars[2], 1);
-        fence_barrier_init();
-    }
-    if (warp == 0) tmem_alloc<512>(tmem_slot);
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem = *tmem_slot;
-
-    if (tid == 0) {
-        mbar_arrive_expect_tx(&bars[0], 2 * TILE * 128 + 2 * sq_pad * 128);
-        tma_load_3d(sK, &tk, &bars[0], k.col0 + h * k.head_stride, k0, b);
-        tma_load_3d(sV, &tv, &bars[0], v.col0 + h * v.head_stride, k0, b);
-        tma_load_3d(sQ, &tq, &bars[0], q.col0 + h * q.head_stride, 0, b);
-        tma_load_3d(sdO, &tdo, &bars[0], dout.col0 + h * dout.head_stride, 0, b);
-        mbar_wait(&bars[0], 0);
-        tc_fence_after();
-        mma_k64(tmem, smem_u32(sK), smem_u32(sQ), sq_pad);          // Sᵀ  = K·Qᵀ   -> cols [0, 256)
-        mma_k64(tmem + 256, smem_u32(sV), smem_u32(sdO), sq_pad);   // dPᵀ = V·dOᵀ  -> cols [256, 512)
-        umma_commit(&bars[1]);
-    }
-    // per-query statistics for every query row of this (b, h): lse and D = rowsum(dO ∘ O)
-    {
-        const int qr = tid;  // kThreads == MAXS
-        float D = 0.f, l2 = 0.f;
-        if (qr < Sq) {
-            D = row_dot64(o.ptr + ((long long)b * Sq + qr) * o.ld + o.col0 + h * o.head_stride,
-                          dout.ptr + ((long long)b * Sq + qr) * dout.ld + dout.col0 + h * dout.head_stride);
-            l2 = lse[((long long)b * H + h) * Sq + qr] * kLog2e;
-        }
-        s_lse[qr] = l2;
-        s_D[qr] = D;
-    }
-    __syncthreads();
-    mbar_wait(&bars[1], 0);
-    tc_fence_after();
-    const int krow = k0 + r;
-    const uint32_t trow = tmem + (static_cast<uint32_t>(quarter * 32) << 16);
-    const float sc = scale * kLog2e;
-    for (int c = half * 32; c < sq_pad; c += 64) {
-        uint32_t rs[32], rp[32];
-        tmem_ld_32x32b_x32(trow + c, rs);
-        tmem_ld_32x32b_x32(trow + 256 + c, rp);
-        tmem_ld_wait();
-        float pt[32], ds[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            const int qc = c + j;
-            const float x = __uint_as_float(rs[j]) * sc + bias_of(mask_mode, qc, krow) * kLog2e;
-            const bool ok = qc < Sq && krow < Skv;
-            const float p = ok ? exp2f(x - s_lse[qc]) : 0.f;
-            pt[j] = p;
-            ds[j] = ok ? p * (__uint_as_float(rp[j]) - s_D[qc]) * scale : 0.f;
-        }
-        store_row_chunk32(sPt, TILE * 128, r, c, pt);
-        store_row_chunk32(sdSt, TILE * 128, r, c, ds);
-    }
-    tc_fence_before();
-    fence_proxy_async_smem();
-    __syncthreads();
-    if (tid == 0) {
-        tc_fence_after();
-        mma_tiles_x_mn(tmem, smem_u32(sPt), smem_u32(sdO), sq_pad);       // dV -> cols [0, 64)
-        mma_tiles_x_mn(tmem + 64, smem_u32(sdSt), smem_u32(sQ), sq_pad);  // dK -> cols [64, 128)
-        umma_commit(&bars[2]);
-    }
-    mbar_wait(&bars[2], 0);
-    tc_fence_after();
-#pragma unroll
-    for (int which = 0; which < 2; ++which) {
-        const Operand& dst = which == 0 ? dv : dk;
-        __nv_bfloat16* out = dst.ptr + ((long long)b * Skv + krow) * dst.ld + dst.col0 + h * dst.head_stride;
-        const int c = half * 32;
-        uint32_t rg[32];
-        tmem_ld_32x32b_x32(trow + which * 64 + c, rg);
-        tmem_ld_wait();
-        if (krow < Skv) store_row32_bf16(out + c, rg);
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (warp == 0) {
-        tc_fence_after();
-        tmem_dealloc<512>(tmem);
     }
 }
 
@@ -801,56 +579,21 @@ int b200ml_attn_bwd(const b200ml_attn_operand* q, const b200ml_attn_operand* k, 
     B200_REQUIRE(Sq >= 1 && Skv >= 1 && Sq <= MAXS && Skv <= MAXS, "attention bwd: need S <= %d (got %d, %d)", MAXS, Sq,
                  Skv);
     const int skv_pad = (Skv + 15) / 16 * 16, sq_pad = (Sq + 15) / 16 * 16;
-    // B200ML_ATTN_BWD=split keeps the two-kernel backward (dQ, then dK/dV); default is the fused single kernel
-    static const bool split = [] { const char* e = getenv("B200ML_ATTN_BWD"); return e && e[0] == 's'; }();
-    if (!split) {
-        static bool attr_f = false;
-        if (!attr_f) {
-            B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                 kBwdFusedSmem + 1024));
-            attr_f = true;
-        }
-        CUtensorMap tq, tdo, tk, tv;
-        if (head_tmap(&tq, q, B, Sq, H, sq_pad) || head_tmap(&tdo, dout, B, Sq, H, sq_pad) ||
-            head_tmap(&tk, k, B, Skv, H, skv_pad) || head_tmap(&tv, v, B, Skv, H, skv_pad))
-            return -1;
-        dim3 grid(1, H, B);
-        b200::pdl(attn_bwd_fused_kernel, dim3(grid), dim3(kThreads), kBwdFusedSmem + 1024, stream)(
-            tq, tdo, tk, tv, dev_op(q), dev_op(k), dev_op(v), dev_op(out), dev_op(dout), dev_op(dq), dev_op(dk), dev_op(dv),
-            lse, H, Sq, Skv, sq_pad, skv_pad, scale, mask_mode);
-        B200_CHECK_CUDA(cudaGetLastError());
-        return 0;
+    static bool attr_f = false;
+    if (!attr_f) {
+        B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             kBwdFusedSmem + 1024));
+        attr_f = true;
     }
-    static bool attr = false;
-    if (!attr) {
-        B200_CHECK_CUDA(
-            cudaFuncSetAttribute(attn_bwd_q_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdQSmem));
-        B200_CHECK_CUDA(
-            cudaFuncSetAttribute(attn_bwd_kv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdKVSmem));
-        attr = true;
-    }
-    {
-        CUtensorMap tq, tdo, tk, tv;
-        if (head_tmap(&tq, q, B, Sq, H, TILE) || head_tmap(&tdo, dout, B, Sq, H, TILE) ||
-            head_tmap(&tk, k, B, Skv, H, skv_pad) || head_tmap(&tv, v, B, Skv, H, skv_pad))
-            return -1;
-        dim3 grid((Sq + TILE - 1) / TILE, H, B);
-        b200::pdl(attn_bwd_q_kernel, dim3(grid), dim3(kThreads), kBwdQSmem, stream)(tq, tdo, tk, tv, dev_op(q), dev_op(k), dev_op(v),
-                                                            dev_op(out), dev_op(dout), dev_op(dq), lse, H, Sq, Skv,
-                                                            skv_pad, scale, mask_mode);
-        B200_CHECK_CUDA(cudaGetLastError());
-    }
-    {
-        CUtensorMap tk, tv, tq, tdo;
-        if (head_tmap(&tk, k, B, Skv, H, TILE) || head_tmap(&tv, v, B, Skv, H, TILE) ||
-            head_tmap(&tq, q, B, Sq, H, sq_pad) || head_tmap(&tdo, dout, B, Sq, H, sq_pad))
-            return -1;
-        dim3 grid((Skv + TILE - 1) / TILE, H, B);
-        b200::pdl(attn_bwd_kv_kernel, dim3(grid), dim3(kThreads), kBwdKVSmem, stream)(tk, tv, tq, tdo, dev_op(q), dev_op(k), dev_op(v),
-                                                              dev_op(out), dev_op(dout), dev_op(dk), dev_op(dv), lse, H,
-                                                              Sq, Skv, sq_pad, scale, mask_mode);
-        B200_CHECK_CUDA(cudaGetLastError());
-    }
+    CUtensorMap tq, tdo, tk, tv;
+    if (head_tmap(&tq, q, B, Sq, H, sq_pad) || head_tmap(&tdo, dout, B, Sq, H, sq_pad) ||
+        head_tmap(&tk, k, B, Skv, H, skv_pad) || head_tmap(&tv, v, B, Skv, H, skv_pad))
+        return -1;
+    dim3 grid(1, H, B);
+    b200::pdl(attn_bwd_fused_kernel, dim3(grid), dim3(kThreads), kBwdFusedSmem + 1024, stream)(
+        tq, tdo, tk, tv, dev_op(q), dev_op(k), dev_op(v), dev_op(out), dev_op(dout), dev_op(dq), dev_op(dk), dev_op(dv),
+        lse, H, Sq, Skv, sq_pad, skv_pad, scale, mask_mode);
+    B200_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
 

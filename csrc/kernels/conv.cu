@@ -384,6 +384,144 @@ conv_igemm_kernel(Src src, const float* __restrict__ w, const float* __restrict_
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// tcgen05 weight gradient: per CTA (one image x one 16 x 16 tile) a GEMM whose REDUCTION dimension is the tile's 256
+// pixels (split-K over B·H·W: every CTA contributes one partial, summed afterwards in CTA order):
+//     D[kw][co] = sum_pix  Xcol[kw][pix] * dZ[co][pix]       kw = ci * 9 + tap  (M, padded to blocks of 128)
+// A = im2col(X) transposed, gathered from the fp32 halo tile and written as bf16 straight into the 128B-swizzled
+// K-major layout (64 pixels = four tile rows per slice), B = dZ (un-pool and ReLU' folded into the load), N = Cout
+// padded to 16.  The accumulator lives in TMEM across the four slices; the epilogue writes partial[cta] in the layout
+// of the direct kernel ([co][ci*9 + t] then the Cout bias sums), so the same fixed-order reduction finishes the job.
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(T* T, 1)
+conv_wgrad_igemm_kernel(DzSource src, const float* __restrict__ x, float* __restrict__ partial, int B, int Cin,
+                        int Cout, int mblocks) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sA = smem;                                         // mblocks x [128 rows][64 pixels] bf16, swizzled
+    uint8_t* sB = smem + (size_t)mblocks * 16384;               // [Np rows][64 pixels] bf16, swizzled (<= 8 KB)
+    uint64_t* bar = reinterpret_cast<uint64_t*>(sB + 8192);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 1);
+    float* s_in = reinterpret_cast<float*>(sB + 8192 + 64);     // [Cin][HALO][HALO]
+    float* s_dz = s_in + Cin * HALO * HALO;                     // [Cout][T*T]
+    const int H = src.H, W = src.W;
+    const int tiles_x = (W + T - 1) / T;
+    const int b = blockIdx.y;
+    const int ty0 = (blockIdx.x / tiles_x) * T, tx0 = (blockIdx.x % tiles_x) * T;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int Np = (Cout + 15) / 16 * 16, Kw = Cin * 9;
+
+    if (tid == 0) {
+        mbar_init(bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) tmem_alloc<512>(tmem_slot);   // mblocks (<= 5) x Np (<= 64) fp32 columns
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+    b200::pdl_trigger();
+    b200::pdl_wait();
+
+    for (int i = tid; i < Cin * HALO * HALO; i += T * T) {
+        const int c = i / (HALO * HALO), rem = i % (HALO * HALO);
+        const int gy = ty0 + rem / HALO - 1, gx = tx0 + rem % HALO - 1;
+        s_in[i] = (gy >= 0 && gy < H && gx >= 0 && gx < W) ? x[((long long)(b * Cin + c) * H + gy) * W + gx] : 0.f;
+    }
+    for (int i = tid; i < Cout * T * T; i += T * T) {
+        const int c = i / (T * T), rem = i % (T * T);
+        s_dz[i] = src.at(b, Cout, c, ty0 + rem / T, tx0 + rem % T);
+    }
+    __syncthreads();
+
+    const int row = tid & 127, half = tid >> 7;   // A: thread fills row `row` of each M block, 32 of the 64 pixels
+    const uint32_t idesc = umma_idesc_bf16(128, Np, false, false);
+    uint32_t phase = 0;
+    for (int sl = 0; sl < 4; ++sl) {              // pixels [sl * 64, sl * 64 + 64) = tile rows 4 sl .. 4 sl + 3
+        for (int mb = 0; mb < mblocks; ++mb) {
+            const int kw = mb * 128 + row;
+            const int ci = kw / 9, t = kw - ci * 9;
+            const float* in = s_in + (ci * HALO + t / 3) * HALO + t % 3;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int c8 = half * 4 + q;                      // 16-byte chunk = 8 consecutive pixels of one tile row
+                const int p = sl * 64 + c8 * 8, py = p >> 4, px = p & 15;
+                float v[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) v[e] = kw < Kw ? in[py * HALO + px + e] : 0.f;
+                uint4 u;
+                u.x = pack_bf16x2(v[0], v[1]);
+                u.y = pack_bf16x2(v[2], v[3]);
+                u.z = pack_bf16x2(v[4], v[5]);
+                u.w = pack_bf16x2(v[6], v[7]);
+                *reinterpret_cast<uint4*>(sA + (size_t)mb * 16384 + swz128_offset(row, c8)) = u;
+            }
+        }
+        for (int i = tid; i < Np * 8; i += T * T) {   // B: dZ rows (output channels) x 64 pixels
+            const int n = i >> 3, c8 = i & 7;
+            float v[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = n < Cout ? s_dz[n * T * T + sl * 64 + c8 * 8 + e] : 0.f;
+            uint4 u;
+            u.x = pack_bf16x2(v[0], v[1]);
+            u.y = pack_bf16x2(v[2], v[3]);
+            u.z = pack_bf16x2(v[4], v[5]);
+            u.w = pack_bf16x2(v[6], v[7]);
+            *reinterpret_cast<uint4*>(sB + swz128_offset(n, c8)) = u;
+        }
+        tc_fence_before();
+        fence_proxy_async_smem();
+        __syncthreads();
+        if (tid == 0) {
+            tc_fence_after();
+            for (int mb = 0; mb < mblocks; ++mb)
+                for (int kk = 0; kk < 4; ++kk)
+                    umma_bf16(tmem + mb * Np, umma_smem_desc(smem_u32(sA) + mb * 16384 + kk * 32, 16, 1024),
+                              umma_smem_desc(smem_u32(sB) + kk * 32, 16, 1024), idesc, (sl > 0 || kk > 0) ? 1u : 0u);
+            umma_commit(bar);
+        }
+        mbar_wait(bar, phase);   // the MMAs have consumed sA / sB (after the last slice: the result is complete)
+        phase ^= 1;
+        tc_fence_after();
+    }
+
+    const int nW = Cout * Kw;
+    const long long cta = (long long)blockIdx.y * gridDim.x + blockIdx.x;
+    float* out = partial + cta * (nW + Cout);
+    // TMEM lane = kw within the M block, column = output channel; warps 0-3 read M blocks 0, 2, 4, warps 4-7 blocks 1, 3
+    const int lane_row = (warp & 3) * 32 + (tid & 31);
+    for (int mb = half; mb < mblocks; mb += 2) {
+        const int kw = mb * 128 + lane_row;
+        const uint32_t taddr = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16) + mb * Np;
+        for (int c0 = 0; c0 < Np; c0 += 16) {
+            uint32_t r[16];
+            tmem_ld_32x32b_x16(taddr + c0, r);
+            tmem_ld_wait();
+            if (kw < Kw) {
+#pragma unroll
+                for (int k = 0; k < 16; ++k)
+                    if (c0 + k < Cout) out[(c0 + k) * Kw + kw] = __uint_as_float(r[k]);
+            }
+        }
+    }
+    for (int co = tid; co < Cout; co += T * T) {   // bias gradient: plain fp32 sums of dZ over the tile
+        const float* dz = s_dz + co * T * T;
+        float sum = 0.f;
+        for (int i = 0; i < T * T; ++i) sum += dz[i];
+        out[nW + co] = sum;
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        tmem_dealloc<512>(tmem);
+    }
+}
+
+static size_t wgrad_igemm_smem(int Cin, int Cout, int mblocks) {
+    return 1024 + (size_t)mblocks * 16384 + 8192 + 64 + sizeof(float) * ((size_t)Cin * HALO * HALO + (size_t)Cout * T * T);
+}
+
 static size_t igemm_smem(int C, int pool) {
     return 1024 + 32768 + 8192 + 64 + sizeof(float) * ((size_t)C * HALO * HALO + (pool ? kChunk * T * (T + 1) : 0));
 }
@@ -480,15 +618,30 @@ int b200ml_conv3x3_relu_bwd(const float* dy, const float* ysaved, const unsigned
         B200_CHECK_CUDA(cudaGetLastError());
     }
     {
-        const size_t smem = sizeof(float) * ((size_t)Cin * HALO * HALO + (size_t)Cout * T * T);
-        static size_t attr = 0;
-        if (smem > attr) {
-            B200_CHECK_CUDA(
-                cudaFuncSetAttribute(conv_bwd_weight_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            attr = smem;
+        // weight gradient: tcgen05 implicit GEMM over the tile's pixels (B200ML_CONV_ALGO=1 keeps the direct fp32 kernel)
+        const int mblocks = (Cin * 9 + 127) / 128;
+        const size_t smem_i = wgrad_igemm_smem(Cin, Cout, mblocks);
+        if (g_conv_algo != 1 && smem_i <= 200 * 1024) {
+            static size_t attr_w = 0;
+            if (smem_i > attr_w) {
+                B200_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_igemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                     (int)smem_i));
+                attr_w = smem_i;
+            }
+            b200::pdl(conv_wgrad_igemm_kernel, dim3(grid), dim3(T * T), smem_i, stream, 3)(src, x, (float*)scratch, B, Cin,
+                                                                                           Cout, mblocks);
+            B200_CHECK_CUDA(cudaGetLastError());
+        } else {
+            const size_t smem = sizeof(float) * ((size_t)Cin * HALO * HALO + (size_t)Cout * T * T);
+            static size_t attr = 0;
+            if (smem > attr) {
+                B200_CHECK_CUDA(
+                    cudaFuncSetAttribute(conv_bwd_weight_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                attr = smem;
+            }
+            b200::pdl(conv_bwd_weight_kernel, dim3(grid), dim3(T * T), smem, stream, 3)(src, x, (float*)scratch, B, Cin, Cout);
+            B200_CHECK_CUDA(cudaGetLastError());
         }
-        b200::pdl(conv_bwd_weight_kernel, dim3(grid), dim3(T * T), smem, stream, 3)(src, x, (float*)scratch, B, Cin, Cout);
-        B200_CHECK_CUDA(cudaGetLastError());
         const int nW = Cout * Cin * 9;
         B200_CHECK_CUDA(b200::launch_reduce_partials((const float*)scratch, (int)(grid.x * grid.y), nW + Cout, nW, dw, db,
                                                      accumulate, stream));
