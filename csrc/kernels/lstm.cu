@@ -15,7 +15,7 @@
 // synchronisation in a step is __syncwarp, there is no CTA barrier in the loop.  Every global access of a warp is a
 // whole 128-byte line (32 consecutive units of one (b, t)) and the next step's operands are prefetched into registers
 // while the current step computes.  fp32 throughout the recurrence, so no rounding error accumulates over time.
-// hidden_size must be 32 (the reference value).
+// This warp-per-row design needs hidden_size == 32 (the reference value); 64 and 128 take the CTA-per-row kernels below.
 #include "../common/pdl.cuh"
 #include "../../include/b200ml.h"
 #include "../common/host.h"
@@ -171,6 +171,148 @@ lstm_rec_bwd_kernel(const float* __restrict__ w_hh, const float* __restrict__ c0
 }
 
 // out_bf16[i] = dropout(x[i]) — the (inter-layer) dropout + cast that feeds the hoisted input-projection GEMM
+// ---------------------------------------------------------------------------------------------------------------
+// Wider hidden sizes (HH = 64, 128; nn.LSTM accepts any hidden_size, distributed_lstm.py:116-118): 128 weights per lane
+// no longer fit, so a CTA of 4 * HH threads owns one batch row and a THREAD owns one gate row r = gate * HH + unit of
+// W_hh (HH values in registers; packed as bf16 pairs for HH = 128, where 512 threads x 128 fp32 would be the whole
+// register file).  A step costs two (forward) / three (backward) CTA barriers instead of two __syncwarp; the layout of
+// every tensor is the one of the HH = 32 kernels, so the hoisted GEMMs around the recurrence are unchanged.
+// ---------------------------------------------------------------------------------------------------------------
+template <int HH, bool kPacked>
+struct WRow {
+    float w[kPacked ? 1 : HH];
+    uint32_t p[kPacked ? HH / 2 : 1];
+    __device__ __forceinline__ void set(int k, float a, float b) {   // k even
+        if (kPacked) p[k / 2] = pack_bf16x2(a, b);
+        else { w[k] = a; w[k + 1] = b; }
+    }
+    __device__ __forceinline__ float2 get(int k) const {            // k even
+        if (kPacked) return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&p[k / 2]));
+        return make_float2(w[k], w[k + 1]);
+    }
+};
+
+template <int HH, bool kPacked>
+__global__ void __launch_bounds__(4 * HH)
+lstm_rec_fwd_wide_kernel(const float* __restrict__ pre, const float* __restrict__ w_hh, const float* __restrict__ h0,
+                         const float* __restrict__ c0, float* __restrict__ h_out, float* __restrict__ gates_out,
+                         float* __restrict__ c_out, float* __restrict__ h_n, float* __restrict__ c_n, int B, int T) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
+    constexpr int GG = 4 * HH;
+    __shared__ __align__(16) float s_h[HH];
+    __shared__ float s_gate[GG];
+    const int r = threadIdx.x, gate = r / HH, u = r % HH;
+    const int b = blockIdx.x;
+    WRow<HH, kPacked> wr;
+#pragma unroll
+    for (int k = 0; k < HH; k += 2) wr.set(k, w_hh[(long long)r * HH + k], w_hh[(long long)r * HH + k + 1]);
+    float c = (r < HH && c0) ? c0[(long long)b * HH + u] : 0.f;
+    if (r < HH) s_h[u] = h0 ? h0[(long long)b * HH + u] : 0.f;
+    const float* pb = pre + (long long)b * T * GG;
+    float pn = pb[r];
+    __syncthreads();
+    for (int t = 0; t < T; ++t) {
+        float a = pn;
+        if (t + 1 < T) pn = pb[(long long)(t + 1) * GG + r];
+        float a1 = 0.f;
+#pragma unroll
+        for (int k = 0; k < HH; k += 4) {
+            const float4 hv = *reinterpret_cast<const float4*>(&s_h[k]);   // CTA-wide broadcast
+            const float2 w0 = wr.get(k), w1 = wr.get(k + 2);
+            a += hv.x * w0.x + hv.y * w0.y;
+            a1 += hv.z * w1.x + hv.w * w1.y;
+        }
+        a += a1;
+        const float act = gate == 2 ? tanhf_(a) : sigmoidf_(a);
+        s_gate[r] = act;
+        const long long bt = (long long)b * T + t;
+        if (gates_out) gates_out[bt * GG + r] = act;
+        __syncthreads();                 // all gates of the step are in s_gate; every thread has read h_{t-1}
+        if (r < HH) {
+            c = s_gate[HH + u] * c + s_gate[u] * s_gate[2 * HH + u];
+            const float hn = s_gate[3 * HH + u] * tanhf_(c);
+            s_h[u] = hn;
+            h_out[bt * HH + u] = hn;
+            if (c_out) c_out[bt * HH + u] = c;
+        }
+        __syncthreads();
+    }
+    if (r < HH) {
+        if (h_n) h_n[(long long)b * HH + u] = s_h[u];
+        if (c_n) c_n[(long long)b * HH + u] = c;
+    }
+}
+
+// thread (q, u): q = r / HH selects a quarter of the gate rows; it holds W_hh[q * HH + j][u], j = 0 .. HH-1
+template <int HH, bool kPacked>
+__global__ void __launch_bounds__(4 * HH)
+lstm_rec_bwd_wide_kernel(const float* __restrict__ w_hh, const float* __restrict__ c0, const float* __restrict__ gates,
+                         const float* __restrict__ c_seq, const float* __restrict__ dh_seq,
+                         const float* __restrict__ dh_n, const float* __restrict__ dc_n,
+                         __nv_bfloat16* __restrict__ dg_out, float* __restrict__ dh0, float* __restrict__ dc0, int B,
+                         int T) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
+    constexpr int GG = 4 * HH;
+    __shared__ __align__(16) float s_dg[GG];
+    __shared__ float s_part[4][HH];
+    const int r = threadIdx.x, q = r / HH, u = r % HH;
+    const int b = blockIdx.x;
+    WRow<HH, kPacked> wc;
+#pragma unroll
+    for (int j = 0; j < HH; j += 2)
+        wc.set(j, w_hh[(long long)(q * HH + j) * HH + u], w_hh[(long long)(q * HH + j + 1) * HH + u]);
+    const bool owner = r < HH;
+    float dc = (owner && dc_n) ? dc_n[(long long)b * HH + u] : 0.f;
+    float dh = (owner && dh_n) ? dh_n[(long long)b * HH + u] : 0.f;
+    const float* gb = gates + (long long)b * T * GG;
+    const float* cb = c_seq + (long long)b * T * HH;
+    const float* db = dh_seq ? dh_seq + (long long)b * T * HH : nullptr;
+    const float c_init = (owner && c0) ? c0[(long long)b * HH + u] : 0.f;
+    for (int t = T - 1; t >= 0; --t) {
+        if (owner) {
+            const float* gt = gb + (long long)t * GG;
+            const float ig = gt[u], fg = gt[HH + u], gg = gt[2 * HH + u], og = gt[3 * HH + u];
+            const float ct = cb[(long long)t * HH + u];
+            const float cp = t > 0 ? cb[(long long)(t - 1) * HH + u] : c_init;
+            const float dht = dh + (db ? db[(long long)t * HH + u] : 0.f);
+            const float tc = tanhf_(ct);
+            const float d = dc + dht * og * (1.f - tc * tc);
+            const float di = d * gg * ig * (1.f - ig), df = d * cp * fg * (1.f - fg), dgg = d * ig * (1.f - gg * gg),
+                        dog = dht * tc * og * (1.f - og);
+            dc = d * fg;
+            s_dg[u] = di;
+            s_dg[HH + u] = df;
+            s_dg[2 * HH + u] = dgg;
+            s_dg[3 * HH + u] = dog;
+            __nv_bfloat16* dgo = dg_out + ((long long)b * T + t) * GG;
+            dgo[u] = __float2bfloat16(di);
+            dgo[HH + u] = __float2bfloat16(df);
+            dgo[2 * HH + u] = __float2bfloat16(dgg);
+            dgo[3 * HH + u] = __float2bfloat16(dog);
+        }
+        __syncthreads();
+        float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+        for (int j = 0; j < HH; j += 4) {
+            const float4 dv = *reinterpret_cast<const float4*>(&s_dg[q * HH + j]);
+            const float2 w0 = wc.get(j), w1 = wc.get(j + 2);
+            a0 += dv.x * w0.x + dv.y * w0.y;
+            a1 += dv.z * w1.x + dv.w * w1.y;
+        }
+        s_part[q][u] = a0 + a1;
+        __syncthreads();
+        if (owner) dh = (s_part[0][u] + s_part[1][u]) + (s_part[2][u] + s_part[3][u]);
+        // the next step's writes to s_dg come after this read of s_part by the same owner threads; the other threads
+        // wait at the next barrier before they read s_dg again
+    }
+    if (owner) {
+        if (dh0) dh0[(long long)b * HH + u] = dh;
+        if (dc0) dc0[(long long)b * HH + u] = dc;
+    }
+}
+
 __global__ void dropout_cast_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, long long n, float p,
                                     const RngState* __restrict__ rng, uint32_t site) {
     b200::pdl_trigger();
@@ -224,9 +366,21 @@ int b200ml_lstm_rec_fwd(const float* pre, const float* w_hh, const float* h0, co
                         cudaStream_t stream) {
     using namespace b200::lstm;
     B200_REQUIRE(pre && w_hh && h_out, "lstm_rec_fwd: null pointer");
-    B200_REQUIRE(hidden == H, "lstm: hidden_size must be %d (got %d)", H, hidden);
+    B200_REQUIRE(hidden == 32 || hidden == 64 || hidden == 128, "lstm: hidden_size must be 32, 64 or 128 (got %d)", hidden);
     B200_REQUIRE((gates_out == nullptr) == (c_out == nullptr), "lstm_rec_fwd: gates_out and c_out go together");
     if (B <= 0 || T <= 0) return 0;
+    if (hidden == 64) {
+        b200::pdl(lstm_rec_fwd_wide_kernel<64, false>, dim3(B), dim3(256), 0, stream)(pre, w_hh, h0, c0, h_out, gates_out,
+                                                                                      c_out, h_n, c_n, B, T);
+        B200_CHECK_CUDA(cudaGetLastError());
+        return 0;
+    }
+    if (hidden == 128) {
+        b200::pdl(lstm_rec_fwd_wide_kernel<128, true>, dim3(B), dim3(512), 0, stream)(pre, w_hh, h0, c0, h_out, gates_out,
+                                                                                      c_out, h_n, c_n, B, T);
+        B200_CHECK_CUDA(cudaGetLastError());
+        return 0;
+    }
     b200::pdl(lstm_rec_fwd_kernel, dim3((B + kWarps - 1) / kWarps), dim3(kThreads), 0, stream)(pre, w_hh, h0, c0, h_out, gates_out, c_out, h_n,
                                                                     c_n, B, T);
     B200_CHECK_CUDA(cudaGetLastError());
@@ -238,8 +392,20 @@ int b200ml_lstm_rec_bwd(const float* w_hh, const float* c0, const float* gates, 
                         float* dc0, int B, int T, int hidden, cudaStream_t stream) {
     using namespace b200::lstm;
     B200_REQUIRE(w_hh && gates && c_seq && dg_out_bf16, "lstm_rec_bwd: null pointer");
-    B200_REQUIRE(hidden == H, "lstm: hidden_size must be %d (got %d)", H, hidden);
+    B200_REQUIRE(hidden == 32 || hidden == 64 || hidden == 128, "lstm: hidden_size must be 32, 64 or 128 (got %d)", hidden);
     if (B <= 0 || T <= 0) return 0;
+    if (hidden == 64) {
+        b200::pdl(lstm_rec_bwd_wide_kernel<64, false>, dim3(B), dim3(256), 0, stream)(
+            w_hh, c0, gates, c_seq, dh_seq, dh_n, dc_n, (__nv_bfloat16*)dg_out_bf16, dh0, dc0, B, T);
+        B200_CHECK_CUDA(cudaGetLastError());
+        return 0;
+    }
+    if (hidden == 128) {
+        b200::pdl(lstm_rec_bwd_wide_kernel<128, true>, dim3(B), dim3(512), 0, stream)(
+            w_hh, c0, gates, c_seq, dh_seq, dh_n, dc_n, (__nv_bfloat16*)dg_out_bf16, dh0, dc0, B, T);
+        B200_CHECK_CUDA(cudaGetLastError());
+        return 0;
+    }
     b200::pdl(lstm_rec_bwd_kernel, dim3((B + kWarps - 1) / kWarps), dim3(kThreads), 0, stream)(w_hh, c0, gates, c_seq, dh_seq, dh_n, dc_n,
                                                                     (__nv_bfloat16*)dg_out_bf16, dh0, dc0, B, T);
     B200_CHECK_CUDA(cudaGetLastError());

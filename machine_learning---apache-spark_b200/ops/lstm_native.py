@@ -122,5 +122,5 @@ class _LSTMStack(torch.autograd.Function):
 
 
 def lstm_forward(x, h0, c0, weights, num_layers, dropout_p, site):
-    assert weights[1].shape[1] == 32, "the LSTM kernels are specialised for hidden_size 32 (the reference value)"
+    assert weights[1].shape[1] in (32, 64, 128), "the LSTM recurrence kernels cover hidden_size 32 (the reference value), 64 and 128"
     return _LSTMStack.apply(x, h0, c0, num_layers, dropout_p, site, *weights)

@@ -50,15 +50,17 @@ def _run_conv_case(B, Cin, Cout, HW, pool, conv3x3_relu, tol_y, tol_g):
     assert _rel(b.grad, br.grad) < (tol_g if tol_g < 1e-3 else 8e-2)
 
 
-@pytest.mark.parametrize("B,T,E", [(32, 128, 32), (5, 17, 32), (40, 9, 24)])
-def test_lstm_matches_torch(B, T, E):
+@pytest.mark.parametrize("B,T,E,HID", [(32, 128, 32, 32), (5, 17, 32, 32), (40, 9, 24, 32), (6, 21, 32, 64), (33, 40, 64, 64),
+                                         (4, 19, 48, 128), (9, 12, 128, 128)])
+def test_lstm_matches_torch(B, T, E, HID):
+    """hidden 32: warp-per-row kernels (the reference size); 64 / 128: CTA-per-row kernels (128 keeps W_hh as bf16)."""
     from b200ml.ops.lstm import lstm_forward
     torch.manual_seed(0)
-    ref = torch.nn.LSTM(E, 32, num_layers=2, batch_first=True, dropout=0.0)
+    ref = torch.nn.LSTM(E, HID, num_layers=2, batch_first=True, dropout=0.0)
     mine = [getattr(ref, n).detach().clone().cuda().requires_grad_() for n in ref._flat_weights_names]
     x = torch.randn(B, T, E, device="cuda", requires_grad=True)
-    h0 = (torch.randn(2, B, 32, device="cuda") * 0.1).requires_grad_()
-    c0 = (torch.randn(2, B, 32, device="cuda") * 0.1).requires_grad_()
+    h0 = (torch.randn(2, B, HID, device="cuda") * 0.1).requires_grad_()
+    c0 = (torch.randn(2, B, HID, device="cuda") * 0.1).requires_grad_()
     out, hn, cn = lstm_forward(x, h0, c0, mine, 2, 0.0, 11)
     g = torch.randn_like(out)
     ((out * g).sum() + hn.sum() * 0.5 + cn.sum() * 0.25).backward()
