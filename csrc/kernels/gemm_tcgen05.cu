@@ -27,6 +27,12 @@
 namespace b200 {
 namespace gemm {
 
+__device__ __forceinline__ float ex2_ftz(float x) {   // 2^x, one MUFU; -inf -> 0
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 64;  // 64 bf16 = 128 B = one swizzle row
 constexpr int UMMA_K = 16;
@@ -53,6 +59,8 @@ struct Epilogue {
     float* splitk_ws;        // != nullptr: write raw fp32 partial tiles to ws[split][M][N] instead of C
     int tma_store;           // bf16 C through smem staging + cp.async.bulk.tensor stores (needs tmap_c)
     int debug;               // B200ML_GEMM_DEBUG (timing experiments only, results are garbage): 1 = no TMA loads, 2 = no MMAs, 4 = no TMA stores
+    float2* row_stats;       // optional [M][stats_ld] per-row (max, sum-exp) of each tile half (TMA-store epilogue only)
+    int stats_ld;
     int cluster_splits;      // > 1: split-K over the CTAs of a cluster, partial tiles reduced through DSMEM (one tile per CTA)
 };
 
@@ -293,11 +301,24 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 
         // fused math on 32 consecutive accumulator columns of one row (ct = column offset inside the tile)
         auto epi_math = [&](float (&v)[32], const uint32_t (&r)[32], int row, int col0, int ct) {
+            if (alpha != 1.f) {   // uniform: the common alpha = 1 case pays no multiply
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * alpha;
+                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * alpha;
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+            }
             if (ep.bias) {
+                // smem broadcast, 16 bytes at a time (ct is a multiple of 32: aligned); zero beyond N
+                const float4* sb4 = reinterpret_cast<const float4*>(s_bias + ct);
 #pragma unroll
-                for (int j = 0; j < 32; ++j) v[j] += s_bias[ct + j];  // smem broadcast; zero beyond N
+                for (int j = 0; j < 8; ++j) {
+                    const float4 bv = sb4[j];
+                    v[4 * j] += bv.x;
+                    v[4 * j + 1] += bv.y;
+                    v[4 * j + 2] += bv.z;
+                    v[4 * j + 3] += bv.w;
+                }
             }
             if (ep.act == 1) {  // branch on the (uniform) activation once per chunk, not per element
 #pragma unroll
@@ -373,6 +394,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             if (use_tma_store) {
                 // this warp owns columns [half*BN/2, (half+1)*BN/2) of the tile, in 64-column slabs
                 const int cbase = half * (BN / 2);
+                float st_m = -INFINITY, st_s = 0.f;   // online softmax statistics of this thread's row over its columns
 #pragma unroll 1
                 for (int g = 0; g < BN / 2; g += 64) {
                     const int c = cbase + g;
@@ -384,6 +406,42 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     float v0[32], v1[32];
                     epi_math(v0, r0, row, t.n0 + c, c);
                     epi_math(v1, r1, row, t.n0 + c + 32, c + 32);
+                    if (ep.row_stats) {
+                        // On the values as they will be stored (bf16-rounded); base-2 domain: st_m holds max * log2(e),
+                        // st_s = sum 2^(v * log2e - st_m): per element one pack (per pair), one unpack, FMNMX, FFMA,
+                        // MUFU.EX2 (ftz: no denormal fix-up code), FADD.  Full 64-column slabs skip the column mask.
+                        const bool full = t.n0 + c + 64 <= N;   // warp-uniform
+                        auto stats = [&](const float (&v)[32], int col0) {
+                            float b[32], cm = -INFINITY;
+#pragma unroll
+                            for (int j = 0; j < 32; j += 2) {
+                                const uint32_t pk = pack_bf16x2(v[j], v[j + 1]);
+                                b[j] = __uint_as_float(pk << 16);
+                                b[j + 1] = __uint_as_float(pk & 0xFFFF0000u);
+                                if (!full) {
+                                    if (col0 + j >= N) b[j] = -INFINITY;
+                                    if (col0 + j + 1 >= N) b[j + 1] = -INFINITY;
+                                }
+                                cm = fmaxf(cm, fmaxf(b[j], b[j + 1]));
+                            }
+                            cm *= 1.4426950408889634f;
+                            if (cm > st_m) {
+                                st_s *= ex2_ftz(st_m - cm);   // 2^(-inf) = 0 on the first block
+                                st_m = cm;
+                            }
+                            if (st_m > -INFINITY) {
+                                float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+                                for (int j = 0; j < 32; j += 2) {
+                                    s0 += ex2_ftz(fmaf(b[j], 1.4426950408889634f, -st_m));
+                                    s1 += ex2_ftz(fmaf(b[j + 1], 1.4426950408889634f, -st_m));
+                                }
+                                st_s += s0 + s1;
+                            }
+                        };
+                        stats(v0, t.n0 + c);
+                        stats(v1, t.n0 + c + 32);
+                    }
                     uint8_t* slab = my_stage + (C::kSlabsPerWarp == 2 ? (g >> 6) * 4096 : 0);
                     // the staging slab must have been read by the store that used it last (previous slab, or - with one
                     // slab per 64 columns - the previous tile)
@@ -410,6 +468,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         tma_store_commit();
                     }
                 }
+                if (ep.row_stats && row < M)
+                    ep.row_stats[static_cast<long long>(row) * ep.stats_ld + 2 * (t.n0 / BN) + half] =
+                        make_float2(st_m * 0.6931471805599453f, st_s);   // back to natural units: (max, sum exp(v - max))
             } else {
 #pragma unroll 1
                 for (int c = half * 32; c < BN; c += 64) {
@@ -693,6 +754,7 @@ static int launch(const b200ml_gemm_args* g, Epilogue ep, int splits, cudaStream
         if (make_tmap_bf16(&tc, g->C, 2, dims, strides, box)) return -1;
         ep.tma_store = 1;
     }
+    B200_REQUIRE(!ep.row_stats || ep.tma_store, "gemm: row_stats needs the TMA-store epilogue (16-byte aligned bf16 rows)");
     auto kern = gemm_bf16_kernel<A_MN, B_MN, BN, kCtas>;
     static bool attr_set = false;  // per instantiation
     if (!attr_set) {
@@ -793,6 +855,11 @@ extern "C" int b200ml_gemm_bf16(const b200ml_gemm_args* g, cudaStream_t stream) 
     ep.splitk_ws = nullptr;
     ep.tma_store = 0;
     ep.cluster_splits = 0;
+    ep.row_stats = reinterpret_cast<float2*>(g->row_stats);
+    ep.stats_ld = g->row_stats_ld;
+    B200_REQUIRE(!g->row_stats || ((g->tile_n == 256 || g->tile_n == 512) && !g->c_fp32 && g->split_k == 1 &&
+                                   g->row_stats_ld >= 2 * ((g->N + 255) / 256)),
+                 "gemm: row_stats needs tile_n 256 / 512, bf16 C, split_k = 1 and row_stats_ld >= 2 * ceil(N / 256)");
     static const int debug_flags = [] { const char* e = getenv("B200ML_GEMM_DEBUG"); return e ? atoi(e) : 0; }();
     ep.debug = debug_flags;
 

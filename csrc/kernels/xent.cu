@@ -183,7 +183,8 @@ constexpr int kBigSmem = 2 * kBigRowBytes + 128;
 __global__ void __launch_bounds__(kBigThreads, 1)
 xent_rows_kernel(__nv_bfloat16* __restrict__ logits, long long ld_logits, const long long* __restrict__ targets,
                  float* __restrict__ row_loss, const float* __restrict__ grad_scale_ptr, float grad_scale_host, int rows,
-                 int V, long long ignore_index, int write_grad, float* __restrict__ col_partial, long long ld_partial) {
+                 int V, long long ignore_index, int write_grad, float* __restrict__ col_partial, long long ld_partial,
+                 const float* __restrict__ lse_in) {
     extern __shared__ __align__(128) uint8_t xsmem[];
     uint64_t* bars = reinterpret_cast<uint64_t*>(xsmem + 2 * kBigRowBytes);
     __shared__ float sh_m[kBigThreads / 32], sh_s[kBigThreads / 32];
@@ -224,64 +225,73 @@ xent_rows_kernel(__nv_bfloat16* __restrict__ logits, long long ld_logits, const 
         mbar_wait(&bars[buf], (it >> 1) & 1);
         const uint4* zs = reinterpret_cast<const uint4*>(xsmem + buf * kBigRowBytes);
         const int ragged = (V & 7) ? nvec - 1 : -1;  // index of the one vector that runs past V (into the row padding)
-        // thread-local max over this thread's columns (packed bf16 compares; the ragged vector goes element-wise)
-        float m = -INFINITY;
-        {
-            __nv_bfloat162 pm = __float2bfloat162_rn(-INFINITY);
-#pragma unroll
+        float m, s;
+        if (lse_in) {
+            // statistics already known (the GEMM that produced the logits took them in its epilogue, b200ml_xent_lse
+            // merged them): one pass, no block reductions.  exp(z - lse) = exp2(z * log2e - m2) with s = 1.
+            m = lse_in[row];
+            s = 1.f;
+        } else {
+            // thread-local max over this thread's columns (packed bf16 compares; the ragged vector goes element-wise)
+            m = -INFINITY;
+            {
+                __nv_bfloat162 pm = __float2bfloat162_rn(-INFINITY);
+    #pragma unroll
+                for (int k = 0; k < kBigVec; ++k) {
+                    const int i = tid + k * kBigThreads;
+                    if (i >= nvec) continue;
+                    const uint4 u = zs[i];
+                    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+                    if (i != ragged) {
+    #pragma unroll
+                        for (int e = 0; e < 4; ++e) pm = __hmax2(pm, h[e]);
+                    } else {
+    #pragma unroll
+                        for (int e = 0; e < 8; ++e)
+                            if (i * 8 + e < V) m = fmaxf(m, __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(&u)[e]));
+                    }
+                }
+                const float2 pf = __bfloat1622float2(pm);
+                m = fmaxf(m, fmaxf(pf.x, pf.y));
+            }
+    #pragma unroll
+            for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+            if ((tid & 31) == 0) sh_m[tid >> 5] = m;
+            __syncthreads();
+    #pragma unroll
+            for (int w = 0; w < kBigThreads / 32; ++w) m = fmaxf(m, sh_m[w]);
+            // sum of exponentials (base-2 domain: one FFMA + one MUFU per element)
+            const float m2 = m * 1.4426950408889634f;
+            s = 0.f;
+    #pragma unroll
             for (int k = 0; k < kBigVec; ++k) {
                 const int i = tid + k * kBigThreads;
                 if (i >= nvec) continue;
                 const uint4 u = zs[i];
                 const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
-                if (i != ragged) {
-#pragma unroll
-                    for (int e = 0; e < 4; ++e) pm = __hmax2(pm, h[e]);
-                } else {
-#pragma unroll
-                    for (int e = 0; e < 8; ++e)
-                        if (i * 8 + e < V) m = fmaxf(m, __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(&u)[e]));
+    #pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float2 t = __bfloat1622float2(h[e]);
+                    const float e0 = ex2_approx(fmaf(t.x, 1.4426950408889634f, -m2));
+                    const float e1 = ex2_approx(fmaf(t.y, 1.4426950408889634f, -m2));
+                    if (i != ragged) {
+                        s += e0 + e1;
+                    } else {
+                        if (i * 8 + 2 * e < V) s += e0;
+                        if (i * 8 + 2 * e + 1 < V) s += e1;
+                    }
                 }
             }
-            const float2 pf = __bfloat1622float2(pm);
-            m = fmaxf(m, fmaxf(pf.x, pf.y));
+    #pragma unroll
+            for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            if ((tid & 31) == 0) sh_s[tid >> 5] = s;
+            __syncthreads();
+            s = 0.f;
+    #pragma unroll
+            for (int w = 0; w < kBigThreads / 32; ++w) s += sh_s[w];
         }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-        if ((tid & 31) == 0) sh_m[tid >> 5] = m;
-        __syncthreads();
-#pragma unroll
-        for (int w = 0; w < kBigThreads / 32; ++w) m = fmaxf(m, sh_m[w]);
-        // sum of exponentials (base-2 domain: one FFMA + one MUFU per element)
         const float m2 = m * 1.4426950408889634f;
-        float s = 0.f;
-#pragma unroll
-        for (int k = 0; k < kBigVec; ++k) {
-            const int i = tid + k * kBigThreads;
-            if (i >= nvec) continue;
-            const uint4 u = zs[i];
-            const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                const float2 t = __bfloat1622float2(h[e]);
-                const float e0 = ex2_approx(fmaf(t.x, 1.4426950408889634f, -m2));
-                const float e1 = ex2_approx(fmaf(t.y, 1.4426950408889634f, -m2));
-                if (i != ragged) {
-                    s += e0 + e1;
-                } else {
-                    if (i * 8 + 2 * e < V) s += e0;
-                    if (i * 8 + 2 * e + 1 < V) s += e1;
-                }
-            }
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-        if ((tid & 31) == 0) sh_s[tid >> 5] = s;
-        __syncthreads();
-        s = 0.f;
-#pragma unroll
-        for (int w = 0; w < kBigThreads / 32; ++w) s += sh_s[w];
-        const float lse = m + __logf(s);
+        const float lse = lse_in ? m : m + __logf(s);
         const float scale = valid ? gscale : 0.f;
         const float inv_s = scale / s;
         uint4* zv = reinterpret_cast<uint4*>(logits + (long long)row * ld_logits);
@@ -341,6 +351,35 @@ xent_rows_kernel(__nv_bfloat16* __restrict__ logits, long long ld_logits, const 
     }
 }
 
+// lse[row] = log sum_j exp(z[row][j]) from the per-tile (max, sum-exp) pairs a GEMM epilogue left in `stats`
+// (b200ml_gemm_args.row_stats): one warp per row, pairs merged in index order per lane, then a butterfly.
+__global__ void __launch_bounds__(256)
+xent_lse_kernel(const float2* __restrict__ stats, long long ld, int n_parts, int rows, float* __restrict__ lse) {
+    b200::pdl_trigger();
+    b200::pdl_wait();
+    const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (row >= rows) return;
+    float m = -INFINITY, s = 0.f;
+    for (int i = lane; i < n_parts; i += 32) {
+        const float2 p = stats[(long long)row * ld + i];
+        if (p.x > m) {
+            s = s * __expf(m - p.x) + p.y;      // exp(-inf) = 0 for the first pair
+            m = p.x;
+        } else if (p.x > -INFINITY) {
+            s += p.y * __expf(p.x - m);
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float om = __shfl_xor_sync(0xffffffffu, m, o);
+        const float os = __shfl_xor_sync(0xffffffffu, s, o);
+        const float nm = fmaxf(m, om);
+        s = (m == -INFINITY ? 0.f : s * __expf(m - nm)) + (om == -INFINITY ? 0.f : os * __expf(om - nm));
+        m = nm;
+    }
+    if (lane == 0) lse[row] = m + __logf(s);
+}
+
 // loss = sum(row_loss) * inv_count  (single block, fixed order => deterministic)
 __global__ void loss_reduce_kernel(const float* __restrict__ row_loss, int rows, const float* __restrict__ inv_count,
                                    float inv_host, float* __restrict__ out) {
@@ -396,10 +435,10 @@ size_t b200ml_xent_rows_scratch_bytes(int V) {
     return (size_t)b200::sm_count() * (size_t)ldp * sizeof(float);
 }
 
-int b200ml_xent_rows(void* logits_bf16, long long ld_logits, const long long* targets, float* row_loss,
+static int xent_rows_impl(void* logits_bf16, long long ld_logits, const long long* targets, float* row_loss,
                      const float* grad_scale_dev, float grad_scale_host, int rows, int V, long long ignore_index,
                      int write_grad, float* colsum_out, int colsum_accumulate, void* scratch, size_t scratch_bytes,
-                     cudaStream_t stream) {
+                     cudaStream_t stream, const float* lse_in) {
     using namespace b200::xent;
     B200_REQUIRE(logits_bf16 && targets && row_loss, "xent_rows: null pointer");
     B200_REQUIRE(V >= 1 && V <= kBigMaxV, "xent_rows: V must be <= %d (got %d)", kBigMaxV, V);
@@ -424,12 +463,38 @@ int b200ml_xent_rows(void* logits_bf16, long long ld_logits, const long long* ta
     }
     b200::pdl(xent_rows_kernel, dim3(grid), dim3(kBigThreads), kBigSmem, stream)(
         (__nv_bfloat16*)logits_bf16, ld_logits, targets, row_loss, grad_scale_dev, grad_scale_host, rows, V, ignore_index,
-        write_grad, partial, ldp);
+        write_grad, partial, ldp, lse_in);
     B200_CHECK_CUDA(cudaGetLastError());
     if (colsum_out)
         // partial rows are pitched at ldp = V rounded up to 8; colsum_out must have room for ldp floats
         B200_CHECK_CUDA(b200::launch_reduce_partials(partial, grid, (int)ldp, (int)ldp, colsum_out, nullptr,
                                                      colsum_accumulate, stream));
+    return 0;
+}
+
+int b200ml_xent_rows(void* logits_bf16, long long ld_logits, const long long* targets, float* row_loss,
+                     const float* grad_scale_dev, float grad_scale_host, int rows, int V, long long ignore_index,
+                     int write_grad, float* colsum_out, int colsum_accumulate, void* scratch, size_t scratch_bytes,
+                     cudaStream_t stream) {
+    return xent_rows_impl(logits_bf16, ld_logits, targets, row_loss, grad_scale_dev, grad_scale_host, rows, V,
+                          ignore_index, write_grad, colsum_out, colsum_accumulate, scratch, scratch_bytes, stream, nullptr);
+}
+
+int b200ml_xent_rows_lse(void* logits_bf16, long long ld_logits, const long long* targets, float* row_loss,
+                         const float* grad_scale_dev, float grad_scale_host, int rows, int V, long long ignore_index,
+                         int write_grad, float* colsum_out, int colsum_accumulate, void* scratch, size_t scratch_bytes,
+                         const float* lse, cudaStream_t stream) {
+    B200_REQUIRE(lse, "xent_rows_lse: lse is null");
+    return xent_rows_impl(logits_bf16, ld_logits, targets, row_loss, grad_scale_dev, grad_scale_host, rows, V,
+                          ignore_index, write_grad, colsum_out, colsum_accumulate, scratch, scratch_bytes, stream, lse);
+}
+
+int b200ml_xent_lse(const void* stats_float2, long long ld, int n_parts, int rows, float* lse, cudaStream_t stream) {
+    B200_REQUIRE(stats_float2 && lse && n_parts >= 1 && ld >= n_parts, "xent_lse: bad arguments");
+    if (rows <= 0) return 0;
+    b200::pdl(b200::xent::xent_lse_kernel, dim3((rows + 7) / 8), dim3(256), 0, stream)(
+        (const float2*)stats_float2, ld, n_parts, rows, lse);
+    B200_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
 

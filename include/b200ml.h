@@ -55,6 +55,12 @@ typedef struct {
     int epilogue_direct; /* testing: 1 = register->global stores even where the TMA-store epilogue applies */
     int max_ctas;    /* > 0: use at most this many CTAs of the persistent tcgen05 kernel (a leaf GEMM that should leave
                         SMs to kernels on the critical path of other streams); 0 = one per SM */
+    void* row_stats; /* optional float2 [M][row_stats_ld]: softmax statistics of every output row per column block, taken
+                        from the (bf16-rounded) values the epilogue holds in registers: entry [row][2 * (n0 / BN) + h] =
+                        (max, sum exp(v - max)) over the h-th half of the tile's columns.  Only with the bf16 TMA-store
+                        epilogue (tile_n = 256 or 512, bf16 C with 16-byte rows); row_stats_ld >= 2 * ceil(N / 256).
+                        Lets the cross-entropy that follows skip its max / sum passes (b200ml_xent_lse). */
+    int row_stats_ld;
 } b200ml_gemm_args;
 int b200ml_gemm_bf16(const b200ml_gemm_args* args, cudaStream_t stream);
 
@@ -149,6 +155,15 @@ int b200ml_xent_rows(void* logits_bf16, long long ld_logits, const long long* ta
                      const float* grad_scale_dev, float grad_scale_host, int rows, int V, long long ignore_index,
                      int write_grad, float* colsum_out, int colsum_accumulate, void* scratch, size_t scratch_bytes,
                      cudaStream_t stream);
+/* The same with the log-sum-exp of every row supplied (lse[rows]): one pass over each row, no max / sum reductions.
+ * b200ml_xent_lse merges the per-tile (max, sum-exp) pairs that b200ml_gemm_bf16 leaves in `row_stats` (float2
+ * [rows][ld], n_parts used per row) into lse - the softmax statistics of the translator's 19 214-wide head come out
+ * of the projection GEMM's epilogue instead of two more passes over its 246 MB of logits. */
+int b200ml_xent_rows_lse(void* logits_bf16, long long ld_logits, const long long* targets, float* row_loss,
+                         const float* grad_scale_dev, float grad_scale_host, int rows, int V, long long ignore_index,
+                         int write_grad, float* colsum_out, int colsum_accumulate, void* scratch, size_t scratch_bytes,
+                         const float* lse, cudaStream_t stream);
+int b200ml_xent_lse(const void* stats_float2, long long ld, int n_parts, int rows, float* lse, cudaStream_t stream);
 
 int b200ml_loss_reduce(const float* row_loss, int rows, const float* inv_count_dev, float inv_host, float* out,
                        cudaStream_t stream);

@@ -43,6 +43,7 @@ class GemmArgs(C.Structure):
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
         ("epilogue_direct", C.c_int),
         ("max_ctas", C.c_int),
+        ("row_stats", C.c_void_p), ("row_stats_ld", C.c_int),
     ]
 
 

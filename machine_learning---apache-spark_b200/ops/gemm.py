@@ -29,7 +29,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
          aux_mode: int = 0, aux_scale: float = 1.0, alpha: float = 1.0, alpha_dev: torch.Tensor | None = None,
          accumulate: bool = False, dropout_p: float = 0.0, site: int = 0, tile_n: int = 0,
          force_simt: bool = False, n_logical: int | None = None, split_k: int = 0,
-         epilogue_direct: bool = False, max_ctas: int = 0) -> torch.Tensor:
+         epilogue_direct: bool = False, max_ctas: int = 0, row_stats: torch.Tensor | None = None) -> torch.Tensor:
     """C[M,N] = epilogue(alpha · A·Bᵀ).
 
     ``a`` is [M,K] (a_mn=False) or stored [K,M] (a_mn=True); ``b`` is [N,K] (b_mn=False) or stored [K,N]
@@ -106,6 +106,9 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     g.split_k = split_k
     g.epilogue_direct = int(epilogue_direct)
     g.max_ctas = int(max_ctas)
+    if row_stats is not None:   # float32 [M, P, 2]: per-row (max, sum-exp) of every half tile (include/b200ml.h)
+        assert row_stats.dtype == torch.float32 and row_stats.is_contiguous() and row_stats.shape[0] >= M
+        g.row_stats, g.row_stats_ld = row_stats.data_ptr(), row_stats.shape[1]
     if split_k != 1 and bias is None and not act and not (aux is not None and aux_mode) and dropout_p <= 0:
         ws = workspace.get(f"gemm_splitk@{workspace.lane()}", SPLITK_WORKSPACE_BYTES, a.device)  # one per stream lane
         g.workspace, g.workspace_bytes = ws.data_ptr(), ws.numel()

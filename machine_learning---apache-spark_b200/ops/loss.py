@@ -21,6 +21,11 @@ from .gemm import colsum, deliver_grad, gemm, working_copy
 _vp, _i, _ll, _f, _sz = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_size_t
 _native_ext.register("b200ml_xent_rows", [_vp, _ll, _vp, _vp, _vp, _f, _i, _i, _ll, _i, _vp, _i, _vp, _sz, _vp])
 _native_ext.register("b200ml_xent_rows_scratch_bytes", [_i], size_t_return=True)
+_native_ext.register("b200ml_xent_rows_lse", [_vp, _ll, _vp, _vp, _vp, _f, _i, _i, _ll, _i, _vp, _i, _vp, _sz, _vp, _vp])
+_native_ext.register("b200ml_xent_lse", [_vp, _ll, _i, _i, _vp, _vp])
+# Softmax statistics from the head GEMM's epilogue (one pass of the loss kernel instead of three): needs the CTA-pair
+# tile (256 rows) and is switched off with B200ML_HEAD_STATS=0
+HEAD_STATS = os.environ.get("B200ML_HEAD_STATS", "1") != "0"
 XENT_ROWS_MAX_V = 20480  # csrc/kernels/xent.cu kBigMaxV
 
 # Optional row-chunking of the head (B200ML_HEAD_CHUNK_MB > 0) keeps each logits chunk L2-resident between the GEMM, the
@@ -121,17 +126,34 @@ class _LinearCrossEntropy(torch.autograd.Function):
             db_pre = None
             if fused_rows and need_grad and bias is not None and bias.requires_grad:
                 db_pre = torch.empty(ld, dtype=torch.float32, device=dev)[:V]  # the kernel writes V rounded up to 8
+            # single chunk, wide vocabulary, enough rows for the 256-row pair tile: the GEMM epilogue also emits each
+            # row's (max, sum-exp) per half tile, a small kernel merges them into lse, and the loss kernel makes ONE pass
+            use_stats = HEAD_STATS and fused_rows and chunk_rows >= rows and rows >= 256 and V >= 512
             for r0 in range(0, rows, chunk_rows):
                 r1 = min(rows, r0 + chunk_rows)
                 lg = logits[r0:r1]
-                gemm(h2[r0:r1], w16, out=lg, bias=b_, n_logical=V)
+                lse = None
+                if use_stats:
+                    parts = 2 * ((V + 255) // 256)
+                    stats = torch.empty(rows, parts, 2, dtype=torch.float32, device=dev)
+                    gemm(h2, w16, out=lg, bias=b_, n_logical=V, tile_n=512, split_k=1, row_stats=stats)
+                    lse = torch.empty(rows, dtype=torch.float32, device=dev)
+                    _native.check(lib.b200ml_xent_lse(stats.data_ptr(), parts, parts, rows, lse.data_ptr(), st), "xent_lse")
+                else:
+                    gemm(h2[r0:r1], w16, out=lg, bias=b_, n_logical=V)
                 if fused_rows:
                     nb = int(lib.b200ml_xent_rows_scratch_bytes(V)) if db_pre is not None else 0
                     ws = workspace.get(f"xent_rows@{workspace.lane()}", nb, dev) if nb else None
-                    _native.check(lib.b200ml_xent_rows(lg.data_ptr(), ld, t[r0:r1].data_ptr(),
-                                                       row_loss[r0:r1].data_ptr(), inv.data_ptr(), 0.0, r1 - r0, V,
-                                                       ignore_index, int(need_grad), _native.ptr(db_pre), int(r0 > 0),
-                                                       _native.ptr(ws), nb, st), "xent_rows")
+                    if lse is not None:
+                        _native.check(lib.b200ml_xent_rows_lse(lg.data_ptr(), ld, t.data_ptr(), row_loss.data_ptr(),
+                                                               inv.data_ptr(), 0.0, rows, V, ignore_index, int(need_grad),
+                                                               _native.ptr(db_pre), 0, _native.ptr(ws), nb,
+                                                               lse.data_ptr(), st), "xent_rows_lse")
+                    else:
+                        _native.check(lib.b200ml_xent_rows(lg.data_ptr(), ld, t[r0:r1].data_ptr(),
+                                                           row_loss[r0:r1].data_ptr(), inv.data_ptr(), 0.0, r1 - r0, V,
+                                                           ignore_index, int(need_grad), _native.ptr(db_pre), int(r0 > 0),
+                                                           _native.ptr(ws), nb, st), "xent_rows")
                 else:
                     _native.check(lib.b200ml_xent_fwd_bwd(lg.data_ptr(), 0, ld, t[r0:r1].data_ptr(),
                                                           row_loss[r0:r1].data_ptr(), inv.data_ptr(), 0.0, r1 - r0, V,

@@ -241,6 +241,30 @@ def test_linear_cross_entropy_head(rows, V):
     assert _rel(b.grad, br.grad) < 0.03
 
 
+def test_head_statistics_from_gemm_epilogue_match_row_kernel(monkeypatch):
+    """The head GEMM's epilogue emits per-row (max, sum-exp) pairs and the loss kernel makes one pass; the result must
+    be the one of the self-contained three-pass kernel (same bf16 logits, same statistics up to fp32 rounding), also
+    with a ragged last tile (V % 256 != 0, rows % 256 != 0) and ignored rows."""
+    from b200ml.ops import loss as L
+    torch.manual_seed(1)
+    rows, V, d = 700, 19214, 512
+    h0 = (torch.randn(rows, d, device="cuda") * 0.5).to(torch.bfloat16)
+    w0 = torch.randn(V, d, device="cuda") * 0.05
+    b0 = torch.randn(V, device="cuda") * 0.05
+    t = torch.randint(0, V, (rows,), device="cuda")
+    t[::4] = 0
+    res = []
+    for stats in (True, False):
+        monkeypatch.setattr(L, "HEAD_STATS", stats)
+        h, w, b = h0.clone().requires_grad_(), w0.clone().requires_grad_(), b0.clone().requires_grad_()
+        loss = L.linear_cross_entropy(h, w, b, t, ignore_index=0)
+        loss.backward()
+        res.append((loss.detach(), h.grad, w.grad, b.grad))
+    assert abs(res[0][0].item() - res[1][0].item()) < 1e-5 * abs(res[1][0].item())
+    for a, c in zip(res[0][1:], res[1][1:]):
+        assert _rel(a, c) < 2e-3
+
+
 @pytest.mark.parametrize("kind", ["sgd", "adam"])
 def test_flat_optimizer_matches_torch(kind):
     from b200ml.ops.optim import FlatOptimizer
