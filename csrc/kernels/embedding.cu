@@ -167,7 +167,7 @@ __host__ __device__ inline IndexLayout index_layout(int n, int V) {
 
 __global__ void __launch_bounds__(kIndexThreads, 1)
 embedding_index_kernel(const long long* __restrict__ tokens, int n_tokens, int n_pad, int V,
-                       unsigned char* __restrict__ index) {
+                       unsigned char* __restrict__ index, unsigned char* __restrict__ touched_ext) {
     extern __shared__ __align__(16) unsigned long long skeys[];
     __shared__ int warp_sums[kIndexThreads / 32];
     __shared__ int s_nhot;
@@ -189,7 +189,10 @@ embedding_index_kernel(const long long* __restrict__ tokens, int n_tokens, int n
         }
         skeys[i] = k;
     }
-    for (int i = tid; i < V; i += kIndexThreads) touched[i] = 0;
+    for (int i = tid; i < V; i += kIndexThreads) {
+        touched[i] = 0;
+        if (touched_ext) touched_ext[i] = 0;   // second copy in a peer-mapped array (row-sparse gradient all-reduce)
+    }
     if (tid == 0) s_nhot = 0;
     __syncthreads();
     for (int size = 2; size <= n_pad; size <<= 1) {
@@ -219,6 +222,7 @@ embedding_index_kernel(const long long* __restrict__ tokens, int n_tokens, int n
         const bool head = i == 0 || (unsigned)(skeys[i - 1] >> 32) != row;
         if (head) {
             touched[row] = 1;
+            if (touched_ext) touched_ext[row] = 1;
             ++local;
         }
     }
@@ -465,7 +469,8 @@ int b200ml_embedding_index_max_tokens(void) { return b200::emb::kIndexMaxTokens;
 
 size_t b200ml_embedding_index_bytes(int n_tokens, int V) { return b200::emb::index_layout(n_tokens, V).total; }
 
-int b200ml_embedding_index(const long long* tokens, int n_tokens, int V, void* index_out, cudaStream_t stream) {
+int b200ml_embedding_index(const long long* tokens, int n_tokens, int V, void* index_out, unsigned char* touched_out,
+                           cudaStream_t stream) {
     using namespace b200::emb;
     B200_REQUIRE(tokens && index_out, "embedding_index: null pointer");
     B200_REQUIRE((reinterpret_cast<uintptr_t>(index_out) & 15) == 0, "embedding_index: the index buffer must be 16-byte aligned");
@@ -481,7 +486,7 @@ int b200ml_embedding_index(const long long* tokens, int n_tokens, int V, void* i
         attr = true;
     }
     b200::pdl(embedding_index_kernel, dim3(1), dim3(kIndexThreads), smem, stream)(tokens, n_tokens, n_pad, V,
-                                                                                   (unsigned char*)index_out);
+                                                                                   (unsigned char*)index_out, touched_out);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
 }

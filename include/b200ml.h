@@ -131,7 +131,8 @@ int b200ml_embedding_bwd(const long long* tokens, const void* dout, int dout_fp3
  * ref: nn.Embedding backward (transformer.py:52-61; distributed_lstm.py:115,128). */
 int b200ml_embedding_index_max_tokens(void);
 size_t b200ml_embedding_index_bytes(int n_tokens, int V);
-int b200ml_embedding_index(const long long* tokens, int n_tokens, int V, void* index_out, cudaStream_t stream);
+int b200ml_embedding_index(const long long* tokens, int n_tokens, int V, void* index_out, unsigned char* touched_out,
+                           cudaStream_t stream);   /* touched_out (optional, V bytes): a second copy of the touched-row flags */
 size_t b200ml_embedding_bwd_sorted_scratch_bytes(int n_tokens, int d);
 int b200ml_embedding_bwd_sorted(const void* index, const void* dout, int dout_fp32, float* dtable, int n_tokens, int d,
                                 int V, long long padding_idx, float dropout_p, const void* rng_state,
@@ -270,6 +271,19 @@ int b200ml_comm_free(void* ptr);
 int b200ml_ipc_export(const void* ptr, unsigned char* handle64);
 int b200ml_ipc_import(const unsigned char* handle64, void** ptr);
 int b200ml_ipc_close(void* ptr);
+/* Row-sparse part of a bucket: [start, start + rows * row_elems) of the flat buffer is a table whose gradient rows are
+ * exactly zero on rank r wherever touched[r][row] == 0 (an embedding table: b200ml_embedding_index writes the flags,
+ * here into peer-mapped byte arrays).  The bulk-async transport then fetches a peer's 4 KB chunk only when that peer
+ * touched one of its rows; the result is bit-identical to the dense reduction.  Other transports ignore it. */
+typedef struct {
+    long long start;
+    int rows, row_elems;
+    const unsigned char* touched[8];   /* rank r's flags as mapped in this process */
+} b200ml_sparse_rows;
+int b200ml_allreduce_update_sparse(const b200ml_comm* cm, long long start, long long n, int algo, int kind, float lr,
+                                   float beta1, float beta2, float eps, float weight_decay, const int* step_dev,
+                                   float* m, float* v, float* out, int push_master, int max_blocks,
+                                   const b200ml_sparse_rows* sparse, cudaStream_t stream);
 int b200ml_allreduce_update(const b200ml_comm* cm, long long start, long long n, int algo, int kind, float lr,
                             float beta1, float beta2, float eps, float weight_decay, const int* step_dev, float* m,
                             float* v, float* out, int push_master, int max_blocks, cudaStream_t stream);

@@ -22,6 +22,7 @@ class LSTM(nn.Module):
                  dropout: float = 0.5):
         super().__init__()
         self.embedding = nn.Embedding(num_embeddings=vocab_size, embedding_dim=embedding_dim, padding_idx=padding_idx)
+        self.embedding.weight._b200_sparse_rows = True   # row-sparse gradient: the DP engine skips untouched rows
         self.lstm = nn.LSTM(input_size=embedding_dim, hidden_size=hidden_size, num_layers=num_layers, batch_first=True,
                             dropout=dropout)
         self.fc_out = nn.Linear(hidden_size, output_size)

@@ -80,6 +80,7 @@ class SentenceEmbedding(nn.Module):
         self.vocab_size = _vocab_len(input_vocab)
         self.max_sequence_length = max_sequence_length
         self.embedding = nn.Embedding(self.vocab_size, d_model)
+        self.embedding.weight._b200_sparse_rows = True   # row-sparse gradient: the DP engine skips untouched rows
         self.language_to_index = input_vocab
         self.position_encoder = PositionalEncoding(d_model, max_sequence_length)
         self.dropout = nn.Dropout(p=0.1)

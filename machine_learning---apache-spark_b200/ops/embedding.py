@@ -17,7 +17,7 @@ from ..utils.rng import DeviceCounters
 from .gemm import working_copy
 
 _vp, _i, _ll, _f, _u = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_uint
-_native_ext.register("b200ml_embedding_index", [_vp, _i, _i, _vp, _vp])
+_native_ext.register("b200ml_embedding_index", [_vp, _i, _i, _vp, _vp, _vp])
 _native_ext.register("b200ml_embedding_index_bytes", [_i, _i], size_t_return=True)
 _native_ext.register("b200ml_embedding_bwd_sorted", [_vp, _vp, _i, _vp, _i, _i, _i, _ll, _f, _vp, _u, _i, _vp,
                                                      C.c_size_t, _vp])
@@ -36,7 +36,7 @@ def _aux_stream(device) -> torch.cuda.Stream:
     return st
 
 
-def build_token_index(tok: torch.Tensor, V: int):
+def build_token_index(tok: torch.Tensor, V: int, touched=None):
     """(index, event): the backward index of one batch (sorted ``token << 32 | position`` keys, segment starts, hot
     segments, touched-row flags - csrc/kernels/embedding.cu IndexLayout), built by ONE CTA on the auxiliary stream;
     ``event`` marks its completion.  Only called for batches of at most INDEX_MAX_TOKENS tokens."""
@@ -49,8 +49,9 @@ def build_token_index(tok: torch.Tensor, V: int):
     index = torch.empty(int(lib.b200ml_embedding_index_bytes(n, V)) // 8 + 1, dtype=torch.int64, device=tok.device)
     aux.wait_stream(cur)
     with torch.cuda.stream(aux):
-        _native.check(lib.b200ml_embedding_index(tok.data_ptr(), n, V, index.data_ptr(), _native.stream_ptr()),
-                      "embedding_index")
+        # `touched` (optional): the table's peer-mapped touched-row flags, read by the other ranks' all-reduce kernels
+        _native.check(lib.b200ml_embedding_index(tok.data_ptr(), n, V, index.data_ptr(), _native.ptr(touched),
+                                                 _native.stream_ptr()), "embedding_index")
         ev = torch.cuda.Event()
         ev.record(aux)
     return index, ev
@@ -94,8 +95,13 @@ class _Embedding(torch.autograd.Function):
                 d, V, p, rng, site, _native.stream_ptr()), "embedding_fwd")
             keys = tok
             ctx.keys_event = None
+            touched = getattr(weight, "_b200_touched", None)   # set by the DP engine for row-sparse all-reduce
+            if weight.requires_grad and touched is not None and (
+                    n > INDEX_MAX_TOKENS or getattr(weight, "_b200_grad_accumulate", False)):
+                touched.fill_(1)      # atomicAdd path / accumulated gradients: every row may be non-zero
+                touched = None
             if weight.requires_grad and n <= INDEX_MAX_TOKENS:
-                keys, ctx.keys_event = build_token_index(tok, V)
+                keys, ctx.keys_event = build_token_index(tok, V, touched)
             ctx.save_for_backward(tok, keys)
             ctx.mask = None
             return out.reshape(*lead, d)

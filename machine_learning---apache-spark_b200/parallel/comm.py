@@ -144,6 +144,13 @@ def make_allocator(device, group=None):
     return SymmetricAllocator(device)
 
 
+class SparseRowsStruct(C.Structure):
+    """b200ml_sparse_rows (include/b200ml.h)."""
+    _fields_ = [("start", C.c_longlong), ("rows", C.c_int), ("row_elems", C.c_int), ("touched", C.c_void_p * 8)]
+
+
+_native_ext.register("b200ml_allreduce_update_sparse", [C.POINTER(CommStruct), ll, ll, i, i, f, f, f, f, f, vp, vp, vp, vp,
+                                                        i, i, C.POINTER(SparseRowsStruct), vp])
 _native_ext.register("b200ml_allreduce_sum_f64", [C.POINTER(CommStruct), C.POINTER(C.c_void_p * 8), ll, vp, vp])
 
 
@@ -289,16 +296,39 @@ class FusedAllReduce:
         torch.cuda.synchronize(dev)
         dist.barrier(group=group)
 
-    def allreduce_update(self, start, n, kind, lr, betas, eps, weight_decay, step_tensor, out=None, algo: int = 0):
+    def allreduce_update(self, start, n, kind, lr, betas, eps, weight_decay, step_tensor, out=None, algo: int = 0,
+                         sparse: "SparseRowsStruct | None" = None):
         lib = _native.load()
         n4 = (n + 3) // 4 * 4  # slots are 64-element aligned, so rounding up stays inside the bucket
         if algo == 0 and kind != 0 and n4 * 4 > (512 << 10):
             algo = self.default_algo
-        _native.check(lib.b200ml_allreduce_update(
+        _native.check(lib.b200ml_allreduce_update_sparse(
             C.byref(self.cs), start, n4, algo, kind, lr, betas[0], betas[1], eps, weight_decay, step_tensor.data_ptr(),
             None if self.m is None else self.m.data_ptr(), None if self.v is None else self.v.data_ptr(),
-            None if out is None else out.data_ptr(), self.push_master, self.max_blocks, _native.stream_ptr()),
-            "allreduce_update")
+            None if out is None else out.data_ptr(), self.push_master, self.max_blocks,
+            None if sparse is None else C.byref(sparse), _native.stream_ptr()), "allreduce_update")
+
+    def make_sparse_rows(self, start: int, rows: int, row_elems: int):
+        """Peer-mapped touched-row flags for a row-sparse table at flat offset ``start``: returns (descriptor, local
+        uint8 tensor of ``rows`` flags, initialised to 1 = "every row may be non-zero").  Collective."""
+        dev = self.flat.device
+        buf = SymmetricBuffer(rows, torch.uint8, dev)
+        buf.tensor.fill_(1)
+        torch.cuda.synchronize(dev)
+        gathered = [None] * self.world
+        dist.all_gather_object(gathered, buf.export(), group=self.group)
+        d = SparseRowsStruct()
+        d.start, d.rows, d.row_elems = start, rows, row_elems
+        for r in range(self.world):
+            if r == self.rank:
+                d.touched[r] = buf.ptr
+            else:
+                p = _import(gathered[r])
+                self._imported.append(p)
+                d.touched[r] = p
+        self._sparse_bufs = getattr(self, "_sparse_bufs", []) + [buf]
+        dist.barrier(group=self.group)
+        return d, buf.tensor
 
     def owned_slice(self, start: int, n: int, sliced: bool | None = None, rank: int | None = None):
         """(lo, hi) relative to ``start``: the part of bucket [start, start+n) whose optimizer state (fp32 master under

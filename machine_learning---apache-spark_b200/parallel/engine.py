@@ -122,6 +122,7 @@ class DataParallelEngine:
 
                 self.comm = FusedAllReduce(self.flat, self.m, self.v, self.pg, allocator=sym_alloc)
                 self.allreduce_mode = "fused:" + self.comm.transport + (":bf16push" if self._bf16_push else "")
+                self._setup_sparse_rows()
                 if self._bf16_push:
                     # model.state_dict() on any rank first pulls the fp32 slices it does not own
                     self._sd_hook = module.register_state_dict_pre_hook(lambda *a, **k: self.sync_master())
@@ -141,6 +142,30 @@ class DataParallelEngine:
             self.comm_stream = self._opt_streams[0]
         self._in_step = False
         self._streams_used: set = set()
+        if not hasattr(self, "_sparse"):
+            self._sparse = {}
+
+    def _setup_sparse_rows(self) -> None:
+        """Row-sparse tables (parameters an op flagged ``_b200_sparse_rows``: embedding tables, whose gradient rows are
+        exactly zero for tokens the rank's batch does not contain).  For each two-shot bucket that holds one, every rank
+        publishes a peer-mapped array of touched-row flags (written at forward time by the embedding's index kernel,
+        ``param._b200_touched``), and the all-reduce fetches a peer's chunk of the table only if that peer touched it."""
+        self._sparse = {}
+        if os.environ.get("B200ML_SPARSE_ROWS", "1") == "0" or not hasattr(self.comm, "make_sparse_rows"):
+            return
+        if self.comm.cs.mc_grads:          # NVLS transport reduces in the switch: always dense
+            return
+        for b, (start, n, ids, _) in enumerate(self.buckets):
+            if self.comm.owned_slice(start, n) is None:
+                continue
+            for i in ids:
+                p = self.flat.params[i]
+                if getattr(p, "_b200_sparse_rows", False) and p.dim() == 2 and b not in self._sparse:
+                    desc, flags = self.comm.make_sparse_rows(self.flat.offsets[i], p.shape[0], p.shape[1])
+                    p._b200_touched = flags
+                    self._sparse[b] = desc
+        if self._sparse:
+            self.allreduce_mode += ":sparse-rows"
 
     def _verify_layout(self) -> None:
         """Every rank must have built the same flat layout (what DDP's constructor verifies across ranks before it
@@ -200,7 +225,7 @@ class DataParallelEngine:
         if self.comm is not None:
             self.comm.push_master = 0 if (bf16_push and self._bf16_push) else 1
             self.comm.allreduce_update(start, n, self.kind, self.lr, self.betas, self.eps, self.weight_decay,
-                                       self.step_tensor)
+                                       self.step_tensor, sparse=self._sparse.get(b) if complete else None)
             return
         if self.world == 1:
             optim_step_flat(self.flat.flat_p, self.flat.flat_g, self.m, self.v, self.flat.flat_w16, self.kind, self.lr,
@@ -370,6 +395,8 @@ class DataParallelEngine:
             self._sd_hook = None
         self.reducer.close()
         for p in self.flat.params:
+            if getattr(p, "_b200_touched", None) is not None:
+                p._b200_touched = None
             p._b200_ready = None
             p._b200_side = None
 
