@@ -5,6 +5,8 @@
 import os
 import sys
 
+os.environ.setdefault("B200ML_SPARSE_ROWS", "1")   # opt-in feature: the tests exercise it
+
 import torch
 import torch.distributed as dist
 

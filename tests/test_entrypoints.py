@@ -17,9 +17,12 @@ EXPECT = {"pytorch_multilayer_perceptron.py": "PyTorch Training Time", "pytorch_
           "distributed_lstm.py": "returned state_dict keys: ['embedding.weight'"}
 
 
-def _run(script, extra, tmp_path):
-    env = dict(os.environ, B200ML_QUICK="1", B200ML_DEVICE="cpu", B200ML_DATA=str(tmp_path), B200ML_EXECUTORS="2",
-               OMP_NUM_THREADS="2")
+def _run(script, extra, tmp_path, device="cpu"):
+    env = dict(os.environ, B200ML_QUICK="1", B200ML_DATA=str(tmp_path), B200ML_EXECUTORS="2", OMP_NUM_THREADS="2")
+    if device == "cpu":
+        env["B200ML_DEVICE"] = "cpu"
+    else:
+        env.pop("B200ML_DEVICE", None)
     r = subprocess.run([sys.executable, os.path.join(ROOT, script), *extra], capture_output=True, text=True, env=env,
                        timeout=900, cwd=str(tmp_path))
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
@@ -39,3 +42,19 @@ def test_single_process_entrypoints(script, tmp_path):
 @pytest.mark.parametrize("script", DIST)
 def test_spark_launched_entrypoints(script, tmp_path):
     _run(script, ["--conf", "spark.executor.instances=2"], tmp_path)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("script", SINGLE)
+def test_single_process_entrypoints_on_gpu(script, tmp_path):
+    """The same scripts on the CUDA device: every model family goes through the native kernels end to end."""
+    _run(script, [], tmp_path, device="cuda")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("script", DIST)
+def test_spark_launched_entrypoints_on_gpu(script, tmp_path):
+    """One Spark-launched worker per GPU (two when the box has them, else one)."""
+    import torch
+    n = 2 if torch.cuda.device_count() >= 2 else 1
+    _run(script, ["--conf", f"spark.executor.instances={n}"], tmp_path, device="cuda")

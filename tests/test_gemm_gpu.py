@@ -12,10 +12,17 @@ def _ref(a, b, a_mn, b_mn):
 
 
 def _check(out, ref, K, tol_scale=1.0):
+    """The operands are exact bf16 values and accumulation is fp32, so an fp32 output must agree with the fp32 oracle
+    to rounding level: relative Frobenius error <= 2e-3 and no element further off than 2e-3 of the largest - a dropped
+    k-block (1 % of K = 6400), a wrong split-K seam or a misplaced tile all exceed that by far.  A bf16 output adds its
+    own rounding (2^-9 relative per element): 6e-3."""
+    fp32_out = out.dtype == torch.float32
     out = out.float().cpu()
-    err = (out - ref).abs().max().item()
-    bound = tol_scale * (0.02 * ref.abs().max().item() + 1e-2)
-    assert err <= bound, f"max err {err} > {bound}"
+    tol = (2e-3 if fp32_out else 6e-3) * tol_scale
+    scale = ref.abs().max().item() + 1e-12
+    rel = ((out - ref).norm() / (ref.norm() + 1e-12)).item()
+    worst = (out - ref).abs().max().item() / scale
+    assert rel <= tol and worst <= tol, f"relative error {rel:.3e} (norm) / {worst:.3e} (worst element) > {tol:.1e}"
 
 
 @pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, False), (True, True)])
