@@ -234,6 +234,21 @@ int b200ml_lstm_rec_fwd(const float* pre, const float* w_hh, const float* h0, co
 int b200ml_lstm_rec_bwd(const float* w_hh, const float* c0, const float* gates, const float* c_seq,
                         const float* dh_seq, const float* dh_n, const float* dc_n, void* dg_out_bf16, float* dh0,
                         float* dc0, int B, int T, int hidden, cudaStream_t stream);
+/* Two-layer wavefront (hidden 32): both layers of nn.LSTM(32, 32, num_layers=2, dropout=p) advance in one persistent
+ * kernel per direction, layer 1 one step behind layer 0; the inter-layer dropout + bf16 cast, the layer-1 input
+ * projection and their backward run inside it.  pre0 [B,T,128] is layer 0's hoisted input projection; per layer l the
+ * kernel writes h_out_l [B,T,32], gates_l [B,T,128], c_seq_l [B,T,32] (gates / c_seq of both layers NULL together at
+ * inference); x1_bf16 [B*T,32] = bf16(dropout(h_out_0)); h_n / c_n, h0 / c0, dh_n / dc_n, dh0 / dc0 are [2,B,32]
+ * (optional).  Backward writes dg0 / dg1 [B*T,128] bf16, the operands of the hoisted weight-gradient GEMMs.
+ * pre0, gates, c_seq and d_out1 must be 16-byte aligned (they are staged by bulk-async copies). */
+int b200ml_lstm2_fwd(const float* pre0, const float* w_hh0, const float* w_ih1, const float* bias1, const float* w_hh1,
+                     const float* h0, const float* c0, float* h_out0, float* gates0, float* c_seq0, float* h_out1,
+                     float* gates1, float* c_seq1, void* x1_bf16, float* h_n, float* c_n, int B, int T, int hidden,
+                     float dropout_p, const void* rng_state, unsigned rng_site1, cudaStream_t stream);
+int b200ml_lstm2_bwd(const float* w_hh0, const float* w_ih1, const float* w_hh1, const float* c0, const float* gates0,
+                     const float* c_seq0, const float* gates1, const float* c_seq1, const float* d_out1,
+                     const float* dh_n, const float* dc_n, void* dg0_bf16, void* dg1_bf16, float* dh0, float* dc0, int B,
+                     int T, int hidden, float dropout_p, const void* rng_state, unsigned rng_site1, cudaStream_t stream);
 int b200ml_dropout_cast(const float* x, void* out_bf16, long long n, float p, const void* rng_state, unsigned rng_site,
                         cudaStream_t stream);
 int b200ml_dropout_bwd(const void* g, int g_fp32, float* dx, long long n, float p, const void* rng_state,

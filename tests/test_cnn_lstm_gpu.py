@@ -52,9 +52,15 @@ def _run_conv_case(B, Cin, Cout, HW, pool, conv3x3_relu, tol_y, tol_g):
 
 @pytest.mark.parametrize("B,T,E,HID", [(32, 128, 32, 32), (5, 17, 32, 32), (40, 9, 24, 32), (6, 21, 32, 64), (33, 40, 64, 64),
                                          (4, 19, 48, 128), (9, 12, 128, 128)])
-def test_lstm_matches_torch(B, T, E, HID):
-    """hidden 32: warp-per-row kernels (the reference size); 64 / 128: CTA-per-row kernels (128 keeps W_hh as bf16)."""
+@pytest.mark.parametrize("wave", [True, False])
+def test_lstm_matches_torch(B, T, E, HID, wave, monkeypatch):
+    """hidden 32: warp-per-row kernels (the reference size) - as the two-layer wavefront kernel (wave) or layer by
+    layer; 64 / 128: CTA-per-row kernels (128 keeps W_hh as bf16)."""
+    from b200ml.ops import lstm_native
     from b200ml.ops.lstm import lstm_forward
+    if HID != 32 and wave:
+        pytest.skip("the wavefront kernels cover hidden 32")
+    monkeypatch.setattr(lstm_native, "WAVEFRONT", wave)
     torch.manual_seed(0)
     ref = torch.nn.LSTM(E, HID, num_layers=2, batch_first=True, dropout=0.0)
     mine = [getattr(ref, n).detach().clone().cuda().requires_grad_() for n in ref._flat_weights_names]
