@@ -26,6 +26,28 @@ constexpr int HALO = T + 2;  // input tile edge
 constexpr int kMaxC = 64;
 constexpr int kChunk = 16;   // output channels accumulated in registers at a time
 
+// Stage n values into shared memory, dst[i] = at(i).  The loads of a batch are issued together before any of the
+// shared-memory stores: written as `dst[i] = at(i)` in a plain loop the compiler keeps each global load behind the
+// previous store (it cannot prove the generic source pointer is not shared memory), and a 10-channel halo tile (3240
+// values, 13 per thread) then costs 13 global round trips in a row instead of 2.
+constexpr int kGatherBatch = 8;
+template <typename F>
+__device__ __forceinline__ void gather_to_smem(float* dst, int n, int tid, F&& at) {
+    for (int base = 0; base < n; base += T * T * kGatherBatch) {
+        float v[kGatherBatch];
+#pragma unroll
+        for (int q = 0; q < kGatherBatch; ++q) {
+            const int i = base + q * T * T + tid;
+            v[q] = i < n ? at(i) : 0.f;
+        }
+#pragma unroll
+        for (int q = 0; q < kGatherBatch; ++q) {
+            const int i = base + q * T * T + tid;
+            if (i < n) dst[i] = v[q];
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // forward
 // ---------------------------------------------------------------------------------------------------------------
@@ -44,12 +66,12 @@ conv_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const 
     const int ty0 = (blockIdx.x / tiles_x) * T, tx0 = (blockIdx.x % tiles_x) * T;
     const int tid = threadIdx.x, ly = tid / T, lx = tid % T;
 
-    for (int i = tid; i < Cin * HALO * HALO; i += T * T) {
+    gather_to_smem(s_in, Cin * HALO * HALO, tid, [&](int i) {
         const int c = i / (HALO * HALO), rem = i % (HALO * HALO);
         const int gy = ty0 + rem / HALO - 1, gx = tx0 + rem % HALO - 1;
-        s_in[i] = (gy >= 0 && gy < H && gx >= 0 && gx < W) ? x[((long long)(b * Cin + c) * H + gy) * W + gx] : 0.f;
-    }
-    for (int i = tid; i < Cout * Cin * 9; i += T * T) s_w[i] = w[i];
+        return (gy >= 0 && gy < H && gx >= 0 && gx < W) ? x[((long long)(b * Cin + c) * H + gy) * W + gx] : 0.f;
+    });
+    gather_to_smem(s_w, Cout * Cin * 9, tid, [&](int i) { return w[i]; });
     __syncthreads();
 
     const int oy = ty0 + ly, ox = tx0 + lx;
@@ -114,14 +136,18 @@ struct DzSource {
     int pool, H, W;
     __device__ __forceinline__ float at(int b, int C, int c, int yy, int xx) const {
         if (yy < 0 || yy >= H || xx < 0 || xx >= W) return 0.f;
+        // every load is issued before the selects: none of them waits for another one's value
         if (!pool) {
             const long long o = ((long long)(b * C + c) * H + yy) * W + xx;
-            return ysaved[o] > 0.f ? dy[o] : 0.f;
+            const float yv = ysaved[o], dv = dy[o];
+            return yv > 0.f ? dv : 0.f;
         }
         const int Hp = H / 2, Wp = W / 2;
         if (yy / 2 >= Hp || xx / 2 >= Wp) return 0.f;
         const long long o = ((long long)(b * C + c) * Hp + yy / 2) * Wp + xx / 2;
-        return (idx[o] == (unsigned char)((yy & 1) * 2 + (xx & 1)) && ysaved[o] > 0.f) ? dy[o] : 0.f;
+        const unsigned char am = idx[o];
+        const float yv = ysaved[o], dv = dy[o];
+        return (am == (unsigned char)((yy & 1) * 2 + (xx & 1)) && yv > 0.f) ? dv : 0.f;
     }
 };
 
@@ -138,11 +164,11 @@ conv_bwd_data_kernel(DzSource src, const float* __restrict__ w, float* __restric
     const int b = blockIdx.y;
     const int ty0 = (blockIdx.x / tiles_x) * T, tx0 = (blockIdx.x % tiles_x) * T;
     const int tid = threadIdx.x, ly = tid / T, lx = tid % T;
-    for (int i = tid; i < Cout * HALO * HALO; i += T * T) {
+    gather_to_smem(s_dz, Cout * HALO * HALO, tid, [&](int i) {
         const int c = i / (HALO * HALO), rem = i % (HALO * HALO);
-        s_dz[i] = src.at(b, Cout, c, ty0 + rem / HALO - 1, tx0 + rem % HALO - 1);
-    }
-    for (int i = tid; i < Cout * Cin * 9; i += T * T) s_w[i] = w[i];
+        return src.at(b, Cout, c, ty0 + rem / HALO - 1, tx0 + rem % HALO - 1);
+    });
+    gather_to_smem(s_w, Cout * Cin * 9, tid, [&](int i) { return w[i]; });
     __syncthreads();
     const int oy = ty0 + ly, ox = tx0 + lx;
     if (oy >= H || ox >= W) return;
@@ -185,15 +211,15 @@ conv_bwd_weight_kernel(DzSource src, const float* __restrict__ x, float* __restr
     const int b = blockIdx.y;
     const int ty0 = (blockIdx.x / tiles_x) * T, tx0 = (blockIdx.x % tiles_x) * T;
     const int tid = threadIdx.x;
-    for (int i = tid; i < Cin * HALO * HALO; i += T * T) {
+    gather_to_smem(s_in, Cin * HALO * HALO, tid, [&](int i) {
         const int c = i / (HALO * HALO), rem = i % (HALO * HALO);
         const int gy = ty0 + rem / HALO - 1, gx = tx0 + rem % HALO - 1;
-        s_in[i] = (gy >= 0 && gy < H && gx >= 0 && gx < W) ? x[((long long)(b * Cin + c) * H + gy) * W + gx] : 0.f;
-    }
-    for (int i = tid; i < Cout * T * T; i += T * T) {
+        return (gy >= 0 && gy < H && gx >= 0 && gx < W) ? x[((long long)(b * Cin + c) * H + gy) * W + gx] : 0.f;
+    });
+    gather_to_smem(s_dz, Cout * T * T, tid, [&](int i) {
         const int c = i / (T * T), rem = i % (T * T);
-        s_dz[i] = src.at(b, Cout, c, ty0 + rem / T, tx0 + rem % T);
-    }
+        return src.at(b, Cout, c, ty0 + rem / T, tx0 + rem % T);
+    });
     __syncthreads();
     const int nW = Cout * Cin * 9;
     const long long cta = (long long)blockIdx.y * gridDim.x + blockIdx.x;
@@ -266,16 +292,42 @@ conv_igemm_kernel(Src src, const float* __restrict__ w, const float* __restrict_
     b200::pdl_trigger();
     b200::pdl_wait();
 
-    for (int i = tid; i < C * HALO * HALO; i += T * T) {
+    gather_to_smem(s_src, C * HALO * HALO, tid, [&](int i) {
         const int c = i / (HALO * HALO), rem = i % (HALO * HALO);
-        s_src[i] = src.at(b, C, c, ty0 + rem / HALO - 1, tx0 + rem % HALO - 1);
-    }
+        return src.at(b, C, c, ty0 + rem / HALO - 1, tx0 + rem % HALO - 1);
+    });
     __syncthreads();
 
     const int mblock = tid >> 7, row = tid & 127;
     const uint32_t idesc = umma_idesc_bf16(128, Np, false, false);
     uint32_t phase = 0;
     for (int k0 = 0; k0 < K; k0 += 64) {
+        // B: weight slice, Np rows x 64 k (rows >= N and k >= K are zero).  Its global loads are issued first and the
+        // values parked in registers, so their latency overlaps the A gather below.
+        uint4 ub[2];   // Np <= 64: at most 512 groups of 8 k = 2 per thread
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            const int i = tid + q * T * T;
+            if (i < Np * 8) {
+                const int n = i >> 3, c8 = i & 7;
+                float v[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    const int k = k0 + c8 * 8 + e;
+                    float val = 0.f;
+                    if (n < N && k < K) {
+                        const int c = k / 9, t = k - c * 9;
+                        val = BWD ? w[((long long)c * Cin_w + n) * 9 + (8 - t)]   // w[co = c][ci = n][flipped tap]
+                                  : w[(long long)n * K + k];                      // w[co = n][ci*9 + t]
+                    }
+                    v[e] = val;
+                }
+                ub[q].x = pack_bf16x2(v[0], v[1]);
+                ub[q].y = pack_bf16x2(v[2], v[3]);
+                ub[q].z = pack_bf16x2(v[4], v[5]);
+                ub[q].w = pack_bf16x2(v[6], v[7]);
+            }
+        }
         // A: this pixel's im2col slice [k0, k0 + 64)
 #pragma unroll
         for (int c8 = 0; c8 < 8; ++c8) {
@@ -293,27 +345,10 @@ conv_igemm_kernel(Src src, const float* __restrict__ w, const float* __restrict_
             u.w = pack_bf16x2(v[6], v[7]);
             *reinterpret_cast<uint4*>(sA + mblock * 16384 + swz128_offset(row, c8)) = u;
         }
-        // B: weight slice, Np rows x 64 k (rows >= N and k >= K are zero)
-        for (int i = tid; i < Np * 8; i += T * T) {
-            const int n = i >> 3, c8 = i & 7;
-            float v[8];
 #pragma unroll
-            for (int e = 0; e < 8; ++e) {
-                const int k = k0 + c8 * 8 + e;
-                float val = 0.f;
-                if (n < N && k < K) {
-                    const int c = k / 9, t = k - c * 9;
-                    val = BWD ? w[((long long)c * Cin_w + n) * 9 + (8 - t)]   // w[co = c][ci = n][flipped tap]
-                              : w[(long long)n * K + k];                      // w[co = n][ci*9 + t]
-                }
-                v[e] = val;
-            }
-            uint4 u;
-            u.x = pack_bf16x2(v[0], v[1]);
-            u.y = pack_bf16x2(v[2], v[3]);
-            u.z = pack_bf16x2(v[4], v[5]);
-            u.w = pack_bf16x2(v[6], v[7]);
-            *reinterpret_cast<uint4*>(sB + swz128_offset(n, c8)) = u;
+        for (int q = 0; q < 2; ++q) {
+            const int i = tid + q * T * T;
+            if (i < Np * 8) *reinterpret_cast<uint4*>(sB + swz128_offset(i >> 3, i & 7)) = ub[q];
         }
         tc_fence_before();
         fence_proxy_async_smem();
@@ -423,15 +458,15 @@ conv_wgrad_igemm_kernel(DzSource src, const float* __restrict__ x, float* __rest
     b200::pdl_trigger();
     b200::pdl_wait();
 
-    for (int i = tid; i < Cin * HALO * HALO; i += T * T) {
+    gather_to_smem(s_in, Cin * HALO * HALO, tid, [&](int i) {
         const int c = i / (HALO * HALO), rem = i % (HALO * HALO);
         const int gy = ty0 + rem / HALO - 1, gx = tx0 + rem % HALO - 1;
-        s_in[i] = (gy >= 0 && gy < H && gx >= 0 && gx < W) ? x[((long long)(b * Cin + c) * H + gy) * W + gx] : 0.f;
-    }
-    for (int i = tid; i < Cout * T * T; i += T * T) {
+        return (gy >= 0 && gy < H && gx >= 0 && gx < W) ? x[((long long)(b * Cin + c) * H + gy) * W + gx] : 0.f;
+    });
+    gather_to_smem(s_dz, Cout * T * T, tid, [&](int i) {
         const int c = i / (T * T), rem = i % (T * T);
-        s_dz[i] = src.at(b, Cout, c, ty0 + rem / T, tx0 + rem % T);
-    }
+        return src.at(b, Cout, c, ty0 + rem / T, tx0 + rem % T);
+    });
     __syncthreads();
 
     const int row = tid & 127, half = tid >> 7;   // A: thread fills row `row` of each M block, 32 of the 64 pixels

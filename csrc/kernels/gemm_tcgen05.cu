@@ -674,29 +674,37 @@ gemm_simt_kernel(const __nv_bfloat16* __restrict__ A, long long lda, int a_mn, c
                  long long ldb, int b_mn, int M, int N, int K, int k_per_split, Epilogue ep) {
     b200::pdl_trigger();
     b200::pdl_wait();
-    __shared__ float sa[16][17];
-    __shared__ float sb[16][17];
+    // K is walked in slices of kSimtK: every thread issues its 2 x kSimtK/16 loads of a slice together, so a long-K,
+    // tiny-MN problem (the CNN head 32 x 10 x 490 runs on two CTAs) pays the global-load latency once per 128 k, not once
+    // per 16 (34 us -> a few us for that shape)
+    constexpr int kSimtK = 128;
+    __shared__ float sa[16][kSimtK + 1];
+    __shared__ float sb[16][kSimtK + 1];
     const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
     const int row = blockIdx.y * 16 + ty, col = blockIdx.x * 16 + tx;
     float acc = 0.f;
     const int k_begin = blockIdx.z * k_per_split;   // split-K over gridDim.z (long-K, tiny-MN weight gradients)
     if (k_begin + k_per_split < K) K = k_begin + k_per_split;
-    for (int k0 = k_begin; k0 < K; k0 += 16) {
-        {
-            const int r = blockIdx.y * 16 + ty, k = k0 + tx;
-            float v = 0.f;
-            if (r < M && k < K) v = __bfloat162float(a_mn ? A[(long long)k * lda + r] : A[(long long)r * lda + k]);
-            sa[ty][tx] = v;
+    const int ra = blockIdx.y * 16 + ty, cb = blockIdx.x * 16 + ty;
+    for (int k0 = k_begin; k0 < K; k0 += kSimtK) {
+        float va[kSimtK / 16], vb[kSimtK / 16];
+#pragma unroll
+        for (int q = 0; q < kSimtK / 16; ++q) {
+            const int k = k0 + tx + 16 * q;
+            va[q] = (ra < M && k < K) ? __bfloat162float(a_mn ? A[(long long)k * lda + ra] : A[(long long)ra * lda + k]) : 0.f;
+            vb[q] = (cb < N && k < K) ? __bfloat162float(b_mn ? B[(long long)k * ldb + cb] : B[(long long)cb * ldb + k]) : 0.f;
         }
-        {
-            const int c = blockIdx.x * 16 + ty, k = k0 + tx;
-            float v = 0.f;
-            if (c < N && k < K) v = __bfloat162float(b_mn ? B[(long long)k * ldb + c] : B[(long long)c * ldb + k]);
-            sb[ty][tx] = v;
+#pragma unroll
+        for (int q = 0; q < kSimtK / 16; ++q) {
+            sa[ty][tx + 16 * q] = va[q];
+            sb[ty][tx + 16 * q] = vb[q];
         }
         __syncthreads();
+        const int kn = K - k0 < kSimtK ? ((K - k0 + 15) & ~15) : kSimtK;   // zero-filled beyond K
+        for (int k = 0; k < kn; k += 16) {
 #pragma unroll
-        for (int k = 0; k < 16; ++k) acc += sa[ty][k] * sb[tx][k];
+            for (int j = 0; j < 16; ++j) acc += sa[ty][k + j] * sb[tx][k + j];
+        }
         __syncthreads();
     }
     if (row >= M || col >= N) return;
