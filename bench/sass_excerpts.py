@@ -19,7 +19,8 @@ KEYS = ("UTCHMMA", "UTCQMMA", "UTCBAR", "LDTM", "STTM", "UTMALDG", "UTMASTG", "U
         "DFMA", "REDUX")
 WANT = ("gemm_bf16_kernel", "attn_fwd_kernel", "attn_bwd_fused_kernel", "conv_igemm_kernel", "conv_wgrad_igemm_kernel",
         "allreduce_bulk_kernel", "allreduce_nvls_kernel", "allreduce_update_kernel", "xent_rows_kernel",
-        "mlpc_dgemm_kernel", "lstm_rec_fwd_kernel", "ln_bwd_kernel", "embedding_bwd_sorted_kernel", "optim_step_kernel")
+        "mlpc_dgemm_kernel", "lstm_rec_fwd_kernel", "lstm2_fwd_kernel", "lstm2_bwd_kernel", "ln_bwd_kernel",
+        "embedding_bwd_sorted_kernel", "optim_step_kernel")
 CONTEXT, MAX_WINDOWS, MAX_LINES = 4, 10, 170
 
 

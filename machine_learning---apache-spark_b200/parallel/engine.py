@@ -47,6 +47,9 @@ class DataParallelEngine:
         self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
         self.pg = process_group
         self.world = dist.get_world_size(self.pg) if dist.is_available() and dist.is_initialized() else 1
+        # models may order the independent branches of their forward by it (models/transformer.py: which of two
+        # concurrent branches is ISSUED first decides which gradient bucket backward completes first)
+        module._b200_dp_world = self.world
         self.rank = dist.get_rank(self.pg) if self.world > 1 else 0
         self.sync_gradients = sync_gradients  # False emulates the reference as written
         params = [p for p in module.parameters() if p.requires_grad]
@@ -402,6 +405,8 @@ class DataParallelEngine:
                 p._b200_touched = None
             p._b200_ready = None
             p._b200_side = None
+        if getattr(self.module, "_b200_dp_world", None) is not None:
+            self.module._b200_dp_world = 1
 
 
 class GraphedStep:
