@@ -250,7 +250,7 @@ constexpr int kBulkSmemBudget = 200 * 1024;
 template <bool kAdam, bool kBulkStore>
 __global__ void __launch_bounds__(kBulkThreads, 1)
 allreduce_bulk_kernel(Peers c, long long start, long long n, OptimSpec o, float* __restrict__ m, float* __restrict__ v,
-                      int push_master, int stages, SparseRows sp) {
+                      int push_master, int stages, SparseRows sp, long long start2, long long n2) {
     extern __shared__ __align__(128) uint8_t bsm[];
     __shared__ __align__(4) unsigned char s_need[kBulkMaxNeed];   // per chunk of this CTA: bit r set = fetch rank r's gradient chunk
     const int tid = threadIdx.x;
@@ -275,6 +275,15 @@ allreduce_bulk_kernel(Peers c, long long start, long long n, OptimSpec o, float*
     const long long len_total = hi - lo;
     const long long nchunks = (len_total + kBulkChunk - 1) / kBulkChunk;
     const long long base = start + lo;
+    // Optional second range [start2, start2 + n2) riding in the same launch (the engine's small fp32 parameters: biases,
+    // LayerNorm vectors): sliced and updated the same way, its chunks follow the first range's, and its fp32 masters
+    // are always pushed to every rank (their consumers read the masters, not the bf16 copies).  One launch = one pair
+    // of cross-GPU barriers instead of two.
+    long long lo2 = 0, hi2 = 0;
+    if (n2 > 0) owned_range(n2, 8, c.world, c.rank, lo2, hi2);
+    const long long len2_total = hi2 - lo2;
+    const long long nchunks_all = nchunks + (len2_total + kBulkChunk - 1) / kBulkChunk;
+    const long long base2 = start2 + lo2;
 
     // which peers must be read for each of this CTA's chunks (all of them unless the chunk lies in a row-sparse table)
     const long long my_chunks = nchunks > blockIdx.x ? (nchunks - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
@@ -303,13 +312,15 @@ allreduce_bulk_kernel(Peers c, long long start, long long n, OptimSpec o, float*
         if (tid == kBulkConsumers) {  // ---------------- producer ----------------
             fence_proxy_async_all();  // the acquire above ordered the peers' writes; make that hold for the TMA reads too
             int k = 0;
-            for (long long ch = blockIdx.x; ch < nchunks; ch += gridDim.x, ++k) {
+            for (long long ch = blockIdx.x; ch < nchunks_all; ch += gridDim.x, ++k) {
                 const int s = k % stages;
                 if (k >= stages) mbar_wait(&empty[s], ((k / stages) - 1) & 1);
-                const long long e = base + ch * kBulkChunk;
-                const long long left = len_total - ch * kBulkChunk;
+                const bool tail = ch >= nchunks;
+                const long long cc = tail ? ch - nchunks : ch;
+                const long long e = (tail ? base2 : base) + cc * kBulkChunk;
+                const long long left = (tail ? len2_total : len_total) - cc * kBulkChunk;
                 const uint32_t bytes = (uint32_t)(left < kBulkChunk ? left : kBulkChunk) * 4u;
-                const unsigned need = use_need ? s_need[k] : 0xFFu;
+                const unsigned need = (use_need && !tail) ? s_need[k] : 0xFFu;
                 int nload = kAdam ? 4 : 2;
                 for (int r = 0; r < c.world; ++r)
                     if (r != c.rank && ((need >> r) & 1u)) ++nload;
@@ -334,15 +345,17 @@ allreduce_bulk_kernel(Peers c, long long start, long long n, OptimSpec o, float*
         AdamCorr corr = {0.f, 0.f};
         if (kAdam) corr = adam_corr(o);
         int k = 0;
-        for (long long ch = blockIdx.x; ch < nchunks; ch += gridDim.x, ++k) {
+        for (long long ch = blockIdx.x; ch < nchunks_all; ch += gridDim.x, ++k) {
             const int s = k % stages;
             mbar_wait(&full[s], (k / stages) & 1);
-            const long long e = base + ch * kBulkChunk;
-            const long long left = len_total - ch * kBulkChunk;
+            const bool tail = ch >= nchunks;
+            const long long cc = tail ? ch - nchunks : ch;
+            const long long e = (tail ? base2 : base) + cc * kBulkChunk;
+            const long long left = (tail ? len2_total : len_total) - cc * kBulkChunk;
             const int len = (int)(left < kBulkChunk ? left : kBulkChunk);
             const float4* st4 = reinterpret_cast<const float4*>(bsm + (size_t)s * stage_bytes);
             uint2* ob = reinterpret_cast<uint2*>(outbuf + (k % kBulkOutBufs) * kBulkOutBytes);
-            const unsigned need = (use_need ? s_need[k] : 0xFFu) | (1u << c.rank);
+            const unsigned need = ((use_need && !tail) ? s_need[k] : 0xFFu) | (1u << c.rank);
             if (tid * 4 < len) {
                 float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
                 for (int r = 0; r < c.world; ++r) {  // rank order, the local copy in its own position
@@ -371,7 +384,7 @@ allreduce_bulk_kernel(Peers c, long long start, long long n, OptimSpec o, float*
                 } else {
                     for (int r = 0; r < c.world; ++r) *reinterpret_cast<uint2*>(c.w16[r] + ee) = pb;
                 }
-                if (push_master) {
+                if (push_master || tail) {
                     for (int r = 0; r < c.world; ++r)
                         if (r != c.rank) *reinterpret_cast<float4*>(c.p[r] + ee) = p;
                 }
@@ -586,7 +599,7 @@ int resident_cap(K kernel, int threads, size_t smem) {
 
 template <bool kAdam, bool kBulkStore>
 int launch_bulk(const Peers& c, long long start, long long n, const OptimSpec& o, float* m, float* v, int push_master,
-                int max_blocks, cudaStream_t stream, const SparseRows& sp) {
+                int max_blocks, cudaStream_t stream, const SparseRows& sp, long long start2, long long n2) {
     const int nslots = c.world - 1 + (kAdam ? 4 : 2);
     const size_t stage_bytes = (size_t)nslots * kBulkChunkBytes;
     const size_t fixed = (size_t)kBulkOutBufs * kBulkOutBytes + 2 * kBulkMaxStages * sizeof(uint64_t);
@@ -610,7 +623,7 @@ int launch_bulk(const Peers& c, long long start, long long n, const OptimSpec& o
     if (cap > res) cap = res;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-    kernel<<<(int)blocks, kBulkThreads, smem, stream>>>(c, start, n, o, m, v, push_master, stages, sp);
+    kernel<<<(int)blocks, kBulkThreads, smem, stream>>>(c, start, n, o, m, v, push_master, stages, sp, start2, n2);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
@@ -619,12 +632,14 @@ int launch_bulk(const Peers& c, long long start, long long n, const OptimSpec& o
 
 extern "C" {
 
-int b200ml_allreduce_update_sparse(const b200ml_comm* cm, long long start, long long n, int algo, int kind, float lr,
-                                   float beta1, float beta2, float eps, float weight_decay, const int* step_dev,
-                                   float* m, float* v, float* out, int push_master, int max_blocks,
-                                   const b200ml_sparse_rows* sparse, cudaStream_t stream) {
+int b200ml_allreduce_update_tail(const b200ml_comm* cm, long long start, long long n, long long start2, long long n2,
+                                 int algo, int kind, float lr, float beta1, float beta2, float eps, float weight_decay,
+                                 const int* step_dev, float* m, float* v, float* out, int push_master, int max_blocks,
+                                 const b200ml_sparse_rows* sparse, cudaStream_t stream) {
     Peers c;
     if (fill_peers(cm, c)) return -1;
+    B200_REQUIRE(n2 >= 0 && (n2 == 0 || (start2 % 8 == 0 && n2 % 8 == 0 && (start2 + n2 <= start || start2 >= start + n))),
+                 "allreduce: the riding range must be 8-element aligned and disjoint from the bucket");
     SparseRows sp{};
     if (sparse && sparse->rows > 0) {
         B200_REQUIRE(sparse->row_elems > 0 && sparse->start >= start &&
@@ -664,12 +679,14 @@ int b200ml_allreduce_update_sparse(const b200ml_comm* cm, long long start, long 
         B200_CHECK_CUDA(cudaGetLastError());
         return 0;
     }
+    B200_REQUIRE(n2 == 0 || (two && al8 && algo != 2 && algo != 3 && !(algo == 0 && have_mc)),
+                 "allreduce: a riding range needs the bulk-async two-shot path (kind 1/2, 8-element aligned bucket)");
     if (two && al8 && algo != 2) {  // bulk-async (algo 0 / 4; 5 = the same with per-thread weight stores)
         if (kind == 2)
-            return algo == 5 ? launch_bulk<true, false>(c, start, n, o, m, v, push_master, max_blocks, stream, sp)
-                             : launch_bulk<true, true>(c, start, n, o, m, v, push_master, max_blocks, stream, sp);
-        return algo == 5 ? launch_bulk<false, false>(c, start, n, o, m, v, push_master, max_blocks, stream, sp)
-                         : launch_bulk<false, true>(c, start, n, o, m, v, push_master, max_blocks, stream, sp);
+            return algo == 5 ? launch_bulk<true, false>(c, start, n, o, m, v, push_master, max_blocks, stream, sp, start2, n2)
+                             : launch_bulk<true, true>(c, start, n, o, m, v, push_master, max_blocks, stream, sp, start2, n2);
+        return algo == 5 ? launch_bulk<false, false>(c, start, n, o, m, v, push_master, max_blocks, stream, sp, start2, n2)
+                         : launch_bulk<false, true>(c, start, n, o, m, v, push_master, max_blocks, stream, sp, start2, n2);
     }
     const int gran = al8 ? 8 : 4;
     const long long work = two ? (n / cm->world + 3) / 4 : n / 4;
@@ -686,6 +703,14 @@ int b200ml_allreduce_update_sparse(const b200ml_comm* cm, long long start, long 
         allreduce_update_kernel<false><<<(int)blocks, kThreads, 0, stream>>>(c, start, n, o, m, v, out, push_master, gran);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
+}
+
+int b200ml_allreduce_update_sparse(const b200ml_comm* cm, long long start, long long n, int algo, int kind, float lr,
+                                   float beta1, float beta2, float eps, float weight_decay, const int* step_dev,
+                                   float* m, float* v, float* out, int push_master, int max_blocks,
+                                   const b200ml_sparse_rows* sparse, cudaStream_t stream) {
+    return b200ml_allreduce_update_tail(cm, start, n, 0, 0, algo, kind, lr, beta1, beta2, eps, weight_decay, step_dev, m, v,
+                                        out, push_master, max_blocks, sparse, stream);
 }
 
 int b200ml_allreduce_update(const b200ml_comm* cm, long long start, long long n, int algo, int kind, float lr,

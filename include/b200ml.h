@@ -299,6 +299,14 @@ int b200ml_allreduce_update_sparse(const b200ml_comm* cm, long long start, long 
                                    float beta1, float beta2, float eps, float weight_decay, const int* step_dev,
                                    float* m, float* v, float* out, int push_master, int max_blocks,
                                    const b200ml_sparse_rows* sparse, cudaStream_t stream);
+/* Same, with a second range [start2, start2 + n2) riding in the launch (bulk-async two-shot path only, n2 = 0: none):
+ * sliced and updated like the bucket, its fp32 masters always pushed to every rank.  The engine sends its small fp32
+ * parameters (biases, LayerNorm vectors) along with the last big bucket of a step this way: one launch, one pair of
+ * cross-GPU barriers, instead of two. */
+int b200ml_allreduce_update_tail(const b200ml_comm* cm, long long start, long long n, long long start2, long long n2,
+                                 int algo, int kind, float lr, float beta1, float beta2, float eps, float weight_decay,
+                                 const int* step_dev, float* m, float* v, float* out, int push_master, int max_blocks,
+                                 const b200ml_sparse_rows* sparse, cudaStream_t stream);
 int b200ml_allreduce_update(const b200ml_comm* cm, long long start, long long n, int algo, int kind, float lr,
                             float beta1, float beta2, float eps, float weight_decay, const int* step_dev, float* m,
                             float* v, float* out, int push_master, int max_blocks, cudaStream_t stream);

@@ -151,6 +151,8 @@ class SparseRowsStruct(C.Structure):
 
 _native_ext.register("b200ml_allreduce_update_sparse", [C.POINTER(CommStruct), ll, ll, i, i, f, f, f, f, f, vp, vp, vp, vp,
                                                         i, i, C.POINTER(SparseRowsStruct), vp])
+_native_ext.register("b200ml_allreduce_update_tail", [C.POINTER(CommStruct), ll, ll, ll, ll, i, i, f, f, f, f, f, vp, vp, vp,
+                                                      vp, i, i, C.POINTER(SparseRowsStruct), vp])
 _native_ext.register("b200ml_allreduce_sum_f64", [C.POINTER(CommStruct), C.POINTER(C.c_void_p * 8), ll, vp, vp])
 
 
@@ -296,14 +298,22 @@ class FusedAllReduce:
         torch.cuda.synchronize(dev)
         dist.barrier(group=group)
 
+    def rider_capable(self) -> bool:
+        """Can a second range ride in the launch of a two-shot bucket (bulk-async transport, no NVLS)?"""
+        return self.default_algo in (0, 4, 5) and not (self.cs.mc_grads and self.cs.mc_w16)
+
     def allreduce_update(self, start, n, kind, lr, betas, eps, weight_decay, step_tensor, out=None, algo: int = 0,
-                         sparse: "SparseRowsStruct | None" = None):
+                         sparse: "SparseRowsStruct | None" = None, tail: "tuple[int, int] | None" = None):
+        """``tail`` = (start2, n2): a second range that rides in the same launch (sliced and updated like the bucket,
+        fp32 masters always pushed) - only on the bulk-async two-shot path."""
         lib = _native.load()
         n4 = (n + 3) // 4 * 4  # slots are 64-element aligned, so rounding up stays inside the bucket
         if algo == 0 and kind != 0 and n4 * 4 > (512 << 10):
             algo = self.default_algo
-        _native.check(lib.b200ml_allreduce_update_sparse(
-            C.byref(self.cs), start, n4, algo, kind, lr, betas[0], betas[1], eps, weight_decay, step_tensor.data_ptr(),
+        start2, n2 = (0, 0) if tail is None else (tail[0], (tail[1] + 7) // 8 * 8)
+        _native.check(lib.b200ml_allreduce_update_tail(
+            C.byref(self.cs), start, n4, start2, n2, algo, kind, lr, betas[0], betas[1], eps, weight_decay,
+            step_tensor.data_ptr(),
             None if self.m is None else self.m.data_ptr(), None if self.v is None else self.v.data_ptr(),
             None if out is None else out.data_ptr(), self.push_master, self.max_blocks,
             None if sparse is None else C.byref(sparse), _native.stream_ptr()), "allreduce_update")

@@ -147,6 +147,33 @@ class DataParallelEngine:
         self._streams_used: set = set()
         if not hasattr(self, "_sparse"):
             self._sparse = {}
+        self._setup_rider()
+
+    def _setup_rider(self) -> None:
+        """The bucket of small fp32 parameters (biases, LayerNorm vectors: a few 10 KB) used to be a launch of its own -
+        two cross-GPU barriers, 25-36 us, for next to no data, usually in the exposed tail of the step.  When the fused
+        bulk-async transport is in use it RIDES in the launch of the first two-shot bucket that becomes ready after it
+        (`b200ml_allreduce_update_tail`).  Its optimizer state is then sliced over the ranks like a two-shot bucket's -
+        in every step, also when it has to be launched alone (no later two-shot bucket in that step) - so that the
+        owners of the Adam moments never change.  `B200ML_AR_RIDER=0` keeps the separate one-shot launch."""
+        self._rider = None            # bucket index of the riding bucket
+        self._rider_waiting = False   # ready in this step, not launched yet
+        self._hosts: set = set()      # buckets that may carry it
+        if (self.comm is None or self.kind == 0 or os.environ.get("B200ML_AR_RIDER", "1") == "0"
+                or not hasattr(self.comm, "rider_capable") or not self.comm.rider_capable()):
+            return
+        small = [b for b, (start, n, _, push) in enumerate(self.buckets)
+                 if not push and self.comm.owned_slice(start, n) is None and start % 8 == 0]
+        hosts = {b for b, (start, n, _, _) in enumerate(self.buckets)
+                 if self.comm.owned_slice(start, n) is not None and start % 8 == 0 and n % 8 == 0}
+        if len(small) == 1 and hosts:
+            self._rider, self._hosts = small[0], hosts
+            self.allreduce_mode += ":rider"
+
+    def _owned_slice(self, b: int):
+        """Slice of bucket b whose optimizer state this rank keeps (None: every rank keeps all of it)."""
+        start, n, _, _ = self.buckets[b]
+        return self.comm.owned_slice(start, n, sliced=True if b == self._rider else None)
 
     def _setup_sparse_rows(self) -> None:
         """Row-sparse tables (parameters an op flagged ``_b200_sparse_rows``: embedding tables, whose gradient rows are
@@ -215,23 +242,38 @@ class DataParallelEngine:
     def _bucket_ready(self, b: int, complete: bool = True) -> None:
         if (self.world == 1 and not self._local_overlap) or not self.sync_gradients:
             return  # single fused optimizer launch in finish_step
+        if self._rider is not None and complete and self.comm_stream is not None:
+            if b == self._rider:
+                self._rider_waiting = True      # launched with the next two-shot bucket (or alone in finish_step)
+                return
         if self.comm_stream is not None:
             st = self._opt_streams[b % len(self._opt_streams)] if self._opt_streams else self.comm_stream
             self._streams_used.add(st)
             st.wait_stream(torch.cuda.current_stream())
             for ev in self._events[b].values():
                 st.wait_event(ev)
+            carry = self._rider_waiting and b in self._hosts and complete
+            if carry:
+                for ev in self._events[self._rider].values():
+                    st.wait_event(ev)
+                self._rider_waiting = False
             with torch.cuda.stream(st):
-                self._reduce_and_update(b, complete)
+                self._reduce_and_update(b, complete, carry)
         else:
             self._reduce_and_update(b, complete)
 
-    def _reduce_and_update(self, b: int, complete: bool = True) -> None:
+    def _reduce_and_update(self, b: int, complete: bool = True, carry: bool = False) -> None:
         start, n, _, bf16_push = self.buckets[b]
         if self.comm is not None:
             self.comm.push_master = 0 if (bf16_push and self._bf16_push) else 1
+            tail = None
+            if carry:
+                tail = (self.buckets[self._rider][0], self.buckets[self._rider][1])
+            # the riding bucket launched alone still takes the sliced (two-shot, bulk) path: see _setup_rider
+            algo = 4 if b == self._rider else 0
             self.comm.allreduce_update(start, n, self.kind, self.lr, self.betas, self.eps, self.weight_decay,
-                                       self.step_tensor, sparse=self._sparse.get(b) if complete else None)
+                                       self.step_tensor, sparse=self._sparse.get(b) if complete else None, tail=tail,
+                                       algo=algo)
             return
         if self.world == 1:
             optim_step_flat(self.flat.flat_p, self.flat.flat_g, self.m, self.v, self.flat.flat_w16, self.kind, self.lr,
@@ -251,6 +293,7 @@ class DataParallelEngine:
         self.reducer.begin_step()
         for b in range(len(self.buckets)):
             self._events[b].clear()
+        self._rider_waiting = False
         self._in_step = True
         if self.side is not None:
             self.side.active = True
@@ -269,6 +312,16 @@ class DataParallelEngine:
         # parameters that never reported (unused in this forward) still need their bucket processed
         for b in self.reducer.flush():
             self._bucket_ready(b, complete=False)
+        if self._rider_waiting:                 # no two-shot bucket came after it in this step: launch it alone
+            self._rider_waiting = False
+            rider = self._rider
+            st = self.comm_stream
+            self._streams_used.add(st)
+            st.wait_stream(torch.cuda.current_stream())
+            for ev in self._events[rider].values():
+                st.wait_event(ev)
+            with torch.cuda.stream(st):
+                self._reduce_and_update(rider, True)
         if self.comm_stream is not None:
             # only the streams this step actually used: inside a graph capture, waiting on a stream that is not part
             # of the capture is an error
@@ -360,7 +413,7 @@ class DataParallelEngine:
         for t in (self.m, self.v):
             full = t.clone()
             for b, (start, n, _, _) in enumerate(self.buckets):
-                own = self.comm.owned_slice(start, n)
+                own = self._owned_slice(b)
                 if own is None:
                     continue        # one-shot bucket: every rank ran the identical update
                 lo, hi = own
