@@ -342,3 +342,26 @@ def test_mlpc_fit_on_gpu_uses_native_kernels_and_matches_cpu(monkeypatch):
     assert _native.launches() - n0 >= 15                     # every evaluation goes through this library's kernels
     c = ml._fit_local(X, y, device="cpu", **kw)
     assert abs(g["objectiveHistory"][-1] - c["objectiveHistory"][-1]) < 1e-6
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("rows,C,dtype", [(32, 10, torch.float32), (257, 4, torch.float32), (64, 19214, torch.bfloat16),
+                                          (5, 3, torch.bfloat16)])
+def test_argmax_accuracy_kernel_matches_torch(rows, C, dtype):
+    """K14 (distributed_cnn.py:144-147,211-212): predicted class = arg-max of the logits (softmax is monotone), the
+    device counter accumulates the number of correct rows over calls; first maximum wins on ties, like torch.argmax."""
+    from b200ml.ops.metrics import argmax_accuracy
+    torch.manual_seed(rows * 31 + C)
+    z = torch.randn(rows, C, device="cuda").to(dtype)
+    z[0, :] = 1.0                                      # a full tie: class 0
+    if C > 2:
+        z[1, 1] = z[1, 2] = 50.0                       # a two-way tie: the lower index
+    y = torch.randint(0, C, (rows,), device="cuda")
+    pred, correct = argmax_accuracy(z, y)
+    ref = z.float().argmax(1)
+    assert torch.equal(pred, ref)
+    assert int(correct.item()) == int((ref == y).sum())
+    pred2, correct = argmax_accuracy(z, y, correct)    # accumulates
+    assert int(correct.item()) == 2 * int((ref == y).sum())
+    pred3, c3 = argmax_accuracy(z)                     # no targets: predictions only
+    assert torch.equal(pred3, ref) and int(c3.item()) == 0

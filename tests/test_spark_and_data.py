@@ -166,3 +166,16 @@ def test_pyspark_shim_import_paths():
         from pyspark.ml.evaluation import MulticlassClassificationEvaluator  # noqa: F401
         from pyspark.ml.torch.distributor import TorchDistributor  # noqa: F401
         from pyspark.sql import SparkSession  # noqa: F401
+
+
+def test_argmax_accuracy_cpu_restatement():
+    """ops/metrics.py on CPU tensors (the oracle of the K14 kernel test): predictions and the accumulating counter."""
+    import torch
+
+    from b200ml.ops.metrics import argmax_accuracy
+    z = torch.tensor([[0.1, 0.9, 0.0], [2.0, 1.0, 2.0], [0.0, 0.0, 3.0]])
+    y = torch.tensor([1, 0, 1])
+    pred, correct = argmax_accuracy(z, y)
+    assert pred.tolist() == [1, 0, 2] and int(correct) == 2
+    _, correct = argmax_accuracy(z, y, correct)
+    assert int(correct) == 4
