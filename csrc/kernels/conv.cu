@@ -2,13 +2,17 @@
 //
 // Reference: FashionMNISTModel's four Conv2d+ReLU pairs and two MaxPool2d(2) (distributed_cnn.py:51-73).
 // Two implementations behind one entry point (b200ml_conv_set_algo / B200ML_CONV_ALGO):
-//   * tcgen05 implicit GEMM (conv_igemm_kernel below) for the forward and the data gradient once K = 9*C reaches one
-//     64-deep slice - the reference's 10->10 layers qualify (K = 90, N padded to 16);
-//   * direct fp32 convolutions on the CUDA cores for the tiny first layer (Cin = 1 or 3: K = 9..27) and for the weight
-//     gradient (partial sums per CTA + fixed-order second stage, deterministic, no atomics).
+//   * tcgen05 implicit GEMMs (conv_igemm_kernel, conv_wgrad_igemm_kernel below) for the forward, the data gradient and
+//     the weight gradient once K = 9*C reaches one 64-deep slice - the reference's 10->10 layers qualify (K = 90, N
+//     padded to 16); the weight gradient reduces over the tile's 256 pixels in TMEM (split-K over B*H*W, per-CTA
+//     partials + a fixed-order second stage: deterministic, no atomics);
+//   * direct fp32 convolutions on the CUDA cores for the tiny first layer (Cin = 1 or 3: K = 9..27) and as the
+//     selectable alternative for every layer.
 // Fused around the MACs in both: bias + ReLU (+ max-pool with a 2-bit argmax) in the forward epilogue - the pre-pool
 // activation never hits HBM; un-pool + ReLU' folded into the loads of both gradient kernels (dZ is never materialised).
-// Measured, CNN training step at batch 32 (bench/bench_models.py): direct 0.217 ms, implicit GEMM 0.212 ms, auto 0.210.
+// The kernels are latency-bound at the reference's sizes (a 10-channel 14 x 14 layer is 45 MFLOP): what matters is the
+// number of dependent global round trips per CTA, hence gather_to_smem below.  Measured, CNN training step at batch 32
+// (bench/bench_models.py): 0.157 ms (0.188 ms before the batched staging loads, 0.225 ms with the direct weight gradient).
 // One CTA = one image x one 16x16 output tile x all channels.  Cin, Cout <= 64.
 #include "../common/pdl.cuh"
 #include "../../include/b200ml.h"
