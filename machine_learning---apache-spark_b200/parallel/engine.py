@@ -262,6 +262,20 @@ class DataParallelEngine:
         else:
             self._reduce_and_update(b, complete)
 
+    def _flush_rider(self) -> None:
+        """End of the step: the riding bucket became ready after the last two-shot bucket - launch it alone."""
+        if not self._rider_waiting:
+            return
+        self._rider_waiting = False
+        rider = self._rider
+        st = self.comm_stream
+        self._streams_used.add(st)
+        st.wait_stream(torch.cuda.current_stream())
+        for ev in self._events[rider].values():
+            st.wait_event(ev)
+        with torch.cuda.stream(st):
+            self._reduce_and_update(rider, True)
+
     def _reduce_and_update(self, b: int, complete: bool = True, carry: bool = False) -> None:
         start, n, _, bf16_push = self.buckets[b]
         if self.comm is not None:
@@ -312,16 +326,7 @@ class DataParallelEngine:
         # parameters that never reported (unused in this forward) still need their bucket processed
         for b in self.reducer.flush():
             self._bucket_ready(b, complete=False)
-        if self._rider_waiting:                 # no two-shot bucket came after it in this step: launch it alone
-            self._rider_waiting = False
-            rider = self._rider
-            st = self.comm_stream
-            self._streams_used.add(st)
-            st.wait_stream(torch.cuda.current_stream())
-            for ev in self._events[rider].values():
-                st.wait_event(ev)
-            with torch.cuda.stream(st):
-                self._reduce_and_update(rider, True)
+        self._flush_rider()
         if self.comm_stream is not None:
             # only the streams this step actually used: inside a graph capture, waiting on a stream that is not part
             # of the capture is an error

@@ -114,3 +114,73 @@ def test_big_parameters_start_their_own_bucket():
         r = R([0, 9 * M, 10 * M, 11 * M, 12 * M, 13 * M, 22 * M], [6], cap)
         assert [ids for _, _, ids, _ in r.buckets] == [[0, 1, 2, 3], [4], [5]], R.__name__
         r.close()
+
+
+def test_small_bucket_rides_with_the_next_two_shot_bucket(monkeypatch):
+    """Scheduling of the riding bucket (DataParallelEngine._setup_rider): once ready it waits for the next two-shot
+    bucket and is passed along as that launch's tail; when no two-shot bucket follows it in the step it is launched
+    alone at the end, through the sliced (algo 4) path, so the owners of its optimizer state never change.  The
+    communicator and the streams are stand-ins: only the engine's decisions are under test."""
+    import contextlib
+
+    import torch
+    from b200ml.models.transformer import Transformer
+    from b200ml.parallel import engine as engine_mod
+    from b200ml.parallel.engine import DataParallelEngine
+
+    eng = DataParallelEngine(Transformer(64, 128, 2, 0.0, 1, 16, 50, 40, 50), optimizer="adam", lr=1e-3, bucket_mb=0.05)
+    assert len(eng.buckets) >= 3, eng.buckets
+    calls = []
+
+    class FakeComm:
+        push_master = 1
+
+        def allreduce_update(self, start, n, kind, lr, betas, eps, wd, step, out=None, algo=0, sparse=None, tail=None):
+            calls.append((start, n, tail, algo))
+
+    class FakeStream:
+        cuda_stream = 0
+
+        def wait_stream(self, other):
+            pass
+
+        def wait_event(self, ev):
+            pass
+
+    fake = FakeStream()
+    monkeypatch.setattr(engine_mod.torch.cuda, "stream", lambda st: contextlib.nullcontext())
+    monkeypatch.setattr(engine_mod.torch.cuda, "current_stream", lambda *a, **k: fake)
+    eng.world, eng.comm, eng.comm_stream, eng._opt_streams, eng._local_overlap = 2, FakeComm(), fake, [], False
+    rider, host, other = len(eng.buckets) - 1, 0, 1
+    eng._rider, eng._hosts = rider, {host}
+    r_start, r_n = eng.buckets[rider][0], eng.buckets[rider][1]
+
+    # rider first, then a bucket that cannot carry it, then the host: ONE launch carries it
+    eng._rider_waiting = False
+    eng._bucket_ready(rider)
+    assert calls == [] and eng._rider_waiting
+    eng._bucket_ready(other)
+    assert calls[-1][2] is None and eng._rider_waiting
+    eng._bucket_ready(host)
+    assert calls[-1][:2] == eng.buckets[host][:2] and calls[-1][2] == (r_start, r_n) and not eng._rider_waiting
+    eng._flush_rider()
+    assert len(calls) == 2
+
+    # host first: the rider has nobody to ride with and goes alone at the end of the step, on the sliced path
+    calls.clear()
+    eng._bucket_ready(host)
+    eng._bucket_ready(rider)
+    assert len(calls) == 1 and calls[0][2] is None and eng._rider_waiting
+    eng._flush_rider()
+    assert calls[-1] == (r_start, r_n, None, 4) and not eng._rider_waiting
+
+    # an incomplete host bucket (flushed at the end because a parameter never reported) does not carry it
+    calls.clear()
+    eng._bucket_ready(rider)
+    eng._bucket_ready(host, complete=False)
+    assert calls[-1][2] is None and eng._rider_waiting
+    eng._flush_rider()
+    assert calls[-1] == (r_start, r_n, None, 4)
+    eng.comm = None
+    eng.world = 1
+    eng.close()
