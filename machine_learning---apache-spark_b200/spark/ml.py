@@ -301,7 +301,61 @@ class _Reducer:
             self.fused.close()
 
 
-def _fit_local(X, y, layers, block_size, max_iter, tol, solver, step_size, seed, initial_weights, device):
+def _block_weights(n: int, block_size: int, dev):
+    """MLlib DataStacker: consecutive rows form blocks of <= blockSize; a row weighs 1 / (rows of its block)."""
+    sizes = torch.full((n,), float(block_size), dtype=torch.float64, device=dev)
+    rem = n % block_size
+    if rem:
+        sizes[n - rem:] = float(rem)
+    return 1.0 / sizes
+
+
+def _chunked_fn(Xd, Yd, layers, block_size, chunk_rows, chunks_local, world, native):
+    """Loss / gradient evaluation whose floating-point result does not depend on the number of workers
+    (``reproducible=True``).  The data set is cut into CANONICAL_CHUNKS row chunks (whole MLlib blocks each); a worker
+    owns a run of consecutive chunks, evaluates [gradient ‖ loss ‖ #blocks] per chunk with the same code on the same
+    rows whatever the worker count, the per-chunk vectors of all workers are all-gathered in chunk order and added
+    pairwise in a fixed tree.  Every addition therefore has the same operands in the same order for 1, 2, 4 or 8
+    workers: objective history and weights are bit-identical (tests/test_spark_and_data.py)."""
+    dev, n, nw = Xd.device, Xd.shape[0], num_weights(layers)
+    vecs = torch.zeros(chunks_local, nw + 2, dtype=torch.float64, device=dev)
+    parts = []
+    for c in range(chunks_local):
+        a, b = min(c * chunk_rows, n), min((c + 1) * chunk_rows, n)
+        if b > a:
+            # own copies: a chunk must look the same (alignment included) whether it is the whole shard or a slice of it
+            parts.append((c, Xd[a:b].clone(), Yd[a:b].clone(), _block_weights(b - a, block_size, dev)))
+            vecs[c, nw + 1] = float(math.ceil((b - a) / block_size))
+
+    def fn(w):
+        wc = w.contiguous()
+        for c, Xc, Yc, rw in parts:
+            if native:
+                _native_loss_grad(wc, layers, Xc, Yc, rw, vecs[c])
+            else:
+                loss, grad = loss_and_grad(wc, layers, Xc, Yc, rw)
+                vecs[c, :nw].copy_(grad)
+                vecs[c, nw] = loss
+        if world > 1:
+            gathered = [torch.empty_like(vecs) for _ in range(world)]
+            dist.all_gather(gathered, vecs)
+            v = torch.cat(gathered)
+        else:
+            v = vecs
+        while v.shape[0] > 1:                       # fixed pairwise tree over the canonical chunks
+            v = v[0::2] + v[1::2]
+        total = v[0]
+        blocks = total[nw + 1].clamp_min(1.0)
+        return total[nw] / blocks, total[:nw] / blocks
+
+    return fn
+
+
+CANONICAL_CHUNKS = 8   # reproducible mode: worker counts 1, 2, 4, 8
+
+
+def _fit_local(X, y, layers, block_size, max_iter, tol, solver, step_size, seed, initial_weights, device,
+               chunk_rows: int = 0, chunks_local: int = 0):
     """Runs on every rank with its shard (or on the single process)."""
     world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
     dev = torch.device(device)
@@ -323,7 +377,7 @@ def _fit_local(X, y, layers, block_size, max_iter, tol, solver, step_size, seed,
     vec[nw + 1] = local_blocks
     native = dev.type == "cuda" and os.environ.get("B200ML_MLPC_NATIVE", "1") != "0"
 
-    def fn(w):
+    def fn(w):   # default: one evaluation over the whole shard, one all-reduce
         if n and native:
             _native_loss_grad(w.contiguous(), layers, Xd, Yd, row_w, vec)
         elif n:
@@ -334,6 +388,13 @@ def _fit_local(X, y, layers, block_size, max_iter, tol, solver, step_size, seed,
         blocks = total[nw + 1].clamp_min(1.0)
         return total[nw] / blocks, total[:nw] / blocks
 
+    threads = None
+    if chunk_rows:
+        fn = _chunked_fn(Xd, Yd, layers, block_size, chunk_rows, chunks_local, world, native)   # noqa: F811
+        if dev.type == "cpu":
+            # a BLAS that splits a product over threads may add in another order: one thread, whatever the host has
+            threads = torch.get_num_threads()
+            torch.set_num_threads(1)
     w0 = (torch.as_tensor(np.asarray(initial_weights), dtype=torch.float64) if initial_weights is not None
           else init_weights(layers, seed)).to(dev)
     if world > 1:
@@ -367,6 +428,8 @@ def _fit_local(X, y, layers, block_size, max_iter, tol, solver, step_size, seed,
         torch.cuda.synchronize(dev)
     fit_s = time.time() - t0
     reducer.close()
+    if threads is not None:
+        torch.set_num_threads(threads)
     return {"weights": w.detach().cpu().numpy(), "objectiveHistory": history, "totalIterations": iters,
             "functionEvaluations": evals, "fitSeconds": fit_s, "world": world}
 
@@ -431,7 +494,8 @@ class _Params:
 class MultilayerPerceptronClassifier(_Params):
     _defaults = dict(featuresCol="features", labelCol="label", predictionCol="prediction", maxIter=100, tol=1e-6,
                      seed=None, layers=None, blockSize=128, stepSize=0.03, solver="l-bfgs", initialWeights=None,
-                     probabilityCol="probability", rawPredictionCol="rawPrediction", numWorkers=None, device=None)
+                     probabilityCol="probability", rawPredictionCol="rawPrediction", numWorkers=None, device=None,
+                     reproducible=False)
 
     def _workers(self) -> int:
         if self._p["numWorkers"]:
@@ -465,16 +529,27 @@ class MultilayerPerceptronClassifier(_Params):
                           p["initialWeights"].toArray() if hasattr(p["initialWeights"], "toArray") else p["initialWeights"]))
         workers = self._workers()
         in_group = dist.is_available() and dist.is_initialized()
+        per_of = lambda w: math.ceil(len(X) / w)   # noqa: E731  rows per worker
+        if p["reproducible"]:
+            # not an MLlib parameter: the result is bit-identical for 1, 2, 4 and 8 workers (see _chunked_fn); the
+            # shards are runs of whole canonical chunks, and a chunk holds whole MLlib blocks
+            w_eff = dist.get_world_size() if in_group else workers
+            if CANONICAL_CHUNKS % w_eff:
+                raise ValueError(f"reproducible=True needs a worker count that divides {CANONICAL_CHUNKS}, got {w_eff}")
+            bs = int(p["blockSize"])
+            chunk_rows = max(1, math.ceil(math.ceil(len(X) / CANONICAL_CHUNKS) / bs)) * bs
+            kwargs.update(chunk_rows=chunk_rows, chunks_local=CANONICAL_CHUNKS // w_eff)
+            per_of = lambda w: chunk_rows * (CANONICAL_CHUNKS // w)   # noqa: E731
         if in_group:  # data-parallel inside an existing job: shard rows by rank
             r, w = dist.get_rank(), dist.get_world_size()
-            per = math.ceil(len(X) / w)
+            per = per_of(w)
             dev = p["device"] or (f"cuda:{torch.cuda.current_device()}" if torch.cuda.is_available() and
                                   dist.get_backend() == "nccl" else "cpu")
             res = _fit_local(X[r * per:(r + 1) * per], yi[r * per:(r + 1) * per], device=dev, **kwargs)
         elif workers > 1:
             from .distributor import TorchDistributor
 
-            per = math.ceil(len(X) / workers)
+            per = per_of(workers)
             shards = [(X[r * per:(r + 1) * per], yi[r * per:(r + 1) * per]) for r in range(workers)]
             use_gpu = torch.cuda.is_available() and torch.cuda.device_count() >= workers and p["device"] != "cpu"
             res = TorchDistributor(num_processes=workers, local_mode=True, use_gpu=use_gpu).run(_fit_worker, shards, kwargs)

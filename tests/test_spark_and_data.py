@@ -179,3 +179,29 @@ def test_argmax_accuracy_cpu_restatement():
     assert pred.tolist() == [1, 0, 2] and int(correct) == 2
     _, correct = argmax_accuracy(z, y, correct)
     assert int(correct) == 4
+
+
+def test_mlpc_reproducible_mode_is_bit_identical_across_worker_counts(tmp_path, monkeypatch):
+    """``reproducible=True`` (SURVEY W13 "1-vs-N identical iterates"): canonical row chunks, per-chunk evaluation, fixed
+    pairwise tree - the objective history and the weights must be EXACTLY the same for 1, 2 and 4 workers."""
+    from b200ml.spark.dataframe import DataFrame
+    from b200ml.spark.ml import MultilayerPerceptronClassifier
+
+    rng = np.random.default_rng(7)
+    n, d, k = 203, 6, 3                      # not a multiple of anything on purpose
+    X = rng.normal(size=(n, d))
+    y = ((X[:, 0] + 0.5 * X[:, 1] > 0).astype(int) + (X[:, 2] > 1.0)).astype(np.float64)
+    df = DataFrame({"label": y}, {"features": X})
+    out = {}
+    for workers in (1, 2, 4):
+        clf = MultilayerPerceptronClassifier(maxIter=12, layers=[d, 5, k], blockSize=16, seed=3, numWorkers=workers,
+                                             device="cpu", reproducible=True)
+        m = clf.fit(df)
+        out[workers] = (list(m.summary.objectiveHistory), np.asarray(m.weights.toArray()))
+        assert m.summary.numWorkers == workers
+    for workers in (2, 4):
+        assert out[workers][0] == out[1][0], (workers, out[workers][0][-3:], out[1][0][-3:])
+        assert np.array_equal(out[workers][1], out[1][1])
+    assert out[1][0][-1] < out[1][0][0]
+    with pytest.raises(ValueError):
+        MultilayerPerceptronClassifier(maxIter=2, layers=[d, 5, k], numWorkers=3, device="cpu", reproducible=True).fit(df)
