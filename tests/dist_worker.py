@@ -283,6 +283,43 @@ def case_checkpoint_adam(rank, world, dev, mode):
     print(f"[rank {rank}] checkpoint_adam ok err={err:.3e} nonzero_v={nz}/{tot} mode={e_b.allreduce_mode}")
 
 
+def case_compat_ddp(rank, world, dev, mode):
+    """The reference's loop vocabulary (DDP(model) + Adam(model.parameters()) + zero_grad / backward / step) over several
+    ranks trains exactly like the engine driven directly, and every rank ends with the same weights."""
+    from b200ml.ops.loss import linear_cross_entropy
+    from b200ml.optim import Adam
+    from b200ml.parallel import DistributedDataParallel as DDP
+    from b200ml.parallel.engine import DataParallelEngine
+
+    ref = small_model(dev)
+    e = DataParallelEngine(ref, optimizer="adam", lr=1e-3, allreduce=mode, bucket_mb=1.0)
+    train(ref, e, rank, world, dev, 3, 8, True)
+    want = torch.cat([p.detach().reshape(-1).clone() for p in ref.parameters()])
+    e.close()
+
+    model = small_model(dev)
+    ddp = DDP(model, bucket_cap_mb=1.0, allreduce=mode)
+    opt = Adam(model.parameters(), lr=1e-3)
+    S = 32
+    g = torch.Generator().manual_seed(99)
+    la = (torch.tril(torch.ones(S, S, device=dev)) == 0)[None, None]
+    per = 8 // world
+    for _ in range(3):
+        src = torch.randint(1, 80, (8, S), generator=g)[rank * per:(rank + 1) * per].to(dev)
+        trg = torch.randint(1, 96, (8, S), generator=g)[rank * per:(rank + 1) * per].to(dev)
+        h = ddp(src, trg, (src != 0)[:, None, None, :], la, la, return_hidden=True)
+        loss = linear_cross_entropy(h, model.linear.weight, model.linear.bias, trg, ignore_index=0)
+        opt.zero_grad()                 # between forward and backward, as in the reference
+        loss.backward()
+        opt.step()
+    ddp.engine.weights_hash()           # raises if the ranks diverged
+    got = torch.cat([p.detach().reshape(-1).clone() for p in model.parameters()])
+    err = (got - want).abs().max().item()
+    assert err == 0.0, f"wrapper API differs from the engine API by {err}"
+    ddp.close()
+    print(f"[rank {rank}] compat_ddp ok")
+
+
 def case_layout_mismatch(rank, world, dev, mode):
     """A rank that built another model must be caught by the constructor, on every rank, before any peer access."""
     from b200ml.models.transformer import Transformer
@@ -325,7 +362,7 @@ def case_mlpc(rank, world, dev, mode):
     print(f"[rank {rank}] mlpc ok evals={out['functionEvaluations']} obj={full:.6f}")
 
 
-CASES = {"mlpc": case_mlpc, "layout_mismatch": case_layout_mismatch, "checkpoint_adam": case_checkpoint_adam,"allreduce_nvls": case_allreduce_nvls, "dp_equals_big_batch": case_dp_equals_big_batch, "fused_matches_nccl": case_fused_matches_nccl,
+CASES = {"compat_ddp": case_compat_ddp, "mlpc": case_mlpc, "layout_mismatch": case_layout_mismatch, "checkpoint_adam": case_checkpoint_adam,"allreduce_nvls": case_allreduce_nvls, "dp_equals_big_batch": case_dp_equals_big_batch, "fused_matches_nccl": case_fused_matches_nccl,
          "allreduce_raw": case_allreduce_raw}
 
 if __name__ == "__main__":

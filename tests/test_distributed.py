@@ -38,6 +38,11 @@ def test_checkpoint_adam_gloo_world2():
     assert out.count("checkpoint_adam ok") == 2
 
 
+def test_reference_style_ddp_api_gloo_world2():
+    out = _launch(["compat_ddp"], 2, 29617, {"B200ML_TEST_CPU": "1", "OMP_NUM_THREADS": "2"})
+    assert out.count("compat_ddp ok") == 2
+
+
 def _ngpu():
     import torch
     return torch.cuda.device_count() if torch.cuda.is_available() else 0

@@ -184,3 +184,78 @@ def test_small_bucket_rides_with_the_next_two_shot_bucket(monkeypatch):
     eng.comm = None
     eng.world = 1
     eng.close()
+
+
+def _toy_batches(n, seed):
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    return [(torch.randn(16, 784, generator=g), torch.randint(0, 10, (16,), generator=g)) for _ in range(n)]
+
+
+def test_reference_style_ddp_and_optimizer_api_matches_the_engine():
+    """``DDP(model)`` + ``SGD / Adam(model.parameters(), lr)`` + ``zero_grad / backward / step`` (the reference's loop,
+    distributed_cnn.py:156,138,175-183) must train exactly like driving the engine directly - with ``zero_grad()``
+    before the forward pass or between forward and backward, and with the forward through the wrapper or the bare
+    module (the reference forwards through the bare one)."""
+    import torch
+    from b200ml.models import mnist_mlp
+    from b200ml.ops.loss import cross_entropy
+    from b200ml.optim import SGD, Adam
+    from b200ml.parallel import DistributedDataParallel as DDP
+    from b200ml.parallel.engine import DataParallelEngine
+
+    for kind, Opt, lr in (("sgd", SGD, 0.05), ("adam", Adam, 1e-3)):
+        torch.manual_seed(0)
+        ref = mnist_mlp()
+        eng = DataParallelEngine(ref, optimizer=kind, lr=lr)
+        for x, y in _toy_batches(5, 1):
+            eng.zero_grad()
+            cross_entropy(ref(x), y).backward()
+            eng.step()
+        want = torch.cat([p.detach().reshape(-1) for p in ref.parameters()])
+        eng.close()
+        for style in ("zero_first_wrapper_forward", "zero_between_bare_forward", "no_zero_wrapper_forward"):
+            torch.manual_seed(0)
+            model = mnist_mlp()
+            ddp = DDP(model)
+            opt = Opt(model.parameters(), lr=lr)          # on the BARE model's parameters, as the reference does
+            assert opt.param_groups[0]["lr"] == lr and ddp.engine is not None
+            for x, y in _toy_batches(5, 1):
+                if style == "zero_first_wrapper_forward":
+                    opt.zero_grad()
+                    loss = cross_entropy(ddp(x), y)
+                elif style == "zero_between_bare_forward":
+                    loss = cross_entropy(model(x), y)
+                    opt.zero_grad()
+                else:
+                    loss = cross_entropy(ddp(x), y)
+                loss.backward()
+                opt.step()
+            got = torch.cat([p.detach().reshape(-1) for p in model.parameters()])
+            assert torch.equal(got, want), (kind, style, (got - want).abs().max().item())
+            assert set(ddp.state_dict()) == {"module." + k for k in model.state_dict()}    # torch DDP's key prefix
+            ddp.close()
+    # without a wrapper the same optimizer classes drive the single-process flat optimizer
+    torch.manual_seed(0)
+    model = mnist_mlp()
+    opt = SGD(model.parameters(), lr=0.05)
+    for x, y in _toy_batches(5, 1):
+        opt.zero_grad()
+        cross_entropy(model(x), y).backward()
+        opt.step()
+    torch.manual_seed(0)
+    ref = mnist_mlp()
+    eng = DataParallelEngine(ref, optimizer="sgd", lr=0.05)
+    for x, y in _toy_batches(5, 1):
+        eng.zero_grad()
+        cross_entropy(ref(x), y).backward()
+        eng.step()
+    a = torch.cat([p.detach().reshape(-1) for p in model.parameters()])
+    b = torch.cat([p.detach().reshape(-1) for p in ref.parameters()])
+    assert torch.allclose(a, b, atol=1e-6)
+    import pytest as _pt
+    with _pt.raises(ValueError):
+        SGD(list(mnist_mlp().parameters()), lr=0.1, momentum=0.9)
+    d2 = DDP(mnist_mlp())
+    with _pt.raises(ValueError):
+        Adam(list(d2.module.parameters())[:2], lr=1e-3)   # a subset of the wrapped module's parameters
