@@ -28,6 +28,8 @@ def main():
     ap.add_argument("--iters", type=int, default=30)
     ap.add_argument("--device", default="cuda" if torch.cuda.is_available() else "cpu")
     ap.add_argument("--workers", default="1")
+    ap.add_argument("--reproducible", action="store_true",
+                    help="canonical chunks + fixed tree: bit-identical objective history for 1/2/4/8 workers")
     a = ap.parse_args()
     rng = np.random.default_rng(0)
     centers = rng.normal(size=(10, 784))
@@ -36,10 +38,10 @@ def main():
     df = DataFrame({"label": y.astype(np.float64)}, {"features": X})
     layers = [784, 512, 256, 10]
     for workers in [int(v) for v in a.workers.split(",")]:
-        if workers > 1 and (not torch.cuda.is_available() or torch.cuda.device_count() < workers):
+        if workers > 1 and a.device != "cpu" and (not torch.cuda.is_available() or torch.cuda.device_count() < workers):
             continue
         clf = ml.MultilayerPerceptronClassifier(layers=layers, maxIter=a.iters, blockSize=128, seed=1, numWorkers=workers,
-                                                device=a.device, tol=0.0)
+                                                device=a.device, tol=0.0, reproducible=a.reproducible)
         if workers == 1:
             clf.fit(df)  # warm-up: library load, kernels, allocator
         model = clf.fit(df)
@@ -48,6 +50,7 @@ def main():
         print(json.dumps({"bench": "mlpc_fit", "device": a.device, "workers": workers, "rows": a.rows, "layers": layers,
                           "max_iter": a.iters, "fit_seconds": sm.fitSeconds, "function_evaluations": sm.functionEvaluations,
                           "final_objective": sm.objectiveHistory[-1], "train_accuracy": acc,
+                          "reproducible": a.reproducible, "objective_history_hash": hash(tuple(sm.objectiveHistory)),
                           "weights": ml.num_weights(layers)}), flush=True)
 
 if __name__ == "__main__":
